@@ -1,0 +1,200 @@
+// Fused embedding / FM kernels (replicated tables).
+//
+// emb_fm_fwd  (reference ops K1+K2+K3: `embedding_lookup` x2, multiply, reduce_sum, square, subtract;
+//              PS:177-187 / HVD:169-179, plus the reshape to the deep input PS:203):
+//     one pass over ids/vals gathers fm_w and fm_v rows with 128-bit loads, scales by the feature value,
+//     writes the deep input X0[b, f*K+k] as bf16, keeps S = sum_f e and sum_f e^2 in registers and emits
+//         yfm[b] = sum_f fm_w[id]*val + 0.5 * sum_k (S_k^2 - sum_f e_k^2)
+//     and S (fp32, needed by the backward pass).
+// emb_bwd     (autograd of the above, reference op K11):
+//     dE[b,f,:] = dX0[b,f,:] + dy[b] * (S[b,:] - e[b,f,:]);   g_v[id,:] += val * dE;   g_w[id] += dy[b] * val
+//     accumulated with red.global.add.v4.f32 into the dense fp32 gradient buffer (the reference's embedding
+//     gradient is dense as well because of the whole-table L2 term).
+//
+// G threads cooperate on one sample, each owning 4 consecutive embedding columns (K = 4*G, G | 32).
+#include "common.cuh"
+
+namespace dfm {
+
+constexpr int kEmbThreads = 256;
+constexpr int kEmbUnroll = 4;
+
+template <int G>
+__device__ __forceinline__ float group_sum(float v) {
+#pragma unroll
+  for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+template <int G>
+__global__ void __launch_bounds__(kEmbThreads)
+emb_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, const float* __restrict__ fm_w,
+                  const float* __restrict__ fm_v, __nv_bfloat16* __restrict__ x0, int ldx, float* __restrict__ S,
+                  float* __restrict__ yfm, int B, int F, int N) {
+  constexpr int K = 4 * G;
+  const int gtid = blockIdx.x * kEmbThreads + threadIdx.x;
+  const int sample_raw = gtid / G;
+  const int t = gtid % G;
+  const bool active = sample_raw < B;
+  const int sample = active ? sample_raw : B - 1;  // keep the whole warp alive for the shuffles
+  const int* sid = ids + (size_t)sample * F;
+  const float* sval = vals + (size_t)sample * F;
+
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f), ss = make_float4(0.f, 0.f, 0.f, 0.f);
+  float yw = 0.f;
+  for (int f0 = 0; f0 < F; f0 += kEmbUnroll) {
+    int id[kEmbUnroll];
+    float val[kEmbUnroll];
+    float4 row[kEmbUnroll];
+#pragma unroll
+    for (int u = 0; u < kEmbUnroll; ++u) {
+      const int f = f0 + u;
+      id[u] = 0; val[u] = 0.f;
+      if (f < F) {
+        id[u] = __ldg(sid + f);
+        val[u] = __ldg(sval + f);
+        if ((unsigned)id[u] >= (unsigned)N) { id[u] = 0; val[u] = 0.f; }  // out-of-range ids contribute nothing
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kEmbUnroll; ++u)
+      row[u] = __ldg(reinterpret_cast<const float4*>(fm_v + (size_t)id[u] * K) + t);
+#pragma unroll
+    for (int u = 0; u < kEmbUnroll; ++u) {
+      const int f = f0 + u;
+      if (f < F) {
+        const float4 e = make_float4(row[u].x * val[u], row[u].y * val[u], row[u].z * val[u], row[u].w * val[u]);
+        s.x += e.x; s.y += e.y; s.z += e.z; s.w += e.w;
+        ss.x += e.x * e.x; ss.y += e.y * e.y; ss.z += e.z * e.z; ss.w += e.w * e.w;
+        if (active) {
+          uint2 pk;
+          pk.x = pack_bf16x2(e.x, e.y);
+          pk.y = pack_bf16x2(e.z, e.w);
+          *reinterpret_cast<uint2*>(x0 + (size_t)sample * ldx + (size_t)f * K + 4 * t) = pk;
+        }
+        if ((f % G) == t) yw += __ldg(fm_w + id[u]) * val[u];
+      }
+    }
+  }
+  float yv = (s.x * s.x - ss.x) + (s.y * s.y - ss.y) + (s.z * s.z - ss.z) + (s.w * s.w - ss.w);
+  yv = group_sum<G>(yv);
+  yw = group_sum<G>(yw);
+  if (active) {
+    reinterpret_cast<float4*>(S + (size_t)sample * K)[t] = s;
+    if (t == 0) yfm[sample] = yw + 0.5f * yv;
+  }
+}
+
+template <int G>
+__global__ void __launch_bounds__(kEmbThreads)
+emb_bwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, const float* __restrict__ fm_v,
+               const float* __restrict__ S, const float* __restrict__ dy, const __nv_bfloat16* __restrict__ dx0,
+               int ldx, float* __restrict__ g_w, float* __restrict__ g_v, int B, int F, int N) {
+  constexpr int K = 4 * G;
+  const int gtid = blockIdx.x * kEmbThreads + threadIdx.x;
+  const int sample = gtid / G;
+  const int t = gtid % G;
+  if (sample >= B) return;
+  const int* sid = ids + (size_t)sample * F;
+  const float* sval = vals + (size_t)sample * F;
+  const float4 s = reinterpret_cast<const float4*>(S + (size_t)sample * K)[t];
+  const float d = dy[sample];
+
+  for (int f0 = 0; f0 < F; f0 += kEmbUnroll) {
+    int id[kEmbUnroll];
+    float val[kEmbUnroll];
+    float4 row[kEmbUnroll];
+    uint2 dxp[kEmbUnroll];
+#pragma unroll
+    for (int u = 0; u < kEmbUnroll; ++u) {
+      const int f = f0 + u;
+      id[u] = 0; val[u] = 0.f;
+      if (f < F) {
+        id[u] = __ldg(sid + f);
+        val[u] = __ldg(sval + f);
+        if ((unsigned)id[u] >= (unsigned)N) { id[u] = 0; val[u] = 0.f; }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kEmbUnroll; ++u) {
+      row[u] = __ldg(reinterpret_cast<const float4*>(fm_v + (size_t)id[u] * K) + t);
+      const int f = min(f0 + u, F - 1);
+      dxp[u] = __ldg(reinterpret_cast<const uint2*>(dx0 + (size_t)sample * ldx + (size_t)f * K + 4 * t));
+    }
+#pragma unroll
+    for (int u = 0; u < kEmbUnroll; ++u) {
+      const int f = f0 + u;
+      if (f < F && val[u] != 0.f) {  // a zero value (padding) has an exactly-zero gradient
+        const float v = val[u];
+        const float gx = v * (bf16_lo(dxp[u].x) + d * (s.x - row[u].x * v));
+        const float gy = v * (bf16_hi(dxp[u].x) + d * (s.y - row[u].y * v));
+        const float gz = v * (bf16_lo(dxp[u].y) + d * (s.z - row[u].z * v));
+        const float gw = v * (bf16_hi(dxp[u].y) + d * (s.w - row[u].w * v));
+        red_add_f32x4(g_v + (size_t)id[u] * K + 4 * t, gx, gy, gz, gw);
+        if ((f % G) == t) atomicAdd(g_w + id[u], d * v);
+      }
+    }
+  }
+}
+
+template <int G>
+static int launch_fwd(const int* ids, const float* vals, const float* fm_w, const float* fm_v, __nv_bfloat16* x0,
+                      int ldx, float* S, float* yfm, int B, int F, int N, cudaStream_t st) {
+  const long threads = (long)B * G;
+  emb_fm_fwd_kernel<G><<<(unsigned)ceil_div_ll(threads, kEmbThreads), kEmbThreads, 0, st>>>(ids, vals, fm_w, fm_v, x0,
+                                                                                         ldx, S, yfm, B, F, N);
+  DFM_CHECK(cudaGetLastError());
+  return DFM_OK;
+}
+
+template <int G>
+static int launch_bwd(const int* ids, const float* vals, const float* fm_v, const float* S, const float* dy,
+                      const __nv_bfloat16* dx0, int ldx, float* g_w, float* g_v, int B, int F, int N, cudaStream_t st) {
+  const long threads = (long)B * G;
+  emb_bwd_kernel<G><<<(unsigned)ceil_div_ll(threads, kEmbThreads), kEmbThreads, 0, st>>>(ids, vals, fm_v, S, dy, dx0,
+                                                                                      ldx, g_w, g_v, B, F, N);
+  DFM_CHECK(cudaGetLastError());
+  return DFM_OK;
+}
+
+}  // namespace dfm
+
+using namespace dfm;
+
+#define DFM_DISPATCH_G(K, CALL)                                                         \
+  switch (K) {                                                                          \
+    case 4: return CALL(1);                                                             \
+    case 8: return CALL(2);                                                             \
+    case 16: return CALL(4);                                                            \
+    case 32: return CALL(8);                                                            \
+    case 64: return CALL(16);                                                           \
+    case 128: return CALL(32);                                                          \
+    default:                                                                            \
+      dfm_set_error("embedding_size %d unsupported by the fused kernels (need 4,8,16,32,64,128)", K); \
+      return DFM_ERR_UNSUPPORTED;                                                       \
+  }
+
+extern "C" {
+
+// ids [B,F] int32, vals [B,F] f32, fm_w [N] f32, fm_v [N,K] f32 (16-byte aligned rows)
+// -> x0 [B, ldx>=F*K] bf16, S [B,K] f32, yfm [B] f32
+int dfm_emb_fm_fwd(const int* ids, const float* vals, const float* fm_w, const float* fm_v, void* x0, int ldx, float* S,
+                   float* yfm, int B, int F, int K, int N, void* stream) {
+  DFM_REQUIRE(B > 0 && F > 0 && N > 0, "emb_fm_fwd: empty problem");
+  DFM_REQUIRE(ldx >= F * K && ldx % 4 == 0, "emb_fm_fwd: ldx must be >= F*K and a multiple of 4");
+#define CALL(G) launch_fwd<G>(ids, vals, fm_w, fm_v, (__nv_bfloat16*)x0, ldx, S, yfm, B, F, N, (cudaStream_t)stream)
+  DFM_DISPATCH_G(K, CALL)
+#undef CALL
+}
+
+// dy [B] f32, dx0 [B, ldx] bf16 -> g_w [N] f32 +=, g_v [N,K] f32 +=
+int dfm_emb_bwd(const int* ids, const float* vals, const float* fm_v, const float* S, const float* dy, const void* dx0,
+                int ldx, float* g_w, float* g_v, int B, int F, int K, int N, void* stream) {
+  DFM_REQUIRE(B > 0 && F > 0 && N > 0, "emb_bwd: empty problem");
+#define CALL(G) \
+  launch_bwd<G>(ids, vals, fm_v, S, dy, (const __nv_bfloat16*)dx0, ldx, g_w, g_v, B, F, N, (cudaStream_t)stream)
+  DFM_DISPATCH_G(K, CALL)
+#undef CALL
+}
+
+}  // extern "C"

@@ -1,0 +1,26 @@
+// Error plumbing for the C ABI: every entry point returns 0 on success, a DFM_ERR_* code otherwise,
+// and leaves a human-readable message retrievable through dfm_last_error().
+#include <stdarg.h>
+#include <stdio.h>
+#include <cuda_runtime.h>
+
+static thread_local char g_err[1024] = "";
+
+extern "C" void dfm_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+extern "C" const char* dfm_last_error() { return g_err; }
+
+extern "C" int dfm_abi_version() { return 1; }
+
+// 1 when the current device is Blackwell-class (compute capability 10.x), 0 otherwise, <0 on error.
+extern "C" int dfm_device_is_sm100() {
+  int dev = 0, major = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return -1;
+  if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return -1;
+  return major == 10 ? 1 : 0;
+}

@@ -1,0 +1,186 @@
+// Fused output head: final-layer dot product, 4-way logit sum, sigmoid, numerically stable log-loss and its
+// gradient, plus every reduction that hangs off dy (reference ops K7+K8: PS:221-232,244 / HVD:213-224,236).
+//
+//   y_d  = x[b,:] . w_out + b_out            y = fm_bias + yfm[b] + y_d          prob = sigmoid(y)
+//   loss += max(y,0) - y*label + log1p(exp(-|y|))          (sum; divided by the global batch on the host side
+//                                                           through inv_batch being folded into dy and loss_scale)
+//   dy[b] = (prob - label) * inv_batch
+//   dZ[b,j] = dy[b] * w_out[j] * (x[b,j] != 0) * mask_scale   <- gradient w.r.t. the last hidden pre-activation
+//                                                              (x = dropout(relu(z)): its zero pattern IS the mask)
+//   g_w_out[j] += dy[b]*x[b,j]    g_b_out += dy[b]    g_fm_bias += dy[b]    g_b_last[j] += dZ[b,j]
+//
+// One warp per sample, block-level shared-memory accumulators flushed with one atomic per column per block.
+#include "common.cuh"
+
+namespace dfm {
+
+constexpr int kLossThreads = 256;
+constexpr int kLossWarps = kLossThreads / 32;
+
+__global__ void __launch_bounds__(kLossThreads)
+logit_loss_kernel(const __nv_bfloat16* __restrict__ x, int ldx, int H, const float* __restrict__ w_out,
+                  const float* __restrict__ b_out, const float* __restrict__ fm_bias, const float* __restrict__ yfm,
+                  const float* __restrict__ labels, int B, float inv_batch, float mask_scale, int train,
+                  float* __restrict__ prob, float* __restrict__ logit, float* __restrict__ dy,
+                  __nv_bfloat16* __restrict__ dz, int lddz, float* __restrict__ loss_sum, float* __restrict__ g_w_out,
+                  float* __restrict__ g_b_out, float* __restrict__ g_fm_bias, float* __restrict__ g_b_last) {
+  extern __shared__ float sacc[];  // [2*H]: g_w_out partials, g_b_last partials
+  float* s_gw = sacc;
+  float* s_gb = sacc + H;
+  __shared__ float s_scalar[2];  // loss, sum dy
+  for (int j = threadIdx.x; j < 2 * H; j += kLossThreads) sacc[j] = 0.f;
+  if (threadIdx.x < 2) s_scalar[threadIdx.x] = 0.f;
+  __syncthreads();
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float bias = __ldg(b_out) + __ldg(fm_bias);
+  float loss_acc = 0.f, dy_acc = 0.f;
+  for (int b = blockIdx.x * kLossWarps + warp; b < B; b += gridDim.x * kLossWarps) {
+    const __nv_bfloat16* xr = x + (size_t)b * ldx;
+    float dot = 0.f;
+    for (int j = lane * 2; j < H; j += 64) {
+      if (j + 1 < H) {
+        const uint32_t u = *reinterpret_cast<const uint32_t*>(xr + j);
+        dot += bf16_lo(u) * __ldg(w_out + j) + bf16_hi(u) * __ldg(w_out + j + 1);
+      } else {
+        dot += __bfloat162float(xr[j]) * __ldg(w_out + j);
+      }
+    }
+    dot = warp_sum(dot);
+    const float y = bias + yfm[b] + dot;
+    const float p = 1.f / (1.f + __expf(-y));
+    if (lane == 0) {
+      if (prob) prob[b] = p;
+      if (logit) logit[b] = y;
+    }
+    if (labels == nullptr) continue;  // predict mode
+    const float lab = labels[b];
+    const float l = fmaxf(y, 0.f) - y * lab + log1pf(__expf(-fabsf(y)));
+    const float d = (p - lab) * inv_batch;
+    if (lane == 0) { loss_acc += l; dy_acc += d; }
+    if (!train) continue;
+    if (lane == 0) dy[b] = d;
+    __nv_bfloat16* dzr = dz + (size_t)b * lddz;
+    for (int j = lane * 2; j < H; j += 64) {
+      if (j + 1 < H) {
+        const uint32_t u = *reinterpret_cast<const uint32_t*>(xr + j);
+        const float x0 = bf16_lo(u), x1 = bf16_hi(u);
+        const float z0 = x0 != 0.f ? d * __ldg(w_out + j) * mask_scale : 0.f;
+        const float z1 = x1 != 0.f ? d * __ldg(w_out + j + 1) * mask_scale : 0.f;
+        *reinterpret_cast<uint32_t*>(dzr + j) = pack_bf16x2(z0, z1);
+        atomicAdd(&s_gw[j], d * x0);
+        atomicAdd(&s_gw[j + 1], d * x1);
+        atomicAdd(&s_gb[j], z0);
+        atomicAdd(&s_gb[j + 1], z1);
+      } else {
+        const float x0 = __bfloat162float(xr[j]);
+        const float z0 = x0 != 0.f ? d * __ldg(w_out + j) * mask_scale : 0.f;
+        dzr[j] = __float2bfloat16(z0);
+        atomicAdd(&s_gw[j], d * x0);
+        atomicAdd(&s_gb[j], z0);
+      }
+    }
+  }
+  if (lane == 0 && labels != nullptr) {
+    atomicAdd(&s_scalar[0], loss_acc);
+    atomicAdd(&s_scalar[1], dy_acc);
+  }
+  __syncthreads();
+  if (labels == nullptr) return;
+  if (threadIdx.x == 0) {
+    atomicAdd(loss_sum, s_scalar[0]);
+    if (train) {
+      atomicAdd(g_b_out, s_scalar[1]);
+      atomicAdd(g_fm_bias, s_scalar[1]);
+    }
+  }
+  if (train) {
+    for (int j = threadIdx.x; j < H; j += kLossThreads) {
+      atomicAdd(g_w_out + j, s_gw[j]);
+      if (g_b_last) atomicAdd(g_b_last + j, s_gb[j]);
+    }
+  }
+}
+
+// Column sums of a bf16 [B,H] matrix into fp32 (bias gradients of the lower MLP layers): out[j] += sum_b a[b,j].
+__global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* __restrict__ a, int lda, int B, int H,
+                                                          float* __restrict__ out, int rows_per_block) {
+  const int j = blockIdx.x * 256 + threadIdx.x;
+  if (j >= H) return;
+  const int r0 = blockIdx.y * rows_per_block;
+  const int r1 = min(B, r0 + rows_per_block);
+  float acc = 0.f;
+  for (int r = r0; r < r1; ++r) acc += __bfloat162float(a[(size_t)r * lda + j]);
+  atomicAdd(out + j, acc);
+}
+
+// 200-threshold confusion histogram for streaming AUC (`tf.metrics.auc`, PS:249-251): hist[c][k] counts class-c
+// samples whose prediction has exactly k thresholds strictly below it (thr sorted ascending, T entries).
+__global__ void __launch_bounds__(256) auc_hist_kernel(const float* __restrict__ prob, const float* __restrict__ labels,
+                                                       int B, const float* __restrict__ thr, int T,
+                                                       float* __restrict__ hist) {
+  extern __shared__ float sh[];  // [2*(T+1)]
+  for (int i = threadIdx.x; i < 2 * (T + 1); i += 256) sh[i] = 0.f;
+  __syncthreads();
+  for (int b = blockIdx.x * 256 + threadIdx.x; b < B; b += gridDim.x * 256) {
+    const float p = prob[b];
+    int lo = 0, hi = T;  // first index with thr[idx] >= p  == number of thresholds < p
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (__ldg(thr + mid) < p) lo = mid + 1; else hi = mid;
+    }
+    const int c = labels[b] > 0.5f ? 1 : 0;
+    atomicAdd(&sh[c * (T + 1) + lo], 1.f);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2 * (T + 1); i += 256)
+    if (sh[i] != 0.f) atomicAdd(hist + i, sh[i]);
+}
+
+}  // namespace dfm
+
+using namespace dfm;
+
+extern "C" {
+
+// labels == NULL -> predict mode (only prob/logit written). train == 0 -> eval (loss only, no gradients).
+int dfm_logit_loss(const void* x, int ldx, int H, const float* w_out, const float* b_out, const float* fm_bias,
+                   const float* yfm, const float* labels, int B, float inv_batch, float mask_scale, int train,
+                   float* prob, float* logit, float* dy, void* dz, int lddz, float* loss_sum, float* g_w_out,
+                   float* g_b_out, float* g_fm_bias, float* g_b_last, void* stream) {
+  DFM_REQUIRE(B > 0 && H > 0, "logit_loss: empty problem");
+  DFM_REQUIRE(ldx % 2 == 0 && (!train || lddz % 2 == 0), "logit_loss: leading dimensions must be even");
+  DFM_REQUIRE(H <= 6000, "logit_loss: last hidden width > 6000 unsupported");
+  int blocks = ceil_div(B, kLossWarps * 4);
+  if (blocks > 296) blocks = 296;
+  if (blocks < 1) blocks = 1;
+  logit_loss_kernel<<<blocks, kLossThreads, 2 * H * sizeof(float), (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)x, ldx, H, w_out, b_out, fm_bias, yfm, labels, B, inv_batch, mask_scale, train, prob, logit,
+      dy, (__nv_bfloat16*)dz, lddz, loss_sum, g_w_out, g_b_out, g_fm_bias, g_b_last);
+  DFM_CHECK(cudaGetLastError());
+  return DFM_OK;
+}
+
+int dfm_colsum_bf16(const void* a, int lda, int B, int H, float* out, void* stream) {
+  DFM_REQUIRE(B > 0 && H > 0, "colsum: empty problem");
+  int ysplit = ceil_div(B, 64);
+  if (ysplit > 64) ysplit = 64;
+  const int rows_per_block = ceil_div(B, ysplit);
+  dim3 grid(ceil_div(H, 256), ceil_div(B, rows_per_block));
+  colsum_bf16_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)a, lda, B, H, out, rows_per_block);
+  DFM_CHECK(cudaGetLastError());
+  return DFM_OK;
+}
+
+// hist [2, T+1] f32 +=
+int dfm_auc_hist(const float* prob, const float* labels, int B, const float* thr, int T, float* hist, void* stream) {
+  DFM_REQUIRE(B > 0 && T > 0 && T <= 4096, "auc_hist: bad sizes");
+  int blocks = ceil_div(B, 256 * 4);
+  if (blocks > 148) blocks = 148;
+  if (blocks < 1) blocks = 1;
+  auc_hist_kernel<<<blocks, 256, 2 * (T + 1) * sizeof(float), (cudaStream_t)stream>>>(prob, labels, B, thr, T, hist);
+  DFM_CHECK(cudaGetLastError());
+  return DFM_OK;
+}
+
+}  // extern "C"

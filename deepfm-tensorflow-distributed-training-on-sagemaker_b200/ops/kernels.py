@@ -1,0 +1,123 @@
+"""Thin typed wrappers over the C ABI (include/deepfm_b200.h): torch tensors in, kernels launched on the
+current CUDA stream. No allocation, no synchronisation — callers own every buffer (CUDA-graph friendly)."""
+from __future__ import annotations
+
+import ctypes
+from ctypes import c_float, c_int, c_longlong, c_uint64, c_void_p
+from typing import Optional
+
+import torch
+
+from . import lib as _lib
+from ..optim.tf1 import OPT_IDS
+
+
+def _p(t: Optional[torch.Tensor]) -> c_void_p:
+    return c_void_p(0 if t is None else t.data_ptr())
+
+
+def _stream() -> c_void_p:
+    return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _chk_dev(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise ValueError("fused kernels need CUDA tensors")
+
+
+def emb_fm_fwd(ids: torch.Tensor, vals: torch.Tensor, fm_w: torch.Tensor, fm_v: torch.Tensor, x0: torch.Tensor,
+               S: torch.Tensor, yfm: torch.Tensor) -> None:
+    """ids [B,F] int32, vals [B,F] f32, fm_w [N], fm_v [N,K] -> x0 [B, >=F*K] bf16, S [B,K] f32, yfm [B] f32."""
+    _chk_dev(ids, vals, fm_w, fm_v, x0, S, yfm)
+    assert ids.dtype == torch.int32 and vals.dtype == torch.float32 and x0.dtype == torch.bfloat16
+    B, F = ids.shape
+    N, K = fm_v.shape
+    _lib.check(_lib.load().dfm_emb_fm_fwd(_p(ids), _p(vals), _p(fm_w), _p(fm_v), _p(x0), c_int(x0.stride(0)), _p(S),
+                                          _p(yfm), c_int(B), c_int(F), c_int(K), c_int(N), _stream()))
+
+
+def emb_bwd(ids, vals, fm_v, S, dy, dx0, g_w, g_v) -> None:
+    _chk_dev(ids, vals, fm_v, S, dy, dx0, g_w, g_v)
+    B, F = ids.shape
+    N, K = fm_v.shape
+    _lib.check(_lib.load().dfm_emb_bwd(_p(ids), _p(vals), _p(fm_v), _p(S), _p(dy), _p(dx0), c_int(dx0.stride(0)),
+                                       _p(g_w), _p(g_v), c_int(B), c_int(F), c_int(K), c_int(N), _stream()))
+
+
+class GemmPlan:
+    """A tcgen05 GEMM bound to fixed buffers (owns the host-side TMA descriptors).
+
+    mode 'fwd'  : out[M,N] bf16 = dropout(relu(A[M,K] @ B[N,K]^T + bias))
+    mode 'dgrad': out[M,N] bf16 = (A[M,K] @ B[K,N]) * (mask != 0) * mask_scale
+    mode 'wgrad': out[M,N] f32 += A[K,M]^T @ B[K,N]
+    """
+    MODES = {"fwd": 0, "dgrad": 1, "wgrad": 2}
+
+    def __init__(self, mode: str, A: torch.Tensor, B: torch.Tensor, out: torch.Tensor, M: int, N: int, K: int,
+                 bias: Optional[torch.Tensor] = None, relu: bool = False, keep_prob: float = 1.0, seed: int = 0,
+                 layer: int = 0, row_offset: int = 0, step_ptr: Optional[torch.Tensor] = None,
+                 mask: Optional[torch.Tensor] = None, mask_scale: float = 1.0, split_k: int = 0):
+        _chk_dev(A, B, out, bias, mask, step_ptr)
+        assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16
+        self._keep = (A, B, out, bias, step_ptr, mask)  # keep buffers alive as long as the descriptors exist
+        self.mode, self.M, self.N, self.K = mode, M, N, K
+        h = c_void_p()
+        lib = _lib.load()
+        _lib.check(lib.dfm_gemm_plan_create(
+            ctypes.byref(h), c_int(self.MODES[mode]), _p(A), c_int(A.stride(0)), _p(B), c_int(B.stride(0)),
+            c_int(M), c_int(N), c_int(K), _p(out), c_int(out.stride(0)), _p(bias), c_int(1 if relu else 0),
+            c_float(keep_prob), c_uint64(seed), c_int(layer), c_int(row_offset), _p(step_ptr), _p(mask),
+            c_int(mask.stride(0) if mask is not None else 0), c_float(mask_scale), c_int(split_k)))
+        self._h = h
+
+    def info(self):
+        bn, gx, gy, gz = c_int(), c_int(), c_int(), c_int()
+        _lib.load().dfm_gemm_plan_info(self._h, ctypes.byref(bn), ctypes.byref(gx), ctypes.byref(gy), ctypes.byref(gz))
+        return {"bn": bn.value, "grid": (gx.value, gy.value, gz.value)}
+
+    def run(self) -> None:
+        _lib.check(_lib.load().dfm_gemm_run(self._h, _stream()))
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                _lib.load().dfm_gemm_plan_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+
+def logit_loss(x, w_out, b_out, fm_bias, yfm, labels, inv_batch: float, mask_scale: float, train: bool,
+               prob=None, logit=None, dy=None, dz=None, loss_sum=None, g_w_out=None, g_b_out=None, g_fm_bias=None,
+               g_b_last=None) -> None:
+    B, H = x.shape
+    _lib.check(_lib.load().dfm_logit_loss(
+        _p(x), c_int(x.stride(0)), c_int(H), _p(w_out), _p(b_out), _p(fm_bias), _p(yfm), _p(labels), c_int(B),
+        c_float(inv_batch), c_float(mask_scale), c_int(1 if train else 0), _p(prob), _p(logit), _p(dy), _p(dz),
+        c_int(dz.stride(0) if dz is not None else 0), _p(loss_sum), _p(g_w_out), _p(g_b_out), _p(g_fm_bias),
+        _p(g_b_last), _stream()))
+
+
+def colsum_bf16(a: torch.Tensor, out: torch.Tensor) -> None:
+    B, H = a.shape
+    _lib.check(_lib.load().dfm_colsum_bf16(_p(a), c_int(a.stride(0)), c_int(B), c_int(H), _p(out), _stream()))
+
+
+def auc_hist(prob: torch.Tensor, labels: torch.Tensor, thr: torch.Tensor, hist: torch.Tensor) -> None:
+    _lib.check(_lib.load().dfm_auc_hist(_p(prob), _p(labels), c_int(prob.numel()), _p(thr), c_int(thr.numel()),
+                                        _p(hist), _stream()))
+
+
+def flat_opt_step(w, g, s0, s1, opt_name: str, lr: float, beta1: float, beta2: float, eps: float, momentum: float,
+                  grad_scale: float, decay_range, l2: float, shadow_range, shadow, step_ptr, reg_loss,
+                  done_counter) -> None:
+    _lib.check(_lib.load().dfm_flat_opt_step(
+        _p(w), _p(g), _p(s0), _p(s1), c_longlong(w.numel()), c_int(OPT_IDS[opt_name]), c_float(lr), c_float(beta1),
+        c_float(beta2), c_float(eps), c_float(momentum), c_float(grad_scale), c_longlong(decay_range[0]),
+        c_longlong(decay_range[1]), c_float(l2), c_longlong(shadow_range[0]), c_longlong(shadow_range[1]), _p(shadow),
+        _p(step_ptr), _p(reg_loss), _p(done_counter), _stream()))
+
+
+def cast_f32_bf16(src: torch.Tensor, dst: torch.Tensor) -> None:
+    _lib.check(_lib.load().dfm_cast_f32_bf16(_p(src), _p(dst), c_longlong(src.numel()), _stream()))

@@ -1,0 +1,65 @@
+/* deepfm_b200 C ABI — every entry point of ops/_lib/libdeepfm_b200.so (sm_100a only).
+ *
+ * Conventions: all functions return 0 on success or a DFM_ERR_* code; dfm_last_error() returns the message of
+ * the calling thread's last failure. Pointers are device pointers unless noted. `stream` is a cudaStream_t.
+ * Kernels are asynchronous on `stream`. Nothing here allocates device memory unless stated.
+ * "Reference" citations: PS = 1-ps-cpu/DeepFM-dist-ps-for-multipleCPU-multiInstance.py,
+ *                        HVD = 2-hvd-gpu/DeepFM-hvd-tfrecord-vectorized-map.py  (of the upstream repository).
+ */
+#ifndef DEEPFM_B200_H_
+#define DEEPFM_B200_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DFM_OK 0
+#define DFM_ERR_CUDA 1
+#define DFM_ERR_ARG 2
+#define DFM_ERR_UNSUPPORTED 3
+
+const char* dfm_last_error(void);
+int dfm_abi_version(void);
+int dfm_device_is_sm100(void);
+
+/* ---- embedding + FM (replaces embedding_lookup x2 + FM reductions, PS:177-187,203) ---- */
+int dfm_emb_fm_fwd(const int* ids, const float* vals, const float* fm_w, const float* fm_v, void* x0_bf16, int ldx,
+                   float* S, float* yfm, int B, int F, int K, int N, void* stream);
+int dfm_emb_bwd(const int* ids, const float* vals, const float* fm_v, const float* S, const float* dy,
+                const void* dx0_bf16, int ldx, float* g_w, float* g_v, int B, int F, int K, int N, void* stream);
+
+/* ---- tcgen05 MLP GEMMs (replaces fully_connected fwd/bwd, PS:212-223) ----
+ * mode 0 forward: out[M,N] bf16 = dropout(relu(A[M,K] B[N,K]^T + bias));  mode 1 dgrad: out[M,N] bf16 =
+ * (A[M,K] B[K,N]) * (mask != 0) * mask_scale;  mode 2 wgrad: out[M,N] f32 += A[K,M]^T B[K,N].
+ * The plan is host memory (holds the TMA descriptors); create once per buffer set, run many times. */
+int dfm_gemm_plan_create(void** plan_out, int mode, const void* A, int lda, const void* B, int ldb, int M, int N, int K,
+                         void* out, int ldo, const float* bias, int relu, float keep_prob, unsigned long long seed,
+                         int layer, int row_offset, const unsigned long long* step_ptr, const void* mask, int ldmask,
+                         float mask_scale, int split_k);
+int dfm_gemm_plan_info(void* plan, int* bn, int* grid_x, int* grid_y, int* grid_z);
+int dfm_gemm_plan_set_row_offset(void* plan, int row_offset);
+void dfm_gemm_plan_destroy(void* plan);
+int dfm_gemm_run(void* plan, void* stream);
+
+/* ---- output head: logit sum + sigmoid + log-loss + gradients (PS:221-232,244) ---- */
+int dfm_logit_loss(const void* x_bf16, int ldx, int H, const float* w_out, const float* b_out, const float* fm_bias,
+                   const float* yfm, const float* labels, int B, float inv_batch, float mask_scale, int train,
+                   float* prob, float* logit, float* dy, void* dz_bf16, int lddz, float* loss_sum, float* g_w_out,
+                   float* g_b_out, float* g_fm_bias, float* g_b_last, void* stream);
+int dfm_colsum_bf16(const void* a_bf16, int lda, int B, int H, float* out, void* stream);
+
+/* ---- streaming AUC histogram (tf.metrics.auc, PS:249-251) ---- */
+int dfm_auc_hist(const float* prob, const float* labels, int B, const float* thr, int T, float* hist, void* stream);
+
+/* ---- flat multi-tensor optimizer with TF-1 update rules (PS:260-269); opt: 0 Adam 1 Adagrad 2 Momentum 3 ftrl 4 GD.
+ * `done_counter`: 4 bytes of zero-initialised device scratch owned by the caller. */
+int dfm_flat_opt_step(float* w, float* g, float* s0, float* s1, long long n, int opt, float lr, float beta1, float beta2,
+                      float eps, float momentum, float grad_scale, long long decay_begin, long long decay_end, float l2,
+                      long long shadow_begin, long long shadow_end, void* shadow_bf16, unsigned long long* step_ptr,
+                      float* reg_loss, unsigned int* done_counter, void* stream);
+int dfm_cast_f32_bf16(const float* in, void* out_bf16, long long n, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DEEPFM_B200_H_ */

@@ -1,0 +1,225 @@
+"""sm_100a kernel numerics vs plain PyTorch fp32 references of the same op (SURVEY section 4 'Kernel' tests)."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel_err(a, b):
+    a, b = a.float(), b.float()
+    return float((a - b).abs().max() / (b.abs().max() + 1e-12))
+
+
+GEMM_SHAPES = [
+    # (M, N, K)
+    (1024, 400, 1248),
+    (1024, 400, 400),
+    (256, 128, 1248),
+    (100, 32, 64),
+    (1024, 64, 128),
+    (4096, 256, 512),
+    (130, 80, 72),
+]
+
+
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+def test_gemm_fwd(cuda_lib, M, N, K):
+    from deepfm_b200.ops.kernels import GemmPlan
+    g = torch.Generator(device="cuda").manual_seed(M + N + K)
+    A = (torch.randn(M, K, device="cuda", generator=g) * 0.5).bfloat16()
+    W = (torch.randn(N, K, device="cuda", generator=g) * 0.1).bfloat16()
+    bias = torch.randn(N, device="cuda", generator=g)
+    out = torch.full((M, N), 7.0, device="cuda", dtype=torch.bfloat16)
+    plan = GemmPlan("fwd", A, W, out, M, N, K, bias=bias, relu=True)
+    plan.run()
+    torch.cuda.synchronize()
+    ref = torch.relu(A.float() @ W.float().t() + bias)
+    err = _rel_err(out, ref)
+    assert err < 1e-2, (err, plan.info())
+
+
+def test_gemm_fwd_dropout_matches_philox(cuda_lib):
+    from deepfm_b200.ops.kernels import GemmPlan
+    from deepfm_b200.utils.philox import dropout_keep_mask
+    M, N, K = 300, 400, 128
+    A = torch.randn(M, K, device="cuda").bfloat16()
+    W = (torch.randn(N, K, device="cuda") * 0.1).bfloat16()
+    bias = torch.zeros(N, device="cuda")
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    step = torch.tensor([5], device="cuda", dtype=torch.int64)
+    plan = GemmPlan("fwd", A, W, out, M, N, K, bias=bias, relu=False, keep_prob=0.5, seed=1234, layer=2,
+                    row_offset=7, step_ptr=step)
+    plan.run()
+    torch.cuda.synchronize()
+    keep = torch.from_numpy(dropout_keep_mask(M, N, 0.5, 1234, 5, 2, row_offset=7)).cuda()
+    ref = torch.where(keep, (A.float() @ W.float().t()) * 2.0, torch.zeros((), device="cuda"))
+    assert _rel_err(out, ref) < 1e-2
+    assert 0.45 < keep.float().mean().item() < 0.55
+
+
+@pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
+def test_gemm_dgrad(cuda_lib, M, N, K):
+    """out[M,N] = (dZ[M,K] @ W[K,N]) * (mask != 0) * scale — B operand is N-major (no transpose materialised)."""
+    from deepfm_b200.ops.kernels import GemmPlan
+    if N % 8 or K % 8:
+        pytest.skip("TMA stride rule")
+    g = torch.Generator(device="cuda").manual_seed(M * 3 + N + K)
+    dZ = (torch.randn(M, K, device="cuda", generator=g) * 0.5).bfloat16()
+    W = (torch.randn(K, N, device="cuda", generator=g) * 0.1).bfloat16()
+    mask = torch.relu(torch.randn(M, N, device="cuda", generator=g)).bfloat16()
+    out = torch.full((M, N), 3.0, device="cuda", dtype=torch.bfloat16)
+    plan = GemmPlan("dgrad", dZ, W, out, M, N, K, mask=mask, mask_scale=2.0)
+    plan.run()
+    torch.cuda.synchronize()
+    ref = (dZ.float() @ W.float()) * (mask.float() != 0).float() * 2.0
+    err = _rel_err(out, ref)
+    assert err < 1e-2, (err, plan.info())
+    out2 = torch.empty_like(out)
+    GemmPlan("dgrad", dZ, W, out2, M, N, K).run()
+    torch.cuda.synchronize()
+    assert _rel_err(out2, dZ.float() @ W.float()) < 1e-2
+
+
+@pytest.mark.parametrize("M,N,K", [(400, 1248, 1024), (400, 400, 1024), (128, 64, 256), (32, 1248, 100 * 8),
+                                   (64, 128, 4096), (400, 1248, 16384)])
+@pytest.mark.parametrize("split_k", [0, 1])
+def test_gemm_wgrad(cuda_lib, M, N, K, split_k):
+    """dW[M=out,N=in] += dZ[K=batch,M]^T @ X[K=batch,N] — both operands MN-major, fp32 atomic accumulate."""
+    from deepfm_b200.ops.kernels import GemmPlan
+    g = torch.Generator(device="cuda").manual_seed(M + N * 5 + K)
+    dZ = (torch.randn(K, M, device="cuda", generator=g) * 0.1).bfloat16()
+    X = (torch.randn(K, N, device="cuda", generator=g) * 0.5).bfloat16()
+    out = torch.ones(M, N, device="cuda", dtype=torch.float32)
+    plan = GemmPlan("wgrad", dZ, X, out, M, N, K, split_k=split_k)
+    plan.run()
+    torch.cuda.synchronize()
+    ref = 1.0 + dZ.float().t() @ X.float()
+    err = _rel_err(out, ref)
+    assert err < 2e-3, (err, plan.info())
+
+
+@pytest.mark.parametrize("B,F,K,N", [(1024, 39, 32, 117581), (77, 39, 64, 5000), (512, 13, 16, 1000), (33, 5, 128, 64),
+                                     (64, 39, 8, 100), (64, 3, 4, 50)])
+def test_emb_fm_fwd_bwd(cuda_lib, B, F, K, N):
+    from deepfm_b200.ops import kernels as k
+    g = torch.Generator(device="cuda").manual_seed(B + F + K)
+    ids = torch.randint(0, N, (B, F), device="cuda", generator=g, dtype=torch.int64)
+    ids[:, 0] = ids[0, 0]  # heavy duplicate id
+    vals = torch.rand(B, F, device="cuda", generator=g)
+    vals[:, -1] = 0.0  # padding-style zero values
+    fm_w = torch.randn(N, device="cuda", generator=g) * 0.1
+    fm_v = torch.randn(N, K, device="cuda", generator=g) * 0.1
+    x0 = torch.zeros(B, F * K, device="cuda", dtype=torch.bfloat16)
+    S = torch.zeros(B, K, device="cuda")
+    yfm = torch.zeros(B, device="cuda")
+    ids32 = ids.int()
+    k.emb_fm_fwd(ids32, vals, fm_w, fm_v, x0, S, yfm)
+    torch.cuda.synchronize()
+    e = fm_v[ids] * vals.unsqueeze(-1)
+    ref_y = (fm_w[ids] * vals).sum(1) + 0.5 * (e.sum(1).pow(2) - e.pow(2).sum(1)).sum(1)
+    assert torch.allclose(yfm, ref_y, rtol=1e-4, atol=1e-5), (yfm - ref_y).abs().max()
+    assert torch.allclose(S, e.sum(1), rtol=1e-5, atol=1e-6)
+    assert torch.allclose(x0.float(), e.reshape(B, F * K), rtol=1e-2, atol=1e-4)
+    # backward
+    dy = torch.randn(B, device="cuda", generator=g) / B
+    dx0 = (torch.randn(B, F * K, device="cuda", generator=g) * 0.01).bfloat16()
+    g_w = torch.zeros(N, device="cuda")
+    g_v = torch.zeros(N, K, device="cuda")
+    k.emb_bwd(ids32, vals, fm_v, S, dy, dx0, g_w, g_v)
+    torch.cuda.synchronize()
+    fm_w_r = fm_w.clone().requires_grad_(True)
+    fm_v_r = fm_v.clone().requires_grad_(True)
+    e_r = fm_v_r[ids] * vals.unsqueeze(-1)
+    y_r = (fm_w_r[ids] * vals).sum(1) + 0.5 * (e_r.sum(1).pow(2) - e_r.pow(2).sum(1)).sum(1)
+    total = (y_r * dy).sum() + (e_r.reshape(B, F * K) * dx0.float()).sum()
+    total.backward()
+    assert torch.allclose(g_w, fm_w_r.grad, rtol=1e-4, atol=1e-6), (g_w - fm_w_r.grad).abs().max()
+    assert torch.allclose(g_v, fm_v_r.grad, rtol=1e-3, atol=1e-6), (g_v - fm_v_r.grad).abs().max()
+
+
+@pytest.mark.parametrize("B,H", [(1024, 400), (37, 32), (256, 64), (100, 33 * 2)])
+def test_logit_loss(cuda_lib, B, H):
+    from deepfm_b200.ops import kernels as k
+    g = torch.Generator(device="cuda").manual_seed(B + H)
+    x = torch.relu(torch.randn(B, H, device="cuda", generator=g)).bfloat16()
+    w = torch.randn(H, device="cuda", generator=g) * 0.1
+    b_out = torch.randn(1, device="cuda", generator=g)
+    fm_bias = torch.randn(1, device="cuda", generator=g)
+    yfm = torch.randn(B, device="cuda", generator=g)
+    labels = (torch.rand(B, device="cuda", generator=g) > 0.7).float()
+    prob = torch.empty(B, device="cuda"); logit = torch.empty(B, device="cuda"); dy = torch.empty(B, device="cuda")
+    dz = torch.empty(B, H, device="cuda", dtype=torch.bfloat16)
+    loss = torch.zeros(1, device="cuda"); gw = torch.zeros(H, device="cuda"); gb = torch.zeros(1, device="cuda")
+    gfb = torch.zeros(1, device="cuda"); gbl = torch.zeros(H, device="cuda")
+    k.logit_loss(x, w, b_out, fm_bias, yfm, labels, 1.0 / B, 2.0, True, prob, logit, dy, dz, loss, gw, gb, gfb, gbl)
+    torch.cuda.synchronize()
+    xr = x.float()
+    y = fm_bias + b_out + yfm + xr @ w
+    ref_loss = torch.nn.functional.binary_cross_entropy_with_logits(y, labels, reduction="sum")
+    ref_dy = (torch.sigmoid(y) - labels) / B
+    assert torch.allclose(logit, y, rtol=1e-4, atol=1e-4)
+    assert torch.allclose(prob, torch.sigmoid(y), rtol=1e-3, atol=1e-5)
+    assert torch.allclose(loss[0], ref_loss, rtol=1e-4)
+    assert torch.allclose(dy, ref_dy, rtol=1e-3, atol=1e-7)
+    ref_dz = ref_dy[:, None] * w[None, :] * (xr != 0).float() * 2.0
+    assert _rel_err(dz, ref_dz) < 1e-2
+    assert torch.allclose(gw, xr.t() @ ref_dy, rtol=1e-3, atol=1e-6)
+    assert torch.allclose(gb[0], ref_dy.sum(), rtol=1e-3, atol=1e-6)
+    assert torch.allclose(gfb[0], ref_dy.sum(), rtol=1e-3, atol=1e-6)
+    assert torch.allclose(gbl, dz.float().sum(0), rtol=2e-2, atol=1e-5)
+    # colsum helper
+    cs = torch.zeros(H, device="cuda")
+    k.colsum_bf16(dz, cs)
+    torch.cuda.synchronize()
+    assert torch.allclose(cs, dz.float().sum(0), rtol=1e-4, atol=1e-6)
+
+
+@pytest.mark.parametrize("opt", ["Adam", "Adagrad", "Momentum", "ftrl", "GD"])
+def test_flat_opt_matches_tf1_reference(cuda_lib, opt):
+    from deepfm_b200.ops import kernels as k
+    from deepfm_b200.optim import TF1Optimizer, SLOT_INIT
+    n = 4096 * 3 + 64
+    g = torch.Generator(device="cuda").manual_seed(11)
+    w = torch.randn(n, device="cuda", generator=g)
+    w_ref = w.clone()
+    ref = TF1Optimizer(opt, 1e-2)
+    inits = SLOT_INIT[ref.name] + [0.0, 0.0]
+    s0 = torch.full((n,), inits[0], device="cuda"); s1 = torch.full((n,), inits[1], device="cuda")
+    slots_ref = [torch.full((n,), v, device="cuda") for v in SLOT_INIT[ref.name]]
+    shadow = torch.zeros(1024, device="cuda", dtype=torch.bfloat16)
+    step = torch.zeros(1, device="cuda", dtype=torch.int64)
+    reg = torch.zeros(1, device="cuda"); done = torch.zeros(1, device="cuda", dtype=torch.int32)
+    l2 = 1e-3
+    for it in range(3):
+        grad = torch.randn(n, device="cuda", generator=g)
+        gbuf = grad.clone()
+        reg.zero_()
+        ref_reg = 0.5 * l2 * w_ref[64:2048].pow(2).sum()
+        k.flat_opt_step(w, gbuf, s0, s1, ref.name, 1e-2, 0.9, 0.999, 1e-8, 0.95, 1.0, (64, 2048), l2, (2048, 3072),
+                        shadow, step, reg, done)
+        torch.cuda.synchronize()
+        g_ref = grad.clone()
+        g_ref[64:2048] += l2 * w_ref[64:2048]
+        ref.apply_dense(w_ref, g_ref, slots_ref, it + 1)
+        assert int(step.item()) == it + 1
+        assert float(gbuf.abs().max()) == 0.0
+        assert torch.allclose(w, w_ref, rtol=2e-4, atol=2e-6), (opt, it, (w - w_ref).abs().max())
+        assert torch.allclose(reg[0], ref_reg, rtol=1e-4)
+        assert torch.allclose(shadow.float(), w[2048:3072], rtol=1e-2, atol=1e-3)
+
+
+def test_auc_hist_matches_streaming_auc(cuda_lib):
+    from deepfm_b200.ops import kernels as k
+    from deepfm_b200.utils.auc import StreamingAUC, thresholds
+    B = 10000
+    prob = torch.rand(B, device="cuda")
+    prob[:5] = torch.tensor([0.0, 1.0, 0.5, 1.0 / 199, 198.0 / 199])
+    labels = (torch.rand(B, device="cuda") < prob).float()
+    thr = torch.from_numpy(thresholds()).cuda()
+    hist = torch.zeros(2, 201, device="cuda")
+    k.auc_hist(prob, labels, thr, hist)
+    torch.cuda.synchronize()
+    ref = StreamingAUC()
+    ref.update(labels, prob)
+    assert torch.equal(hist.cpu().double(), ref.hist)
