@@ -1,0 +1,605 @@
+// Host-side native IO for deepfm_b200 (no CUDA, no TensorFlow):
+//   * CRC32C (SSE4.2 `crc32` instruction, software table fallback)                       [reference dep N1]
+//   * TFRecord framing reader/writer over files, FIFOs and pipes (read()-only: "pipe mode") [N1, N3]
+//   * fixed-schema `tf.train.Example` batch parser {label f32 x1, ids i64 xF, values f32 xF} writing
+//     straight into caller-provided (pinned) staging buffers — the vectorised `tf.parse_example` of
+//     HVD:76-89 / PS:79-92                                                                 [N2]
+//   * prefetching loader: 1 sequential reader thread (shard -> batch, like `dataset.shard().batch()`),
+//     P parser threads, ordered hand-off through a ring of caller-owned batch slots          [N4]
+// Wire formats: SURVEY Appendix B. C ABI at the bottom; Python binding: data/native.py.
+#include <errno.h>
+#include <fcntl.h>
+#include <stdarg.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <unistd.h>
+
+#include <atomic>
+#include <condition_variable>
+#include <deque>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#if defined(__SSE4_2__)
+#include <nmmintrin.h>
+#endif
+
+namespace dfmio {
+
+static thread_local char g_err[512] = "";
+static void set_err(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+// ------------------------------------------------------------------------------------------ crc32c
+static uint32_t g_tbl[256];
+static std::once_flag g_tbl_once;
+static void init_tbl() {
+  for (uint32_t i = 0; i < 256; ++i) {
+    uint32_t c = i;
+    for (int k = 0; k < 8; ++k) c = (c & 1) ? (c >> 1) ^ 0x82F63B78u : c >> 1;
+    g_tbl[i] = c;
+  }
+}
+static uint32_t crc32c_sw(const uint8_t* p, size_t n, uint32_t crc) {
+  std::call_once(g_tbl_once, init_tbl);
+  uint32_t c = crc ^ 0xFFFFFFFFu;
+  for (size_t i = 0; i < n; ++i) c = g_tbl[(c ^ p[i]) & 0xFF] ^ (c >> 8);
+  return c ^ 0xFFFFFFFFu;
+}
+uint32_t crc32c(const uint8_t* p, size_t n, uint32_t crc = 0) {
+#if defined(__SSE4_2__)
+  uint64_t c = crc ^ 0xFFFFFFFFu;
+  while (n >= 8) {
+    uint64_t v;
+    memcpy(&v, p, 8);
+    c = _mm_crc32_u64(c, v);
+    p += 8;
+    n -= 8;
+  }
+  uint32_t c32 = (uint32_t)c;
+  while (n--) c32 = _mm_crc32_u8(c32, *p++);
+  return c32 ^ 0xFFFFFFFFu;
+#else
+  return crc32c_sw(p, n, crc);
+#endif
+}
+static inline uint32_t mask_crc(uint32_t c) { return ((c >> 15) | (c << 17)) + 0xA282EAD8u; }
+
+// ------------------------------------------------------------------------------------------ record reader
+class RecordReader {
+ public:
+  ~RecordReader() { close_fd(); }
+  bool open_path(const char* path) {
+    close_fd();
+    fd_ = ::open(path, O_RDONLY);
+    if (fd_ < 0) {
+      set_err("cannot open %s: %s", path, strerror(errno));
+      return false;
+    }
+    buf_.resize(1 << 20);
+    beg_ = end_ = 0;
+    return true;
+  }
+  void close_fd() {
+    if (fd_ >= 0) ::close(fd_);
+    fd_ = -1;
+  }
+  // 1 = record appended to `out`, 0 = clean EOF, -1 = error
+  int next(std::vector<uint8_t>& out, size_t* off, size_t* len, bool check_crc) {
+    uint8_t hdr[12];
+    int r = read_exact(hdr, 12, true);
+    if (r <= 0) return r;
+    uint64_t n;
+    uint32_t c;
+    memcpy(&n, hdr, 8);
+    memcpy(&c, hdr + 8, 4);
+    if (check_crc && mask_crc(crc32c(hdr, 8)) != c) {
+      set_err("corrupted record length CRC");
+      return -1;
+    }
+    if (n > (1ull << 31)) {
+      set_err("record too large (%llu bytes)", (unsigned long long)n);
+      return -1;
+    }
+    const size_t o = out.size();
+    out.resize(o + n);
+    if (read_exact(out.data() + o, n, false) <= 0 && n > 0) return -1;
+    uint8_t tail[4];
+    if (read_exact(tail, 4, false) <= 0) return -1;
+    memcpy(&c, tail, 4);
+    if (check_crc && mask_crc(crc32c(out.data() + o, n)) != c) {
+      set_err("corrupted record data CRC");
+      return -1;
+    }
+    *off = o;
+    *len = n;
+    return 1;
+  }
+
+ private:
+  int read_exact(uint8_t* dst, size_t n, bool eof_ok) {
+    size_t got = 0;
+    while (got < n) {
+      if (beg_ == end_) {
+        ssize_t k = ::read(fd_, buf_.data(), buf_.size());
+        if (k < 0) {
+          if (errno == EINTR) continue;
+          set_err("read failed: %s", strerror(errno));
+          return -1;
+        }
+        if (k == 0) {
+          if (eof_ok && got == 0) return 0;
+          set_err("truncated record");
+          return -1;
+        }
+        beg_ = 0;
+        end_ = (size_t)k;
+      }
+      const size_t take = std::min(n - got, end_ - beg_);
+      memcpy(dst + got, buf_.data() + beg_, take);
+      beg_ += take;
+      got += take;
+    }
+    return 1;
+  }
+  int fd_ = -1;
+  std::vector<uint8_t> buf_;
+  size_t beg_ = 0, end_ = 0;
+};
+
+// ------------------------------------------------------------------------------------------ proto parsing
+static inline bool rd_varint(const uint8_t*& p, const uint8_t* e, uint64_t* v) {
+  uint64_t r = 0;
+  int s = 0;
+  while (p < e && s <= 63) {
+    const uint8_t b = *p++;
+    r |= (uint64_t)(b & 0x7F) << s;
+    if (!(b & 0x80)) {
+      *v = r;
+      return true;
+    }
+    s += 7;
+  }
+  return false;
+}
+static inline bool skip_field(const uint8_t*& p, const uint8_t* e, uint32_t wt) {
+  uint64_t n;
+  switch (wt) {
+    case 0: return rd_varint(p, e, &n);
+    case 1: p += 8; return p <= e;
+    case 2: if (!rd_varint(p, e, &n)) return false; p += n; return p <= e;
+    case 5: p += 4; return p <= e;
+    default: return false;
+  }
+}
+static inline bool rd_ld(const uint8_t*& p, const uint8_t* e, const uint8_t** b, const uint8_t** be) {
+  uint64_t n;
+  if (!rd_varint(p, e, &n) || n > (uint64_t)(e - p)) return false;
+  *b = p;
+  *be = p + n;
+  p += n;
+  return true;
+}
+
+static int parse_floats(const uint8_t* p, const uint8_t* e, float* out, int cap) {  // FloatList body
+  int cnt = 0;
+  while (p < e) {
+    uint64_t tag;
+    if (!rd_varint(p, e, &tag)) return -1;
+    if ((tag >> 3) == 1 && (tag & 7) == 2) {
+      const uint8_t *b, *be;
+      if (!rd_ld(p, e, &b, &be)) return -1;
+      const int n = (int)((be - b) / 4);
+      if (cnt + n > cap) return -2;
+      memcpy(out + cnt, b, (size_t)n * 4);
+      cnt += n;
+    } else if ((tag >> 3) == 1 && (tag & 7) == 5) {
+      if (p + 4 > e) return -1;
+      if (cnt + 1 > cap) return -2;
+      memcpy(out + cnt, p, 4);
+      p += 4;
+      ++cnt;
+    } else if (!skip_field(p, e, tag & 7)) {
+      return -1;
+    }
+  }
+  return cnt;
+}
+static int parse_ints(const uint8_t* p, const uint8_t* e, int32_t* out, int cap) {  // Int64List body -> int32
+  int cnt = 0;
+  while (p < e) {
+    uint64_t tag;
+    if (!rd_varint(p, e, &tag)) return -1;
+    if ((tag >> 3) == 1 && (tag & 7) == 2) {
+      const uint8_t *b, *be;
+      if (!rd_ld(p, e, &b, &be)) return -1;
+      while (b < be) {
+        uint64_t v;
+        if (!rd_varint(b, be, &v)) return -1;
+        if (cnt + 1 > cap) return -2;
+        if (v > 0x7FFFFFFFull) return -3;
+        out[cnt++] = (int32_t)v;
+      }
+    } else if ((tag >> 3) == 1 && (tag & 7) == 0) {
+      uint64_t v;
+      if (!rd_varint(p, e, &v)) return -1;
+      if (cnt + 1 > cap) return -2;
+      if (v > 0x7FFFFFFFull) return -3;
+      out[cnt++] = (int32_t)v;
+    } else if (!skip_field(p, e, tag & 7)) {
+      return -1;
+    }
+  }
+  return cnt;
+}
+
+// One serialized Example -> label, ids[F], vals[F]. 0 on success.
+static int parse_example(const uint8_t* p, size_t len, int F, float* label, int32_t* ids, float* vals) {
+  const uint8_t* e = p + len;
+  bool got_l = false, got_i = false, got_v = false;
+  while (p < e) {
+    uint64_t tag;
+    if (!rd_varint(p, e, &tag)) goto malformed;
+    if (tag != ((1u << 3) | 2)) {
+      if (!skip_field(p, e, tag & 7)) goto malformed;
+      continue;
+    }
+    const uint8_t *f, *fe;
+    if (!rd_ld(p, e, &f, &fe)) goto malformed;
+    while (f < fe) {  // Features: repeated map entries
+      uint64_t t2;
+      if (!rd_varint(f, fe, &t2)) goto malformed;
+      if (t2 != ((1u << 3) | 2)) {
+        if (!skip_field(f, fe, t2 & 7)) goto malformed;
+        continue;
+      }
+      const uint8_t *m, *me;
+      if (!rd_ld(f, fe, &m, &me)) goto malformed;
+      const uint8_t* key = nullptr;
+      size_t klen = 0;
+      const uint8_t *val = nullptr, *vale = nullptr;
+      while (m < me) {
+        uint64_t t3;
+        if (!rd_varint(m, me, &t3)) goto malformed;
+        if ((t3 & 7) != 2) {
+          if (!skip_field(m, me, t3 & 7)) goto malformed;
+          continue;
+        }
+        const uint8_t *b, *be;
+        if (!rd_ld(m, me, &b, &be)) goto malformed;
+        if ((t3 >> 3) == 1) { key = b; klen = (size_t)(be - b); }
+        else if ((t3 >> 3) == 2) { val = b; vale = be; }
+      }
+      if (!key || !val) continue;
+      int which = -1;
+      if (klen == 5 && !memcmp(key, "label", 5)) which = 0;
+      else if (klen == 3 && !memcmp(key, "ids", 3)) which = 1;
+      else if (klen == 6 && !memcmp(key, "values", 6)) which = 2;
+      if (which < 0) continue;
+      // Feature: oneof { bytes_list=1, float_list=2, int64_list=3 }
+      const uint8_t* q = val;
+      while (q < vale) {
+        uint64_t t4;
+        if (!rd_varint(q, vale, &t4)) goto malformed;
+        if ((t4 & 7) != 2) {
+          if (!skip_field(q, vale, t4 & 7)) goto malformed;
+          continue;
+        }
+        const uint8_t *b, *be;
+        if (!rd_ld(q, vale, &b, &be)) goto malformed;
+        const uint32_t fld = (uint32_t)(t4 >> 3);
+        if (which == 0 && fld == 2) {
+          float tmp[2];
+          if (parse_floats(b, be, tmp, 1) != 1) { set_err("feature 'label' must hold exactly 1 float"); return -1; }
+          *label = tmp[0];
+          got_l = true;
+        } else if (which == 1 && fld == 3) {
+          const int n = parse_ints(b, be, ids, F);
+          if (n == -3) { set_err("feature id does not fit in int32"); return -1; }
+          if (n != F) { set_err("feature 'ids': expected %d values per record, got %s", F, n == -2 ? "more" : "fewer/malformed"); return -1; }
+          got_i = true;
+        } else if (which == 2 && fld == 2) {
+          const int n = parse_floats(b, be, vals, F);
+          if (n != F) { set_err("feature 'values': expected %d values per record, got %s", F, n == -2 ? "more" : "fewer/malformed"); return -1; }
+          got_v = true;
+        }
+      }
+    }
+  }
+  if (!got_l || !got_i || !got_v) {
+    set_err("Example is missing feature %s", !got_l ? "'label'" : !got_i ? "'ids'" : "'values'");
+    return -1;
+  }
+  return 0;
+malformed:
+  set_err("malformed Example protobuf");
+  return -1;
+}
+
+// ------------------------------------------------------------------------------------------ loader
+struct RawBatch {
+  long seq = 0;
+  int rows = 0;
+  std::vector<uint8_t> bytes;
+  std::vector<size_t> off, len;
+};
+
+class Loader {
+ public:
+  Loader(std::vector<std::string> paths, int F, int batch, int shard_n, int shard_i, int epochs, int threads,
+         bool drop_remainder, bool check_crc, uint8_t* slots, int nslots, size_t slot_stride)
+      : paths_(std::move(paths)), F_(F), B_(batch), shard_n_(shard_n < 1 ? 1 : shard_n), shard_i_(shard_i),
+        epochs_(epochs), drop_(drop_remainder), crc_(check_crc), slots_(slots), nslots_(nslots),
+        stride_(slot_stride) {
+    for (int i = 0; i < nslots_; ++i) free_slots_.push_back(i);
+    reader_ = std::thread([this] { reader_main(); });
+    for (int i = 0; i < (threads < 1 ? 1 : threads); ++i) parsers_.emplace_back([this] { parser_main(); });
+  }
+  ~Loader() {
+    {
+      std::lock_guard<std::mutex> l(mu_);
+      stop_ = true;
+    }
+    cv_work_.notify_all();
+    cv_free_.notify_all();
+    cv_done_.notify_all();
+    cv_raw_space_.notify_all();
+    if (reader_.joinable()) reader_.join();
+    for (auto& t : parsers_) t.join();
+  }
+  static size_t slot_bytes(int B, int F) {  // labels f32[B] | ids i32[B*F] | vals f32[B*F], 256-byte aligned parts
+    auto al = [](size_t x) { return (x + 255) & ~size_t(255); };
+    return al((size_t)B * 4) + 2 * al((size_t)B * F * 4);
+  }
+  float* slot_labels(int s) const { return reinterpret_cast<float*>(slots_ + (size_t)s * stride_); }
+  int32_t* slot_ids(int s) const {
+    return reinterpret_cast<int32_t*>(slots_ + (size_t)s * stride_ + (((size_t)B_ * 4 + 255) & ~size_t(255)));
+  }
+  float* slot_vals(int s) const {
+    return reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(slot_ids(s)) + (((size_t)B_ * F_ * 4 + 255) & ~size_t(255)));
+  }
+
+  // Blocks until the next batch (in order) is parsed. Returns rows (>0), 0 at end of data, -1 on error.
+  int next(int* slot_out) {
+    std::unique_lock<std::mutex> l(mu_);
+    for (;;) {
+      if (!err_.empty()) {
+        set_err("%s", err_.c_str());
+        return -1;
+      }
+      if (!done_.empty() && done_.front().seq == next_seq_) {
+        Done d = done_.front();
+        done_.pop_front();
+        ++next_seq_;
+        *slot_out = d.slot;
+        return d.rows;
+      }
+      if (reader_finished_ && next_seq_ >= total_batches_) return 0;
+      cv_done_.wait(l);
+    }
+  }
+  void release(int slot) {
+    {
+      std::lock_guard<std::mutex> l(mu_);
+      free_slots_.push_back(slot);
+    }
+    cv_work_.notify_all();  // parsers wait on cv_work_ for (raw batch AND free slot)
+  }
+  long records_read() const { return records_read_.load(); }
+
+ private:
+  struct Done { long seq; int slot; int rows; };
+
+  void fail(const std::string& m) {
+    std::lock_guard<std::mutex> l(mu_);
+    if (err_.empty()) err_ = m;
+    cv_done_.notify_all();
+    cv_work_.notify_all();
+  }
+
+  void reader_main() {
+    long seq = 0, rec_idx = 0;
+    std::unique_ptr<RawBatch> cur(new RawBatch());
+    RecordReader rr;
+    std::vector<uint8_t> scratch;
+    for (int ep = 0; ep < epochs_ && !stopped(); ++ep) {
+      for (const auto& path : paths_) {
+        if (!rr.open_path(path.c_str())) { fail(g_err); return; }
+        for (;;) {
+          if (stopped()) return;
+          if (rec_idx % shard_n_ != shard_i_) {  // `dataset.shard(n, i)`: keep every n-th record
+            scratch.clear();
+            size_t o, n;
+            int r = rr.next(scratch, &o, &n, false);
+            if (r < 0) { fail(g_err); return; }
+            if (r == 0) break;
+            ++rec_idx;
+            continue;
+          }
+          size_t o, n;
+          int r = rr.next(cur->bytes, &o, &n, crc_);
+          if (r < 0) { fail(std::string(g_err) + " in " + path); return; }
+          if (r == 0) break;
+          ++rec_idx;
+          records_read_.fetch_add(1);
+          cur->off.push_back(o);
+          cur->len.push_back(n);
+          if (++cur->rows == B_) {
+            cur->seq = seq++;
+            if (!push_raw(std::move(cur))) return;
+            cur.reset(new RawBatch());
+          }
+        }
+      }
+    }
+    if (cur->rows > 0 && !drop_) {
+      cur->seq = seq++;
+      if (!push_raw(std::move(cur))) return;
+    }
+    {
+      std::lock_guard<std::mutex> l(mu_);
+      total_batches_ = seq;
+      reader_finished_ = true;
+    }
+    cv_work_.notify_all();
+    cv_done_.notify_all();
+  }
+
+  bool push_raw(std::unique_ptr<RawBatch> b) {
+    std::unique_lock<std::mutex> l(mu_);
+    cv_raw_space_.wait(l, [this] { return stop_ || (int)raw_.size() < nslots_ + 2; });
+    if (stop_) return false;
+    raw_.push_back(std::move(b));
+    l.unlock();
+    cv_work_.notify_one();
+    return true;
+  }
+
+  void parser_main() {
+    for (;;) {
+      std::unique_ptr<RawBatch> b;
+      int slot = -1;
+      {
+        std::unique_lock<std::mutex> l(mu_);
+        // take work only when a slot is free; the OLDEST raw batch always gets the next free slot (no deadlock)
+        cv_work_.wait(l, [this] { return stop_ || !err_.empty() || (!raw_.empty() && !free_slots_.empty()) || (reader_finished_ && raw_.empty()); });
+        if (stop_ || !err_.empty() || (raw_.empty() && reader_finished_)) return;
+        b = std::move(raw_.front());
+        raw_.pop_front();
+        slot = free_slots_.front();
+        free_slots_.pop_front();
+      }
+      cv_raw_space_.notify_one();
+      float* lab = slot_labels(slot);
+      int32_t* ids = slot_ids(slot);
+      float* vals = slot_vals(slot);
+      for (int r = 0; r < b->rows; ++r) {
+        if (parse_example(b->bytes.data() + b->off[r], b->len[r], F_, lab + r, ids + (size_t)r * F_, vals + (size_t)r * F_)) {
+          fail(g_err);
+          return;
+        }
+      }
+      {
+        std::lock_guard<std::mutex> l(mu_);
+        Done d{b->seq, slot, b->rows};
+        auto it = done_.begin();
+        while (it != done_.end() && it->seq < d.seq) ++it;
+        done_.insert(it, d);
+      }
+      cv_done_.notify_all();
+    }
+  }
+  bool stopped() {
+    std::lock_guard<std::mutex> l(mu_);
+    return stop_;
+  }
+
+  std::vector<std::string> paths_;
+  int F_, B_, shard_n_, shard_i_, epochs_;
+  bool drop_, crc_;
+  uint8_t* slots_;
+  int nslots_;
+  size_t stride_;
+  std::mutex mu_;
+  std::condition_variable cv_work_, cv_free_, cv_done_, cv_raw_space_;
+  std::deque<std::unique_ptr<RawBatch>> raw_;
+  std::deque<int> free_slots_;
+  std::deque<Done> done_;
+  long next_seq_ = 0, total_batches_ = 0;
+  bool reader_finished_ = false, stop_ = false;
+  std::string err_;
+  std::atomic<long> records_read_{0};
+  std::thread reader_;
+  std::vector<std::thread> parsers_;
+};
+
+}  // namespace dfmio
+
+using namespace dfmio;
+
+extern "C" {
+
+const char* dfmio_last_error() { return g_err; }
+uint32_t dfmio_crc32c(const uint8_t* p, size_t n) { return crc32c(p, n); }
+uint32_t dfmio_masked_crc32c(const uint8_t* p, size_t n) { return mask_crc(crc32c(p, n)); }
+
+// ---- writer: frames `n` payload bytes as one TFRecord and appends to fd-backed FILE*
+void* dfmio_writer_open(const char* path) {
+  FILE* f = fopen(path, "wb");
+  if (!f) set_err("cannot open %s for writing: %s", path, strerror(errno));
+  return f;
+}
+int dfmio_writer_write(void* w, const uint8_t* data, uint64_t n) {
+  FILE* f = (FILE*)w;
+  uint8_t hdr[12];
+  memcpy(hdr, &n, 8);
+  const uint32_t c1 = mask_crc(crc32c(hdr, 8));
+  memcpy(hdr + 8, &c1, 4);
+  const uint32_t c2 = mask_crc(crc32c(data, n));
+  if (fwrite(hdr, 1, 12, f) != 12 || fwrite(data, 1, n, f) != n || fwrite(&c2, 1, 4, f) != 4) {
+    set_err("write failed: %s", strerror(errno));
+    return -1;
+  }
+  return 0;
+}
+int dfmio_writer_close(void* w) { return fclose((FILE*)w); }
+
+// ---- sequential reader (used for tests and the Python fallback path)
+void* dfmio_reader_open(const char* path) {
+  RecordReader* r = new RecordReader();
+  if (!r->open_path(path)) {
+    delete r;
+    return nullptr;
+  }
+  return r;
+}
+// Returns record length (>=0) with bytes copied into buf (cap bytes), -1 = EOF, -2 = error, -3 = buffer too small.
+long dfmio_reader_next(void* rd, uint8_t* buf, size_t cap, int check_crc) {
+  static thread_local std::vector<uint8_t> tmp;
+  tmp.clear();
+  size_t o, n;
+  int r = ((RecordReader*)rd)->next(tmp, &o, &n, check_crc != 0);
+  if (r == 0) return -1;
+  if (r < 0) return -2;
+  if (n > cap) return -3;
+  memcpy(buf, tmp.data(), n);
+  return (long)n;
+}
+void dfmio_reader_close(void* rd) { delete (RecordReader*)rd; }
+
+// ---- batch parse: `nrec` serialized Examples (concatenated in `bytes`, located by off/len) -> dense arrays
+int dfmio_parse_batch(const uint8_t* bytes, const uint64_t* off, const uint64_t* len, int nrec, int F, float* labels,
+                      int32_t* ids, float* vals) {
+  for (int r = 0; r < nrec; ++r)
+    if (parse_example(bytes + off[r], len[r], F, labels + r, ids + (size_t)r * F, vals + (size_t)r * F)) return -1;
+  return 0;
+}
+
+// ---- prefetching loader
+uint64_t dfmio_loader_slot_bytes(int batch, int F) { return Loader::slot_bytes(batch, F); }
+void* dfmio_loader_create(const char** paths, int npaths, int F, int batch, int shard_n, int shard_i, int epochs,
+                          int threads, int drop_remainder, int check_crc, uint8_t* slots, int nslots,
+                          uint64_t slot_stride) {
+  if (npaths <= 0 || F <= 0 || batch <= 0 || nslots < 2 || !slots || slot_stride < Loader::slot_bytes(batch, F) ||
+      shard_i < 0 || shard_i >= (shard_n < 1 ? 1 : shard_n)) {
+    set_err("loader_create: bad arguments");
+    return nullptr;
+  }
+  std::vector<std::string> p(paths, paths + npaths);
+  return new Loader(std::move(p), F, batch, shard_n, shard_i, epochs, threads, drop_remainder != 0, check_crc != 0,
+                    slots, nslots, slot_stride);
+}
+int dfmio_loader_next(void* ld, int* slot) { return ((Loader*)ld)->next(slot); }
+void dfmio_loader_release(void* ld, int slot) { ((Loader*)ld)->release(slot); }
+long dfmio_loader_records(void* ld) { return ((Loader*)ld)->records_read(); }
+void dfmio_loader_destroy(void* ld) { delete (Loader*)ld; }
+
+}  // extern "C"
