@@ -1,0 +1,215 @@
+#!/usr/bin/env python
+"""Headline benchmark: DeepFM train samples/sec (BASELINE.json config 2 — Criteo-shaped DeepFM, field 39,
+feature 117581, emb 32, MLP 400-400-400, Adam, bf16 compute, replicated embeddings, data parallel).
+
+    python bench.py --gpus N --steps K --warmup W            (N>1: launched by torch.distributed.run, one rank/GPU)
+    python bench.py --impl reference ...                       (the unmodified TF1/Horovod reference: unavailable here)
+    python bench.py --impl proxy ...                           (NCCL + cuBLAS + torch.optim proxy of 2-hvd-gpu)
+
+Prints ONE JSON line on rank 0. `value` = device-timed (CUDA events, max over ranks) whole-job samples/s with
+device-resident input batches rotated through a pool larger than L2; `e2e.value` = the same metric through the
+public API `Trainer.train_batch` with, every step, the H2D copy of that step's batch from pinned host memory and
+a D2H read of the step's loss.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+
+METRIC = "DeepFM train samples/sec (whole job, device-timed max over ranks)"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "proxy"])
+    ap.add_argument("--batch_size", type=int, default=1024, help="per-GPU batch (reference: 1024 per worker, NB-HVD:97)")
+    ap.add_argument("--deep_layers", default="400,400,400")
+    ap.add_argument("--embedding_size", type=int, default=32)
+    ap.add_argument("--feature_size", type=int, default=117581)
+    ap.add_argument("--field_size", type=int, default=39)
+    ap.add_argument("--optimizer", default="Adam")
+    ap.add_argument("--pool", type=int, default=0, help="distinct batches in the input pool (0 = enough to exceed L2)")
+    ap.add_argument("--no_graph", action="store_true")
+    ap.add_argument("--comm", default="auto", choices=["auto", "p2p", "nvls", "nccl"])
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi sampling DURING the timed region (B200_PROFILING.md 'clocks' recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx, self.proc, self.path = gpu_index, None, "/tmp/dfm_clocks_%d.csv" % os.getpid()
+
+    def start(self):
+        try:
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                         stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.f.close()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path):
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 9:
+                continue
+            try:
+                sm.append(float(parts[1])); mx.append(float(parts[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, parts[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if sm:
+            sm.sort()
+            out.update(sm_mhz=sm[len(sm) // 2], sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        try:
+            os.remove(self.path)
+        except OSError:
+            pass
+        return out
+
+
+def main():
+    a = parse_args()
+    if a.impl == "reference":
+        print(json.dumps({"impl": "reference",
+                          "unavailable": "reference is two TF1.14/1.15 + Horovod + sagemaker_tensorflow scripts with no "
+                                         "setup.py/pyproject (pip: 'not installable'); tensorflow/horovod/mpirun absent offline"}))
+        return 0
+
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != a.gpus and world > 1:
+        a.gpus = world
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    from deepfm_b200.models import DeepFMConfig
+    from deepfm_b200.optim import TF1Optimizer
+    from deepfm_b200.data.synthetic import SyntheticCTR
+    from deepfm_b200.runtime.trainer import Trainer
+
+    cfg = DeepFMConfig(field_size=a.field_size, feature_size=a.feature_size, embedding_size=a.embedding_size,
+                       deep_layers=a.deep_layers, dropout=[0.5] * len(a.deep_layers.split(",")), l2_reg=1e-4)
+    B = a.batch_size
+    # reference scales LR by world size (HVD:149)
+    opt = TF1Optimizer(a.optimizer, 5e-4 * world)
+    backend = "proxy" if a.impl == "proxy" else "fused"
+    tr = Trainer(cfg, B, opt, seed=1234, device=dev, backend=backend, world_size=world, rank=rank,
+                 use_graph=not a.no_graph, comm=a.comm)
+
+    # ---- input pool: distinct batches, total bytes > L2 (126 MB) so no step re-reads a cached batch
+    bytes_per_batch = B * a.field_size * 8 + B * 4
+    pool = a.pool or max(8, int(140e6 // bytes_per_batch) + 1)
+    gen = SyntheticCTR(a.field_size, a.feature_size, seed=rank)
+    host_pool = []
+    for i in range(pool):
+        ids, vals, labels = gen.batch(B, i)
+        host_pool.append((ids.pin_memory(), vals.pin_memory(), labels.pin_memory()))
+    dev_pool = [(i.to(dev), v.to(dev), l.to(dev)) for (i, v, l) in host_pool]
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- (1) device-resident timing ----------------------------------------------------------------------
+    for s in range(a.warmup):
+        tr.train_batch_device(*dev_pool[s % pool])
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for s in range(a.steps):
+        tr.train_batch_device(*dev_pool[(a.warmup + s) % pool])
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = tr.kernels_per_step * a.steps
+    final_loss = float(tr.last_loss().item())
+
+    # ---- (2) end-to-end through the public API: pinned H2D every step + D2H loss read every step ------------
+    for s in range(max(3, a.warmup // 2)):
+        tr.train_batch(*host_pool[s % pool])
+    tr.drain()
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    for s in range(a.steps):
+        tr.train_batch(*host_pool[(a.warmup + s) % pool])
+    losses = tr.drain()
+    f1.record()
+    barrier()
+    ms_e2e = f0.elapsed_time(f1)
+    clocks = sampler.stop() if rank == 0 else None
+
+    t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = float(t[0]), float(t[1])
+    if rank == 0:
+        gb = B * world
+        value = gb * a.steps / (ms / 1e3)
+        e2e = gb * a.steps / (ms_e2e / 1e3)
+        out = {
+            "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": a.steps,
+            "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic Criteo-shaped (random-init weights)",
+            "impl": a.impl,
+            "config": {"model": "DeepFM field39 feat117581 emb%d mlp%s %s" % (a.embedding_size, a.deep_layers, a.optimizer),
+                       "global_batch": gb, "per_gpu_batch": B, "seq_len": a.field_size,
+                       "parallelism": "dp%d" % world, "comm": tr.comm_name,
+                       "l2_cache_policy": "inputs rotate through a pool of %d distinct batches (%.0f MB > 126 MB L2)"
+                                          % (pool, pool * bytes_per_batch / 1e6),
+                       "cuda_graph": not a.no_graph},
+            "clocks": clocks,
+            "e2e": {"value": e2e, "unit": "samples/s", "ms_per_step": ms_e2e / a.steps,
+                    "h2d_bytes_per_step": bytes_per_batch, "d2h_bytes_per_step": 4,
+                    "api": "deepfm_b200.runtime.trainer.Trainer.train_batch"},
+            "gpu_launches": launches, "kernels_per_step": tr.kernels_per_step,
+            "final_loss": final_loss, "e2e_last_loss": losses[-1] if losses else None,
+        }
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    raise SystemExit(main())

@@ -1,0 +1,319 @@
+"""FusedDeepFM — the B200 execution engine for the reference `model_fn` (PS:149-278 / HVD:141-273).
+
+One training step is a fixed sequence of hand-written sm_100a kernels over persistent buffers, captured once in
+a CUDA graph and replayed (no autograd, no allocator traffic, no host sync):
+
+    emb_fm_fwd  ->  mlp_fwd x L (tcgen05, bias+ReLU+dropout epilogue)  ->  logit_loss (loss, dy, dZ_top, head grads)
+    -> per layer, top down:  wgrad (tcgen05, MN-major operands, split-K atomics)  ||  dgrad (tcgen05, mask epilogue)
+       || colsum (bias grads)            [wgrad/colsum run on a forked graph branch]
+    -> emb_bwd (vector atomics into the dense grad buffer)
+    -> flat optimizer (L2 decay + TF-1 update + grad zeroing + bf16 weight shadows + step counter)
+       or, under data parallelism, the fused all-reduce + optimizer kernel (parallel/dp.py)
+
+Layout: models/layout.py. Numerics oracle: models/oracle.py. Kernel ABI: include/deepfm_b200.h.
+"""
+from __future__ import annotations
+
+from collections import OrderedDict
+from typing import Callable, Dict, List, Optional
+
+import torch
+
+from ..optim.tf1 import SLOT_INIT, SLOT_SUFFIXES, TF1Optimizer
+from ..ops import kernels as K
+from ..ops import lib as _native
+from ..utils.auc import NUM_THRESHOLDS, thresholds
+from .config import DeepFMConfig
+from .layout import FlatLayout
+from .params import init_params
+
+
+class FusedDeepFM:
+    def __init__(self, cfg: DeepFMConfig, batch_size: int, optimizer: Optional[TF1Optimizer] = None, seed: int = 0,
+                 device: Optional[torch.device] = None, params: Optional[Dict[str, torch.Tensor]] = None,
+                 global_batch: Optional[int] = None, row_offset: int = 0, grad_alloc: Optional[Callable] = None,
+                 use_graph: bool = True, input_slots: int = 2):
+        """`global_batch`/`row_offset`: under data parallelism the loss is the mean over the GLOBAL batch and the
+        dropout mask of row r is that of global row row_offset+r, so DP-N is bit-comparable to DP-1.
+        `grad_alloc(numel) -> fp32 tensor`: lets parallel/dp.py place the gradient buffer in symmetric memory."""
+        if cfg.batch_norm:
+            raise NotImplementedError("batch_norm=True runs on the torch backend (models/torch_backend.py)")
+        _native.require_gpu()
+        self.cfg = cfg
+        self.B = int(batch_size)
+        self.global_batch = int(global_batch or batch_size)
+        self.row_offset = int(row_offset)
+        self.dev = device or torch.device("cuda", torch.cuda.current_device())
+        self.opt = optimizer or TF1Optimizer("Adam", 5e-4)
+        self.seed = int(seed)
+        self.layout = FlatLayout(cfg)
+        self.use_graph = use_graph
+        L = self.layout
+        F_, Kd = cfg.field_size, cfg.embedding_size
+        dev = self.dev
+        f32 = dict(device=dev, dtype=torch.float32)
+
+        # ---- parameters / grads / slots (flat) ------------------------------------------------------------
+        self.P = torch.zeros(L.total_numel, **f32)
+        self.G = grad_alloc(L.total_numel) if grad_alloc else torch.zeros(L.total_numel, **f32)
+        inits = SLOT_INIT[self.opt.name]
+        self.S0 = torch.full((L.trainable_numel,), inits[0], **f32) if len(inits) > 0 else None
+        self.S1 = torch.full((L.trainable_numel,), inits[1], **f32) if len(inits) > 1 else None
+        self.shadow = torch.zeros(L.shadow_range[1] - L.shadow_range[0], device=dev, dtype=torch.bfloat16)
+        src = params if params is not None else init_params(cfg, seed)
+        for name in L.names():
+            L.view(self.P, name).copy_(src[name].to(dev))
+        self.refresh_shadow()
+
+        # ---- scalars ---------------------------------------------------------------------------------------
+        self.step_t = torch.zeros(1, device=dev, dtype=torch.int64)
+        self.scalars = torch.zeros(2, **f32)
+        self.loss_sum = self.scalars[0:1]
+        self.reg_loss = self.scalars[1:2]
+        self.loss_out = torch.zeros(1, **f32)
+        self.done_counter = torch.zeros(1, device=dev, dtype=torch.int32)
+
+        # ---- activations -----------------------------------------------------------------------------------
+        B = self.B
+        bf = dict(device=dev, dtype=torch.bfloat16)
+        self.in_slots = [dict(ids=torch.zeros(B, F_, device=dev, dtype=torch.int32), vals=torch.zeros(B, F_, **f32),
+                              labels=torch.zeros(B, **f32)) for _ in range(max(1, input_slots))]
+        self.x0 = torch.zeros(B, F_ * Kd, **bf)
+        self.dx0 = torch.zeros(B, F_ * Kd, **bf)
+        self.Ssum = torch.zeros(B, Kd, **f32)
+        self.yfm = torch.zeros(B, **f32)
+        self.acts = [torch.zeros(B, h, **bf) for h in cfg.deep_layers]
+        self.dz = [torch.zeros(B, h, **bf) for h in cfg.deep_layers]
+        self.dy = torch.zeros(B, **f32)
+        self.prob = torch.zeros(B, **f32)
+        self.logit = torch.zeros(B, **f32)
+        self.auc_thr = torch.from_numpy(thresholds()).to(dev)
+        self.auc_hist = torch.zeros(2, NUM_THRESHOLDS + 1, **f32)
+
+        self._build_plans()
+        self._graphs: Dict[int, torch.cuda.CUDAGraph] = {}
+        self._side = torch.cuda.Stream(device=dev)
+        self.kernels_per_step = 0
+        self.host_step = 0
+
+    # ------------------------------------------------------------------------------------------------ plans
+    def _w(self, name):  # fp32 view
+        return self.layout.view(self.P, name)
+
+    def _g(self, name):
+        return self.layout.view(self.G, name)
+
+    def _wb(self, name):  # bf16 shadow view
+        return self.layout.shadow_view(self.shadow, name)
+
+    def _build_plans(self):
+        cfg, B = self.cfg, self.B
+        nl = len(cfg.deep_layers)
+        self.fwd_train, self.fwd_eval, self.wgrad, self.dgrad = [], [], [], []
+        x_in = self.x0
+        for i, h in enumerate(cfg.deep_layers):
+            d_in = x_in.shape[1]
+            Wb = self._wb("mlp%d.weight" % i)
+            bias = self._w("mlp%d.bias" % i)
+            self.fwd_train.append(K.GemmPlan("fwd", x_in, Wb, self.acts[i], B, h, d_in, bias=bias, relu=True,
+                                             keep_prob=cfg.dropout[i], seed=self.seed, layer=i,
+                                             row_offset=self.row_offset, step_ptr=self.step_t))
+            self.fwd_eval.append(K.GemmPlan("fwd", x_in, Wb, self.acts[i], B, h, d_in, bias=bias, relu=True))
+            self.wgrad.append(K.GemmPlan("wgrad", self.dz[i], x_in, self._g("mlp%d.weight" % i), h, d_in, B))
+            if i == 0:
+                self.dgrad.append(K.GemmPlan("dgrad", self.dz[0], Wb, self.dx0, B, d_in, h))
+            else:
+                self.dgrad.append(K.GemmPlan("dgrad", self.dz[i], Wb, self.dz[i - 1], B, d_in, h,
+                                             mask=self.acts[i - 1], mask_scale=1.0 / cfg.dropout[i - 1]))
+            x_in = self.acts[i]
+        self.n_layers = nl
+
+    def refresh_shadow(self):
+        a, b = self.layout.shadow_range
+        K.cast_f32_bf16(self.P[a:b], self.shadow)
+
+    # ------------------------------------------------------------------------------------------------ kernels
+    def _forward(self, slot, train: bool, rows: Optional[int] = None):
+        cfg = self.cfg
+        K.emb_fm_fwd(slot["ids"], slot["vals"], self._w("fm_w"), self._w("fm_v"), self.x0, self.Ssum, self.yfm)
+        for p in (self.fwd_train if train else self.fwd_eval):
+            p.run()
+        return 1 + self.n_layers
+
+    def _train_kernels(self, slot) -> int:
+        """Enqueue one full training step on the current stream (+ a forked side branch). Returns #kernels."""
+        cfg, nl = self.cfg, self.n_layers
+        cur = torch.cuda.current_stream()
+        n = 0
+        self.scalars.zero_()  # loss_sum, reg_loss (one memset node)
+        n += self._forward(slot, True)
+        top = nl - 1
+        K.logit_loss(self.acts[top], self._w("deep_out.weight"), self._w("deep_out.bias"), self._w("fm_bias"), self.yfm,
+                     slot["labels"], 1.0 / self.global_batch, 1.0 / cfg.dropout[top], True, self.prob, self.logit,
+                     self.dy, self.dz[top], self.loss_sum, self._g("deep_out.weight"), self._g("deep_out.bias"),
+                     self._g("fm_bias"), self._g("mlp%d.bias" % top))
+        n += 1
+        side = self._side
+        for i in range(top, -1, -1):
+            # fork: wgrad (+ bias colsum) of layer i only needs dz[i]; the dgrad chain continues on `cur`
+            ev = torch.cuda.Event()
+            ev.record(cur)
+            side.wait_event(ev)
+            with torch.cuda.stream(side):
+                self.wgrad[i].run()
+                n += 1
+                if i != top:
+                    K.colsum_bf16(self.dz[i], self._g("mlp%d.bias" % i))
+                    n += 1
+            self.dgrad[i].run()
+            n += 1
+        K.emb_bwd(slot["ids"], slot["vals"], self._w("fm_v"), self.Ssum, self.dy, self.dx0, self._g("fm_w"),
+                  self._g("fm_v"))
+        n += 1
+        ev = torch.cuda.Event()
+        ev.record(side)
+        cur.wait_event(ev)  # join
+        n += self._optimizer_kernels()
+        return n
+
+    def _optimizer_kernels(self) -> int:
+        o, L = self.opt, self.layout
+        lt = L.trainable_numel
+        decay = L.decay_range if self.cfg.l2_reg > 0 else (0, 0)
+        K.flat_opt_step(self.P[:lt], self.G[:lt], self.S0, self.S1, o.name, o.lr, o.beta1, o.beta2, o.eps, o.momentum,
+                        1.0, decay, self.cfg.l2_reg, L.shadow_range, self.shadow, self.step_t, self.reg_loss,
+                        self.done_counter)
+        return 1
+
+    # ------------------------------------------------------------------------------------------------ public API
+    def load_inputs(self, ids: torch.Tensor, vals: torch.Tensor, labels: Optional[torch.Tensor], slot_idx: int = 0,
+                    non_blocking: bool = True):
+        """Copy one batch (host pinned or device; ids int32 or int64) into input slot `slot_idx`."""
+        s = self.in_slots[slot_idx]
+        n = ids.shape[0]
+        if ids.dtype != torch.int32:
+            ids = ids.to(torch.int32)
+        s["ids"][:n].copy_(ids, non_blocking=non_blocking)
+        s["vals"][:n].copy_(vals, non_blocking=non_blocking)
+        if labels is not None:
+            s["labels"][:n].copy_(labels.reshape(-1), non_blocking=non_blocking)
+        if n < self.B:  # pad: id 0 with value 0 contributes nothing
+            s["ids"][n:].zero_()
+            s["vals"][n:].zero_()
+            s["labels"][n:].zero_()
+        return n
+
+    def train_step_slot(self, slot_idx: int = 0) -> torch.Tensor:
+        """Run one optimizer step on the batch already resident in input slot `slot_idx`.
+        Returns the device scalar `loss_sum` holder; call `last_loss()` for the reference-defined loss."""
+        if self.use_graph:
+            g = self._graphs.get(slot_idx)
+            if g is None:
+                # warm-up outside capture (loads modules, sets func attributes) on a state snapshot, then capture
+                snap = self._snapshot()
+                self._train_kernels(self.in_slots[slot_idx])
+                torch.cuda.synchronize()
+                self._restore(snap)
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    self.kernels_per_step = self._train_kernels(self.in_slots[slot_idx])
+                self._graphs[slot_idx] = g
+            g.replay()
+        else:
+            self.kernels_per_step = self._train_kernels(self.in_slots[slot_idx])
+        self.host_step += 1
+        return self.loss_sum
+
+    def _snapshot(self):
+        return [t.clone() if t is not None else None for t in (self.P, self.S0, self.S1, self.step_t, self.shadow)]
+
+    def _restore(self, snap):
+        for dst, src in zip((self.P, self.S0, self.S1, self.step_t, self.shadow), snap):
+            if dst is not None:
+                dst.copy_(src)
+        self.G.zero_()
+        self.done_counter.zero_()
+        torch.cuda.synchronize()
+
+    def train_step(self, ids, vals, labels, slot_idx: int = 0) -> torch.Tensor:
+        self.load_inputs(ids, vals, labels, slot_idx)
+        return self.train_step_slot(slot_idx)
+
+    def last_loss(self) -> torch.Tensor:
+        """mean log-loss over the global batch + L2 terms, as the reference defines `loss` (PS:244-246)."""
+        torch.add(self.loss_sum / self.global_batch, self.reg_loss, out=self.loss_out)
+        return self.loss_out
+
+    @torch.no_grad()
+    def predict(self, ids, vals) -> torch.Tensor:
+        n = self.load_inputs(ids, vals, None, 0)
+        s = self.in_slots[0]
+        self._forward(s, False)
+        top = self.n_layers - 1
+        K.logit_loss(self.acts[top], self._w("deep_out.weight"), self._w("deep_out.bias"), self._w("fm_bias"), self.yfm,
+                     None, 1.0, 1.0, False, self.prob, self.logit)
+        return self.prob[:n]
+
+    @torch.no_grad()
+    def eval_step(self, ids, vals, labels, update_auc: bool = True):
+        """Forward + loss (+ AUC histogram). Returns (sum of per-example log-loss [1], probs [n])."""
+        n = self.load_inputs(ids, vals, labels, 0)
+        s = self.in_slots[0]
+        self._forward(s, False)
+        top = self.n_layers - 1
+        self.loss_sum.zero_()
+        x = self.acts[top][:n]
+        K.logit_loss(x, self._w("deep_out.weight"), self._w("deep_out.bias"), self._w("fm_bias"), self.yfm[:n],
+                     s["labels"][:n], 1.0, 1.0, False, self.prob[:n], self.logit[:n], None, None, self.loss_sum)
+        if update_auc:
+            K.auc_hist(self.prob[:n], s["labels"][:n], self.auc_thr, self.auc_hist)
+        return self.loss_sum.clone(), self.prob[:n]
+
+    def l2_penalty(self) -> torch.Tensor:
+        return 0.5 * self.cfg.l2_reg * (self._w("fm_w").pow(2).sum() + self._w("fm_v").pow(2).sum())
+
+    # ------------------------------------------------------------------------------------------------ state
+    @property
+    def global_step(self) -> int:
+        return int(self.step_t.item())
+
+    def named_parameters(self) -> "OrderedDict[str, torch.Tensor]":
+        return OrderedDict((n, self.layout.view(self.P, n)) for n in self.layout.names())
+
+    def named_slots(self) -> "OrderedDict[str, List[torch.Tensor]]":
+        out = OrderedDict()
+        for n in self.layout.names(trainable_only=True):
+            sl = []
+            if self.S0 is not None:
+                sl.append(self.layout.view(self.S0, n))
+            if self.S1 is not None:
+                sl.append(self.layout.view(self.S1, n))
+            out[n] = sl
+        return out
+
+    def state_dict(self) -> Dict[str, torch.Tensor]:
+        sd = OrderedDict()
+        for n, t in self.named_parameters().items():
+            sd[n] = t.detach().clone()
+        for n, sl in self.named_slots().items():
+            for suffix, t in zip(SLOT_SUFFIXES[self.opt.name], sl):
+                sd["%s/%s" % (n, suffix)] = t.detach().clone()
+        sd["global_step"] = self.step_t.detach().clone()
+        return sd
+
+    def load_state_dict(self, sd: Dict[str, torch.Tensor], strict: bool = True):
+        for n, t in self.named_parameters().items():
+            if n in sd:
+                t.copy_(sd[n].to(self.dev))
+            elif strict:
+                raise KeyError("missing parameter %s" % n)
+        for n, sl in self.named_slots().items():
+            for suffix, t in zip(SLOT_SUFFIXES[self.opt.name], sl):
+                key = "%s/%s" % (n, suffix)
+                if key in sd:
+                    t.copy_(sd[key].to(self.dev))
+        if "global_step" in sd:
+            self.step_t.copy_(sd["global_step"].to(self.dev).reshape(1))
+            self.opt.step = int(self.step_t.item())
+        self.refresh_shadow()
+        self.G.zero_()

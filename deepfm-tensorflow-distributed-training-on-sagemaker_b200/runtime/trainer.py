@@ -1,0 +1,183 @@
+"""Trainer — the public training/eval/predict API (the role `tf.estimator.Estimator` plays in the reference:
+`.train / .evaluate / .predict`, PS:435-449 / HVD:365-413), bound to one GPU (one process per GPU).
+
+    tr = Trainer(cfg, batch_size, TF1Optimizer("Adam", 5e-4), world_size=W, rank=r)
+    tr.train_batch(ids, vals, labels)        # host tensors (pinned): async H2D on a copy stream, double-buffered
+    tr.train_batch_device(ids, vals, labels) # tensors already on the GPU
+    tr.drain() -> [loss, ...]                # losses of the steps since the last drain (async D2H ring)
+    tr.evaluate(batches) -> {"auc", "loss", "global_step"};  tr.predict(batches) -> probs
+
+Backends: 'fused' = sm_100a kernels + CUDA graph (+ fused all-reduce/optimizer kernel when world_size > 1);
+'torch' = plain PyTorch fp32 (CPU-capable; gloo); 'proxy' = NCCL + cuBLAS + torch.optim stand-in for the
+reference's Horovod build (baseline only).
+"""
+from __future__ import annotations
+
+from typing import Dict, Iterable, List, Optional
+
+import torch
+
+from ..models import DeepFMConfig, TorchDeepFM
+from ..optim.tf1 import TF1Optimizer
+from ..utils.auc import StreamingAUC, auc_from_hist
+
+
+class Trainer:
+    def __init__(self, cfg: DeepFMConfig, batch_size: int, optimizer: Optional[TF1Optimizer] = None, seed: int = 0,
+                 device=None, backend: str = "auto", world_size: int = 1, rank: int = 0, use_graph: bool = True,
+                 comm: str = "auto", params: Optional[Dict[str, torch.Tensor]] = None, process_group=None):
+        self.cfg, self.B = cfg, batch_size
+        self.world, self.rank = world_size, rank
+        self.opt = optimizer or TF1Optimizer("Adam", 5e-4)
+        if backend == "auto":
+            backend = "fused" if (torch.cuda.is_available() and not cfg.batch_norm) else "torch"
+        self.backend = backend
+        self.comm_name = "none"
+        gb = batch_size * world_size
+        ro = rank * batch_size
+        if backend == "fused":
+            self.dev = device or torch.device("cuda", torch.cuda.current_device())
+            if world_size > 1:
+                from ..parallel.dp import FusedDataParallel
+                self.model = FusedDataParallel(cfg, batch_size, self.opt, seed, self.dev, world_size, rank, comm=comm,
+                                               use_graph=use_graph, params=params, process_group=process_group)
+                self.comm_name = self.model.comm_name
+            else:
+                from ..models.fused import FusedDeepFM
+                self.model = FusedDeepFM(cfg, batch_size, self.opt, seed, self.dev, params=params, use_graph=use_graph)
+        elif backend == "proxy":
+            from ..parallel.proxy_baseline import ProxyDeepFM
+            self.dev = device or torch.device("cuda", torch.cuda.current_device())
+            self.model = ProxyDeepFM(cfg, batch_size, self.opt, seed, self.dev, world_size, rank)
+            self.comm_name = "nccl-allreduce" if world_size > 1 else "none"
+        else:
+            self.dev = torch.device(device if device is not None else "cpu")
+            self.model = TorchDeepFM(cfg, batch_size, self.opt, seed, self.dev, params=params,
+                                     global_batch=gb if world_size > 1 else None, row_offset=ro)
+            if world_size > 1:
+                from ..parallel.dp import install_torch_allreduce
+                install_torch_allreduce(self.model, process_group)
+                self.comm_name = "torch.distributed.all_reduce"
+        self._cuda = self.dev.type == "cuda"
+        self._nslots = len(getattr(self.model, "in_slots", [])) or 1
+        self._k = 0
+        self._pending: List[int] = []
+        if self._cuda:
+            self._copy_stream = torch.cuda.Stream(device=self.dev)
+            self._slot_free = [None] * self._nslots
+            self._ring_n = 4096
+            self._ring = torch.zeros(self._ring_n, 2, dtype=torch.float32).pin_memory()
+            self._ring_pos = 0
+        self._host_losses: List[float] = []
+
+    # ------------------------------------------------------------------------------------------- training
+    @property
+    def kernels_per_step(self) -> int:
+        return getattr(self.model, "kernels_per_step", 0)
+
+    @property
+    def global_step(self) -> int:
+        return self.model.global_step
+
+    def last_loss(self) -> torch.Tensor:
+        return self.model.last_loss()
+
+    def train_batch_device(self, ids, vals, labels):
+        """One optimizer step on a batch that already lives on this trainer's device."""
+        if self.backend == "fused":
+            slot = self._k % self._nslots
+            self._k += 1
+            self.model.load_inputs(ids, vals, labels, slot)
+            return self.model.train_step_slot(slot)
+        return self.model.train_step(ids, vals, labels)
+
+    def train_batch(self, ids, vals, labels):
+        """One optimizer step on a HOST batch. On CUDA: pinned-memory async H2D on a side stream into the next input
+        slot (overlapping the previous step), graph replay, async D2H of the step's loss scalars."""
+        if self.backend != "fused":
+            loss = self.model.train_step(ids.to(self.dev, non_blocking=True), vals.to(self.dev, non_blocking=True),
+                                         labels.to(self.dev, non_blocking=True))
+            if self._cuda:
+                self._push_loss(torch.stack([loss.reshape(()), torch.zeros((), device=self.dev)]), already_mean=True)
+            else:
+                self._host_losses.append(float(loss))
+            return
+        main = torch.cuda.current_stream(self.dev)
+        slot = self._k % self._nslots
+        self._k += 1
+        cs = self._copy_stream
+        if self._slot_free[slot] is not None:
+            cs.wait_event(self._slot_free[slot])  # the step that last read this slot has finished
+        with torch.cuda.stream(cs):
+            self.model.load_inputs(ids, vals, labels, slot, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(cs)
+        main.wait_event(ev)
+        self.model.train_step_slot(slot)
+        done = torch.cuda.Event()
+        done.record(main)
+        self._slot_free[slot] = done
+        self._push_loss(self.model.scalars, already_mean=False)
+
+    def _push_loss(self, scalars: torch.Tensor, already_mean: bool):
+        if self._ring_pos == self._ring_n:
+            self.drain(keep=True)
+        self._ring[self._ring_pos].copy_(scalars, non_blocking=True)
+        self._pending.append(1 if already_mean else 0)
+        self._ring_pos += 1
+
+    def drain(self, keep: bool = False) -> List[float]:
+        """Wait for outstanding steps; return the per-step losses (mean log-loss + L2 terms, PS:244-246)."""
+        if self._cuda:
+            torch.cuda.synchronize(self.dev)
+            gb = float(self.B * self.world)
+            for i, mean_flag in enumerate(self._pending):
+                a, b = float(self._ring[i, 0]), float(self._ring[i, 1])
+                self._host_losses.append(a if mean_flag else a / gb + b)
+            self._pending = []
+            self._ring_pos = 0
+        if keep:
+            return []
+        out, self._host_losses = self._host_losses, []
+        return out
+
+    # ------------------------------------------------------------------------------------------- eval / predict
+    def evaluate(self, batches: Iterable) -> Dict[str, float]:
+        """`Estimator.evaluate` (PS:443-444): mean loss (incl. the L2 terms, as the reference's EVAL loss does) and
+        streaming AUC with tf.metrics.auc defaults."""
+        auc = StreamingAUC()
+        fused = self.backend == "fused"
+        if fused:
+            self.model.auc_hist.zero_()
+        tot = torch.zeros(1, device=self.dev, dtype=torch.float64)
+        n = 0
+        for ids, vals, labels in batches:
+            ids, vals, labels = ids.to(self.dev), vals.to(self.dev), labels.to(self.dev)
+            loss_sum, probs = self.model.eval_step(ids, vals, labels)
+            tot += loss_sum.double()
+            n += ids.shape[0]
+            if not fused:
+                auc.update(labels, probs)
+        hist = self.model.auc_hist.double().cpu() if fused else auc.hist
+        stats = torch.cat([tot.cpu(), torch.tensor([float(n)], dtype=torch.float64), hist.reshape(-1)])
+        if self.world > 1 and torch.distributed.is_initialized():
+            s = stats.to(self.dev) if torch.distributed.get_backend() == "nccl" else stats
+            torch.distributed.all_reduce(s)
+            stats = s.cpu()
+        tot_f, n_f = float(stats[0]), float(stats[1])
+        hist = stats[2:].reshape(2, -1)
+        return {"loss": tot_f / max(n_f, 1.0) + float(self.model.l2_penalty()), "auc": auc_from_hist(hist),
+                "global_step": self.global_step, "examples": int(n_f)}
+
+    def predict(self, batches: Iterable):
+        """`Estimator.predict(predict_keys="prob")` (PS:445-446): yields a 1-D tensor of probabilities per batch."""
+        for b in batches:
+            ids, vals = b[0].to(self.dev), b[1].to(self.dev)
+            yield self.model.predict(ids, vals).detach().float().cpu()
+
+    # ------------------------------------------------------------------------------------------- state
+    def state_dict(self):
+        return self.model.state_dict()
+
+    def load_state_dict(self, sd, strict: bool = True):
+        self.model.load_state_dict(sd, strict)
