@@ -11,7 +11,7 @@
 //     accumulated with red.global.add.v4.f32 into the dense fp32 gradient buffer (the reference's embedding
 //     gradient is dense as well because of the whole-table L2 term).
 //
-// G threads cooperate on one sample, each owning 4 consecutive embedding columns (K = 4*G, G | 32).
+// Lanes own 4 consecutive embedding columns each (K = 4*G, G | 32).
 #include "common.cuh"
 
 namespace dfm {
@@ -26,29 +26,30 @@ __device__ __forceinline__ float group_sum(float v) {
   return v;
 }
 
+// One warp per sample: lane = fg * G + g, g = 4-column chunk of the embedding row, fg = field group.
+// Field group fg walks fields fg, fg+FG, ... so FG = 32/G row gathers of one sample are in flight per step.
 template <int G>
 __global__ void __launch_bounds__(kEmbThreads)
 emb_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, const float* __restrict__ fm_w,
                   const float* __restrict__ fm_v, __nv_bfloat16* __restrict__ x0, int ldx, float* __restrict__ S,
                   float* __restrict__ yfm, int B, int F, int N) {
   constexpr int K = 4 * G;
-  const int gtid = blockIdx.x * kEmbThreads + threadIdx.x;
-  const int sample_raw = gtid / G;
-  const int t = gtid % G;
-  const bool active = sample_raw < B;
-  const int sample = active ? sample_raw : B - 1;  // keep the whole warp alive for the shuffles
+  constexpr int FG = 32 / G;
+  const int lane = threadIdx.x & 31;
+  const int sample = blockIdx.x * (kEmbThreads / 32) + (threadIdx.x >> 5);
+  if (sample >= B) return;  // warp-uniform
+  const int g = lane % G, fg = lane / G;
   const int* sid = ids + (size_t)sample * F;
   const float* sval = vals + (size_t)sample * F;
 
   float4 s = make_float4(0.f, 0.f, 0.f, 0.f), ss = make_float4(0.f, 0.f, 0.f, 0.f);
-  float yw = 0.f;
-  for (int f0 = 0; f0 < F; f0 += kEmbUnroll) {
+  for (int f0 = fg; f0 < F; f0 += FG * kEmbUnroll) {
     int id[kEmbUnroll];
     float val[kEmbUnroll];
     float4 row[kEmbUnroll];
 #pragma unroll
     for (int u = 0; u < kEmbUnroll; ++u) {
-      const int f = f0 + u;
+      const int f = f0 + u * FG;
       id[u] = 0; val[u] = 0.f;
       if (f < F) {
         id[u] = __ldg(sid + f);
@@ -58,91 +59,75 @@ emb_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, c
     }
 #pragma unroll
     for (int u = 0; u < kEmbUnroll; ++u)
-      row[u] = __ldg(reinterpret_cast<const float4*>(fm_v + (size_t)id[u] * K) + t);
+      row[u] = __ldg(reinterpret_cast<const float4*>(fm_v + (size_t)id[u] * K) + g);
 #pragma unroll
     for (int u = 0; u < kEmbUnroll; ++u) {
-      const int f = f0 + u;
+      const int f = f0 + u * FG;
       if (f < F) {
         const float4 e = make_float4(row[u].x * val[u], row[u].y * val[u], row[u].z * val[u], row[u].w * val[u]);
         s.x += e.x; s.y += e.y; s.z += e.z; s.w += e.w;
         ss.x += e.x * e.x; ss.y += e.y * e.y; ss.z += e.z * e.z; ss.w += e.w * e.w;
-        if (active) {
-          uint2 pk;
-          pk.x = pack_bf16x2(e.x, e.y);
-          pk.y = pack_bf16x2(e.z, e.w);
-          *reinterpret_cast<uint2*>(x0 + (size_t)sample * ldx + (size_t)f * K + 4 * t) = pk;
-        }
-        if ((f % G) == t) yw += __ldg(fm_w + id[u]) * val[u];
+        uint2 pk;
+        pk.x = pack_bf16x2(e.x, e.y);
+        pk.y = pack_bf16x2(e.z, e.w);
+        *reinterpret_cast<uint2*>(x0 + (size_t)sample * ldx + (size_t)f * K + 4 * g) = pk;
       }
     }
   }
-  float yv = (s.x * s.x - ss.x) + (s.y * s.y - ss.y) + (s.z * s.z - ss.z) + (s.w * s.w - ss.w);
-  yv = group_sum<G>(yv);
-  yw = group_sum<G>(yw);
-  if (active) {
-    reinterpret_cast<float4*>(S + (size_t)sample * K)[t] = s;
-    if (t == 0) yfm[sample] = yw + 0.5f * yv;
+  // reduce over field groups (lanes with equal g): xor offsets G, 2G, ..., 16
+#pragma unroll
+  for (int o = G; o < 32; o <<= 1) {
+    s.x += __shfl_xor_sync(0xffffffffu, s.x, o); s.y += __shfl_xor_sync(0xffffffffu, s.y, o);
+    s.z += __shfl_xor_sync(0xffffffffu, s.z, o); s.w += __shfl_xor_sync(0xffffffffu, s.w, o);
+    ss.x += __shfl_xor_sync(0xffffffffu, ss.x, o); ss.y += __shfl_xor_sync(0xffffffffu, ss.y, o);
+    ss.z += __shfl_xor_sync(0xffffffffu, ss.z, o); ss.w += __shfl_xor_sync(0xffffffffu, ss.w, o);
   }
+  float acc = 0.f;
+  if (fg == 0) {
+    reinterpret_cast<float4*>(S + (size_t)sample * K)[g] = s;
+    acc = 0.5f * ((s.x * s.x - ss.x) + (s.y * s.y - ss.y) + (s.z * s.z - ss.z) + (s.w * s.w - ss.w));
+  }
+  for (int f = lane; f < F; f += 32) {  // first-order term
+    const int id = __ldg(sid + f);
+    if ((unsigned)id < (unsigned)N) acc += __ldg(fm_w + id) * __ldg(sval + f);
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) yfm[sample] = acc;
 }
 
+// One G-lane group per (sample, field): B*F*G threads, every row gradient is an independent vector atomic.
 template <int G>
 __global__ void __launch_bounds__(kEmbThreads)
 emb_bwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, const float* __restrict__ fm_v,
                const float* __restrict__ S, const float* __restrict__ dy, const __nv_bfloat16* __restrict__ dx0,
                int ldx, float* __restrict__ g_w, float* __restrict__ g_v, int B, int F, int N) {
   constexpr int K = 4 * G;
-  const int gtid = blockIdx.x * kEmbThreads + threadIdx.x;
-  const int sample = gtid / G;
-  const int t = gtid % G;
-  if (sample >= B) return;
-  const int* sid = ids + (size_t)sample * F;
-  const float* sval = vals + (size_t)sample * F;
-  const float4 s = reinterpret_cast<const float4*>(S + (size_t)sample * K)[t];
-  const float d = dy[sample];
-
-  for (int f0 = 0; f0 < F; f0 += kEmbUnroll) {
-    int id[kEmbUnroll];
-    float val[kEmbUnroll];
-    float4 row[kEmbUnroll];
-    uint2 dxp[kEmbUnroll];
-#pragma unroll
-    for (int u = 0; u < kEmbUnroll; ++u) {
-      const int f = f0 + u;
-      id[u] = 0; val[u] = 0.f;
-      if (f < F) {
-        id[u] = __ldg(sid + f);
-        val[u] = __ldg(sval + f);
-        if ((unsigned)id[u] >= (unsigned)N) { id[u] = 0; val[u] = 0.f; }
-      }
-    }
-#pragma unroll
-    for (int u = 0; u < kEmbUnroll; ++u) {
-      row[u] = __ldg(reinterpret_cast<const float4*>(fm_v + (size_t)id[u] * K) + t);
-      const int f = min(f0 + u, F - 1);
-      dxp[u] = __ldg(reinterpret_cast<const uint2*>(dx0 + (size_t)sample * ldx + (size_t)f * K + 4 * t));
-    }
-#pragma unroll
-    for (int u = 0; u < kEmbUnroll; ++u) {
-      const int f = f0 + u;
-      if (f < F && val[u] != 0.f) {  // a zero value (padding) has an exactly-zero gradient
-        const float v = val[u];
-        const float gx = v * (bf16_lo(dxp[u].x) + d * (s.x - row[u].x * v));
-        const float gy = v * (bf16_hi(dxp[u].x) + d * (s.y - row[u].y * v));
-        const float gz = v * (bf16_lo(dxp[u].y) + d * (s.z - row[u].z * v));
-        const float gw = v * (bf16_hi(dxp[u].y) + d * (s.w - row[u].w * v));
-        red_add_f32x4(g_v + (size_t)id[u] * K + 4 * t, gx, gy, gz, gw);
-        if ((f % G) == t) atomicAdd(g_w + id[u], d * v);
-      }
-    }
-  }
+  const long long gtid = (long long)blockIdx.x * kEmbThreads + threadIdx.x;
+  const long long pair = gtid / G;
+  const int g = (int)(gtid % G);
+  if (pair >= (long long)B * F) return;
+  const int sample = (int)(pair / F);
+  const int f = (int)(pair % F);
+  const int id = __ldg(ids + pair);
+  const float v = __ldg(vals + pair);
+  if (v == 0.f || (unsigned)id >= (unsigned)N) return;  // padding / out-of-range: exactly-zero gradient
+  const float4 row = __ldg(reinterpret_cast<const float4*>(fm_v + (size_t)id * K) + g);
+  const float4 s = __ldg(reinterpret_cast<const float4*>(S + (size_t)sample * K) + g);
+  const uint2 dxp = __ldg(reinterpret_cast<const uint2*>(dx0 + (size_t)sample * ldx + (size_t)f * K + 4 * g));
+  const float d = __ldg(dy + sample);
+  const float gx = v * (bf16_lo(dxp.x) + d * (s.x - row.x * v));
+  const float gy = v * (bf16_hi(dxp.x) + d * (s.y - row.y * v));
+  const float gz = v * (bf16_lo(dxp.y) + d * (s.z - row.z * v));
+  const float gw = v * (bf16_hi(dxp.y) + d * (s.w - row.w * v));
+  red_add_f32x4(g_v + (size_t)id * K + 4 * g, gx, gy, gz, gw);
+  if (g == 0) atomicAdd(g_w + id, d * v);
 }
 
 template <int G>
 static int launch_fwd(const int* ids, const float* vals, const float* fm_w, const float* fm_v, __nv_bfloat16* x0,
                       int ldx, float* S, float* yfm, int B, int F, int N, cudaStream_t st) {
-  const long threads = (long)B * G;
-  emb_fm_fwd_kernel<G><<<(unsigned)ceil_div_ll(threads, kEmbThreads), kEmbThreads, 0, st>>>(ids, vals, fm_w, fm_v, x0,
-                                                                                         ldx, S, yfm, B, F, N);
+  emb_fm_fwd_kernel<G><<<(unsigned)ceil_div(B, kEmbThreads / 32), kEmbThreads, 0, st>>>(ids, vals, fm_w, fm_v, x0, ldx,
+                                                                                        S, yfm, B, F, N);
   DFM_CHECK(cudaGetLastError());
   return DFM_OK;
 }
@@ -150,7 +135,7 @@ static int launch_fwd(const int* ids, const float* vals, const float* fm_w, cons
 template <int G>
 static int launch_bwd(const int* ids, const float* vals, const float* fm_v, const float* S, const float* dy,
                       const __nv_bfloat16* dx0, int ldx, float* g_w, float* g_v, int B, int F, int N, cudaStream_t st) {
-  const long threads = (long)B * G;
+  const long long threads = (long long)B * F * G;
   emb_bwd_kernel<G><<<(unsigned)ceil_div_ll(threads, kEmbThreads), kEmbThreads, 0, st>>>(ids, vals, fm_v, S, dy, dx0,
                                                                                       ldx, g_w, g_v, B, F, N);
   DFM_CHECK(cudaGetLastError());

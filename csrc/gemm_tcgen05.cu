@@ -14,7 +14,7 @@
 //               K = 1248 (19.5 k-blocks) and N = 400 without padding anything in global memory
 //   warp 1      MMA issuer: one elected thread issues tcgen05.mma.cta_group::1.kind::f16 (UMMA 128 x BN x 16),
 //               frees smem stages with tcgen05.commit -> mbarrier
-//   warps 2-5   epilogue: tcgen05.ld 32x32b from TMEM, then fused
+//   warps 2-9   epilogue: tcgen05.ld 32x32b from TMEM, then fused
 //                 EPI_BIAS_ACT : + bias, ReLU, inverted dropout (Philox, keep-prob, PS:218), bf16 store
 //                 EPI_MASK     : * (relu'/dropout mask of the previous layer, recovered as X_prev != 0) * 1/keep
 //                 EPI_ACCUM_F32: red.global.add.v4.f32 into the flat fp32 gradient buffer (split-K safe)
@@ -27,7 +27,8 @@ namespace dfm {
 
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int kGemmThreads = 192;
+constexpr int kEpiWarps = 8;  // 2 warps per TMEM lane quarter
+constexpr int kGemmThreads = 64 + 32 * kEpiWarps;
 
 enum { EPI_BIAS_ACT = 0, EPI_MASK = 1, EPI_ACCUM_F32 = 2 };
 
@@ -152,22 +153,27 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       umma_commit(tmem_full_bar);  // accumulator complete
     }
   } else {
-    // ------------------------------------------------------------------ epilogue warps (TMEM lane quarter = warp % 4)
+    // ------------------------------------------------------------------ epilogue warps
+    // TMEM lane quarter = warp % 4 (hardware rule); kEpiWarps/4 warps share a quarter and interleave 16-column
+    // chunks, so several independent dependency chains per scheduler hide the ALU/LDG latency of the epilogue.
     const int q = warp & 3;
+    const int sub = (warp - 2) >> 2;
     const int row = m0 + q * 32 + lane;
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
     const bool row_ok = row < p.M;
-    unsigned long long step = 0;
-    if constexpr (EPI == EPI_BIAS_ACT) {
-      if (p.drop.enabled && p.step_ptr) step = *p.step_ptr;
-    }
     DropoutCfg drop = p.drop;
-    drop.step_lo = (uint32_t)step;
-    drop.step_hi = (uint32_t)(step >> 32);
+    if constexpr (EPI == EPI_BIAS_ACT) {
+      if (drop.enabled && p.step_ptr) {
+        const unsigned long long step = *p.step_ptr;
+        drop.step_lo = (uint32_t)step;
+        drop.step_hi = (uint32_t)(step >> 32);
+      }
+    }
+    const bool n_mult4 = (p.N & 3) == 0;
 
 #pragma unroll 1
-    for (int c = 0; c < BN; c += 16) {
+    for (int c = sub * 16; c < BN; c += 16 * (kEpiWarps / 4)) {
       float v[16];
       tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
       const int n = n0 + c;
@@ -175,25 +181,54 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const bool full16 = (n + 16 <= p.N);
 
       if constexpr (EPI == EPI_BIAS_ACT) {
-        uint64_t last_quad = ~0ull;
-        uint4 rnd = make_uint4(0, 0, 0, 0);
+        if (full16 && n_mult4) {
+          // fast path: vector bias loads, branch-free activation, 4 independent Philox streams
+          if (p.bias) {
+            const float4* bp = reinterpret_cast<const float4*>(p.bias + n);
+            const float4 b0 = __ldg(bp), b1 = __ldg(bp + 1), b2 = __ldg(bp + 2), b3 = __ldg(bp + 3);
+            v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
+            v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+            v[8] += b2.x; v[9] += b2.y; v[10] += b2.z; v[11] += b2.w;
+            v[12] += b3.x; v[13] += b3.y; v[14] += b3.z; v[15] += b3.w;
+          }
+          if (p.relu) {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int nn = n + j;
-          float x = v[j];
-          if (nn < p.N) {
-            if (p.bias) x += __ldg(p.bias + nn);
-            if (p.relu) x = fmaxf(x, 0.f);
-            if (drop.enabled) {
-              const uint64_t elem = (uint64_t)(row + drop.row_offset) * (uint64_t)p.N + (uint64_t)nn;
-              const uint64_t quad = elem >> 2;
-              if (quad != last_quad) { rnd = dropout_words(drop, quad); last_quad = quad; }
-              const uint32_t sel = (uint32_t)(elem & 3);
-              const uint32_t u = sel == 0 ? rnd.x : sel == 1 ? rnd.y : sel == 2 ? rnd.z : rnd.w;
-              x = (u < drop.threshold) ? x * drop.scale : 0.f;
+            for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
+          }
+          if (drop.enabled) {
+            const uint64_t quad0 = ((uint64_t)(row + drop.row_offset) * (uint64_t)p.N + (uint64_t)n) >> 2;
+            uint4 r[4];
+#pragma unroll
+            for (int t = 0; t < 4; ++t) r[t] = dropout_words(drop, quad0 + t);
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+              v[4 * t + 0] = (r[t].x < drop.threshold) ? v[4 * t + 0] * drop.scale : 0.f;
+              v[4 * t + 1] = (r[t].y < drop.threshold) ? v[4 * t + 1] * drop.scale : 0.f;
+              v[4 * t + 2] = (r[t].z < drop.threshold) ? v[4 * t + 2] * drop.scale : 0.f;
+              v[4 * t + 3] = (r[t].w < drop.threshold) ? v[4 * t + 3] * drop.scale : 0.f;
             }
           }
-          v[j] = x;
+        } else {
+          uint64_t last_quad = ~0ull;
+          uint4 rnd = make_uint4(0, 0, 0, 0);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int nn = n + j;
+            float x = v[j];
+            if (nn < p.N) {
+              if (p.bias) x += __ldg(p.bias + nn);
+              if (p.relu) x = fmaxf(x, 0.f);
+              if (drop.enabled) {
+                const uint64_t elem = (uint64_t)(row + drop.row_offset) * (uint64_t)p.N + (uint64_t)nn;
+                const uint64_t quad = elem >> 2;
+                if (quad != last_quad) { rnd = dropout_words(drop, quad); last_quad = quad; }
+                const uint32_t sel = (uint32_t)(elem & 3);
+                const uint32_t u = sel == 0 ? rnd.x : sel == 1 ? rnd.y : sel == 2 ? rnd.z : rnd.w;
+                x = (u < drop.threshold) ? x * drop.scale : 0.f;
+              }
+            }
+            v[j] = x;
+          }
         }
       } else if constexpr (EPI == EPI_MASK) {
         if (p.mask) {
@@ -305,10 +340,12 @@ template <int BN, bool A_MN, bool B_MN, int EPI>
 static int launch_gemm(const GemmPlan& pl, cudaStream_t stream) {
   using Cfg = GemmCfg<BN>;
   auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, EPI>;
-  static bool attr_set = false;
-  if (!attr_set) {
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  DFM_CHECK(cudaGetDevice(&dev));
+  if (dev < 64 && !attr_set[dev]) {
     DFM_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-    attr_set = true;
+    attr_set[dev] = true;
   }
   kern<<<pl.grid, kGemmThreads, Cfg::SMEM_BYTES, stream>>>(pl.tmA, pl.tmB, pl.p);
   DFM_CHECK(cudaGetLastError());

@@ -7,9 +7,8 @@
 //   dy[b] = (prob - label) * inv_batch
 //   dZ[b,j] = dy[b] * w_out[j] * (x[b,j] != 0) * mask_scale   <- gradient w.r.t. the last hidden pre-activation
 //                                                              (x = dropout(relu(z)): its zero pattern IS the mask)
-//   g_w_out[j] += dy[b]*x[b,j]    g_b_out += dy[b]    g_fm_bias += dy[b]    g_b_last[j] += dZ[b,j]
-//
-// One warp per sample, block-level shared-memory accumulators flushed with one atomic per column per block.
+//   g_b_out += dy[b]    g_fm_bias += dy[b]
+//   (g_w_out[j] = sum_b dy[b]*x[b,j] and g_b_last[j] = sum_b dZ[b,j] are weighted column sums: colsum_bf16)
 #include "common.cuh"
 
 namespace dfm {
@@ -17,21 +16,18 @@ namespace dfm {
 constexpr int kLossThreads = 256;
 constexpr int kLossWarps = kLossThreads / 32;
 
+// One warp per sample, pure streaming: no column accumulators here (those are the two weighted column sums
+// g_w_out = colsum(x, w=dy) and g_b_last = colsum(dz), run by colsum_bf16 on the wgrad branch of the step graph).
 __global__ void __launch_bounds__(kLossThreads)
 logit_loss_kernel(const __nv_bfloat16* __restrict__ x, int ldx, int H, const float* __restrict__ w_out,
                   const float* __restrict__ b_out, const float* __restrict__ fm_bias, const float* __restrict__ yfm,
                   const float* __restrict__ labels, int B, float inv_batch, float mask_scale, int train,
                   float* __restrict__ prob, float* __restrict__ logit, float* __restrict__ dy,
-                  __nv_bfloat16* __restrict__ dz, int lddz, float* __restrict__ loss_sum, float* __restrict__ g_w_out,
-                  float* __restrict__ g_b_out, float* __restrict__ g_fm_bias, float* __restrict__ g_b_last) {
-  extern __shared__ float sacc[];  // [2*H]: g_w_out partials, g_b_last partials
-  float* s_gw = sacc;
-  float* s_gb = sacc + H;
+                  __nv_bfloat16* __restrict__ dz, int lddz, float* __restrict__ loss_sum,
+                  float* __restrict__ g_b_out, float* __restrict__ g_fm_bias) {
   __shared__ float s_scalar[2];  // loss, sum dy
-  for (int j = threadIdx.x; j < 2 * H; j += kLossThreads) sacc[j] = 0.f;
   if (threadIdx.x < 2) s_scalar[threadIdx.x] = 0.f;
   __syncthreads();
-
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const float bias = __ldg(b_out) + __ldg(fm_bias);
   float loss_acc = 0.f, dy_acc = 0.f;
@@ -64,29 +60,21 @@ logit_loss_kernel(const __nv_bfloat16* __restrict__ x, int ldx, int H, const flo
     for (int j = lane * 2; j < H; j += 64) {
       if (j + 1 < H) {
         const uint32_t u = *reinterpret_cast<const uint32_t*>(xr + j);
-        const float x0 = bf16_lo(u), x1 = bf16_hi(u);
-        const float z0 = x0 != 0.f ? d * __ldg(w_out + j) * mask_scale : 0.f;
-        const float z1 = x1 != 0.f ? d * __ldg(w_out + j + 1) * mask_scale : 0.f;
+        const float z0 = (u & 0x7FFFu) ? d * __ldg(w_out + j) * mask_scale : 0.f;
+        const float z1 = (u & 0x7FFF0000u) ? d * __ldg(w_out + j + 1) * mask_scale : 0.f;
         *reinterpret_cast<uint32_t*>(dzr + j) = pack_bf16x2(z0, z1);
-        atomicAdd(&s_gw[j], d * x0);
-        atomicAdd(&s_gw[j + 1], d * x1);
-        atomicAdd(&s_gb[j], z0);
-        atomicAdd(&s_gb[j + 1], z1);
       } else {
         const float x0 = __bfloat162float(xr[j]);
-        const float z0 = x0 != 0.f ? d * __ldg(w_out + j) * mask_scale : 0.f;
-        dzr[j] = __float2bfloat16(z0);
-        atomicAdd(&s_gw[j], d * x0);
-        atomicAdd(&s_gb[j], z0);
+        dzr[j] = __float2bfloat16(x0 != 0.f ? d * __ldg(w_out + j) * mask_scale : 0.f);
       }
     }
   }
-  if (lane == 0 && labels != nullptr) {
+  if (labels == nullptr) return;
+  if (lane == 0) {
     atomicAdd(&s_scalar[0], loss_acc);
     atomicAdd(&s_scalar[1], dy_acc);
   }
   __syncthreads();
-  if (labels == nullptr) return;
   if (threadIdx.x == 0) {
     atomicAdd(loss_sum, s_scalar[0]);
     if (train) {
@@ -94,24 +82,47 @@ logit_loss_kernel(const __nv_bfloat16* __restrict__ x, int ldx, int H, const flo
       atomicAdd(g_fm_bias, s_scalar[1]);
     }
   }
-  if (train) {
-    for (int j = threadIdx.x; j < H; j += kLossThreads) {
-      atomicAdd(g_w_out + j, s_gw[j]);
-      if (g_b_last) atomicAdd(g_b_last + j, s_gb[j]);
-    }
-  }
 }
 
-// Column sums of a bf16 [B,H] matrix into fp32 (bias gradients of the lower MLP layers): out[j] += sum_b a[b,j].
+// Weighted column sums of a bf16 [B,H] matrix: out[j] += sum_b a[b,j] * (w ? w[b] : 1).
+// Used for every bias gradient (w = null) and for g_w_out = X_top^T dy (w = dy).
+// Block = 32 lanes x 8 row-lanes over a 64-column x kColsumRows tile; grid = (ceil(H/64), ceil(B/kColsumRows)).
+constexpr int kColsumRows = 64;
 __global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* __restrict__ a, int lda, int B, int H,
-                                                          float* __restrict__ out, int rows_per_block) {
-  const int j = blockIdx.x * 256 + threadIdx.x;
-  if (j >= H) return;
-  const int r0 = blockIdx.y * rows_per_block;
-  const int r1 = min(B, r0 + rows_per_block);
-  float acc = 0.f;
-  for (int r = r0; r < r1; ++r) acc += __bfloat162float(a[(size_t)r * lda + j]);
-  atomicAdd(out + j, acc);
+                                                          const float* __restrict__ w, float* __restrict__ out) {
+  __shared__ float s_part[8][64];
+  const int lane = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int j = blockIdx.x * 64 + lane * 2;
+  const int r0 = blockIdx.y * kColsumRows;
+  float a0 = 0.f, a1 = 0.f;
+  if (j < H) {
+    const bool pair = (j + 1 < H) && ((lda & 1) == 0);
+#pragma unroll
+    for (int i = 0; i < kColsumRows / 8; ++i) {
+      const int r = r0 + ty + i * 8;
+      if (r < B) {
+        const float wr = w ? __ldg(w + r) : 1.f;
+        if (pair) {
+          const uint32_t u = __ldg(reinterpret_cast<const uint32_t*>(a + (size_t)r * lda + j));
+          a0 += bf16_lo(u) * wr;
+          a1 += bf16_hi(u) * wr;
+        } else {
+          a0 += __bfloat162float(a[(size_t)r * lda + j]) * wr;
+          if (j + 1 < H) a1 += __bfloat162float(a[(size_t)r * lda + j + 1]) * wr;
+        }
+      }
+    }
+  }
+  s_part[ty][lane * 2] = a0;
+  s_part[ty][lane * 2 + 1] = a1;
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += s_part[k][threadIdx.x];
+    const int jj = blockIdx.x * 64 + threadIdx.x;
+    if (jj < H) atomicAdd(out + jj, t);
+  }
 }
 
 // 200-threshold confusion histogram for streaming AUC (`tf.metrics.auc`, PS:249-251): hist[c][k] counts class-c
@@ -146,28 +157,24 @@ extern "C" {
 // labels == NULL -> predict mode (only prob/logit written). train == 0 -> eval (loss only, no gradients).
 int dfm_logit_loss(const void* x, int ldx, int H, const float* w_out, const float* b_out, const float* fm_bias,
                    const float* yfm, const float* labels, int B, float inv_batch, float mask_scale, int train,
-                   float* prob, float* logit, float* dy, void* dz, int lddz, float* loss_sum, float* g_w_out,
-                   float* g_b_out, float* g_fm_bias, float* g_b_last, void* stream) {
+                   float* prob, float* logit, float* dy, void* dz, int lddz, float* loss_sum, float* g_b_out,
+                   float* g_fm_bias, void* stream) {
   DFM_REQUIRE(B > 0 && H > 0, "logit_loss: empty problem");
   DFM_REQUIRE(ldx % 2 == 0 && (!train || lddz % 2 == 0), "logit_loss: leading dimensions must be even");
-  DFM_REQUIRE(H <= 6000, "logit_loss: last hidden width > 6000 unsupported");
-  int blocks = ceil_div(B, kLossWarps * 4);
-  if (blocks > 296) blocks = 296;
-  if (blocks < 1) blocks = 1;
-  logit_loss_kernel<<<blocks, kLossThreads, 2 * H * sizeof(float), (cudaStream_t)stream>>>(
+  int blocks = ceil_div(B, kLossWarps);
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  logit_loss_kernel<<<blocks, kLossThreads, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)x, ldx, H, w_out, b_out, fm_bias, yfm, labels, B, inv_batch, mask_scale, train, prob, logit,
-      dy, (__nv_bfloat16*)dz, lddz, loss_sum, g_w_out, g_b_out, g_fm_bias, g_b_last);
+      dy, (__nv_bfloat16*)dz, lddz, loss_sum, g_b_out, g_fm_bias);
   DFM_CHECK(cudaGetLastError());
   return DFM_OK;
 }
 
-int dfm_colsum_bf16(const void* a, int lda, int B, int H, float* out, void* stream) {
+// out[j] += sum_b a[b,j] * (w ? w[b] : 1)
+int dfm_colsum_bf16(const void* a, int lda, int B, int H, const float* w, float* out, void* stream) {
   DFM_REQUIRE(B > 0 && H > 0, "colsum: empty problem");
-  int ysplit = ceil_div(B, 64);
-  if (ysplit > 64) ysplit = 64;
-  const int rows_per_block = ceil_div(B, ysplit);
-  dim3 grid(ceil_div(H, 256), ceil_div(B, rows_per_block));
-  colsum_bf16_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)a, lda, B, H, out, rows_per_block);
+  dim3 grid(ceil_div(H, 64), ceil_div(B, kColsumRows));
+  colsum_bf16_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)a, lda, B, H, w, out);
   DFM_CHECK(cudaGetLastError());
   return DFM_OK;
 }

@@ -28,6 +28,33 @@ from .layout import FlatLayout
 from .params import init_params
 
 
+def packed_slot_bytes(B: int, F: int) -> int:
+    al = lambda x: (x + 255) & ~255
+    return al(B * 4) + 2 * al(B * F * 4)
+
+
+def make_packed_slot(B: int, F: int, device, pin: bool = False) -> Dict[str, torch.Tensor]:
+    """One batch in the loader's slot layout; returns the raw buffer plus typed views."""
+    al = lambda x: (x + 255) & ~255
+    buf = torch.zeros(packed_slot_bytes(B, F), dtype=torch.uint8, device=device)
+    if pin:
+        buf = buf.pin_memory()
+    o_ids = al(B * 4)
+    o_vals = o_ids + al(B * F * 4)
+    return dict(packed=buf, labels=buf[0:B * 4].view(torch.float32),
+                ids=buf[o_ids:o_ids + B * F * 4].view(torch.int32).view(B, F),
+                vals=buf[o_vals:o_vals + B * F * 4].view(torch.float32).view(B, F))
+
+
+def pack_batch(ids: torch.Tensor, vals: torch.Tensor, labels: torch.Tensor, pin: bool = False, device="cpu"):
+    B, F = ids.shape
+    s = make_packed_slot(B, F, device, pin)
+    s["ids"].copy_(ids.to(torch.int32))
+    s["vals"].copy_(vals)
+    s["labels"].copy_(labels.reshape(-1))
+    return s["packed"]
+
+
 class FusedDeepFM:
     def __init__(self, cfg: DeepFMConfig, batch_size: int, optimizer: Optional[TF1Optimizer] = None, seed: int = 0,
                  device: Optional[torch.device] = None, params: Optional[Dict[str, torch.Tensor]] = None,
@@ -76,8 +103,9 @@ class FusedDeepFM:
         # ---- activations -----------------------------------------------------------------------------------
         B = self.B
         bf = dict(device=dev, dtype=torch.bfloat16)
-        self.in_slots = [dict(ids=torch.zeros(B, F_, device=dev, dtype=torch.int32), vals=torch.zeros(B, F_, **f32),
-                              labels=torch.zeros(B, **f32)) for _ in range(max(1, input_slots))]
+        # input slots use the native loader's packed slot layout (labels | ids | vals, 256-byte aligned parts) so a
+        # whole batch moves host->device with ONE copy
+        self.in_slots = [make_packed_slot(B, F_, dev) for _ in range(max(1, input_slots))]
         self.x0 = torch.zeros(B, F_ * Kd, **bf)
         self.dx0 = torch.zeros(B, F_ * Kd, **bf)
         self.Ssum = torch.zeros(B, Kd, **f32)
@@ -140,7 +168,7 @@ class FusedDeepFM:
             p.run()
         return 1 + self.n_layers
 
-    def _train_kernels(self, slot) -> int:
+    def _train_kernels(self, slot, with_optimizer: bool = True) -> int:
         """Enqueue one full training step on the current stream (+ a forked side branch). Returns #kernels."""
         cfg, nl = self.cfg, self.n_layers
         cur = torch.cuda.current_stream()
@@ -150,8 +178,7 @@ class FusedDeepFM:
         top = nl - 1
         K.logit_loss(self.acts[top], self._w("deep_out.weight"), self._w("deep_out.bias"), self._w("fm_bias"), self.yfm,
                      slot["labels"], 1.0 / self.global_batch, 1.0 / cfg.dropout[top], True, self.prob, self.logit,
-                     self.dy, self.dz[top], self.loss_sum, self._g("deep_out.weight"), self._g("deep_out.bias"),
-                     self._g("fm_bias"), self._g("mlp%d.bias" % top))
+                     self.dy, self.dz[top], self.loss_sum, self._g("deep_out.bias"), self._g("fm_bias"))
         n += 1
         side = self._side
         for i in range(top, -1, -1):
@@ -161,9 +188,10 @@ class FusedDeepFM:
             side.wait_event(ev)
             with torch.cuda.stream(side):
                 self.wgrad[i].run()
-                n += 1
-                if i != top:
-                    K.colsum_bf16(self.dz[i], self._g("mlp%d.bias" % i))
+                K.colsum_bf16(self.dz[i], self._g("mlp%d.bias" % i))
+                n += 2
+                if i == top:  # g_w_out = X_top^T dy
+                    K.colsum_bf16(self.acts[top], self._g("deep_out.weight"), self.dy)
                     n += 1
             self.dgrad[i].run()
             n += 1
@@ -173,8 +201,20 @@ class FusedDeepFM:
         ev = torch.cuda.Event()
         ev.record(side)
         cur.wait_event(ev)  # join
-        n += self._optimizer_kernels()
+        if with_optimizer:
+            n += self._optimizer_kernels()
         return n
+
+    def compute_grads(self, ids, vals, labels) -> "OrderedDict[str, torch.Tensor]":
+        """Debug/test path: forward+backward WITHOUT the optimizer; returns copies of the data gradients
+        (the whole-table L2 term is applied inside the optimizer sweep and is not part of these)."""
+        self.G.zero_()
+        self.load_inputs(ids, vals, labels, 0)
+        self._train_kernels(self.in_slots[0], with_optimizer=False)
+        torch.cuda.synchronize()
+        out = OrderedDict((n, self.layout.view(self.G, n).clone()) for n in self.layout.names(trainable_only=True))
+        self.G.zero_()
+        return out
 
     def _optimizer_kernels(self) -> int:
         o, L = self.opt, self.layout
@@ -202,6 +242,11 @@ class FusedDeepFM:
             s["vals"][n:].zero_()
             s["labels"][n:].zero_()
         return n
+
+    def load_packed(self, packed: torch.Tensor, slot_idx: int = 0, non_blocking: bool = True):
+        """Copy one full batch in packed slot layout (see make_packed_slot / the native loader) with a single copy."""
+        self.in_slots[slot_idx]["packed"].copy_(packed, non_blocking=non_blocking)
+        return self.B
 
     def train_step_slot(self, slot_idx: int = 0) -> torch.Tensor:
         """Run one optimizer step on the batch already resident in input slot `slot_idx`.

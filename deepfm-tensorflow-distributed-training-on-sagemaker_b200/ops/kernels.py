@@ -89,19 +89,18 @@ class GemmPlan:
 
 
 def logit_loss(x, w_out, b_out, fm_bias, yfm, labels, inv_batch: float, mask_scale: float, train: bool,
-               prob=None, logit=None, dy=None, dz=None, loss_sum=None, g_w_out=None, g_b_out=None, g_fm_bias=None,
-               g_b_last=None) -> None:
+               prob=None, logit=None, dy=None, dz=None, loss_sum=None, g_b_out=None, g_fm_bias=None) -> None:
     B, H = x.shape
     _lib.check(_lib.load().dfm_logit_loss(
         _p(x), c_int(x.stride(0)), c_int(H), _p(w_out), _p(b_out), _p(fm_bias), _p(yfm), _p(labels), c_int(B),
         c_float(inv_batch), c_float(mask_scale), c_int(1 if train else 0), _p(prob), _p(logit), _p(dy), _p(dz),
-        c_int(dz.stride(0) if dz is not None else 0), _p(loss_sum), _p(g_w_out), _p(g_b_out), _p(g_fm_bias),
-        _p(g_b_last), _stream()))
+        c_int(dz.stride(0) if dz is not None else 0), _p(loss_sum), _p(g_b_out), _p(g_fm_bias), _stream()))
 
 
-def colsum_bf16(a: torch.Tensor, out: torch.Tensor) -> None:
+def colsum_bf16(a: torch.Tensor, out: torch.Tensor, w: Optional[torch.Tensor] = None) -> None:
+    """out[j] += sum_b a[b,j] * (w[b] if w is given else 1)."""
     B, H = a.shape
-    _lib.check(_lib.load().dfm_colsum_bf16(_p(a), c_int(a.stride(0)), c_int(B), c_int(H), _p(out), _stream()))
+    _lib.check(_lib.load().dfm_colsum_bf16(_p(a), c_int(a.stride(0)), c_int(B), c_int(H), _p(w), _p(out), _stream()))
 
 
 def auc_hist(prob: torch.Tensor, labels: torch.Tensor, thr: torch.Tensor, hist: torch.Tensor) -> None:

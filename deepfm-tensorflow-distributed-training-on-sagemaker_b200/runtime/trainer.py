@@ -91,6 +91,18 @@ class Trainer:
             return self.model.train_step_slot(slot)
         return self.model.train_step(ids, vals, labels)
 
+    def train_packed_device(self, packed: torch.Tensor):
+        """One optimizer step on a device-resident batch in packed slot layout (one d2d copy + graph replay)."""
+        slot = self._k % self._nslots
+        self._k += 1
+        self.model.load_packed(packed, slot)
+        return self.model.train_step_slot(slot)
+
+    def train_packed(self, packed: torch.Tensor):
+        """One optimizer step on a HOST batch in packed slot layout (what the native loader produces): a single
+        pinned async H2D copy on the copy stream, graph replay, async D2H of the loss scalars."""
+        self._train_host(lambda slot: self.model.load_packed(packed, slot, non_blocking=True))
+
     def train_batch(self, ids, vals, labels):
         """One optimizer step on a HOST batch. On CUDA: pinned-memory async H2D on a side stream into the next input
         slot (overlapping the previous step), graph replay, async D2H of the step's loss scalars."""
@@ -102,6 +114,9 @@ class Trainer:
             else:
                 self._host_losses.append(float(loss))
             return
+        self._train_host(lambda slot: self.model.load_inputs(ids, vals, labels, slot, non_blocking=True))
+
+    def _train_host(self, load_fn):
         main = torch.cuda.current_stream(self.dev)
         slot = self._k % self._nslots
         self._k += 1
@@ -109,7 +124,7 @@ class Trainer:
         if self._slot_free[slot] is not None:
             cs.wait_event(self._slot_free[slot])  # the step that last read this slot has finished
         with torch.cuda.stream(cs):
-            self.model.load_inputs(ids, vals, labels, slot, non_blocking=True)
+            load_fn(slot)
             ev = torch.cuda.Event()
             ev.record(cs)
         main.wait_event(ev)

@@ -44,9 +44,10 @@ int dfm_gemm_run(void* plan, void* stream);
 /* ---- output head: logit sum + sigmoid + log-loss + gradients (PS:221-232,244) ---- */
 int dfm_logit_loss(const void* x_bf16, int ldx, int H, const float* w_out, const float* b_out, const float* fm_bias,
                    const float* yfm, const float* labels, int B, float inv_batch, float mask_scale, int train,
-                   float* prob, float* logit, float* dy, void* dz_bf16, int lddz, float* loss_sum, float* g_w_out,
-                   float* g_b_out, float* g_fm_bias, float* g_b_last, void* stream);
-int dfm_colsum_bf16(const void* a_bf16, int lda, int B, int H, float* out, void* stream);
+                   float* prob, float* logit, float* dy, void* dz_bf16, int lddz, float* loss_sum, float* g_b_out,
+                   float* g_fm_bias, void* stream);
+/* out[j] += sum_b a[b,j] * (w ? w[b] : 1): bias gradients (w = NULL) and g_w_out = X_top^T dy (w = dy). */
+int dfm_colsum_bf16(const void* a_bf16, int lda, int B, int H, const float* w, float* out, void* stream);
 
 /* ---- streaming AUC histogram (tf.metrics.auc, PS:249-251) ---- */
 int dfm_auc_hist(const float* prob, const float* labels, int B, const float* thr, int T, float* hist, void* stream);

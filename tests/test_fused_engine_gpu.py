@@ -52,6 +52,28 @@ def test_fused_step_matches_oracle(cuda_lib, opt, use_graph):
     assert float((got["fm_w"] - ref_p["fm_w"]).abs().max()) < 1e-3
 
 
+def test_fused_grads_match_oracle(cuda_lib):
+    """Forward+backward kernels only (no optimizer): every gradient vs autograd of the bf16-emulating oracle."""
+    from deepfm_b200.models import DeepFMConfig, init_params
+    from deepfm_b200.models.fused import FusedDeepFM
+    from deepfm_b200.models.oracle import oracle_grads
+    cfg = DeepFMConfig(field_size=39, feature_size=5000, embedding_size=32, deep_layers=[400, 400, 400],
+                       dropout=[0.5, 0.8, 1.0], l2_reg=0.0)
+    B = 512
+    params = init_params(cfg, seed=3)
+    for k in params:  # non-trivial biases
+        if k.endswith("bias"):
+            params[k].normal_(0, 0.05)
+    m = FusedDeepFM(cfg, B, seed=77, params=params, use_graph=False)
+    ids, vals, labels = _mk(cfg, B, seed=1)
+    g = m.compute_grads(ids.cuda(), vals.cuda(), labels.cuda())
+    ref_p = {k: v.clone().cuda() for k, v in params.items()}
+    r = oracle_grads(ref_p, cfg, ids.cuda(), vals.cuda(), labels.cuda(), True, 77, 0, 0, compute_dtype=torch.bfloat16)
+    for k, ref in r["grads"].items():
+        err = float((g[k] - ref).abs().max()) / (float(ref.abs().max()) + 1e-12)
+        assert err < 2e-2, (k, err)
+
+
 def test_fused_eval_predict_and_auc(cuda_lib):
     from deepfm_b200.models import DeepFMConfig, init_params
     from deepfm_b200.models.fused import FusedDeepFM
