@@ -60,6 +60,20 @@ int dfm_flat_opt_step(float* w, float* g, float* s0, float* s1, long long n, int
                       float* reg_loss, unsigned int* done_counter, void* stream);
 int dfm_cast_f32_bf16(const float* in, void* out_bf16, long long n, void* stream);
 
+/* ---- flat optimizer step that allocates nothing (no counterpart in the reference: TF owns its own allocator).
+ * Same update as dfm_flat_opt_step, but the scratch it needs sits in a static device array inside the library
+ * (262,400 bytes per GPU, held until exit) instead of being supplied by the caller. For callers that cannot call
+ * cudaMalloc: the GPU's memory already belongs to another allocator or a memory cap, or the call site cannot afford
+ * the device-wide serialisation of cudaMalloc/cudaFree. Limit: n <= dfm_flat_opt_static_max_elems() (64 Mi);
+ * larger n returns DFM_ERR_ARG. The first call on a device does the per-device set-up and should be made before
+ * any stream capture begins. All calls on a device share the array; calls that overlap on the GPU race. */
+long long dfm_flat_opt_static_max_elems(void);
+long long dfm_flat_opt_static_scratch_bytes(void);
+int dfm_flat_opt_step_static(float* w, float* g, float* s0, float* s1, long long n, int opt, float lr, float beta1,
+                             float beta2, float eps, float momentum, float grad_scale, long long decay_begin,
+                             long long decay_end, float l2, long long shadow_begin, long long shadow_end,
+                             void* shadow_bf16, unsigned long long* step_ptr, float* reg_loss, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
