@@ -187,7 +187,8 @@ class NativeLoader:
         return slot.value, rows, lab, ids, vals
 
     def release(self, slot: int) -> None:
-        load().dfmio_loader_release(self._h, slot)
+        if getattr(self, "_h", None):  # releasing into a closed loader is a no-op
+            load().dfmio_loader_release(self._h, slot)
 
     def records_read(self) -> int:
         return int(load().dfmio_loader_records(self._h))

@@ -1,0 +1,1 @@
+from .local import LocalEstimator, hyperparameters_to_argv  # noqa: F401

@@ -1,0 +1,153 @@
+"""Task driver: `python -m deepfm_b200 --task_type {train,eval,infer,export} ...`
+
+Reference: `main()` of both trainers (PS:341-467, HVD:289-431):
+  * echo arguments, discover `tr*/va*/te*.tfrecords` recursively, shuffle the training file order
+  * optional `--clear_existing_model`
+  * train: file mode = per-epoch train -> chief-only evaluate loop (HVD:390-394); pipe mode = one train call with
+    `num_epochs` baked into the stream, channel per local rank (HVD:403-405); then export on the chief
+  * eval -> {auc, loss}; infer -> "%f\\n" per example into <val_data_dir>/pred.txt (PS:447-449); export
+Strategy is chosen with --strategy {dp, sharded, ps} instead of by picking one of two scripts.
+"""
+from __future__ import annotations
+
+import json
+import os
+import shutil
+import sys
+from typing import List, Optional
+
+from ..models import DeepFMConfig
+from ..optim.tf1 import TF1Optimizer
+from ..parallel import shard as shard_rules
+from ..parallel.dist import barrier, init_from_env, shutdown
+from ..data.pipeline import InputPipeline, channel_fifo, discover_files
+from .estimator import Estimator
+from .flags import flags_help, parse_flags, print_flags
+
+
+def build_config(F) -> DeepFMConfig:
+    return DeepFMConfig(field_size=F.field_size, feature_size=F.feature_size, embedding_size=F.embedding_size,
+                        deep_layers=F.deep_layers, dropout=F.dropout, l2_reg=F.l2_reg, batch_norm=F.batch_norm,
+                        batch_norm_decay=F.batch_norm_decay, l2_mode=F.l2_mode)
+
+
+def channel_names(env=os.environ) -> List[str]:
+    """SM_CHANNELS, sorted the way SageMaker presents them (alphabetical: 'evaluation' first, HVD:375-380)."""
+    try:
+        names = json.loads(env.get("SM_CHANNELS", "") or "null")
+        if isinstance(names, list) and names:
+            return sorted(str(n) for n in names)
+    except ValueError:
+        pass
+    return ["evaluation", "training"]
+
+
+def main(argv: Optional[List[str]] = None) -> int:
+    argv = list(sys.argv[1:] if argv is None else argv)
+    if "--help" in argv or "-h" in argv:
+        print(__doc__)
+        print(flags_help())
+        return 0
+    F = parse_flags(argv)
+    use_cuda = None if F.backend == "auto" else (F.backend == "fused")
+    if F.backend == "torch" and F.num_GPUs == 0:
+        use_cuda = False
+    env = init_from_env(use_cuda)
+    if env.is_chief:
+        print(sys.argv)
+        print_flags(F)
+    if F.field_size <= 0 or F.feature_size <= 0:
+        raise SystemExit("--field_size and --feature_size are required")
+
+    # ------ init envs: file discovery (PS:373-381 / HVD:320-328)
+    pipe = F.pipe_mode != 0
+    if not pipe:
+        tr_files = discover_files(F.training_data_dir, "tr", shuffle=True, seed=F.seed)
+        va_files = discover_files(F.val_data_dir, "va")
+        te_files = discover_files(F.val_data_dir, "te")
+    else:
+        tr_files = va_files = te_files = []
+    if env.is_chief:
+        print("tr_files:", tr_files)
+        print("va_files:", va_files)
+        print("te_files:", te_files)
+
+    if F.clear_existing_model and env.is_chief and F.model_dir:
+        try:
+            shutil.rmtree(F.model_dir)
+        except Exception as e:  # same tolerance as HVD:334-340
+            print(e, "at clear_existing_model")
+        else:
+            print("existing model cleaned at %s" % F.model_dir)
+    barrier(env)
+
+    cfg = build_config(F)
+    lr = F.learning_rate * (env.world_size if (F.scale_lr_by_world and F.strategy != "ps") else 1)  # HVD:149
+    opt = TF1Optimizer(F.optimizer, lr)
+    est = Estimator(cfg, F.batch_size, opt, F.model_dir or None, env, backend=F.backend, seed=F.seed,
+                    log_steps=F.log_steps, save_checkpoints_secs=F.save_checkpoints_secs,
+                    save_checkpoints_steps=F.save_checkpoints_steps, keep_checkpoint_max=F.keep_checkpoint_max,
+                    metrics_file=F.metrics_file or None, comm=F.comm, strategy=F.strategy)
+
+    num_hosts = len(F.hosts)
+    if F.strategy == "ps":
+        spec = shard_rules.ps_shard(F.enable_s3_shard, F.hosts, F.current_host)
+        if spec is None or num_hosts == 1:  # several worker processes on one box still split the data
+            spec = (env.world_size, env.rank)
+    else:
+        spec = shard_rules.hvd_shard(pipe, F.enable_s3_shard, F.enable_data_multi_path, env.world_size, env.rank,
+                                     env.local_rank, F.worker_per_host, num_hosts)
+    train_shard = shard_rules.normalise(spec)
+    pin = env.device is not None
+
+    def input_fn(files, num_epochs=1, shard=(1, 0), drop_remainder=True):
+        return InputPipeline(files, F.field_size, F.batch_size, num_epochs, shard, drop_remainder, F.loader_threads, pin)
+
+    names = channel_names()
+    metrics = None
+    if F.task_type == "train":
+        if not pipe:
+            for _ in range(F.num_epochs):  # HVD:391-394
+                est.train(lambda: input_fn(tr_files, 1, train_shard), max_steps=F.max_steps)
+                if env.is_chief and va_files:
+                    metrics = est.evaluate(lambda: input_fn(va_files, 1, (1, 0), False))
+                barrier(env)
+                if F.max_steps and est.trainer.global_step >= F.max_steps:
+                    break
+        else:
+            # one train() call; epochs are separate FIFOs <channel>_<epoch> consumed in order (HVD:396-405)
+            ch = F.training_channel_name or shard_rules.pipe_train_channel(names, env.local_rank) \
+                if (F.enable_data_multi_path or len(names) > 2) else (F.training_channel_name or names[-1])
+            fifos = [channel_fifo(F.data_base_dir, ch, e) for e in range(F.num_epochs)]
+            est.train(lambda: input_fn(fifos, 1, train_shard), max_steps=F.max_steps)
+            if env.is_chief:
+                ev = F.evaluation_channel_name or shard_rules.pipe_eval_channel(names)
+                ev_fifo = channel_fifo(F.data_base_dir, ev, 0)
+                if os.path.exists(ev_fifo):
+                    metrics = est.evaluate(lambda: input_fn([ev_fifo], 1, (1, 0), False))
+            barrier(env)
+    elif F.task_type == "eval":
+        # the reference runs this on every rank although only rank 0 has a checkpoint (HVD:407-408); gate it
+        if env.is_chief:
+            metrics = est.evaluate(lambda: input_fn(va_files, 1, (1, 0), False))
+    elif F.task_type == "infer":
+        if env.is_chief:
+            out_path = os.path.join(F.val_data_dir, "pred.txt")
+            with open(out_path, "w") as fo:
+                for p in est.predict(lambda: input_fn(te_files, 1, (1, 0), False)):
+                    fo.write("%f\n" % p["prob"])
+            print("predictions written to %s" % out_path)
+    elif F.task_type != "export":
+        raise SystemExit("unknown --task_type %r" % F.task_type)
+
+    if F.task_type in ("export", "train") and F.servable_model_dir:  # PS:451-467 / HVD:415-431
+        est.export_savedmodel(F.servable_model_dir)
+    if metrics is not None and env.is_chief:
+        print(json.dumps({"eval": metrics}))
+    barrier(env)
+    shutdown()
+    return 0
+
+
+if __name__ == "__main__":
+    raise SystemExit(main())

@@ -1,0 +1,156 @@
+"""Estimator — the train / evaluate / predict / export driver with the reference's Estimator semantics
+(PS:435-467, HVD:365-431): a `model_dir` that is restored from on entry, checkpoints written by the chief only,
+`evaluate` returning {auc, loss, global_step}, `predict` yielding probabilities, `export_savedmodel` writing a
+servable with the raw serving signature (feat_ids [None,F] int64, feat_vals [None,F] float32 -> prob)."""
+from __future__ import annotations
+
+import collections
+import os
+import shutil
+import sys
+import time
+from typing import Callable, Iterable, Optional
+
+import torch
+
+from ..models import DeepFMConfig
+from ..optim.tf1 import TF1Optimizer
+from ..parallel.dist import DistEnv, agree_min, barrier
+from ..utils.checkpoint import latest_checkpoint, load_checkpoint
+from .hooks import CheckpointSaverHook, LoggingHook
+from .trainer import Trainer
+
+
+class Estimator:
+    def __init__(self, cfg: DeepFMConfig, batch_size: int, optimizer: TF1Optimizer, model_dir: Optional[str],
+                 env: Optional[DistEnv] = None, backend: str = "auto", seed: int = 0, log_steps: int = 100,
+                 save_checkpoints_secs: int = 600, save_checkpoints_steps: int = 0, keep_checkpoint_max: int = 5,
+                 metrics_file: Optional[str] = None, comm: str = "auto", strategy: str = "dp", out=sys.stdout):
+        self.cfg, self.B, self.opt = cfg, batch_size, optimizer
+        self.env = env or DistEnv()
+        # like the reference, only the chief owns a model_dir (HVD:365-368); other ranks get state by broadcast
+        self.model_dir = model_dir if (model_dir and self.env.is_chief) else None
+        self.shared_model_dir = model_dir
+        self.out = out
+        self.strategy = strategy
+        if strategy == "sharded" and self.env.world_size > 1:
+            from ..parallel.sharded import ShardedTrainer
+            self.trainer = ShardedTrainer(cfg, batch_size, optimizer, seed, self.env)
+        elif strategy == "ps":
+            from ..parallel.ps import AsyncPSTrainer
+            self.trainer = AsyncPSTrainer(cfg, batch_size, optimizer, seed, self.env, backend=backend)
+        else:
+            self.trainer = Trainer(cfg, batch_size, optimizer, seed, self.env.device, backend, self.env.world_size,
+                                   self.env.rank, comm=comm)
+        gb = batch_size * self.env.world_size
+        mf = metrics_file or (os.path.join(model_dir, "metrics.jsonl") if model_dir else None)
+        self.log = LoggingHook(log_steps, gb, mf if self.env.is_chief else None, out, enabled=self.env.is_chief)
+        self.saver = CheckpointSaverHook(self.model_dir or "", save_checkpoints_secs, save_checkpoints_steps,
+                                         keep_checkpoint_max, enabled=self.env.is_chief and bool(model_dir))
+        self._restored = False
+
+    # ------------------------------------------------------------------------------------------ state
+    def restore_latest(self) -> Optional[str]:
+        """Estimator behaviour: every train/evaluate/predict call starts from the latest checkpoint in model_dir.
+        The chief reads it; with several ranks the state is then broadcast from rank 0 (the reference does this
+        with BroadcastGlobalVariablesHook(0), HVD:372)."""
+        prefix = latest_checkpoint(self.model_dir) if self.model_dir else None
+        if prefix:
+            names = list(self.trainer.model.named_parameters().keys()) if hasattr(self.trainer, "model") else \
+                self.trainer.parameter_names()
+            self.trainer.load_state_dict(load_checkpoint(prefix, names, self.opt.name), strict=False)
+            print("INFO:deepfm_b200:Restoring parameters from %s" % prefix, file=self.out)
+        if self.env.world_size > 1 and hasattr(self.trainer, "broadcast_state"):
+            self.trainer.broadcast_state()
+        self._restored = True
+        return prefix
+
+    # ------------------------------------------------------------------------------------------ train
+    def train(self, input_fn: Callable[[], Iterable], max_steps: int = 0, steps_hint: Optional[int] = None) -> int:
+        """One `Estimator.train` call: consume `input_fn()` to exhaustion (or `max_steps`)."""
+        self.restore_latest()
+        tr = self.trainer
+        step = tr.global_step
+        self.log.begin(step)
+        fused = getattr(tr, "backend", "") == "fused"
+        inflight = collections.deque()
+        n_local = 0
+        limit = agree_min(self.env, steps_hint) if steps_hint is not None else None
+        for batch in input_fn():
+            if limit is not None and n_local >= limit:
+                batch.release()
+                break
+            if batch.rows != self.B:  # drop_remainder=True upstream; a short batch would change the graph shape
+                batch.release()
+                continue
+            if fused and batch.packed is not None:
+                ev = tr.train_packed(batch.packed)
+            else:
+                ev = tr.train_batch(batch.ids, batch.vals, batch.labels)
+            inflight.append((batch, ev))
+            while inflight and (len(inflight) > 3 or (inflight[0][1] is not None and inflight[0][1].query())):
+                b, e = inflight.popleft()
+                if e is not None:
+                    e.synchronize()
+                b.release()
+            step += 1
+            n_local += 1
+            self.log.after_step(step, lambda: self._current_loss())
+            if self.saver.due(step):
+                self.saver.save(tr, self.out)
+            if max_steps and step >= max_steps:
+                break
+        for b, e in inflight:
+            if e is not None:
+                e.synchronize()
+            b.release()
+        tail = tr.drain()
+        if tail:
+            self._last_loss = tail[-1]
+        if self.env.is_chief and self.saver.enabled:
+            self.saver.save(tr, self.out)
+        print("INFO:deepfm_b200:Loss for final step: %.8g." % self._current_loss(), file=self.out)
+        return n_local
+
+    def _current_loss(self) -> float:
+        tr = self.trainer
+        losses = tr.drain()
+        if losses:
+            self._last_loss = losses[-1]
+        return float(getattr(self, "_last_loss", float("nan")))
+
+    # ------------------------------------------------------------------------------------------ eval / predict
+    def evaluate(self, input_fn: Callable[[], Iterable]) -> dict:
+        if not self._restored:
+            self.restore_latest()
+        t0 = time.time()
+        m = self.trainer.evaluate(self._tuples(input_fn()))
+        m["eval_seconds"] = time.time() - t0
+        self.log.log_eval(m)
+        return m
+
+    def predict(self, input_fn: Callable[[], Iterable]):
+        if not self._restored:
+            self.restore_latest()
+        for probs in self.trainer.predict(self._tuples(input_fn())):
+            for p in probs.tolist():
+                yield {"prob": p}
+
+    @staticmethod
+    def _tuples(batches):
+        for b in batches:
+            t = (b.ids.clone(), b.vals.clone(), b.labels.clone())
+            b.release()
+            yield t
+
+    def export_savedmodel(self, export_dir_base: str) -> Optional[str]:
+        if not self.env.is_chief:
+            return None
+        if not self._restored:
+            self.restore_latest()
+        from ..serving.export import export_servable
+        params = {k: v.detach().float().cpu() for k, v in self.trainer.state_dict().items() if "/" not in k
+                  and k != "global_step"}
+        path = export_servable(export_dir_base, self.cfg, params, self.trainer.global_step)
+        print("INFO:deepfm_b200:SavedModel written to: %s" % path, file=self.out)
+        return path

@@ -101,7 +101,7 @@ class Trainer:
     def train_packed(self, packed: torch.Tensor):
         """One optimizer step on a HOST batch in packed slot layout (what the native loader produces): a single
         pinned async H2D copy on the copy stream, graph replay, async D2H of the loss scalars."""
-        self._train_host(lambda slot: self.model.load_packed(packed, slot, non_blocking=True))
+        return self._train_host(lambda slot: self.model.load_packed(packed, slot, non_blocking=True))
 
     def train_batch(self, ids, vals, labels):
         """One optimizer step on a HOST batch. On CUDA: pinned-memory async H2D on a side stream into the next input
@@ -113,8 +113,8 @@ class Trainer:
                 self._push_loss(torch.stack([loss.reshape(()), torch.zeros((), device=self.dev)]), already_mean=True)
             else:
                 self._host_losses.append(float(loss))
-            return
-        self._train_host(lambda slot: self.model.load_inputs(ids, vals, labels, slot, non_blocking=True))
+            return None
+        return self._train_host(lambda slot: self.model.load_inputs(ids, vals, labels, slot, non_blocking=True))
 
     def _train_host(self, load_fn):
         main = torch.cuda.current_stream(self.dev)
@@ -133,6 +133,7 @@ class Trainer:
         done.record(main)
         self._slot_free[slot] = done
         self._push_loss(self.model.scalars, already_mean=False)
+        return ev  # completes when the host buffer has been copied out (the caller may then reuse it)
 
     def _push_loss(self, scalars: torch.Tensor, already_mean: bool):
         if self._ring_pos == self._ring_n:
@@ -157,9 +158,11 @@ class Trainer:
         return out
 
     # ------------------------------------------------------------------------------------------- eval / predict
-    def evaluate(self, batches: Iterable) -> Dict[str, float]:
+    def evaluate(self, batches: Iterable, distributed: bool = False) -> Dict[str, float]:
         """`Estimator.evaluate` (PS:443-444): mean loss (incl. the L2 terms, as the reference's EVAL loss does) and
-        streaming AUC with tf.metrics.auc defaults."""
+        streaming AUC with tf.metrics.auc defaults. The reference evaluates on the chief only (HVD:393); pass
+        `distributed=True` when EVERY rank calls this on its own shard: loss sums and the 2x201 confusion histogram
+        are then combined with one small all-reduce."""
         auc = StreamingAUC()
         fused = self.backend == "fused"
         if fused:
@@ -175,7 +178,7 @@ class Trainer:
                 auc.update(labels, probs)
         hist = self.model.auc_hist.double().cpu() if fused else auc.hist
         stats = torch.cat([tot.cpu(), torch.tensor([float(n)], dtype=torch.float64), hist.reshape(-1)])
-        if self.world > 1 and torch.distributed.is_initialized():
+        if distributed and self.world > 1 and torch.distributed.is_initialized():
             s = stats.to(self.dev) if torch.distributed.get_backend() == "nccl" else stats
             torch.distributed.all_reduce(s)
             stats = s.cpu()
@@ -191,6 +194,15 @@ class Trainer:
             yield self.model.predict(ids, vals).detach().float().cpu()
 
     # ------------------------------------------------------------------------------------------- state
+    def broadcast_state(self, src: int = 0):
+        """Make every rank's parameters / slots / step equal to rank `src`'s (HVD:372)."""
+        if self.world > 1 and torch.distributed.is_initialized():
+            if hasattr(self.model, "broadcast_state"):
+                self.model.broadcast_state(src)
+            else:
+                from ..parallel.dp import broadcast_model
+                broadcast_model(self.model, src)
+
     def state_dict(self):
         return self.model.state_dict()
 

@@ -1,0 +1,82 @@
+"""Python binding of the C++ TensorFlow tensor-bundle codec (csrc/io/tensor_bundle.cc)."""
+from __future__ import annotations
+
+import ctypes
+from ctypes import c_char_p, c_int, c_int64, c_uint64, c_void_p
+from typing import Dict
+
+import numpy as np
+import torch
+
+from ..data import native as _n
+
+DT_FLOAT, DT_INT32, DT_INT64 = 1, 3, 9
+_NP = {DT_FLOAT: np.float32, DT_INT32: np.int32, DT_INT64: np.int64}
+_DT = {np.dtype(np.float32): DT_FLOAT, np.dtype(np.int32): DT_INT32, np.dtype(np.int64): DT_INT64}
+
+
+def _lib():
+    lib = _n.load()
+    if not getattr(lib, "_bundle_ready", False):
+        lib.dfmio_bundle_last_error.restype = c_char_p
+        lib.dfmio_bundle_writer_create.restype = c_void_p
+        lib.dfmio_bundle_writer_create.argtypes = [c_char_p]
+        lib.dfmio_bundle_writer_add.argtypes = [c_void_p, c_char_p, c_int, c_int, c_void_p, c_void_p, c_uint64]
+        lib.dfmio_bundle_writer_finish.argtypes = [c_void_p]
+        lib.dfmio_bundle_reader_open.restype = c_void_p
+        lib.dfmio_bundle_reader_open.argtypes = [c_char_p]
+        lib.dfmio_bundle_reader_count.argtypes = [c_void_p]
+        lib.dfmio_bundle_reader_entry.argtypes = [c_void_p, c_int, c_char_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p]
+        lib.dfmio_bundle_reader_read.argtypes = [c_void_p, c_int, c_void_p, c_uint64, c_int]
+        lib.dfmio_bundle_reader_close.argtypes = [c_void_p]
+        lib._bundle_ready = True
+    return lib
+
+
+def _err(lib):
+    m = lib.dfmio_bundle_last_error()
+    return m.decode() if m else "?"
+
+
+def write_bundle(prefix: str, tensors: Dict[str, torch.Tensor]) -> None:
+    """Write `<prefix>.index` + `<prefix>.data-00000-of-00001` holding `tensors` (keys = TF variable names)."""
+    lib = _lib()
+    h = lib.dfmio_bundle_writer_create(prefix.encode())
+    if not h:
+        raise IOError(_err(lib))
+    for name in sorted(tensors):
+        a = np.array(tensors[name].detach().cpu().numpy(), order="C", copy=True)  # keeps 0-d scalars 0-d
+        if a.dtype not in _DT:
+            a = a.astype(np.float32)
+        dims = (c_int64 * max(a.ndim, 1))(*a.shape)
+        if lib.dfmio_bundle_writer_add(h, name.encode(), _DT[a.dtype], a.ndim, dims, a.ctypes.data, a.nbytes) != 0:
+            raise IOError(_err(lib))
+    if lib.dfmio_bundle_writer_finish(h) != 0:
+        raise IOError(_err(lib))
+
+
+def read_bundle(prefix: str, verify_crc: bool = True) -> Dict[str, torch.Tensor]:
+    lib = _lib()
+    h = lib.dfmio_bundle_reader_open(prefix.encode())
+    if not h:
+        raise IOError(_err(lib))
+    out = {}
+    try:
+        name = ctypes.create_string_buffer(1024)
+        for i in range(lib.dfmio_bundle_reader_count(h)):
+            dtype, ndim, nbytes = c_int(), c_int(), c_uint64()
+            dims = (c_int64 * 8)()
+            lib.dfmio_bundle_reader_entry(h, i, name, 1024, ctypes.byref(dtype), ctypes.byref(ndim), dims,
+                                          ctypes.byref(nbytes))
+            if dtype.value not in _NP:
+                continue  # not a numeric tensor we know (e.g. string tensors in foreign checkpoints)
+            shape = tuple(dims[k] for k in range(ndim.value))
+            a = np.empty(shape, dtype=_NP[dtype.value])
+            if a.nbytes != nbytes.value:
+                raise IOError("size mismatch for %s" % name.value.decode())
+            if lib.dfmio_bundle_reader_read(h, i, a.ctypes.data, a.nbytes, 1 if verify_crc else 0) != 0:
+                raise IOError(_err(lib))
+            out[name.value.decode()] = torch.from_numpy(a)
+    finally:
+        lib.dfmio_bundle_reader_close(h)
+    return out

@@ -1,0 +1,128 @@
+"""End-to-end on CPU (torch backend): flags -> train -> checkpoint -> resume -> eval -> infer -> export -> serve,
+plus the launcher with world_size=2 over gloo (SURVEY section 4 'End-to-end' and 'Distributed without a cluster')."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+F, N = 13, 2000
+COMMON = ["--field_size", str(F), "--feature_size", str(N), "--embedding_size", "8", "--deep_layers", "32,16",
+          "--dropout", "0.9,0.9", "--batch_size", "64", "--learning_rate", "0.005", "--log_steps", "10",
+          "--backend", "torch", "--loader_threads", "2"]
+
+
+@pytest.fixture(scope="module")
+def data(tmp_path_factory):
+    from deepfm_b200.data.synthetic import write_synthetic_tfrecords
+    d = tmp_path_factory.mktemp("data")
+    write_synthetic_tfrecords(str(d / "train"), "tr", 2, 1280, F, N, seed=1)
+    write_synthetic_tfrecords(str(d / "val"), "va", 1, 640, F, N, seed=2)
+    write_synthetic_tfrecords(str(d / "val"), "te", 1, 100, F, N, seed=3)
+    return d
+
+
+def _run(args, env=None, timeout=600):
+    e = dict(os.environ, PYTHONPATH=REPO, CUDA_VISIBLE_DEVICES="")
+    e.update(env or {})
+    r = subprocess.run([sys.executable, "-m", "deepfm_b200"] + args, capture_output=True, text=True, env=e,
+                       timeout=timeout, cwd=REPO)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    return r.stdout
+
+
+def test_flags_sagemaker_style():
+    from deepfm_b200.runtime.flags import parse_flags
+    f = parse_flags(["--field_size", "39", "--feature_size=117581", "--batch_norm", "True", "--enable_s3_shard", "False",
+                     "--deep_layers", "128,64,32", "--model_dir", "s3://x", "--perform_shuffle", "False",
+                     "--some_unknown", "1", "--clear_existing_model"], env={})
+    assert f.field_size == 39 and f.feature_size == 117581 and f.batch_norm is True and f.enable_s3_shard is False
+    assert f.checkpoint_dir == "s3://x" and f.clear_existing_model is True and f.hosts == ["localhost"]
+    assert "--some_unknown" in f.unknown
+    f = parse_flags([], env={"SM_HOSTS": '["algo-1","algo-2"]', "SM_CURRENT_HOST": "algo-2", "SM_NUM_GPUS": "4"})
+    assert f.hosts == ["algo-1", "algo-2"] and f.current_host == "algo-2" and f.num_GPUs == 4
+
+
+def test_shard_decision_table():
+    from deepfm_b200.parallel.shard import hvd_shard, normalise, pipe_train_channel, ps_shard
+    # README-EN:86-91 / HVD:92-120, world 8 = 2 hosts x 4 workers, this is global rank 5 (local 1)
+    kw = dict(world_size=8, rank=5, local_rank=1, worker_per_host=4, num_hosts=2)
+    assert hvd_shard(False, True, False, **kw) == (4, 1)
+    assert hvd_shard(False, False, False, **kw) == (8, 5)
+    assert hvd_shard(True, True, True, **kw) is None
+    assert hvd_shard(True, False, True, **kw) == (2, 1)
+    assert hvd_shard(True, False, True, world_size=4, rank=3, local_rank=3, worker_per_host=4, num_hosts=1) is None
+    assert hvd_shard(True, True, False, **kw) == (4, 1)
+    assert hvd_shard(True, False, False, **kw) == (8, 5)
+    assert ps_shard(False, ["a", "b"], "b") == (2, 1) and ps_shard(True, ["a", "b"], "b") is None
+    assert normalise(None) == (1, 0)
+    assert pipe_train_channel(["evaluation", "training", "training-1"], 1) == "training-1"
+
+
+def test_train_eval_infer_export_resume(data, tmp_path):
+    ckpt, serv = str(tmp_path / "ckpt"), str(tmp_path / "model")
+    base = COMMON + ["--training_data_dir", str(data / "train"), "--val_data_dir", str(data / "val"),
+                     "--model_dir", ckpt]
+    out = _run(base + ["--task_type", "train", "--num_epochs", "2", "--servable_model_dir", serv,
+                       "--save_checkpoints_steps", "20"])
+    assert "loss = " in out and "Saving checkpoints for 40" in out and "Saving checkpoints for 80" in out
+    ev = json.loads([l for l in out.splitlines() if l.startswith('{"eval"')][-1])["eval"]
+    assert ev["global_step"] == 80 and 0.0 < ev["loss"] < 0.8 and ev["auc"] > 0.5 and ev["examples"] == 640
+    first_loss = float(out.split("loss = ")[1].split(",")[0])
+    assert 0.3 < first_loss < 0.9  # step-10 loss, already below ln 2 (the reference logs 0.696 at step 1, PDF p34)
+    assert os.path.exists(os.path.join(ckpt, "checkpoint")) and os.path.exists(os.path.join(ckpt, "metrics.jsonl"))
+    # resume: a second train call continues from step 80
+    out2 = _run(base + ["--task_type", "train", "--num_epochs", "1"])
+    assert "Restoring parameters from" in out2 and "Saving checkpoints for 120" in out2
+    # eval / infer / export as separate tasks
+    out3 = _run(base + ["--task_type", "eval"])
+    ev3 = json.loads([l for l in out3.splitlines() if l.startswith('{"eval"')][-1])["eval"]
+    assert ev3["global_step"] == 120
+    _run(base + ["--task_type", "infer"])
+    preds = [float(x) for x in open(data / "val" / "pred.txt")]
+    assert len(preds) == 100 and all(0.0 <= p <= 1.0 for p in preds)
+    _run(base + ["--task_type", "export", "--servable_model_dir", serv])
+    from deepfm_b200.serving import Predictor
+    from deepfm_b200.data.pipeline import InputPipeline
+    p = Predictor.load(serv, backend="torch-cpu")
+    b = next(iter(InputPipeline([str(data / "val" / "te000.tfrecords")], F, 100, drop_remainder=False, pin_memory=False)))
+    probs = p.predict({"feat_ids": b.ids.long(), "feat_vals": b.vals})["prob"]
+    assert torch.allclose(probs, torch.tensor(preds), atol=2e-6)
+    sig = json.load(open(os.path.join(serv, sorted(os.listdir(serv))[-1], "signature.json")))
+    assert set(sig["serving_default"]["inputs"]) == {"feat_ids", "feat_vals"}
+
+
+def test_launcher_dp2_gloo_matches_single_process(data, tmp_path):
+    """Horovod-style DP over gloo with 2 processes == 1 process on the concatenated batches (sync invariant)."""
+    from deepfm_b200.launch import LocalEstimator
+    hp = dict(field_size=F, feature_size=N, embedding_size=8, deep_layers="32,16", dropout="1.0,1.0", batch_size=32,
+              learning_rate=0.005, backend="torch", task_type="train", num_epochs=1, log_steps=1000,
+              scale_lr_by_world=False, loader_threads=1)
+    env = {"PYTHONPATH": REPO, "CUDA_VISIBLE_DEVICES": ""}
+    d2 = str(tmp_path / "dp2")
+    LocalEstimator(dict(hp, model_dir=d2), {"mpi": {"enabled": True, "processes_per_host": 2}}, env=env,
+                   cwd=REPO).fit({"training": str(data / "train"), "evaluation": str(data / "val")}, timeout=600)
+    d1 = str(tmp_path / "dp1")
+    LocalEstimator(dict(hp, model_dir=d1, batch_size=64), env=env, cwd=REPO).fit(
+        {"training": str(data / "train"), "evaluation": str(data / "val")}, timeout=600)
+    from deepfm_b200.utils.checkpoint import latest_checkpoint
+    from deepfm_b200.utils.tf_bundle import read_bundle
+    a, b = read_bundle(latest_checkpoint(d1)), read_bundle(latest_checkpoint(d2))
+    assert int(a["global_step"]) == int(b["global_step"]) == 40
+    # rank r of 2 takes records r, r+2, ...; its batch k is global batch k's odd/even half -> same global batches
+    for k in ("fm_w", "fm_v", "Deep-part/mlp0/weights", "Deep-part/deep_out/weights"):
+        assert torch.allclose(a[k], b[k], rtol=1e-4, atol=1e-6), k
+
+
+def test_pipe_mode_training(data, tmp_path):
+    from deepfm_b200.launch import LocalEstimator
+    hp = dict(field_size=F, feature_size=N, embedding_size=8, deep_layers="16", dropout="1.0", batch_size=64,
+              backend="torch", task_type="train", num_epochs=2, log_steps=1000, model_dir=str(tmp_path / "pm"),
+              loader_threads=1)
+    LocalEstimator(hp, input_mode="Pipe", env={"PYTHONPATH": REPO, "CUDA_VISIBLE_DEVICES": ""}, cwd=REPO).fit(
+        {"training": str(data / "train"), "evaluation": str(data / "val")}, timeout=600)
+    from deepfm_b200.utils.checkpoint import latest_checkpoint
+    assert latest_checkpoint(str(tmp_path / "pm")).endswith("model.ckpt-80")  # 2 epochs x 2560 rows / 64
