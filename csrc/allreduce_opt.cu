@@ -1,0 +1,237 @@
+// dense_allreduce_opt — gradient all-reduce FUSED with the optimizer step, over NVLink 5 / NVSwitch peer memory.
+//
+// Replaces, in one kernel per step per rank (SURVEY K12 + X1; reference: Horovod's NCCL ring all-reduce of the
+// 16-19 MB fusion buffer HVD:262 followed by 11 ApplyAdam launches PS:269):
+//
+//   1. cross-GPU barrier A   every rank's backward has finished writing its flat fp32 gradient buffer
+//   2. reduce-scatter        rank r sums ITS 1/W slice of the gradients across all W ranks
+//                              P2P  : ld.volatile.global.v4.f32 from each peer's mapped buffer
+//                              NVLS : multimem.ld_reduce.add.v4.f32 on the multicast address (reduced in the switch)
+//   3. optimizer on slice    L2 decay of fm_w/fm_v + TF-1 Adam/Adagrad/Momentum/FTRL/GD on that slice only; optimizer
+//                            slots are sharded W ways (the HBM sweep shrinks W-fold compared with a replicated step)
+//   4. all-gather            updated fp32 weights and bf16 GEMM shadows stored straight into EVERY rank's replica
+//                              P2P  : st.global.v4 to each peer pointer       NVLS : multimem.st
+//   5. cross-GPU barrier B   by the last CTA to finish: all replicas are complete when any rank's kernel exits
+//
+// Gradients are NOT zeroed here: peers may still be reading them; the step graph zeroes them with a memset node
+// that overlaps the next forward pass. Barriers use monotonically increasing sequence numbers (the step counter),
+// release/acquire at system scope, one flag per (CTA, peer) for A and one per peer for B; all CTAs are co-resident
+// (grid <= 148 x occupancy) so the spin-waits cannot deadlock.
+#include "common.cuh"
+#include "optim_math.cuh"
+
+namespace dfm {
+
+constexpr int kMaxRanks = 8;
+constexpr int kArThreads = 256;
+constexpr int kArMaxBlocks = 296;
+
+struct ArOptArgs {
+  float* g[kMaxRanks];             // every rank's flat gradient buffer (peer-mapped), index [rank]
+  float* p[kMaxRanks];             // every rank's flat parameter buffer
+  __nv_bfloat16* sh[kMaxRanks];    // every rank's bf16 shadow buffer
+  uint32_t* flags[kMaxRanks];      // every rank's flag array: [kArMaxBlocks*kMaxRanks] for A, then [kMaxRanks] for B
+  float* reg_parts[kMaxRanks];     // every rank's [kMaxRanks] array of per-rank L2-loss partials
+  float* g_mc;                     // multicast mappings (NVLS), may be null
+  float* p_mc;
+  __nv_bfloat16* sh_mc;
+  float* s0;                       // local slot slices (index relative to slice_begin)
+  float* s1;
+  int rank, world;
+  long long slice_begin, slice_end;  // this rank's element range (multiples of 4)
+  OptHyper h;
+  float grad_scale;
+  long long decay_begin, decay_end;
+  float l2;
+  long long shadow_begin, shadow_end;
+  unsigned long long* step_ptr;
+  float* reg_local;                // scratch accumulator (1 float, zero between steps)
+  unsigned int* done_counter;      // scratch (1 word, zero between steps)
+  unsigned int* seq_ptr;           // barrier sequence number: monotonic, never rewound (unlike the step counter)
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_volatile_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.volatile.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 multimem_ld_reduce_f4(const float* p) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_f4(float* p, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void multimem_st_bf16x4(__nv_bfloat16* p, uint2 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+}
+
+template <bool NVLS>
+__global__ void __launch_bounds__(kArThreads) allreduce_opt_kernel(const ArOptArgs a) {
+  __shared__ float s_lr;
+  __shared__ float s_red[kArThreads / 32];
+  __shared__ bool s_last;
+  const int W = a.world;
+  const unsigned long long t = *a.step_ptr + 1ull;
+  const uint32_t seq = *a.seq_ptr + 1u;
+  if (threadIdx.x == 0) s_lr = opt_step_lr(a.h, t);
+
+  // ---- barrier A: one flag per (CTA, peer)
+  if (threadIdx.x < W) {
+    const int peer = threadIdx.x;
+    st_release_sys(a.flags[peer] + (size_t)blockIdx.x * kMaxRanks + a.rank, seq);
+    const uint32_t* mine = a.flags[a.rank] + (size_t)blockIdx.x * kMaxRanks + peer;
+    while ((int32_t)(ld_acquire_sys(mine) - seq) < 0) {
+    }
+  }
+  __syncthreads();
+  const float lr_t = s_lr;
+  const int nslots = opt_num_slots(a.h.opt);
+  float reg = 0.f;
+  float* wl = a.p[a.rank];
+  const long long b4 = a.slice_begin >> 2, e4 = a.slice_end >> 2;
+  for (long long i = b4 + (long long)blockIdx.x * kArThreads + threadIdx.x; i < e4; i += (long long)gridDim.x * kArThreads) {
+    const long long e = i << 2;
+    float4 g;
+    if constexpr (NVLS) {
+      g = multimem_ld_reduce_f4(a.g_mc + e);
+    } else {
+      g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+      for (int r = 0; r < W; ++r) {
+        const float4 x = ld_volatile_f4(a.g[(a.rank + r) % W] + e);  // stagger peers across ranks
+        g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
+      }
+    }
+    float4 w = reinterpret_cast<const float4*>(wl)[i];
+    const long long li = i - b4;
+    float4 s0 = nslots > 0 ? reinterpret_cast<float4*>(a.s0)[li] : make_float4(0, 0, 0, 0);
+    float4 s1 = nslots > 1 ? reinterpret_cast<float4*>(a.s1)[li] : make_float4(0, 0, 0, 0);
+    g.x *= a.grad_scale; g.y *= a.grad_scale; g.z *= a.grad_scale; g.w *= a.grad_scale;
+    if (e >= a.decay_begin && e < a.decay_end) {
+      reg += w.x * w.x + w.y * w.y + w.z * w.z + w.w * w.w;
+      g.x += a.l2 * w.x; g.y += a.l2 * w.y; g.z += a.l2 * w.z; g.w += a.l2 * w.w;
+    }
+    opt_update(a.h, lr_t, g.x, w.x, s0.x, s1.x);
+    opt_update(a.h, lr_t, g.y, w.y, s0.y, s1.y);
+    opt_update(a.h, lr_t, g.z, w.z, s0.z, s1.z);
+    opt_update(a.h, lr_t, g.w, w.w, s0.w, s1.w);
+    if (nslots > 0) reinterpret_cast<float4*>(a.s0)[li] = s0;
+    if (nslots > 1) reinterpret_cast<float4*>(a.s1)[li] = s1;
+    const bool in_shadow = (e >= a.shadow_begin && e < a.shadow_end);
+    uint2 pk;
+    if (in_shadow) {
+      pk.x = pack_bf16x2(w.x, w.y);
+      pk.y = pack_bf16x2(w.z, w.w);
+    }
+    if constexpr (NVLS) {
+      multimem_st_f4(a.p_mc + e, w);
+      if (in_shadow) multimem_st_bf16x4(a.sh_mc + (e - a.shadow_begin), pk);
+    } else {
+#pragma unroll 1
+      for (int r = 0; r < W; ++r) {
+        const int peer = (a.rank + r) % W;
+        reinterpret_cast<float4*>(a.p[peer])[i] = w;
+        if (in_shadow) *reinterpret_cast<uint2*>(a.sh[peer] + (e - a.shadow_begin)) = pk;
+      }
+    }
+  }
+  reg = warp_sum(reg);
+  if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = reg;
+  __threadfence_system();  // this CTA's peer stores are visible system-wide before it reports completion
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float tot = 0.f;
+    for (int i = 0; i < kArThreads / 32; ++i) tot += s_red[i];
+    if (tot != 0.f) atomicAdd(a.reg_local, tot);
+    __threadfence();
+    s_last = (atomicAdd(a.done_counter, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last) return;
+
+  // ---- last CTA of this rank: publish the L2-loss partial, advance the step, barrier B
+  __threadfence();
+  if (threadIdx.x < W) {
+    const float part = 0.5f * a.l2 * atomicAdd(a.reg_local, 0.f);
+    a.reg_parts[threadIdx.x][a.rank] = part;  // slot [rank] on every peer
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    *a.reg_local = 0.f;
+    *a.done_counter = 0u;
+    *a.step_ptr = t;
+    *a.seq_ptr = seq;
+  }
+  if (threadIdx.x < W) {
+    const int peer = threadIdx.x;
+    uint32_t* bflags_peer = a.flags[peer] + (size_t)kArMaxBlocks * kMaxRanks;
+    const uint32_t* bflags_mine = a.flags[a.rank] + (size_t)kArMaxBlocks * kMaxRanks;
+    st_release_sys(bflags_peer + a.rank, seq);
+    while ((int32_t)(ld_acquire_sys(bflags_mine + peer) - seq) < 0) {
+    }
+  }
+}
+
+}  // namespace dfm
+
+using namespace dfm;
+
+extern "C" {
+
+int dfm_allreduce_opt_flag_words(void) { return kArMaxBlocks * kMaxRanks + kMaxRanks; }
+int dfm_allreduce_opt_max_blocks(void) { return kArMaxBlocks; }
+
+// Pointer tables are host arrays of `world` device pointers (peer-mapped symmetric memory). mc pointers may be NULL
+// (then the P2P path is used). s0/s1: this rank's slot slices. Ranges in elements, multiples of 4.
+int dfm_allreduce_opt_step(void* const* g_ptrs, void* const* p_ptrs, void* const* sh_ptrs, void* const* flag_ptrs,
+                           void* const* reg_ptrs, void* g_mc, void* p_mc, void* sh_mc, float* s0, float* s1, int rank,
+                           int world, long long slice_begin, long long slice_end, int opt, float lr, float beta1,
+                           float beta2, float eps, float momentum, float grad_scale, long long decay_begin,
+                           long long decay_end, float l2, long long shadow_begin, long long shadow_end,
+                           unsigned long long* step_ptr, float* reg_local, unsigned int* done_counter,
+                           unsigned int* seq_ptr, int use_nvls, int grid_blocks, void* stream) {
+  DFM_REQUIRE(world >= 1 && world <= kMaxRanks, "allreduce_opt: world size %d not in [1,%d]", world, kMaxRanks);
+  DFM_REQUIRE(rank >= 0 && rank < world, "allreduce_opt: bad rank");
+  DFM_REQUIRE(slice_begin % 4 == 0 && slice_end % 4 == 0 && slice_end >= slice_begin, "allreduce_opt: bad slice");
+  DFM_REQUIRE(!use_nvls || (g_mc && p_mc && sh_mc), "allreduce_opt: NVLS requested without multicast mappings");
+  ArOptArgs a;
+  for (int r = 0; r < kMaxRanks; ++r) {
+    const int s = r < world ? r : 0;
+    a.g[r] = (float*)g_ptrs[s];
+    a.p[r] = (float*)p_ptrs[s];
+    a.sh[r] = (__nv_bfloat16*)sh_ptrs[s];
+    a.flags[r] = (uint32_t*)flag_ptrs[s];
+    a.reg_parts[r] = (float*)reg_ptrs[s];
+  }
+  a.g_mc = (float*)g_mc; a.p_mc = (float*)p_mc; a.sh_mc = (__nv_bfloat16*)sh_mc;
+  a.s0 = s0; a.s1 = s1; a.rank = rank; a.world = world;
+  a.slice_begin = slice_begin; a.slice_end = slice_end;
+  a.h.opt = opt; a.h.lr = lr; a.h.beta1 = beta1; a.h.beta2 = beta2; a.h.eps = eps; a.h.momentum = momentum;
+  a.grad_scale = grad_scale; a.decay_begin = decay_begin; a.decay_end = decay_end; a.l2 = l2;
+  a.shadow_begin = shadow_begin; a.shadow_end = shadow_end;
+  a.step_ptr = step_ptr; a.reg_local = reg_local; a.done_counter = done_counter; a.seq_ptr = seq_ptr;
+  // the grid must be IDENTICAL on every rank (barrier A pairs CTA b of rank r with CTA b of every peer)
+  DFM_REQUIRE(grid_blocks >= 1 && grid_blocks <= kArMaxBlocks, "allreduce_opt: grid_blocks %d not in [1,%d]",
+              grid_blocks, kArMaxBlocks);
+  const long long blocks = grid_blocks;
+  if (use_nvls)
+    allreduce_opt_kernel<true><<<(unsigned)blocks, kArThreads, 0, (cudaStream_t)stream>>>(a);
+  else
+    allreduce_opt_kernel<false><<<(unsigned)blocks, kArThreads, 0, (cudaStream_t)stream>>>(a);
+  DFM_CHECK(cudaGetLastError());
+  return DFM_OK;
+}
+
+}  // extern "C"

@@ -58,11 +58,10 @@ def pack_batch(ids: torch.Tensor, vals: torch.Tensor, labels: torch.Tensor, pin:
 class FusedDeepFM:
     def __init__(self, cfg: DeepFMConfig, batch_size: int, optimizer: Optional[TF1Optimizer] = None, seed: int = 0,
                  device: Optional[torch.device] = None, params: Optional[Dict[str, torch.Tensor]] = None,
-                 global_batch: Optional[int] = None, row_offset: int = 0, grad_alloc: Optional[Callable] = None,
-                 use_graph: bool = True, input_slots: int = 2):
+                 global_batch: Optional[int] = None, row_offset: int = 0, use_graph: bool = True,
+                 input_slots: int = 2):
         """`global_batch`/`row_offset`: under data parallelism the loss is the mean over the GLOBAL batch and the
-        dropout mask of row r is that of global row row_offset+r, so DP-N is bit-comparable to DP-1.
-        `grad_alloc(numel) -> fp32 tensor`: lets parallel/dp.py place the gradient buffer in symmetric memory."""
+        dropout mask of row r is that of global row row_offset+r, so DP-N is comparable to DP-1."""
         if cfg.batch_norm:
             raise NotImplementedError("batch_norm=True runs on the torch backend (models/torch_backend.py)")
         _native.require_gpu()
@@ -81,12 +80,13 @@ class FusedDeepFM:
         f32 = dict(device=dev, dtype=torch.float32)
 
         # ---- parameters / grads / slots (flat) ------------------------------------------------------------
-        self.P = torch.zeros(L.total_numel, **f32)
-        self.G = grad_alloc(L.total_numel) if grad_alloc else torch.zeros(L.total_numel, **f32)
+        self.P = self._alloc("P", L.total_numel, torch.float32)
+        self.G = self._alloc("G", L.total_numel, torch.float32)
         inits = SLOT_INIT[self.opt.name]
-        self.S0 = torch.full((L.trainable_numel,), inits[0], **f32) if len(inits) > 0 else None
-        self.S1 = torch.full((L.trainable_numel,), inits[1], **f32) if len(inits) > 1 else None
-        self.shadow = torch.zeros(L.shadow_range[1] - L.shadow_range[0], device=dev, dtype=torch.bfloat16)
+        ns = self._slot_numel()
+        self.S0 = self._alloc("S0", ns, torch.float32).fill_(inits[0]) if len(inits) > 0 else None
+        self.S1 = self._alloc("S1", ns, torch.float32).fill_(inits[1]) if len(inits) > 1 else None
+        self.shadow = self._alloc("shadow", L.shadow_range[1] - L.shadow_range[0], torch.bfloat16)
         src = params if params is not None else init_params(cfg, seed)
         for name in L.names():
             L.view(self.P, name).copy_(src[name].to(dev))
@@ -118,11 +118,23 @@ class FusedDeepFM:
         self.auc_thr = torch.from_numpy(thresholds()).to(dev)
         self.auc_hist = torch.zeros(2, NUM_THRESHOLDS + 1, **f32)
 
+        self._side = torch.cuda.Stream(device=dev)
         self._build_plans()
         self._graphs: Dict[int, torch.cuda.CUDAGraph] = {}
-        self._side = torch.cuda.Stream(device=dev)
         self.kernels_per_step = 0
         self.host_step = 0
+
+    # ------------------------------------------------------------------------------------------------ allocation
+    def _alloc(self, name: str, numel: int, dtype) -> torch.Tensor:
+        """Persistent buffer allocation; parallel/dp.py overrides this to place P/G/shadow/slots in symmetric memory."""
+        return torch.zeros(numel, device=self.dev, dtype=dtype)
+
+    def _slot_numel(self) -> int:
+        return self.layout.trainable_numel
+
+    def _pre_step(self, side) -> int:
+        """Hook at the start of a step (runs inside graph capture); returns #kernels it launched."""
+        return 0
 
     # ------------------------------------------------------------------------------------------------ plans
     def _w(self, name):  # fp32 view
@@ -174,7 +186,12 @@ class FusedDeepFM:
         cur = torch.cuda.current_stream()
         n = 0
         self.scalars.zero_()  # loss_sum, reg_loss (one memset node)
+        pre = self._pre_step(self._side)
         n += self._forward(slot, True)
+        if pre:  # join the pre-step branch (e.g. gradient zeroing under data parallelism) before the first grad write
+            evp = torch.cuda.Event()
+            evp.record(self._side)
+            cur.wait_event(evp)
         top = nl - 1
         K.logit_loss(self.acts[top], self._w("deep_out.weight"), self._w("deep_out.bias"), self._w("fm_bias"), self.yfm,
                      slot["labels"], 1.0 / self.global_batch, 1.0 / cfg.dropout[top], True, self.prob, self.logit,

@@ -50,3 +50,212 @@ def broadcast_model(model, src: int = 0, group=None) -> None:
         dist.broadcast(t, src, group=group)
         sd[k] = t
     model.load_state_dict(sd, strict=False)
+
+
+# ------------------------------------------------------------------------------------------------------------
+from ctypes import c_float, c_int, c_longlong, c_void_p  # noqa: E402
+
+from ..models.fused import FusedDeepFM  # noqa: E402
+from ..models.layout import FlatLayout  # noqa: E402
+from ..ops import lib as _nlib  # noqa: E402
+from ..optim.tf1 import OPT_IDS, SLOT_INIT, SLOT_SUFFIXES  # noqa: E402
+
+
+class FusedDataParallel(FusedDeepFM):
+    """FusedDeepFM whose optimizer step is the fused all-reduce + sharded optimizer + all-gather kernel."""
+
+    def __init__(self, cfg, batch_size, optimizer, seed, device, world_size, rank, comm: str = "auto",
+                 use_graph: bool = True, params=None, process_group=None):
+        from .symm import SymmArena
+        self.world, self.rank = world_size, rank
+        self.group = process_group if process_group is not None else dist.group.WORLD
+        self.comm = comm
+        L = FlatLayout(cfg)
+        n = L.trainable_numel
+        chunk = ((n + world_size - 1) // world_size + 1023) // 1024 * 1024
+        self.slice = (min(n, rank * chunk), min(n, (rank + 1) * chunk))
+        self._chunk = chunk
+        self._nccl = comm == "nccl"
+        lib = _nlib.require_gpu()
+        nslots = len(SLOT_INIT[optimizer.name])
+        slot_n = n if self._nccl else chunk
+        regions = [("P", L.total_numel, torch.float32), ("G", L.total_numel, torch.float32),
+                   ("shadow", L.shadow_range[1] - L.shadow_range[0], torch.bfloat16),
+                   ("flags", lib.dfm_allreduce_opt_flag_words(), torch.int32), ("reg_parts", 8, torch.float32)]
+        for i in range(nslots):
+            regions.append(("S%d" % i, slot_n, torch.float32))
+        self.arena = SymmArena(regions, device, self.group)
+        self._slot_n = slot_n
+        super().__init__(cfg, batch_size, optimizer, seed, device, params, global_batch=batch_size * world_size,
+                         row_offset=rank * batch_size, use_graph=use_graph)
+        self.reg_local = torch.zeros(1, device=device, dtype=torch.float32)
+        self.seq = torch.zeros(1, device=device, dtype=torch.int32)
+        self._tables = {k: self.arena.ptr_table(k) for k in ("G", "P", "shadow", "flags", "reg_parts")}
+        use_nvls = (comm == "nvls") or (comm == "auto" and self.arena.mc_ptr != 0 and world_size > 1)
+        if comm == "nvls" and not self.arena.mc_ptr:
+            raise RuntimeError("comm='nvls' requested but no multicast mapping is available on this fabric")
+        self.use_nvls = bool(use_nvls)
+        self.comm_name = "nccl-allreduce+flat_opt (baseline)" if self._nccl else \
+            ("fused-nvls-multimem" if self.use_nvls else "fused-p2p")
+        blocks = (chunk // 4 + 255) // 256
+        self._grid_blocks = max(1, min(lib.dfm_allreduce_opt_max_blocks(), blocks))
+        torch.cuda.synchronize(device)
+        dist.barrier(group=self.group)
+
+    # ---- allocation in symmetric memory
+    def _alloc(self, name, numel, dtype):
+        if name in ("P", "G", "shadow"):
+            return self.arena.view(name)
+        if name in ("S0", "S1"):
+            return self.arena.view(name)
+        return super()._alloc(name, numel, dtype)
+
+    def _slot_numel(self) -> int:
+        return self._slot_n
+
+    def _pre_step(self, side) -> int:
+        # gradients are zeroed on a forked branch that overlaps the forward pass (peers finished reading them at
+        # barrier B of the previous step)
+        cur = torch.cuda.current_stream()
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        side.wait_event(ev)
+        with torch.cuda.stream(side):
+            self.G.zero_()
+        return 1
+
+    def _optimizer_kernels(self) -> int:
+        o, L = self.opt, self.layout
+        if self._nccl:
+            lt = L.trainable_numel
+            dist.all_reduce(self.G[:lt], group=self.group)
+            from ..ops import kernels as K
+            decay = L.decay_range if self.cfg.l2_reg > 0 else (0, 0)
+            K.flat_opt_step(self.P[:lt], self.G[:lt], self.S0, self.S1, o.name, o.lr, o.beta1, o.beta2, o.eps, o.momentum,
+                            1.0, decay, self.cfg.l2_reg, L.shadow_range, self.shadow, self.step_t, self.reg_loss,
+                            self.done_counter)
+            return 1
+        lib = _nlib.load()
+        decay = L.decay_range if self.cfg.l2_reg > 0 else (0, 0)
+        t = self._tables
+        st = c_void_p(torch.cuda.current_stream().cuda_stream)
+        _nlib.check(lib.dfm_allreduce_opt_step(
+            t["G"], t["P"], t["shadow"], t["flags"], t["reg_parts"], c_void_p(self.arena.mc("G")),
+            c_void_p(self.arena.mc("P")), c_void_p(self.arena.mc("shadow")),
+            c_void_p(self.S0.data_ptr() if self.S0 is not None else 0),
+            c_void_p(self.S1.data_ptr() if self.S1 is not None else 0), c_int(self.rank), c_int(self.world),
+            c_longlong(self.slice[0]), c_longlong(self.slice[1]), c_int(OPT_IDS[o.name]), c_float(o.lr), c_float(o.beta1),
+            c_float(o.beta2), c_float(o.eps), c_float(o.momentum), c_float(1.0), c_longlong(decay[0]),
+            c_longlong(decay[1]), c_float(self.cfg.l2_reg), c_longlong(L.shadow_range[0]), c_longlong(L.shadow_range[1]),
+            c_void_p(self.step_t.data_ptr()), c_void_p(self.reg_local.data_ptr()), c_void_p(self.done_counter.data_ptr()),
+            c_void_p(self.seq.data_ptr()), c_int(1 if self.use_nvls else 0), c_int(self._grid_blocks), st))
+        return 1
+
+    def _snapshot(self):
+        snap = super()._snapshot()
+        return snap
+
+    def _restore(self, snap):
+        super()._restore(snap)
+        self.reg_local.zero_()
+        torch.cuda.synchronize()
+        dist.barrier(group=self.group)
+
+    def last_loss(self) -> torch.Tensor:
+        if self._nccl:
+            return super().last_loss()
+        # data loss: each rank holds its local sum -> the global mean needs the other ranks' sums; report the local
+        # estimate scaled to the global batch plus the L2 terms gathered by the kernel (reg_parts from every rank)
+        reg = self.arena.view("reg_parts").sum()
+        torch.add(self.loss_sum * (self.world / self.global_batch), reg, out=self.loss_out)
+        return self.loss_out
+
+    # ---- state: slots are sharded; the chief assembles them through peer-mapped views (no collective needed)
+    def named_slots(self):
+        from collections import OrderedDict
+        if self._nccl:
+            return super().named_slots()
+        L = self.layout
+        n = L.trainable_numel
+        full = []
+        for i in range(len(SLOT_INIT[self.opt.name])):
+            buf = torch.empty(n, device=self.dev, dtype=torch.float32)
+            for r in range(self.world):
+                b, e = min(n, r * self._chunk), min(n, (r + 1) * self._chunk)
+                if e > b:
+                    buf[b:e].copy_(self.arena.peer_view("S%d" % i, r)[: e - b])
+            full.append(buf)
+        out = OrderedDict()
+        for name in L.names(trainable_only=True):
+            out[name] = [L.view(f, name) for f in full]
+        return out
+
+    def load_state_dict(self, sd, strict: bool = True):
+        L = self.layout
+        for name, t in self.named_parameters().items():
+            if name in sd:
+                t.copy_(sd[name].to(self.dev))
+            elif strict:
+                raise KeyError("missing parameter %s" % name)
+        n = L.trainable_numel
+        self._loaded_full = []
+        for i, suffix in enumerate(SLOT_SUFFIXES[self.opt.name]):
+            full = torch.full((n,), SLOT_INIT[self.opt.name][i], device=self.dev, dtype=torch.float32)
+            self._loaded_full.append(full)
+            for name in L.names(trainable_only=True):
+                key = "%s/%s" % (name, suffix)
+                if key in sd:
+                    L.view(full, name).copy_(sd[key].to(self.dev))
+            mine = self.S0 if i == 0 else self.S1
+            if self._nccl:
+                mine.copy_(full)
+            else:
+                b, e = self.slice
+                mine[: e - b].copy_(full[b:e])
+        if "global_step" in sd:
+            self.step_t.copy_(sd["global_step"].to(self.dev).reshape(1))
+            self.opt.step = int(self.step_t.item())
+        self.refresh_shadow()
+        self.G.zero_()
+
+    def broadcast_state(self, src: int = 0):
+        """Initial/restored state from rank `src` to every replica with P2P copies into the peers' mapped buffers
+        (reference: BroadcastGlobalVariablesHook(0), HVD:372 — an NCCL broadcast of ~36 tensors per train() call)."""
+        torch.cuda.synchronize(self.dev)
+        dist.barrier(group=self.group)
+        n = self.layout.trainable_numel
+        if self.rank == src:
+            for r in range(self.world):
+                if r == src:
+                    continue
+                self.arena.peer_view("P", r).copy_(self.P)
+                self.arena.peer_view("shadow", r).copy_(self.shadow)
+        step = self.step_t.clone()
+        dist.broadcast(step, src, group=self.group)
+        self.step_t.copy_(step)
+        self.opt.step = int(step.item())
+        # slot slices: every rank re-derives ITS slice from src's full vector (only src loaded the checkpoint)
+        for i in range(len(SLOT_INIT[self.opt.name])):
+            mine = self.S0 if i == 0 else self.S1
+            if self._nccl:
+                dist.broadcast(mine, src, group=self.group)
+            else:
+                full = torch.empty(n, device=self.dev, dtype=torch.float32)
+                if self.rank == src:
+                    loaded = getattr(self, "_loaded_full", None)
+                    full.copy_(loaded[i] if loaded else self._full_slot_for_broadcast(i))
+                dist.broadcast(full, src, group=self.group)
+                b, e = self.slice
+                mine[: e - b].copy_(full[b:e])
+        self._loaded_full = None
+        torch.cuda.synchronize(self.dev)
+        dist.barrier(group=self.group)
+
+    def _full_slot_for_broadcast(self, i: int) -> torch.Tensor:
+        n = self.layout.trainable_numel
+        buf = torch.empty(n, device=self.dev, dtype=torch.float32)
+        for r in range(self.world):
+            b, e = min(n, r * self._chunk), min(n, (r + 1) * self._chunk)
+            if e > b:
+                buf[b:e].copy_(self.arena.peer_view("S%d" % i, r)[: e - b])
+        return buf

@@ -60,6 +60,21 @@ int dfm_flat_opt_step(float* w, float* g, float* s0, float* s1, long long n, int
                       float* reg_loss, unsigned int* done_counter, void* stream);
 int dfm_cast_f32_bf16(const float* in, void* out_bf16, long long n, void* stream);
 
+/* ---- gradient all-reduce fused with the optimizer step over NVLink peer memory (replaces Horovod's NCCL all-reduce
+ * HVD:262 + ApplyAdam PS:269). Pointer tables: host arrays of `world` device pointers into symmetric memory; *_mc are
+ * NVLS multicast mappings or NULL. Every rank must launch with the same grid_blocks (<= dfm_allreduce_opt_max_blocks()).
+ * flags: dfm_allreduce_opt_flag_words() zero-initialised uint32 per rank; reg_parts: 8 floats per rank; seq_ptr: one
+ * zero-initialised device word per rank (barrier sequence number, advanced by the kernel). */
+int dfm_allreduce_opt_flag_words(void);
+int dfm_allreduce_opt_max_blocks(void);
+int dfm_allreduce_opt_step(void* const* g_ptrs, void* const* p_ptrs, void* const* sh_ptrs, void* const* flag_ptrs,
+                           void* const* reg_ptrs, void* g_mc, void* p_mc, void* sh_mc, float* s0, float* s1, int rank,
+                           int world, long long slice_begin, long long slice_end, int opt, float lr, float beta1,
+                           float beta2, float eps, float momentum, float grad_scale, long long decay_begin,
+                           long long decay_end, float l2, long long shadow_begin, long long shadow_end,
+                           unsigned long long* step_ptr, float* reg_local, unsigned int* done_counter,
+                           unsigned int* seq_ptr, int use_nvls, int grid_blocks, void* stream);
+
 /* ---- flat optimizer step that allocates nothing (no counterpart in the reference: TF owns its own allocator).
  * Same update as dfm_flat_opt_step, but the scratch it needs sits in a static device array inside the library
  * (262,400 bytes per GPU, held until exit) instead of being supplied by the caller. For callers that cannot call
