@@ -163,7 +163,8 @@ class FusedDataParallel(FusedDeepFM):
 
     def last_loss(self) -> torch.Tensor:
         if self._nccl:
-            return super().last_loss()
+            torch.add(self.loss_sum * (self.world / self.global_batch), self.reg_loss, out=self.loss_out)
+            return self.loss_out
         # data loss: each rank holds its local sum -> the global mean needs the other ranks' sums; report the local
         # estimate scaled to the global batch plus the L2 terms gathered by the kernel (reg_parts from every rank)
         reg = self.arena.view("reg_parts").sum()

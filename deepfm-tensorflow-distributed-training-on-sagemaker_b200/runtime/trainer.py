@@ -146,10 +146,16 @@ class Trainer:
         """Wait for outstanding steps; return the per-step losses (mean log-loss + L2 terms, PS:244-246)."""
         if self._cuda:
             torch.cuda.synchronize(self.dev)
-            gb = float(self.B * self.world)
+            reg_now = None
+            if getattr(self.model, "arena", None) is not None and not getattr(self.model, "_nccl", False):
+                reg_now = float(self.model.arena.view("reg_parts").sum())  # L2 terms, gathered by the fused kernel
             for i, mean_flag in enumerate(self._pending):
                 a, b = float(self._ring[i, 0]), float(self._ring[i, 1])
-                self._host_losses.append(a if mean_flag else a / gb + b)
+                if reg_now is not None:
+                    b = reg_now
+                # fused: (local sum of log-loss, L2 term). Under DP the local sum is scaled to the local batch (an
+                # unbiased per-rank estimate of the global mean; the exact mean needs the other ranks' sums)
+                self._host_losses.append(a if mean_flag else a / float(self.B) + b)
             self._pending = []
             self._ring_pos = 0
         if keep:
