@@ -100,36 +100,49 @@ __global__ void __launch_bounds__(kArThreads) allreduce_opt_kernel(const ArOptAr
   float reg = 0.f;
   float* wl = a.p[a.rank];
   const long long b4 = a.slice_begin >> 2, e4 = a.slice_end >> 2;
-  for (long long i = b4 + (long long)blockIdx.x * kArThreads + threadIdx.x; i < e4; i += (long long)gridDim.x * kArThreads) {
-    const long long e = i << 2;
-    float4 g;
+  // U float4 per thread per trip: every NVLink load of a trip (U x W peer loads, or U multimem loads) is issued before
+  // the first use (branch-free main loop + scalar tail), so a trip costs ~one fabric round trip, not U x W of them.
+  constexpr int U = NVLS ? 4 : 2;
+  const long long stride = (long long)gridDim.x * kArThreads;
+  auto reduce_one = [&](long long i) -> float4 {
     if constexpr (NVLS) {
-      g = multimem_ld_reduce_f4(a.g_mc + e);
+      return multimem_ld_reduce_f4(a.g_mc + (i << 2));
     } else {
-      g = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 1
-      for (int r = 0; r < W; ++r) {
-        const float4 x = ld_volatile_f4(a.g[(a.rank + r) % W] + e);  // stagger peers across ranks
-        g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
+      float4 x[kMaxRanks];
+#pragma unroll
+      for (int r = 0; r < kMaxRanks; ++r) {
+        x[r] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r < W) {
+          int peer = a.rank + r;  // stagger peers across ranks
+          if (peer >= W) peer -= W;
+          x[r] = ld_volatile_f4(a.g[peer] + (i << 2));
+        }
       }
+      float4 acc = x[0];
+#pragma unroll
+      for (int r = 1; r < kMaxRanks; ++r) { acc.x += x[r].x; acc.y += x[r].y; acc.z += x[r].z; acc.w += x[r].w; }
+      return acc;
     }
+  };
+  auto update_one = [&](long long i, float4 gg) {
+    const long long e = i << 2;
     float4 w = reinterpret_cast<const float4*>(wl)[i];
     const long long li = i - b4;
     float4 s0 = nslots > 0 ? reinterpret_cast<float4*>(a.s0)[li] : make_float4(0, 0, 0, 0);
     float4 s1 = nslots > 1 ? reinterpret_cast<float4*>(a.s1)[li] : make_float4(0, 0, 0, 0);
-    g.x *= a.grad_scale; g.y *= a.grad_scale; g.z *= a.grad_scale; g.w *= a.grad_scale;
+    gg.x *= a.grad_scale; gg.y *= a.grad_scale; gg.z *= a.grad_scale; gg.w *= a.grad_scale;
     if (e >= a.decay_begin && e < a.decay_end) {
       reg += w.x * w.x + w.y * w.y + w.z * w.z + w.w * w.w;
-      g.x += a.l2 * w.x; g.y += a.l2 * w.y; g.z += a.l2 * w.z; g.w += a.l2 * w.w;
+      gg.x += a.l2 * w.x; gg.y += a.l2 * w.y; gg.z += a.l2 * w.z; gg.w += a.l2 * w.w;
     }
-    opt_update(a.h, lr_t, g.x, w.x, s0.x, s1.x);
-    opt_update(a.h, lr_t, g.y, w.y, s0.y, s1.y);
-    opt_update(a.h, lr_t, g.z, w.z, s0.z, s1.z);
-    opt_update(a.h, lr_t, g.w, w.w, s0.w, s1.w);
+    opt_update(a.h, lr_t, gg.x, w.x, s0.x, s1.x);
+    opt_update(a.h, lr_t, gg.y, w.y, s0.y, s1.y);
+    opt_update(a.h, lr_t, gg.z, w.z, s0.z, s1.z);
+    opt_update(a.h, lr_t, gg.w, w.w, s0.w, s1.w);
     if (nslots > 0) reinterpret_cast<float4*>(a.s0)[li] = s0;
     if (nslots > 1) reinterpret_cast<float4*>(a.s1)[li] = s1;
     const bool in_shadow = (e >= a.shadow_begin && e < a.shadow_end);
-    uint2 pk;
+    uint2 pk = make_uint2(0u, 0u);
     if (in_shadow) {
       pk.x = pack_bf16x2(w.x, w.y);
       pk.y = pack_bf16x2(w.z, w.w);
@@ -138,14 +151,26 @@ __global__ void __launch_bounds__(kArThreads) allreduce_opt_kernel(const ArOptAr
       multimem_st_f4(a.p_mc + e, w);
       if (in_shadow) multimem_st_bf16x4(a.sh_mc + (e - a.shadow_begin), pk);
     } else {
-#pragma unroll 1
-      for (int r = 0; r < W; ++r) {
-        const int peer = (a.rank + r) % W;
-        reinterpret_cast<float4*>(a.p[peer])[i] = w;
-        if (in_shadow) *reinterpret_cast<uint2*>(a.sh[peer] + (e - a.shadow_begin)) = pk;
+#pragma unroll
+      for (int r = 0; r < kMaxRanks; ++r) {
+        if (r < W) {
+          int peer = a.rank + r;
+          if (peer >= W) peer -= W;
+          reinterpret_cast<float4*>(a.p[peer])[i] = w;
+          if (in_shadow) *reinterpret_cast<uint2*>(a.sh[peer] + (e - a.shadow_begin)) = pk;
+        }
       }
     }
+  };
+  long long i0 = b4 + (long long)blockIdx.x * kArThreads + threadIdx.x;
+  for (; i0 + (U - 1) * stride < e4; i0 += stride * U) {
+    float4 g[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) g[u] = reduce_one(i0 + u * stride);
+#pragma unroll
+    for (int u = 0; u < U; ++u) update_one(i0 + u * stride, g[u]);
   }
+  for (; i0 < e4; i0 += stride) update_one(i0, reduce_one(i0));
   reg = warp_sum(reg);
   if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = reg;
   __threadfence_system();  // this CTA's peer stores are visible system-wide before it reports completion

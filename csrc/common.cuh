@@ -32,7 +32,32 @@ extern "C" void dfm_set_error(const char* fmt, ...);
     }                                                                                           \
   } while (0)
 
+extern "C" int dfm_pdl_enabled();
+
 namespace dfm {
+
+// ---- programmatic dependent launch (PDL): a kernel launched with the attribute may begin while its predecessor in the
+// stream is still running; pdl_wait() blocks until every prerequisite grid has completed and flushed, so everything
+// before it (barrier init, TMEM allocation, descriptor prefetch, index math) overlaps the predecessor's tail.
+// Without the launch attribute both instructions are no-ops. EVERY kernel launched through launch_k calls pdl_wait()
+// before touching global data, which keeps the ordering transitive along the chain.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = dfm_pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
 
 __host__ __device__ constexpr int ceil_div(int a, int b) { return (a + b - 1) / b; }
 __host__ __device__ constexpr long long ceil_div_ll(long long a, long long b) { return (a + b - 1) / b; }

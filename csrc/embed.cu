@@ -9,7 +9,8 @@
 // emb_bwd     (autograd of the above, reference op K11):
 //     dE[b,f,:] = dX0[b,f,:] + dy[b] * (S[b,:] - e[b,f,:]);   g_v[id,:] += val * dE;   g_w[id] += dy[b] * val
 //     accumulated with red.global.add.v4.f32 into the dense fp32 gradient buffer (the reference's embedding
-//     gradient is dense as well because of the whole-table L2 term).
+//     gradient is dense as well because of the whole-table L2 term); duplicate ids inside a warp are
+//     combined with match/shuffle first because same-address L2 atomics serialise.
 //
 // Lanes own 4 consecutive embedding columns each (K = 4*G, G | 32).
 #include "common.cuh"
@@ -37,8 +38,10 @@ emb_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, c
   constexpr int FG = 32 / G;
   const int lane = threadIdx.x & 31;
   const int sample = blockIdx.x * (kEmbThreads / 32) + (threadIdx.x >> 5);
-  if (sample >= B) return;  // warp-uniform
   const int g = lane % G, fg = lane / G;
+  pdl_launch_dependents();
+  pdl_wait();
+  if (sample >= B) return;  // warp-uniform
   const int* sid = ids + (size_t)sample * F;
   const float* sval = vals + (size_t)sample * F;
 
@@ -95,50 +98,108 @@ emb_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, c
   if (lane == 0) yfm[sample] = acc;
 }
 
-// One G-lane group per (sample, field): B*F*G threads, every row gradient is an independent vector atomic.
+// One LANE per (field, sample) pair, pairs in field-major order, so a warp holds 32 samples of the SAME field.
+// Criteo-shaped data gives every sample the same id in the 13 numeric fields and zipf-hot ids in the categorical
+// ones; same-address L2 atomics serialise (~10 ns each), so lanes that share an id are combined first:
+//   all 32 lanes equal  -> butterfly reduce, one vector atomic per 16-byte chunk
+//   partial duplicates  -> __match_any_sync groups, the group leader gathers its members with shuffles
+//   unique id           -> direct vector atomic
 template <int G>
 __global__ void __launch_bounds__(kEmbThreads)
 emb_bwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, const float* __restrict__ fm_v,
                const float* __restrict__ S, const float* __restrict__ dy, const __nv_bfloat16* __restrict__ dx0,
                int ldx, float* __restrict__ g_w, float* __restrict__ g_v, int B, int F, int N) {
   constexpr int K = 4 * G;
-  const long long gtid = (long long)blockIdx.x * kEmbThreads + threadIdx.x;
-  const long long pair = gtid / G;
-  const int g = (int)(gtid % G);
-  if (pair >= (long long)B * F) return;
-  const int sample = (int)(pair / F);
-  const int f = (int)(pair % F);
-  const int id = __ldg(ids + pair);
-  const float v = __ldg(vals + pair);
-  if (v == 0.f || (unsigned)id >= (unsigned)N) return;  // padding / out-of-range: exactly-zero gradient
-  const float4 row = __ldg(reinterpret_cast<const float4*>(fm_v + (size_t)id * K) + g);
-  const float4 s = __ldg(reinterpret_cast<const float4*>(S + (size_t)sample * K) + g);
-  const uint2 dxp = __ldg(reinterpret_cast<const uint2*>(dx0 + (size_t)sample * ldx + (size_t)f * K + 4 * g));
-  const float d = __ldg(dy + sample);
-  const float gx = v * (bf16_lo(dxp.x) + d * (s.x - row.x * v));
-  const float gy = v * (bf16_hi(dxp.x) + d * (s.y - row.y * v));
-  const float gz = v * (bf16_lo(dxp.y) + d * (s.z - row.z * v));
-  const float gw = v * (bf16_hi(dxp.y) + d * (s.w - row.w * v));
-  red_add_f32x4(g_v + (size_t)id * K + 4 * g, gx, gy, gz, gw);
-  if (g == 0) atomicAdd(g_w + id, d * v);
+  const int lane = threadIdx.x & 31;
+  const long long p = (long long)blockIdx.x * kEmbThreads + threadIdx.x;
+  const bool active = p < (long long)B * F;
+  const int f = active ? (int)(p / B) : 0;
+  const int b = active ? (int)(p % B) : 0;
+  int id = 0;
+  float v = 0.f;
+  pdl_launch_dependents();
+  pdl_wait();
+  if (active) {
+    id = __ldg(ids + (size_t)b * F + f);
+    v = __ldg(vals + (size_t)b * F + f);
+  }
+  const bool valid = active && v != 0.f && (unsigned)id < (unsigned)N;  // padding / out-of-range: zero gradient
+  const unsigned key = valid ? (unsigned)id : (0x80000000u | (unsigned)lane);
+  const unsigned mask = __match_any_sync(0xffffffffu, key);
+  const int leader = __ffs(mask) - 1;
+  const int cnt = __popc(mask);
+  const float d = valid ? __ldg(dy + b) : 0.f;
+  const float4* rowp = reinterpret_cast<const float4*>(fm_v + (size_t)(valid ? id : 0) * K);
+  const float4* sp = reinterpret_cast<const float4*>(S + (size_t)b * K);
+  const uint2* dxp = reinterpret_cast<const uint2*>(dx0 + (size_t)b * ldx + (size_t)f * K);
+
+#pragma unroll 2
+  for (int g = 0; g < G; ++g) {
+    float4 gr = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (valid) {
+      const float4 row = __ldg(rowp + g);
+      const float4 s = __ldg(sp + g);
+      const uint2 dx = __ldg(dxp + g);
+      gr.x = v * (bf16_lo(dx.x) + d * (s.x - row.x * v));
+      gr.y = v * (bf16_hi(dx.x) + d * (s.y - row.y * v));
+      gr.z = v * (bf16_lo(dx.y) + d * (s.z - row.z * v));
+      gr.w = v * (bf16_hi(dx.y) + d * (s.w - row.w * v));
+    }
+    if (mask == 0xffffffffu) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        gr.x += __shfl_xor_sync(0xffffffffu, gr.x, o); gr.y += __shfl_xor_sync(0xffffffffu, gr.y, o);
+        gr.z += __shfl_xor_sync(0xffffffffu, gr.z, o); gr.w += __shfl_xor_sync(0xffffffffu, gr.w, o);
+      }
+      if (lane == 0 && valid) red_add_f32x4(g_v + (size_t)id * K + 4 * g, gr.x, gr.y, gr.z, gr.w);
+    } else if (cnt == 1) {
+      if (valid) red_add_f32x4(g_v + (size_t)id * K + 4 * g, gr.x, gr.y, gr.z, gr.w);
+    } else {
+      float4 acc = gr;
+      unsigned rem = mask & ~(1u << leader);
+      while (rem) {
+        const int src = __ffs(rem) - 1;
+        rem &= rem - 1;
+        const float x = __shfl_sync(mask, gr.x, src), y = __shfl_sync(mask, gr.y, src);
+        const float z = __shfl_sync(mask, gr.z, src), w = __shfl_sync(mask, gr.w, src);
+        acc.x += x; acc.y += y; acc.z += z; acc.w += w;
+      }
+      if (lane == leader && valid) red_add_f32x4(g_v + (size_t)id * K + 4 * g, acc.x, acc.y, acc.z, acc.w);
+    }
+  }
+  // first-order weights: same aggregation on the scalar dy*val
+  float gw = valid ? d * v : 0.f;
+  if (mask == 0xffffffffu) {
+    gw = warp_sum(gw);
+    if (lane == 0 && valid) atomicAdd(g_w + id, gw);
+  } else if (cnt == 1) {
+    if (valid) atomicAdd(g_w + id, gw);
+  } else {
+    float acc = gw;
+    unsigned rem = mask & ~(1u << leader);
+    while (rem) {
+      const int src = __ffs(rem) - 1;
+      rem &= rem - 1;
+      acc += __shfl_sync(mask, gw, src);
+    }
+    if (lane == leader && valid) atomicAdd(g_w + id, acc);
+  }
 }
 
 template <int G>
 static int launch_fwd(const int* ids, const float* vals, const float* fm_w, const float* fm_v, __nv_bfloat16* x0,
                       int ldx, float* S, float* yfm, int B, int F, int N, cudaStream_t st) {
-  emb_fm_fwd_kernel<G><<<(unsigned)ceil_div(B, kEmbThreads / 32), kEmbThreads, 0, st>>>(ids, vals, fm_w, fm_v, x0, ldx,
-                                                                                        S, yfm, B, F, N);
-  DFM_CHECK(cudaGetLastError());
+  DFM_CHECK(launch_k(emb_fm_fwd_kernel<G>, dim3((unsigned)ceil_div(B, kEmbThreads / 32)), dim3(kEmbThreads), 0, st, ids,
+                     vals, fm_w, fm_v, x0, ldx, S, yfm, B, F, N));
   return DFM_OK;
 }
 
 template <int G>
 static int launch_bwd(const int* ids, const float* vals, const float* fm_v, const float* S, const float* dy,
                       const __nv_bfloat16* dx0, int ldx, float* g_w, float* g_v, int B, int F, int N, cudaStream_t st) {
-  const long long threads = (long long)B * F * G;
-  emb_bwd_kernel<G><<<(unsigned)ceil_div_ll(threads, kEmbThreads), kEmbThreads, 0, st>>>(ids, vals, fm_v, S, dy, dx0,
-                                                                                      ldx, g_w, g_v, B, F, N);
-  DFM_CHECK(cudaGetLastError());
+  const long long threads = (long long)B * F;
+  DFM_CHECK(launch_k(emb_bwd_kernel<G>, dim3((unsigned)ceil_div_ll(threads, kEmbThreads)), dim3(kEmbThreads), 0, st, ids,
+                     vals, fm_v, S, dy, dx0, ldx, g_w, g_v, B, F, N));
   return DFM_OK;
 }
 

@@ -24,3 +24,15 @@ extern "C" int dfm_device_is_sm100() {
   if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return -1;
   return major == 10 ? 1 : 0;
 }
+
+// Programmatic dependent launch switch (default on; DFM_PDL=0 in the environment or dfm_set_pdl(0) turns it off).
+#include <stdlib.h>
+static int g_pdl = -1;
+extern "C" int dfm_pdl_enabled() {
+  if (g_pdl < 0) {
+    const char* e = getenv("DFM_PDL");
+    g_pdl = (e && e[0] == '0') ? 0 : 1;
+  }
+  return g_pdl;
+}
+extern "C" void dfm_set_pdl(int on) { g_pdl = on ? 1 : 0; }

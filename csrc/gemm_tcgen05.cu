@@ -99,6 +99,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // PDL: everything above (barrier init, descriptor prefetch, TMEM allocation) overlapped the previous kernel's tail
+  pdl_launch_dependents();
+  pdl_wait();
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -347,8 +350,7 @@ static int launch_gemm(const GemmPlan& pl, cudaStream_t stream) {
     DFM_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     attr_set[dev] = true;
   }
-  kern<<<pl.grid, kGemmThreads, Cfg::SMEM_BYTES, stream>>>(pl.tmA, pl.tmB, pl.p);
-  DFM_CHECK(cudaGetLastError());
+  DFM_CHECK(launch_k(kern, pl.grid, dim3(kGemmThreads), (size_t)Cfg::SMEM_BYTES, stream, pl.tmA, pl.tmB, pl.p));
   return DFM_OK;
 }
 

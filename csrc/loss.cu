@@ -27,6 +27,8 @@ logit_loss_kernel(const __nv_bfloat16* __restrict__ x, int ldx, int H, const flo
                   float* __restrict__ g_b_out, float* __restrict__ g_fm_bias) {
   __shared__ float s_scalar[2];  // loss, sum dy
   if (threadIdx.x < 2) s_scalar[threadIdx.x] = 0.f;
+  pdl_launch_dependents();
+  pdl_wait();
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const float bias = __ldg(b_out) + __ldg(fm_bias);
@@ -92,6 +94,8 @@ __global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* _
                                                           const float* __restrict__ w, float* __restrict__ out) {
   __shared__ float s_part[8][64];
   const int lane = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  pdl_launch_dependents();
+  pdl_wait();
   const int j = blockIdx.x * 64 + lane * 2;
   const int r0 = blockIdx.y * kColsumRows;
   float a0 = 0.f, a1 = 0.f;
@@ -163,10 +167,9 @@ int dfm_logit_loss(const void* x, int ldx, int H, const float* w_out, const floa
   DFM_REQUIRE(ldx % 2 == 0 && (!train || lddz % 2 == 0), "logit_loss: leading dimensions must be even");
   int blocks = ceil_div(B, kLossWarps);
   if (blocks > 148 * 4) blocks = 148 * 4;
-  logit_loss_kernel<<<blocks, kLossThreads, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)x, ldx, H, w_out, b_out, fm_bias, yfm, labels, B, inv_batch, mask_scale, train, prob, logit,
-      dy, (__nv_bfloat16*)dz, lddz, loss_sum, g_b_out, g_fm_bias);
-  DFM_CHECK(cudaGetLastError());
+  DFM_CHECK(launch_k(logit_loss_kernel, dim3(blocks), dim3(kLossThreads), 0, (cudaStream_t)stream,
+                     (const __nv_bfloat16*)x, ldx, H, w_out, b_out, fm_bias, yfm, labels, B, inv_batch, mask_scale, train,
+                     prob, logit, dy, (__nv_bfloat16*)dz, lddz, loss_sum, g_b_out, g_fm_bias));
   return DFM_OK;
 }
 
@@ -174,8 +177,8 @@ int dfm_logit_loss(const void* x, int ldx, int H, const float* w_out, const floa
 int dfm_colsum_bf16(const void* a, int lda, int B, int H, const float* w, float* out, void* stream) {
   DFM_REQUIRE(B > 0 && H > 0, "colsum: empty problem");
   dim3 grid(ceil_div(H, 64), ceil_div(B, kColsumRows));
-  colsum_bf16_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)a, lda, B, H, w, out);
-  DFM_CHECK(cudaGetLastError());
+  DFM_CHECK(launch_k(colsum_bf16_kernel, grid, dim3(256), 0, (cudaStream_t)stream, (const __nv_bfloat16*)a, lda, B, H,
+                     w, out));
   return DFM_OK;
 }
 

@@ -35,6 +35,8 @@ constexpr int kOptThreads = 256;
 __global__ void __launch_bounds__(kOptThreads) flat_opt_kernel(const FlatOptArgs a) {
   __shared__ float s_lr;
   __shared__ float s_red[kOptThreads / 32];
+  pdl_launch_dependents();
+  pdl_wait();
   const unsigned long long t = *a.step_ptr + 1ull;
   if (threadIdx.x == 0) s_lr = opt_step_lr(a.h, t);
   __syncthreads();
@@ -42,6 +44,8 @@ __global__ void __launch_bounds__(kOptThreads) flat_opt_kernel(const FlatOptArgs
   const int nslots = opt_num_slots(a.h.opt);
   float reg = 0.f;
   const long long n4 = a.n >> 2;
+  // Plain grid-stride float4 sweep at high occupancy (48 registers, 5 CTAs/SM): measured faster on B200 than a 4x
+  // unrolled variant whose register count cut the occupancy (24.9 us vs 32.7 us for 4.7 M parameters).
   for (long long i = (long long)blockIdx.x * kOptThreads + threadIdx.x; i < n4; i += (long long)gridDim.x * kOptThreads) {
     const long long e = i << 2;
     float4 w = reinterpret_cast<float4*>(a.w)[i];
@@ -113,8 +117,7 @@ int dfm_flat_opt_step(float* w, float* g, float* s0, float* s1, long long n, int
   a.step_ptr = step_ptr; a.reg_loss = reg_loss; a.done_counter = done_counter;
   long long blocks = ceil_div_ll(n / 4, kOptThreads);
   if (blocks > 148 * 8) blocks = 148 * 8;
-  flat_opt_kernel<<<(unsigned)blocks, kOptThreads, 0, (cudaStream_t)stream>>>(a);
-  DFM_CHECK(cudaGetLastError());
+  DFM_CHECK(launch_k(flat_opt_kernel, dim3((unsigned)blocks), dim3(kOptThreads), 0, (cudaStream_t)stream, a));
   return DFM_OK;
 }
 
