@@ -72,7 +72,7 @@ class FusedDeepFM:
         self.dev = device or torch.device("cuda", torch.cuda.current_device())
         self.opt = optimizer or TF1Optimizer("Adam", 5e-4)
         self.seed = int(seed)
-        self.layout = FlatLayout(cfg)
+        self.layout = self._make_layout(cfg)
         self.use_graph = use_graph
         L = self.layout
         F_, Kd = cfg.field_size, cfg.embedding_size
@@ -87,9 +87,10 @@ class FusedDeepFM:
         self.S0 = self._alloc("S0", ns, torch.float32).fill_(inits[0]) if len(inits) > 0 else None
         self.S1 = self._alloc("S1", ns, torch.float32).fill_(inits[1]) if len(inits) > 1 else None
         self.shadow = self._alloc("shadow", L.shadow_range[1] - L.shadow_range[0], torch.bfloat16)
-        src = params if params is not None else init_params(cfg, seed)
+        src = params if params is not None else self._default_params(cfg, seed)
         for name in L.names():
             L.view(self.P, name).copy_(src[name].to(dev))
+        self._init_params_src = src
         self.refresh_shadow()
 
         # ---- scalars ---------------------------------------------------------------------------------------
@@ -125,6 +126,12 @@ class FusedDeepFM:
         self.host_step = 0
 
     # ------------------------------------------------------------------------------------------------ allocation
+    def _make_layout(self, cfg) -> FlatLayout:
+        return FlatLayout(cfg)
+
+    def _default_params(self, cfg, seed):
+        return init_params(cfg, seed)
+
     def _alloc(self, name: str, numel: int, dtype) -> torch.Tensor:
         """Persistent buffer allocation; parallel/dp.py overrides this to place P/G/shadow/slots in symmetric memory."""
         return torch.zeros(numel, device=self.dev, dtype=dtype)
@@ -173,9 +180,17 @@ class FusedDeepFM:
         K.cast_f32_bf16(self.P[a:b], self.shadow)
 
     # ------------------------------------------------------------------------------------------------ kernels
+    def _emb_forward(self, slot) -> None:
+        K.emb_fm_fwd(slot["ids"], slot["vals"], self._w("fm_w"), self._w("fm_v"), self.x0, self.Ssum, self.yfm)
+
+    def _emb_backward(self, slot) -> int:
+        K.emb_bwd(slot["ids"], slot["vals"], self._w("fm_v"), self.Ssum, self.dy, self.dx0, self._g("fm_w"),
+                  self._g("fm_v"))
+        return 1
+
     def _forward(self, slot, train: bool, rows: Optional[int] = None):
         cfg = self.cfg
-        K.emb_fm_fwd(slot["ids"], slot["vals"], self._w("fm_w"), self._w("fm_v"), self.x0, self.Ssum, self.yfm)
+        self._emb_forward(slot)
         for p in (self.fwd_train if train else self.fwd_eval):
             p.run()
         return 1 + self.n_layers
@@ -212,9 +227,7 @@ class FusedDeepFM:
                     n += 1
             self.dgrad[i].run()
             n += 1
-        K.emb_bwd(slot["ids"], slot["vals"], self._w("fm_v"), self.Ssum, self.dy, self.dx0, self._g("fm_w"),
-                  self._g("fm_v"))
-        n += 1
+        n += self._emb_backward(slot)
         ev = torch.cuda.Event()
         ev.record(side)
         cur.wait_event(ev)  # join
@@ -332,6 +345,8 @@ class FusedDeepFM:
         return self.loss_sum.clone(), self.prob[:n]
 
     def l2_penalty(self) -> torch.Tensor:
+        if not self.layout.include_embeddings:
+            return torch.zeros((), device=self.dev)
         return 0.5 * self.cfg.l2_reg * (self._w("fm_w").pow(2).sum() + self._w("fm_v").pow(2).sum())
 
     # ------------------------------------------------------------------------------------------------ state

@@ -35,8 +35,11 @@ class Segment:
 
 
 class FlatLayout:
-    def __init__(self, cfg: DeepFMConfig):
+    def __init__(self, cfg: DeepFMConfig, include_embeddings: bool = True):
+        """`include_embeddings=False`: fm_w / fm_v live elsewhere (row-sharded tables, parameter server); the flat
+        buffer then holds fm_bias and the MLP only and the decay range is empty."""
         self.cfg = cfg
+        self.include_embeddings = include_embeddings
         segs: "OrderedDict[str, Segment]" = OrderedDict()
         off = 0
 
@@ -49,9 +52,12 @@ class FlatLayout:
             off = _al(off + n)
 
         add("fm_bias", (1,))
-        add("fm_w", (cfg.feature_size,))
-        add("fm_v", (cfg.feature_size, cfg.embedding_size))
-        self.decay_range = (segs["fm_w"].offset, off)
+        if include_embeddings:
+            add("fm_w", (cfg.feature_size,))
+            add("fm_v", (cfg.feature_size, cfg.embedding_size))
+            self.decay_range = (segs["fm_w"].offset, off)
+        else:
+            self.decay_range = (0, 0)
         d = cfg.deep_input_dim
         shadow_begin = off
         for i, h in enumerate(cfg.deep_layers):

@@ -70,7 +70,7 @@ class FusedDataParallel(FusedDeepFM):
         self.world, self.rank = world_size, rank
         self.group = process_group if process_group is not None else dist.group.WORLD
         self.comm = comm
-        L = FlatLayout(cfg)
+        L = self._make_layout(cfg)
         n = L.trainable_numel
         chunk = ((n + world_size - 1) // world_size + 1023) // 1024 * 1024
         self.slice = (min(n, rank * chunk), min(n, (rank + 1) * chunk))

@@ -1,0 +1,202 @@
+"""Row-sharded embedding tables with fused all-to-all kernels (BASELINE.json configs 3 and 5).
+
+The reference keeps both FM tables whole on every GPU (HVD) or whole on one parameter server (PS) and only *advises*
+partitioning (`fixed_size_partitioner`, PDF p32; "borrow another GPU's memory", PDF p27). Here fm_w / fm_v are split by
+row across the W GPUs of the box (row id -> rank id % W, local row id // W) while the MLP stays data parallel through
+the fused all-reduce + optimizer kernel (parallel/dp.py). The three kernels in csrc/sharded.cu do the embedding
+all-to-all *inside* the gather / gradient kernels over symmetric memory — see that file's header.
+
+Optimizer semantics for the tables: touched rows only ("lazy"; `l2_mode='touched'`), which is TF's exact sparse rule for
+Adagrad / GD / FTRL and the LazyAdam variant for Adam / Momentum (TF-1's own sparse Adam still sweeps the whole table
+every step — unaffordable at 33 M x 64).
+"""
+from __future__ import annotations
+
+from collections import OrderedDict
+from ctypes import c_float, c_int, c_longlong, c_void_p
+from typing import Dict, Optional
+
+import math
+
+import torch
+import torch.distributed as dist
+
+from ..models.layout import FlatLayout
+from ..ops import lib as _nlib
+from ..optim.tf1 import OPT_IDS, SLOT_INIT, SLOT_SUFFIXES
+from .dp import FusedDataParallel
+from .symm import SymmArena
+
+
+class ShardedDeepFM(FusedDataParallel):
+    def __init__(self, cfg, batch_size, optimizer, seed, device, world_size, rank, comm: str = "auto",
+                 use_graph: bool = True, params: Optional[Dict[str, torch.Tensor]] = None, process_group=None):
+        self._table_src = params
+        N, K = cfg.feature_size, cfg.embedding_size
+        self.rows_local = (N + world_size - 1) // world_size
+        self._tables_ready = False
+        super().__init__(cfg, batch_size, optimizer, seed, device, world_size, rank, comm, use_graph, params,
+                         process_group)
+        lib = _nlib.load()
+        R = self.rows_local
+        self.words = (R + 31) // 32
+        regions = [("V", R * K, torch.float32), ("W", R, torch.float32), ("GV", R * K, torch.float32),
+                   ("GW", R, torch.float32), ("bitmap", self.words, torch.int32),
+                   ("flags", lib.dfm_sharded_flag_words(), torch.int32)]
+        self.tarena = SymmArena(regions, device, self.group)
+        self.V = self.tarena.view("V").view(R, K)
+        self.Wt = self.tarena.view("W")
+        self.GV = self.tarena.view("GV").view(R, K)
+        self.GW = self.tarena.view("GW")
+        self.bitmap = self.tarena.view("bitmap")
+        inits = SLOT_INIT[self.opt.name]
+        f32 = dict(device=device, dtype=torch.float32)
+        self.VS = [torch.full((R, K), v, **f32) for v in inits]
+        self.WS = [torch.full((R,), v, **f32) for v in inits]
+        self._init_tables(seed)
+        self._t = {k: self.tarena.ptr_table(k) for k in ("V", "W", "GV", "GW", "bitmap", "flags")}
+        self.sh_seq = torch.zeros(1, device=device, dtype=torch.int32)
+        self.sh_done = torch.zeros(1, device=device, dtype=torch.int32)
+        self.e32 = torch.zeros(self.B, cfg.field_size * K, **f32)
+        self._fwd_blocks = max(1, min(1184, (self.B + 7) // 8))
+        self._opt_blocks = max(1, min(1184, (self.words + 7) // 8))
+        self.comm_name = "sharded-embeddings fused-a2a (P2P) + " + self.comm_name
+        self._tables_ready = True
+        torch.cuda.synchronize(device)
+        dist.barrier(group=self.group)
+
+    # ---- layout without the tables
+    def _make_layout(self, cfg):
+        return FlatLayout(cfg, include_embeddings=False)
+
+    def _default_params(self, cfg, seed):
+        from ..models.params import native_names
+        from ..models.init import xavier_uniform_
+        gen = torch.Generator().manual_seed(seed)
+        p = OrderedDict()
+        for name, shape, _ in native_names(cfg):
+            if name in ("fm_w", "fm_v"):
+                continue
+            t = torch.zeros(shape)
+            if name.endswith(".weight"):
+                xavier_uniform_(t, shape[0] if name.startswith("deep_out") else shape[1],
+                                1 if name.startswith("deep_out") else shape[0], gen)
+            p[name] = t
+        return p
+
+    def _init_tables(self, seed):
+        cfg, W, r = self.cfg, self.world, self.rank
+        N, K = cfg.feature_size, cfg.embedding_size
+        src = self._table_src
+        n_mine = len(range(r, N, W))
+        if src is not None and "fm_v" in src:
+            self.V[:n_mine].copy_(src["fm_v"][r::W].to(self.dev))
+            self.Wt[:n_mine].copy_(src["fm_w"][r::W].to(self.dev))
+        else:  # shard-local glorot-normal (2-sigma clamp instead of resampling: tables this large are never compared)
+            g = torch.Generator(device=self.dev).manual_seed(seed * 1000 + r)
+            std_v = math.sqrt(1.0 / ((N + K) / 2.0)) / 0.87962566103423978
+            std_w = math.sqrt(1.0 / N) / 0.87962566103423978
+            self.V.normal_(0, std_v, generator=g).clamp_(-2 * std_v, 2 * std_v)
+            self.Wt.normal_(0, std_w, generator=g).clamp_(-2 * std_w, 2 * std_w)
+        self.GV.zero_(); self.GW.zero_(); self.bitmap.zero_()
+
+    # ---- embedding kernels with the all-to-all fused in
+    def _emb_forward(self, slot) -> None:
+        cfg, t = self.cfg, self._t
+        _nlib.check(_nlib.load().dfm_emb_fm_fwd_a2a(
+            t["V"], t["W"], t["GV"], t["GW"], t["bitmap"], t["flags"], c_int(self.rank), c_int(self.world),
+            c_void_p(slot["ids"].data_ptr()), c_void_p(slot["vals"].data_ptr()), c_void_p(self.x0.data_ptr()),
+            c_void_p(self.e32.data_ptr()), c_int(self.x0.stride(0)), c_void_p(self.Ssum.data_ptr()),
+            c_void_p(self.yfm.data_ptr()), c_int(self.B), c_int(cfg.field_size), c_int(cfg.embedding_size),
+            c_longlong(cfg.feature_size), c_void_p(self.sh_seq.data_ptr()), c_int(self._fwd_blocks),
+            c_void_p(torch.cuda.current_stream().cuda_stream)))
+
+    def _emb_backward(self, slot) -> int:
+        cfg, t, o = self.cfg, self._t, self.opt
+        lib = _nlib.load()
+        st = c_void_p(torch.cuda.current_stream().cuda_stream)
+        _nlib.check(lib.dfm_emb_bwd_a2a(
+            t["V"], t["W"], t["GV"], t["GW"], t["bitmap"], t["flags"], c_int(self.rank), c_int(self.world),
+            c_void_p(slot["ids"].data_ptr()), c_void_p(slot["vals"].data_ptr()), c_void_p(self.e32.data_ptr()),
+            c_void_p(self.Ssum.data_ptr()), c_void_p(self.dy.data_ptr()), c_void_p(self.dx0.data_ptr()),
+            c_int(self.dx0.stride(0)), c_int(self.B), c_int(cfg.field_size), c_int(cfg.embedding_size),
+            c_longlong(cfg.feature_size), st))
+        p = lambda x: c_void_p(x.data_ptr())
+        z = c_void_p(0)
+        _nlib.check(lib.dfm_sparse_row_opt(
+            t["V"], t["W"], t["GV"], t["GW"], t["bitmap"], t["flags"], c_int(self.rank), c_int(self.world),
+            p(self.VS[0]) if len(self.VS) > 0 else z, p(self.VS[1]) if len(self.VS) > 1 else z,
+            p(self.WS[0]) if len(self.WS) > 0 else z, p(self.WS[1]) if len(self.WS) > 1 else z,
+            c_longlong(self.rows_local), c_int(cfg.embedding_size), c_int(OPT_IDS[o.name]), c_float(o.lr),
+            c_float(o.beta1), c_float(o.beta2), c_float(o.eps), c_float(o.momentum), c_float(cfg.l2_reg),
+            p(self.step_t), c_int(1), p(self.sh_seq), p(self.sh_done), p(self.reg_loss), c_int(self._opt_blocks), st))
+        return 2
+
+    def _snapshot(self):
+        snap = super()._snapshot()
+        self._tsnap = [self.V.clone(), self.Wt.clone()] + [t.clone() for t in self.VS + self.WS]
+        return snap
+
+    def _restore(self, snap):
+        torch.cuda.synchronize()
+        dist.barrier(group=self.group)
+        for dst, src in zip([self.V, self.Wt] + self.VS + self.WS, self._tsnap):
+            dst.copy_(src)
+        self.GV.zero_(); self.GW.zero_(); self.bitmap.zero_()
+        self._tsnap = None
+        super()._restore(snap)
+
+    def last_loss(self) -> torch.Tensor:
+        reg = self.reg_loss.clone()  # touched-row L2 terms of THIS rank's shard
+        torch.add(self.loss_sum * (self.world / self.global_batch), reg[0] + self.arena.view("reg_parts").sum(),
+                  out=self.loss_out)
+        return self.loss_out
+
+    # ---- state: the chief assembles full tables through peer-mapped views
+    def _gather_table(self, name: str, cols: int) -> torch.Tensor:
+        N, W = self.cfg.feature_size, self.world
+        full = torch.empty((N, cols) if cols > 1 else (N,), device=self.dev, dtype=torch.float32)
+        for r in range(W):
+            n_r = len(range(r, N, W))
+            pv = self.tarena.peer_view(name, r)
+            full[r::W] = pv[: n_r * cols].view(n_r, cols) if cols > 1 else pv[:n_r]
+        return full
+
+    def named_parameters(self):
+        out = OrderedDict()
+        flat = super().named_parameters()
+        out["fm_bias"] = flat["fm_bias"]
+        out["fm_w"] = self._gather_table("W", 1)
+        out["fm_v"] = self._gather_table("V", self.cfg.embedding_size)
+        for k, v in flat.items():
+            if k != "fm_bias":
+                out[k] = v
+        return out
+
+    def state_dict(self):
+        sd = super().state_dict()  # flat (MLP) parameters + slots + step; tables via named_parameters above
+        # table slots stay rank-local in this version (they are re-created at init_value on load)
+        return sd
+
+    def load_state_dict(self, sd, strict: bool = True):
+        W, r, N = self.world, self.rank, self.cfg.feature_size
+        n_mine = len(range(r, N, W))
+        if "fm_v" in sd:
+            self.V[:n_mine].copy_(sd["fm_v"][r::W].to(self.dev))
+        if "fm_w" in sd:
+            self.Wt[:n_mine].copy_(sd["fm_w"][r::W].to(self.dev))
+        sub = {k: v for k, v in sd.items() if not k.startswith(("fm_v", "fm_w"))}
+        super().load_state_dict(sub, strict=False)
+
+    def broadcast_state(self, src: int = 0):
+        super().broadcast_state(src)
+        # tables: every rank needs ITS rows of src's full table; src pushes them through the peer mappings
+        N, W, K = self.cfg.feature_size, self.world, self.cfg.embedding_size
+        if getattr(self, "_loaded_tables", None) is not None and self.rank == src:
+            fv, fw = self._loaded_tables
+            for r in range(W):
+                n_r = len(range(r, N, W))
+                self.tarena.peer_view("V", r)[: n_r * K].copy_(fv[r::W].reshape(-1).to(self.dev))
+                self.tarena.peer_view("W", r)[:n_r].copy_(fw[r::W].to(self.dev))
+        torch.cuda.synchronize(self.dev)
+        dist.barrier(group=self.group)

@@ -33,15 +33,12 @@ class Estimator:
         self.shared_model_dir = model_dir
         self.out = out
         self.strategy = strategy
-        if strategy == "sharded" and self.env.world_size > 1:
-            from ..parallel.sharded import ShardedTrainer
-            self.trainer = ShardedTrainer(cfg, batch_size, optimizer, seed, self.env)
-        elif strategy == "ps":
+        if strategy == "ps":
             from ..parallel.ps import AsyncPSTrainer
             self.trainer = AsyncPSTrainer(cfg, batch_size, optimizer, seed, self.env, backend=backend)
         else:
             self.trainer = Trainer(cfg, batch_size, optimizer, seed, self.env.device, backend, self.env.world_size,
-                                   self.env.rank, comm=comm)
+                                   self.env.rank, comm=comm, strategy=strategy)
         gb = batch_size * self.env.world_size
         mf = metrics_file or (os.path.join(model_dir, "metrics.jsonl") if model_dir else None)
         self.log = LoggingHook(log_steps, gb, mf if self.env.is_chief else None, out, enabled=self.env.is_chief)

@@ -25,7 +25,8 @@ from ..utils.auc import StreamingAUC, auc_from_hist
 class Trainer:
     def __init__(self, cfg: DeepFMConfig, batch_size: int, optimizer: Optional[TF1Optimizer] = None, seed: int = 0,
                  device=None, backend: str = "auto", world_size: int = 1, rank: int = 0, use_graph: bool = True,
-                 comm: str = "auto", params: Optional[Dict[str, torch.Tensor]] = None, process_group=None):
+                 comm: str = "auto", params: Optional[Dict[str, torch.Tensor]] = None, process_group=None,
+                 strategy: str = "dp"):
         self.cfg, self.B = cfg, batch_size
         self.world, self.rank = world_size, rank
         self.opt = optimizer or TF1Optimizer("Adam", 5e-4)
@@ -37,7 +38,13 @@ class Trainer:
         ro = rank * batch_size
         if backend == "fused":
             self.dev = device or torch.device("cuda", torch.cuda.current_device())
-            if world_size > 1:
+            if strategy == "sharded":
+                from ..parallel.sharded import ShardedDeepFM
+                self._ensure_group(world_size, rank)
+                self.model = ShardedDeepFM(cfg, batch_size, self.opt, seed, self.dev, world_size, rank, comm=comm,
+                                           use_graph=use_graph, params=params, process_group=process_group)
+                self.comm_name = self.model.comm_name
+            elif world_size > 1:
                 from ..parallel.dp import FusedDataParallel
                 self.model = FusedDataParallel(cfg, batch_size, self.opt, seed, self.dev, world_size, rank, comm=comm,
                                                use_graph=use_graph, params=params, process_group=process_group)
@@ -69,6 +76,16 @@ class Trainer:
             self._ring = torch.zeros(self._ring_n, 2, dtype=torch.float32).pin_memory()
             self._ring_pos = 0
         self._host_losses: List[float] = []
+
+    @staticmethod
+    def _ensure_group(world_size: int, rank: int):
+        """Symmetric memory needs a process group even for a single rank."""
+        import os
+        if not torch.distributed.is_initialized():
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            os.environ.setdefault("MASTER_PORT", "29517")
+            torch.distributed.init_process_group("nccl", rank=rank, world_size=world_size,
+                                                 device_id=torch.device("cuda", torch.cuda.current_device()))
 
     # ------------------------------------------------------------------------------------------- training
     @property
