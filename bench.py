@@ -40,6 +40,10 @@ def parse_args():
     ap.add_argument("--pool", type=int, default=0, help="distinct batches in the input pool (0 = enough to exceed L2)")
     ap.add_argument("--no_graph", action="store_true")
     ap.add_argument("--comm", default="auto", choices=["auto", "p2p", "nvls", "nccl"])
+    ap.add_argument("--strategy", default="dp", choices=["dp", "sharded", "ps"],
+                    help="dp = BASELINE config 2 (headline); sharded = config 3 (use --feature_size 33554432 "
+                         "--embedding_size 64); ps = config 4 (async PS, use --batch_size 8192 for the 64K global batch)")
+    ap.add_argument("--l2_reg", type=float, default=1e-4)
     return ap.parse_args()
 
 
@@ -122,19 +126,27 @@ def main():
     from deepfm_b200.runtime.trainer import Trainer
 
     cfg = DeepFMConfig(field_size=a.field_size, feature_size=a.feature_size, embedding_size=a.embedding_size,
-                       deep_layers=a.deep_layers, dropout=[0.5] * len(a.deep_layers.split(",")), l2_reg=1e-4)
+                       deep_layers=a.deep_layers, dropout=[0.5] * len(a.deep_layers.split(",")), l2_reg=a.l2_reg,
+                       l2_mode="exact" if a.strategy == "dp" else "touched")
     B = a.batch_size
     # reference scales LR by world size (HVD:149)
     opt = TF1Optimizer(a.optimizer, 5e-4 * world)
     backend = "proxy" if a.impl == "proxy" else "fused"
-    tr = Trainer(cfg, B, opt, seed=1234, device=dev, backend=backend, world_size=world, rank=rank,
-                 use_graph=not a.no_graph, comm=a.comm)
+    if a.strategy == "ps":
+        from deepfm_b200.parallel.dist import DistEnv
+        from deepfm_b200.parallel.ps import AsyncPSTrainer
+        opt = TF1Optimizer(a.optimizer, 5e-4)  # async PS: no LR scaling
+        tr = AsyncPSTrainer(cfg, B, opt, 1234, DistEnv(rank, world, local, "nccl" if world > 1 else "none", dev),
+                            backend="fused", staleness=4)
+    else:
+        tr = Trainer(cfg, B, opt, seed=1234, device=dev, backend=backend, world_size=world, rank=rank,
+                     use_graph=not a.no_graph, comm=a.comm, strategy=a.strategy)
 
     # ---- input pool: distinct batches, total bytes > L2 (126 MB) so no step re-reads a cached batch
     bytes_per_batch = B * a.field_size * 8 + B * 4  # int32 ids + f32 vals + f32 labels
     pool = a.pool or max(8, int(140e6 // bytes_per_batch) + 1)
     gen = SyntheticCTR(a.field_size, a.feature_size, seed=rank)
-    fused = backend == "fused"
+    fused = backend == "fused" and a.strategy != "ps"
     if fused:
         from deepfm_b200.models.fused import pack_batch
     host_pool = []
@@ -148,6 +160,9 @@ def main():
     torch.cuda.synchronize()
     step_dev = tr.train_packed_device if fused else tr.train_batch_device
     step_host = tr.train_packed if fused else tr.train_batch
+    if a.strategy == "ps":  # parameter-server workers are host-coupled by construction: both timings use host batches
+        dev_pool = host_pool
+        step_dev = step_host = tr.train_batch
 
     def barrier():
         if world > 1:
@@ -169,6 +184,8 @@ def main():
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
+    if hasattr(tr, "drain") and a.strategy == "ps":
+        tr.drain()
     launches = tr.kernels_per_step * a.steps
     final_loss = float(tr.last_loss().item())
 
@@ -202,7 +219,8 @@ def main():
             "impl": a.impl,
             "config": {"model": "DeepFM field39 feat117581 emb%d mlp%s %s" % (a.embedding_size, a.deep_layers, a.optimizer),
                        "global_batch": gb, "per_gpu_batch": B, "seq_len": a.field_size,
-                       "parallelism": "dp%d" % world, "comm": tr.comm_name,
+                       "parallelism": ("dp%d" % world) if a.strategy == "dp" else ("%s%d" % (a.strategy, world)),
+                       "comm": tr.comm_name, "strategy": a.strategy, "l2_mode": cfg.l2_mode,
                        "l2_cache_policy": "inputs rotate through a pool of %d distinct batches (%.0f MB > 126 MB L2)"
                                           % (pool, pool * bytes_per_batch / 1e6),
                        "cuda_graph": not a.no_graph},
@@ -214,7 +232,9 @@ def main():
             "final_loss": final_loss, "e2e_last_loss": losses[-1] if losses else None,
         }
         print(json.dumps(out))
-    if world > 1:
+    if hasattr(tr, "close"):
+        tr.close()
+    if dist.is_initialized():
         dist.destroy_process_group()
     return 0
 

@@ -87,7 +87,7 @@ def main(argv: Optional[List[str]] = None) -> int:
     est = Estimator(cfg, F.batch_size, opt, F.model_dir or None, env, backend=F.backend, seed=F.seed,
                     log_steps=F.log_steps, save_checkpoints_secs=F.save_checkpoints_secs,
                     save_checkpoints_steps=F.save_checkpoints_steps, keep_checkpoint_max=F.keep_checkpoint_max,
-                    metrics_file=F.metrics_file or None, comm=F.comm, strategy=F.strategy)
+                    metrics_file=F.metrics_file or None, comm=F.comm, strategy=F.strategy, ps_staleness=F.ps_staleness)
 
     num_hosts = len(F.hosts)
     if F.strategy == "ps":
@@ -144,6 +144,8 @@ def main(argv: Optional[List[str]] = None) -> int:
         est.export_savedmodel(F.servable_model_dir)
     if metrics is not None and env.is_chief:
         print(json.dumps({"eval": metrics}))
+    if hasattr(est.trainer, "close"):
+        est.trainer.close()
     barrier(env)
     shutdown()
     return 0

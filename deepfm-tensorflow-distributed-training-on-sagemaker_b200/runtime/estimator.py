@@ -25,7 +25,8 @@ class Estimator:
     def __init__(self, cfg: DeepFMConfig, batch_size: int, optimizer: TF1Optimizer, model_dir: Optional[str],
                  env: Optional[DistEnv] = None, backend: str = "auto", seed: int = 0, log_steps: int = 100,
                  save_checkpoints_secs: int = 600, save_checkpoints_steps: int = 0, keep_checkpoint_max: int = 5,
-                 metrics_file: Optional[str] = None, comm: str = "auto", strategy: str = "dp", out=sys.stdout):
+                 metrics_file: Optional[str] = None, comm: str = "auto", strategy: str = "dp", ps_staleness: int = 4,
+                 out=sys.stdout):
         self.cfg, self.B, self.opt = cfg, batch_size, optimizer
         self.env = env or DistEnv()
         # like the reference, only the chief owns a model_dir (HVD:365-368); other ranks get state by broadcast
@@ -35,7 +36,8 @@ class Estimator:
         self.strategy = strategy
         if strategy == "ps":
             from ..parallel.ps import AsyncPSTrainer
-            self.trainer = AsyncPSTrainer(cfg, batch_size, optimizer, seed, self.env, backend=backend)
+            self.trainer = AsyncPSTrainer(cfg, batch_size, optimizer, seed, self.env, backend=backend,
+                                          staleness=ps_staleness)
         else:
             self.trainer = Trainer(cfg, batch_size, optimizer, seed, self.env.device, backend, self.env.world_size,
                                    self.env.rank, comm=comm, strategy=strategy)
@@ -53,8 +55,8 @@ class Estimator:
         with BroadcastGlobalVariablesHook(0), HVD:372)."""
         prefix = latest_checkpoint(self.model_dir) if self.model_dir else None
         if prefix:
-            names = list(self.trainer.model.named_parameters().keys()) if hasattr(self.trainer, "model") else \
-                self.trainer.parameter_names()
+            names = self.trainer.parameter_names() if hasattr(self.trainer, "parameter_names") else \
+                list(self.trainer.model.named_parameters().keys())
             self.trainer.load_state_dict(load_checkpoint(prefix, names, self.opt.name), strict=False)
             print("INFO:deepfm_b200:Restoring parameters from %s" % prefix, file=self.out)
         if self.env.world_size > 1 and hasattr(self.trainer, "broadcast_state"):
