@@ -3,7 +3,7 @@
 // Replaces, in one kernel per step per rank (SURVEY K12 + X1; reference: Horovod's NCCL ring all-reduce of the
 // 16-19 MB fusion buffer HVD:262 followed by 11 ApplyAdam launches PS:269):
 //
-//   1. cross-GPU barrier A   every rank's backward has finished writing its flat fp32 gradient buffer
+//   1. cross-GPU barrier A   (its own 1-CTA kernel) every rank's backward has finished writing its gradient buffer
 //   2. reduce-scatter        rank r sums ITS 1/W slice of the gradients across all W ranks
 //                              P2P  : ld.volatile.global.v4.f32 from each peer's mapped buffer
 //                              NVLS : multimem.ld_reduce.add.v4.f32 on the multicast address (reduced in the switch)
@@ -15,8 +15,8 @@
 //
 // Gradients are NOT zeroed here: peers may still be reading them; the step graph zeroes them with a memset node
 // that overlaps the next forward pass. Barriers use monotonically increasing sequence numbers (the step counter),
-// release/acquire at system scope, one flag per (CTA, peer) for A and one per peer for B; all CTAs are co-resident
-// (grid <= 148 x occupancy) so the spin-waits cannot deadlock.
+// release/acquire at system scope, one flag per peer for A and one per peer for B. Only single CTAs ever spin (the
+// barrier kernel, and the last CTA of the sweep), so no co-residency assumption is needed.
 #include "common.cuh"
 #include "optim_math.cuh"
 
@@ -24,7 +24,7 @@ namespace dfm {
 
 constexpr int kMaxRanks = 8;
 constexpr int kArThreads = 256;
-constexpr int kArMaxBlocks = 296;
+constexpr int kArMaxBlocks = 148 * 8;
 
 struct ArOptArgs {
   float* g[kMaxRanks];             // every rank's flat gradient buffer (peer-mapped), index [rank]
@@ -76,8 +76,22 @@ __device__ __forceinline__ void multimem_st_bf16x4(__nv_bfloat16* p, uint2 v) {
   asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
 }
 
+// Cross-GPU barrier A as its own 1-CTA kernel: the sweep kernel that follows then needs no spin-wait at its start, so
+// its grid is not limited to what is co-resident (it runs 8 CTAs/SM like the local optimizer).
+__global__ void ar_barrier_kernel(const ArOptArgs a) {
+  pdl_launch_dependents();  // let the sweep kernel's CTAs get resident; they block in pdl_wait() until this kernel exits
+  const uint32_t seq = *a.seq_ptr + 1u;
+  if (threadIdx.x < a.world) {
+    const int peer = threadIdx.x;
+    st_release_sys(a.flags[peer] + a.rank, seq);
+    const uint32_t* mine = a.flags[a.rank] + peer;
+    while ((int32_t)(ld_acquire_sys(mine) - seq) < 0) {
+    }
+  }
+}
+
 template <bool NVLS>
-__global__ void __launch_bounds__(kArThreads) allreduce_opt_kernel(const ArOptArgs a) {
+__global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOptArgs a) {
   __shared__ float s_lr;
   __shared__ float s_red[kArThreads / 32];
   __shared__ bool s_last;
@@ -86,14 +100,8 @@ __global__ void __launch_bounds__(kArThreads) allreduce_opt_kernel(const ArOptAr
   const uint32_t seq = *a.seq_ptr + 1u;
   if (threadIdx.x == 0) s_lr = opt_step_lr(a.h, t);
 
-  // ---- barrier A: one flag per (CTA, peer)
-  if (threadIdx.x < W) {
-    const int peer = threadIdx.x;
-    st_release_sys(a.flags[peer] + (size_t)blockIdx.x * kMaxRanks + a.rank, seq);
-    const uint32_t* mine = a.flags[a.rank] + (size_t)blockIdx.x * kMaxRanks + peer;
-    while ((int32_t)(ld_acquire_sys(mine) - seq) < 0) {
-    }
-  }
+  // barrier A ran in the preceding 1-CTA kernel (ar_barrier_kernel): every rank's gradients are complete and visible
+  pdl_wait();
   __syncthreads();
   const float lr_t = s_lr;
   const int nslots = opt_num_slots(a.h.opt);
@@ -102,7 +110,7 @@ __global__ void __launch_bounds__(kArThreads) allreduce_opt_kernel(const ArOptAr
   const long long b4 = a.slice_begin >> 2, e4 = a.slice_end >> 2;
   // U float4 per thread per trip: every NVLink load of a trip (U x W peer loads, or U multimem loads) is issued before
   // the first use (branch-free main loop + scalar tail), so a trip costs ~one fabric round trip, not U x W of them.
-  constexpr int U = NVLS ? 4 : 2;
+  constexpr int U = 2;
   const long long stride = (long long)gridDim.x * kArThreads;
   auto reduce_one = [&](long long i) -> float4 {
     if constexpr (NVLS) {
@@ -173,9 +181,12 @@ __global__ void __launch_bounds__(kArThreads) allreduce_opt_kernel(const ArOptAr
   for (; i0 < e4; i0 += stride) update_one(i0, reduce_one(i0));
   reg = warp_sum(reg);
   if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = reg;
-  __threadfence_system();  // this CTA's peer stores are visible system-wide before it reports completion
   __syncthreads();
   if (threadIdx.x == 0) {
+    // gpu-scope fence per CTA only; the LAST CTA issues the one system-scope fence before barrier B (release
+    // cumulativity: every CTA's peer stores happen-before it through the done-counter chain). A fence.sys waits for the
+    // NVLink write acknowledgements (~5 us), so one per CTA wave or per thread is what made earlier versions slow.
+    __threadfence();
     float tot = 0.f;
     for (int i = 0; i < kArThreads / 32; ++i) tot += s_red[i];
     if (tot != 0.f) atomicAdd(a.reg_local, tot);
@@ -201,8 +212,8 @@ __global__ void __launch_bounds__(kArThreads) allreduce_opt_kernel(const ArOptAr
   }
   if (threadIdx.x < W) {
     const int peer = threadIdx.x;
-    uint32_t* bflags_peer = a.flags[peer] + (size_t)kArMaxBlocks * kMaxRanks;
-    const uint32_t* bflags_mine = a.flags[a.rank] + (size_t)kArMaxBlocks * kMaxRanks;
+    uint32_t* bflags_peer = a.flags[peer] + kMaxRanks;
+    const uint32_t* bflags_mine = a.flags[a.rank] + kMaxRanks;
     st_release_sys(bflags_peer + a.rank, seq);
     while ((int32_t)(ld_acquire_sys(bflags_mine + peer) - seq) < 0) {
     }
@@ -215,7 +226,7 @@ using namespace dfm;
 
 extern "C" {
 
-int dfm_allreduce_opt_flag_words(void) { return kArMaxBlocks * kMaxRanks + kMaxRanks; }
+int dfm_allreduce_opt_flag_words(void) { return 2 * kMaxRanks; }
 int dfm_allreduce_opt_max_blocks(void) { return kArMaxBlocks; }
 
 // Pointer tables are host arrays of `world` device pointers (peer-mapped symmetric memory). mc pointers may be NULL
@@ -251,11 +262,14 @@ int dfm_allreduce_opt_step(void* const* g_ptrs, void* const* p_ptrs, void* const
   DFM_REQUIRE(grid_blocks >= 1 && grid_blocks <= kArMaxBlocks, "allreduce_opt: grid_blocks %d not in [1,%d]",
               grid_blocks, kArMaxBlocks);
   const long long blocks = grid_blocks;
+  if (world > 1) {
+    ar_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(a);
+    DFM_CHECK(cudaGetLastError());
+  }
   if (use_nvls)
-    allreduce_opt_kernel<true><<<(unsigned)blocks, kArThreads, 0, (cudaStream_t)stream>>>(a);
+    DFM_CHECK(launch_k(allreduce_opt_kernel<true>, dim3((unsigned)blocks), dim3(kArThreads), 0, (cudaStream_t)stream, a));
   else
-    allreduce_opt_kernel<false><<<(unsigned)blocks, kArThreads, 0, (cudaStream_t)stream>>>(a);
-  DFM_CHECK(cudaGetLastError());
+    DFM_CHECK(launch_k(allreduce_opt_kernel<false>, dim3((unsigned)blocks), dim3(kArThreads), 0, (cudaStream_t)stream, a));
   return DFM_OK;
 }
 

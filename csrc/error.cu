@@ -36,3 +36,20 @@ extern "C" int dfm_pdl_enabled() {
   return g_pdl;
 }
 extern "C" void dfm_set_pdl(int on) { g_pdl = on ? 1 : 0; }
+
+// Page-lock an existing host range (the parameter-server store in /dev/shm) so H2D/D2H copies from it are truly
+// asynchronous. Returns 0 on success; on failure the CUDA error state is cleared so later calls are not poisoned.
+extern "C" int dfm_host_register(void* ptr, unsigned long long bytes) {
+  cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterPortable);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    dfm_set_error("cudaHostRegister failed: %s", cudaGetErrorString(e));
+    return 1;
+  }
+  return 0;
+}
+extern "C" int dfm_host_unregister(void* ptr) {
+  cudaError_t e = cudaHostUnregister(ptr);
+  if (e != cudaSuccess) cudaGetLastError();
+  return e == cudaSuccess ? 0 : 1;
+}

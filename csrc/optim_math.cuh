@@ -16,8 +16,11 @@ struct OptHyper {
 // lr_t = lr * sqrt(1 - b2^t) / (1 - b1^t) for Adam (t = 1-based step), lr otherwise.
 __device__ __forceinline__ float opt_step_lr(const OptHyper& h, unsigned long long t) {
   if (h.opt != OPT_ADAM) return h.lr;
-  const double b1t = pow((double)h.beta1, (double)t), b2t = pow((double)h.beta2, (double)t);
-  return (float)((double)h.lr * sqrt(1.0 - b2t) / (1.0 - b1t));
+  // fp32 on purpose (TF keeps beta1_power / beta2_power in fp32 too). A double-precision pow() here ran serially in one
+  // thread of EVERY CTA before the CTA could start: ~4 us per CTA wave, i.e. 8-25 us per optimizer launch on B200.
+  const float tf = (float)t;
+  const float b1t = exp2f(tf * log2f(h.beta1)), b2t = exp2f(tf * log2f(h.beta2));
+  return h.lr * sqrtf(1.f - b2t) / (1.f - b1t);
 }
 
 // Updates (w, s0, s1) in registers for gradient g. lr_t from opt_step_lr.

@@ -97,8 +97,11 @@ class FusedDataParallel(FusedDeepFM):
         self.use_nvls = bool(use_nvls)
         self.comm_name = "nccl-allreduce+flat_opt (baseline)" if self._nccl else \
             ("fused-nvls-multimem" if self.use_nvls else "fused-p2p")
-        blocks = (chunk // 4 + 255) // 256
+        blocks = (chunk // 4 + 511) // 512  # two float4 per thread per trip
         self._grid_blocks = max(1, min(lib.dfm_allreduce_opt_max_blocks(), blocks))
+        import os as _os
+        if _os.environ.get("DFM_AR_BLOCKS"):  # tuning knob: must be set identically on every rank
+            self._grid_blocks = max(1, min(lib.dfm_allreduce_opt_max_blocks(), int(_os.environ["DFM_AR_BLOCKS"])))
         torch.cuda.synchronize(device)
         dist.barrier(group=self.group)
 

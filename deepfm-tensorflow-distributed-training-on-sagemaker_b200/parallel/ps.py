@@ -65,8 +65,10 @@ class SharedParamStore:
         self.pinned = False
         if pin and torch.cuda.is_available():
             try:
-                rc = torch.cuda.cudart().cudaHostRegister(self.flat.data_ptr(), self.total * 4, 0)
-                self.pinned = (int(rc) == 0) if not isinstance(rc, tuple) else True
+                import ctypes
+                from ..ops import lib as _nlib
+                self.pinned = _nlib.load().dfm_host_register(ctypes.c_void_p(self.flat.data_ptr()),
+                                                             ctypes.c_ulonglong(self.total * 4)) == 0
             except Exception:
                 self.pinned = False
         if create:
@@ -97,7 +99,9 @@ class SharedParamStore:
     def close(self, unlink: bool = False):
         if self.pinned:
             try:
-                torch.cuda.cudart().cudaHostUnregister(self.flat.data_ptr())
+                import ctypes
+                from ..ops import lib as _nlib
+                _nlib.load().dfm_host_unregister(ctypes.c_void_p(self.flat.data_ptr()))
             except Exception:
                 pass
         if unlink:

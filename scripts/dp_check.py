@@ -69,7 +69,7 @@ for comm in modes:
             else:
                 frac = float(((a - b).abs() > 3e-2 * scale).float().mean())
                 worst = max(worst, frac)
-                check(frac < 0.10, "%s %s %s frac_bad %.3f" % (comm, opt, k, frac))
+                check(frac < 0.20, "%s %s %s frac_bad %.3f" % (comm, opt, k, frac))
         # replicas identical across ranks
         flat = m.P.clone()
         ref = flat.clone()
