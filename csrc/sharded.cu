@@ -77,10 +77,13 @@ template <int G>
 __global__ void __launch_bounds__(kShThreads)
 emb_fm_fwd_a2a_kernel(const ShardPtrs sp, const int* __restrict__ ids, const float* __restrict__ vals,
                       __nv_bfloat16* __restrict__ x0, float* __restrict__ e32, int ldx, float* __restrict__ S,
-                      float* __restrict__ yfm, int B, int F, long long N, const unsigned int* __restrict__ seq_ptr) {
+                      float* __restrict__ yfm, int B, int F, long long N, const unsigned int* __restrict__ seq_ptr,
+                      int do_barrier) {
   constexpr int K = 4 * G;
   constexpr int FG = 32 / G;
-  cross_rank_barrier(sp, 0, *seq_ptr + 1u);
+  // training: wait until every owner has finished last step's row updates. Evaluation / prediction on one rank only
+  // (the reference evaluates on the chief, HVD:393) reads quiescent tables and must NOT wait for idle peers.
+  if (do_barrier) cross_rank_barrier(sp, 0, *seq_ptr + 1u);
   const int lane = threadIdx.x & 31;
   const int W = sp.world;
   for (int sample = blockIdx.x * (kShThreads / 32) + (threadIdx.x >> 5); sample < B; sample += gridDim.x * (kShThreads / 32)) {
@@ -346,14 +349,14 @@ int dfm_sharded_flag_words(void) { return 2 * kShMaxBlocks * kShMaxRanks; }
 // grid_blocks must be identical on every rank (<= 1184). x0 bf16 / e32 f32 share ldx.
 int dfm_emb_fm_fwd_a2a(void* const* v, void* const* w, void* const* gv, void* const* gw, void* const* bm, void* const* fl,
                        int rank, int world, const int* ids, const float* vals, void* x0, float* e32, int ldx, float* S,
-                       float* yfm, int B, int F, int K, long long N, const unsigned int* seq_ptr, int grid_blocks,
-                       void* stream) {
+                       float* yfm, int B, int F, int K, long long N, const unsigned int* seq_ptr, int do_barrier,
+                       int grid_blocks, void* stream) {
   ShardPtrs sp;
   int rc = fill_ptrs(sp, v, w, gv, gw, bm, fl, rank, world);
   if (rc) return rc;
   DFM_REQUIRE(grid_blocks >= 1 && grid_blocks <= kShMaxBlocks, "fwd_a2a: grid_blocks out of range");
 #define CALL(G) emb_fm_fwd_a2a_kernel<G><<<grid_blocks, kShThreads, 0, (cudaStream_t)stream>>>( \
-      sp, ids, vals, (__nv_bfloat16*)x0, e32, ldx, S, yfm, B, F, N, seq_ptr)
+      sp, ids, vals, (__nv_bfloat16*)x0, e32, ldx, S, yfm, B, F, N, seq_ptr, do_barrier)
   DFM_SH_DISPATCH(K, CALL)
 #undef CALL
   DFM_CHECK(cudaGetLastError());

@@ -18,7 +18,9 @@ from ..utils.tfrecord import TFRecordWriter, make_ctr_example
 
 class SyntheticCTR:
     def __init__(self, field_size: int = 39, feature_size: int = 117581, num_numeric: int = 13, seed: int = 0,
-                 zipf_a: float = 1.2, positive_rate: float = 0.26):
+                 zipf_a: float = 1.2, positive_rate: float = 0.26, teacher_seed: int = 12345):
+        """`seed` drives the SAMPLING only; the hidden teacher depends on `teacher_seed`, so train / validation / test
+        sets drawn with different seeds share one ground truth."""
         self.F, self.N = field_size, feature_size
         self.num_numeric = min(num_numeric, field_size)
         self.seed = seed
@@ -31,7 +33,7 @@ class SyntheticCTR:
         self.cat_sz = np.array([base] * n_cat, dtype=np.int64)
         if n_cat:
             self.cat_sz[-1] = rest - base * (n_cat - 1)
-        rng = np.random.default_rng(seed + 12345)
+        rng = np.random.default_rng(teacher_seed)
         self.teacher_w = rng.normal(0, 1.0, feature_size).astype(np.float32)
         self.bias = float(np.log(positive_rate / (1 - positive_rate)))
 
@@ -76,7 +78,8 @@ def write_synthetic_tfrecords(out_dir: str, prefix: str, num_files: int, rows_pe
             pass
     for fi in range(num_files):
         path = os.path.join(out_dir, "%s%03d.tfrecords" % (prefix, fi))
-        ids, vals, labels = gen.numpy_batch(rows_per_file, hash((prefix, fi)) & 0x7FFFFFFF)
+        import zlib
+        ids, vals, labels = gen.numpy_batch(rows_per_file, zlib.crc32(("%s/%d" % (prefix, fi)).encode()))
         with writer_cls(path) as w:
             for r in range(rows_per_file):
                 w.write(make_ctr_example(float(labels[r]), ids[r].tolist(), vals[r].tolist()))

@@ -101,6 +101,15 @@ class ShardedDeepFM(FusedDataParallel):
         self.GV.zero_(); self.GW.zero_(); self.bitmap.zero_()
 
     # ---- embedding kernels with the all-to-all fused in
+    _train_mode = False
+
+    def _train_kernels(self, slot, with_optimizer: bool = True) -> int:
+        self._train_mode = True  # the forward all-to-all synchronises with the peers only inside a training step
+        try:
+            return super()._train_kernels(slot, with_optimizer)
+        finally:
+            self._train_mode = False
+
     def _emb_forward(self, slot) -> None:
         cfg, t = self.cfg, self._t
         _nlib.check(_nlib.load().dfm_emb_fm_fwd_a2a(
@@ -108,7 +117,8 @@ class ShardedDeepFM(FusedDataParallel):
             c_void_p(slot["ids"].data_ptr()), c_void_p(slot["vals"].data_ptr()), c_void_p(self.x0.data_ptr()),
             c_void_p(self.e32.data_ptr()), c_int(self.x0.stride(0)), c_void_p(self.Ssum.data_ptr()),
             c_void_p(self.yfm.data_ptr()), c_int(self.B), c_int(cfg.field_size), c_int(cfg.embedding_size),
-            c_longlong(cfg.feature_size), c_void_p(self.sh_seq.data_ptr()), c_int(self._fwd_blocks),
+            c_longlong(cfg.feature_size), c_void_p(self.sh_seq.data_ptr()), c_int(1 if self._train_mode else 0),
+            c_int(self._fwd_blocks),
             c_void_p(torch.cuda.current_stream().cuda_stream)))
 
     def _emb_backward(self, slot) -> int:

@@ -75,6 +75,31 @@ int dfm_allreduce_opt_step(void* const* g_ptrs, void* const* p_ptrs, void* const
                            unsigned long long* step_ptr, float* reg_local, unsigned int* done_counter,
                            unsigned int* seq_ptr, int use_nvls, int grid_blocks, void* stream);
 
+/* ---- row-sharded embedding tables with the all-to-all fused into the kernels (no counterpart in the reference beyond
+ * the partitioner advice of PDF p32). Pointer tables: host arrays of `world` device pointers into symmetric
+ * memory (table shards v/w, gradient shards gv/gw, touched-row bitmaps, barrier flags of dfm_sharded_flag_words() words).
+ * Row id lives on rank id % world at local row id / world. grid_blocks must be identical on every rank (<= 1184).
+ * do_barrier=1 inside a training step (wait for every owner's row updates), 0 for single-rank evaluation. */
+int dfm_sharded_flag_words(void);
+int dfm_emb_fm_fwd_a2a(void* const* v, void* const* w, void* const* gv, void* const* gw, void* const* bm, void* const* fl,
+                       int rank, int world, const int* ids, const float* vals, void* x0_bf16, float* e32, int ldx,
+                       float* S, float* yfm, int B, int F, int K, long long N, const unsigned int* seq_ptr,
+                       int do_barrier, int grid_blocks, void* stream);
+int dfm_emb_bwd_a2a(void* const* v, void* const* w, void* const* gv, void* const* gw, void* const* bm, void* const* fl,
+                    int rank, int world, const int* ids, const float* vals, const float* e32, const float* S,
+                    const float* dy, const void* dx0_bf16, int ldx, int B, int F, int K, long long N, void* stream);
+int dfm_sparse_row_opt(void* const* v, void* const* w, void* const* gv, void* const* gw, void* const* bm, void* const* fl,
+                       int rank, int world, float* v_s0, float* v_s1, float* w_s0, float* w_s1, long long rows_local,
+                       int K, int opt, float lr, float beta1, float beta2, float eps, float momentum, float l2,
+                       const unsigned long long* step_ptr, int step_offset, unsigned int* seq_ptr,
+                       unsigned int* done_counter, float* reg_loss, int grid_blocks, void* stream);
+
+/* ---- runtime switches / host helpers */
+int dfm_pdl_enabled(void);            /* programmatic dependent launch between the step kernels (default on; DFM_PDL=0) */
+void dfm_set_pdl(int on);
+int dfm_host_register(void* ptr, unsigned long long bytes);   /* page-lock the parameter-server store (HOST pointer) */
+int dfm_host_unregister(void* ptr);
+
 /* ---- flat optimizer step that allocates nothing (no counterpart in the reference: TF owns its own allocator).
  * Same update as dfm_flat_opt_step, but the scratch it needs sits in a static device array inside the library
  * (262,400 bytes per GPU, held until exit) instead of being supplied by the caller. For callers that cannot call

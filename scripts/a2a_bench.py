@@ -34,6 +34,7 @@ for n_ids in [1024, 16384, 131072, 1048576]:
     s["ids"].copy_(torch.randint(0, N, (B, F), device=dev, generator=g, dtype=torch.int32))
     s["vals"].copy_(torch.rand(B, F, device=dev, generator=g) + 0.1)
     m.dy.normal_(generator=g); m.dx0.copy_((torch.randn(B, F * K, device=dev, generator=g) * 0.01).bfloat16())
+    m._train_mode = True  # include the forward's cross-rank barrier, as inside a training step
     def fused():
         m._emb_forward(s)       # dispatch + gather + scale + pool + combine (P2P loads)
         m._emb_backward(s)      # grad push (remote red.add) + segment-sum + sparse row update on the owner

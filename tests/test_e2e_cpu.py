@@ -70,7 +70,7 @@ def test_train_eval_infer_export_resume(data, tmp_path):
                        "--save_checkpoints_steps", "20"])
     assert "loss = " in out and "Saving checkpoints for 40" in out and "Saving checkpoints for 80" in out
     ev = json.loads([l for l in out.splitlines() if l.startswith('{"eval"')][-1])["eval"]
-    assert ev["global_step"] == 80 and 0.0 < ev["loss"] < 0.8 and ev["auc"] > 0.5 and ev["examples"] == 640
+    assert ev["global_step"] == 80 and 0.0 < ev["loss"] < 0.8 and ev["auc"] > 0.55 and ev["examples"] == 640
     first_loss = float(out.split("loss = ")[1].split(",")[0])
     assert 0.3 < first_loss < 0.9  # step-10 loss, already below ln 2 (the reference logs 0.696 at step 1, PDF p34)
     assert os.path.exists(os.path.join(ckpt, "checkpoint")) and os.path.exists(os.path.join(ckpt, "metrics.jsonl"))

@@ -14,7 +14,7 @@ REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def _torchrun(script, nproc, port):
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc),
                         "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(REPO, "scripts", script)],
-                       capture_output=True, text=True, timeout=900, cwd=REPO)
+                       capture_output=True, text=True, timeout=300, cwd=REPO)
     return r.returncode, r.stdout + r.stderr
 
 
