@@ -84,9 +84,7 @@ __global__ void ar_barrier_kernel(const ArOptArgs a) {
   if (threadIdx.x < a.world) {
     const int peer = threadIdx.x;
     st_release_sys(a.flags[peer] + a.rank, seq);
-    const uint32_t* mine = a.flags[a.rank] + peer;
-    while ((int32_t)(ld_acquire_sys(mine) - seq) < 0) {
-    }
+    wait_flag_geq(a.flags[a.rank] + peer, seq, peer, 0);
   }
 }
 
@@ -215,9 +213,32 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
     uint32_t* bflags_peer = a.flags[peer] + kMaxRanks;
     const uint32_t* bflags_mine = a.flags[a.rank] + kMaxRanks;
     st_release_sys(bflags_peer + a.rank, seq);
-    while ((int32_t)(ld_acquire_sys(bflags_mine + peer) - seq) < 0) {
+    wait_flag_geq(bflags_mine + peer, seq, peer, 1);
+  }
+}
+
+// bcast_state (reference: BroadcastGlobalVariablesHook(0), HVD:372 — an NCCL broadcast of ~36
+// tensors at the start of every train() call): the source rank writes its buffer into every replica with one pass of
+// multicast stores (NVLS) or per-peer P2P stores. Callers fence with a host barrier before and after (start/resume only).
+template <bool NVLS>
+__global__ void __launch_bounds__(256) bcast_kernel(const ArOptArgs a, long long n4) {
+  const float4* src = reinterpret_cast<const float4*>(a.p[a.rank]);
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n4; i += (long long)gridDim.x * 256) {
+    const float4 v = src[i];
+    if constexpr (NVLS) {
+      multimem_st_f4(a.p_mc + (i << 2), v);
+    } else {
+#pragma unroll
+      for (int r = 1; r < kMaxRanks; ++r) {
+        if (r < a.world) {
+          int peer = a.rank + r;
+          if (peer >= a.world) peer -= a.world;
+          reinterpret_cast<float4*>(a.p[peer])[i] = v;
+        }
+      }
     }
   }
+  __threadfence_system();
 }
 
 }  // namespace dfm
@@ -225,6 +246,22 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
 using namespace dfm;
 
 extern "C" {
+
+// Broadcast n fp32 elements (multiple of 4) from this rank's buffer into every peer's buffer at the same offset.
+int dfm_bcast_f32(void* const* ptrs, void* mc, long long n, int rank, int world, int use_nvls, void* stream) {
+  DFM_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world, "bcast: bad rank/world");
+  DFM_REQUIRE(n > 0 && n % 4 == 0, "bcast: n must be a positive multiple of 4");
+  DFM_REQUIRE(!use_nvls || mc, "bcast: NVLS requested without a multicast mapping");
+  ArOptArgs a = {};
+  for (int r = 0; r < kMaxRanks; ++r) a.p[r] = (float*)ptrs[r < world ? r : 0];
+  a.p_mc = (float*)mc; a.rank = rank; a.world = world;
+  long long blocks = ceil_div_ll(n / 4, 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (use_nvls) bcast_kernel<true><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(a, n / 4);
+  else bcast_kernel<false><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(a, n / 4);
+  DFM_CHECK(cudaGetLastError());
+  return DFM_OK;
+}
 
 int dfm_allreduce_opt_flag_words(void) { return 2 * kMaxRanks; }
 int dfm_allreduce_opt_max_blocks(void) { return kArMaxBlocks; }

@@ -189,6 +189,37 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, int a_mn_ma
          | ((uint32_t)(M >> 4) << 24);    // M / 16
 }
 
+// ----------------------------------------------------------------------------------- cross-GPU flag waits
+// Watchdog for every spin on a flag another GPU writes (reference analogue: Horovod's stall check, PDF p21): if the
+// peer does not show up within DFM_FLAG_TIMEOUT_NS the kernel reports and traps, turning a silent hang (e.g. one rank
+// died, or the ranks disagree on the number of steps, PDF p22) into a CUDA error the host can act on.
+#ifndef DFM_FLAG_TIMEOUT_NS
+#define DFM_FLAG_TIMEOUT_NS 20000000000ull
+#endif
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void wait_flag_geq(const uint32_t* flag, uint32_t seq, int peer, int what) {
+  unsigned long long t0 = 0;
+  unsigned int spins = 0;
+  for (;;) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+    if ((int32_t)(v - seq) >= 0) return;
+    if ((++spins & 0x3FFu) == 0) {
+      const unsigned long long now = global_timer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > DFM_FLAG_TIMEOUT_NS) {
+        printf("deepfm_b200: timed out waiting for rank %d (barrier %d, seq %u, saw %u)\n", peer, what, seq, v);
+        __trap();
+      }
+      __nanosleep(200);
+    }
+  }
+}
+
 // ----------------------------------------------------------------------------------- vector memory ops
 __device__ __forceinline__ void red_add_f32x4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)

@@ -39,12 +39,20 @@ extern "C" void dfm_set_pdl(int on) { g_pdl = on ? 1 : 0; }
 
 // Page-lock an existing host range (the parameter-server store in /dev/shm) so H2D/D2H copies from it are truly
 // asynchronous. Returns 0 on success; on failure the CUDA error state is cleared so later calls are not poisoned.
-extern "C" int dfm_host_register(void* ptr, unsigned long long bytes) {
-  cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterPortable);
+extern "C" int dfm_host_register(void* ptr, unsigned long long bytes, void** dev_ptr) {
+  cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped);
   if (e != cudaSuccess) {
     cudaGetLastError();
     dfm_set_error("cudaHostRegister failed: %s", cudaGetErrorString(e));
     return 1;
+  }
+  if (dev_ptr) {  // device-visible alias of the range, for kernels that read the store directly (dfm_ps_gather)
+    *dev_ptr = nullptr;
+    e = cudaHostGetDevicePointer(dev_ptr, ptr, 0);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      *dev_ptr = nullptr;
+    }
   }
   return 0;
 }

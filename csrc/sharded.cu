@@ -52,9 +52,7 @@ __device__ __forceinline__ void cross_rank_barrier(const ShardPtrs& sp, int phas
       const int peer = threadIdx.x;
       const size_t slot = ((size_t)phase * kShMaxBlocks + blockIdx.x) * kShMaxRanks;
       sh_st_release_sys(sp.flags[peer] + slot + sp.rank, seq);
-      const uint32_t* mine = sp.flags[sp.rank] + slot + peer;
-      while ((int32_t)(sh_ld_acquire_sys(mine) - seq) < 0) {
-      }
+      wait_flag_geq(sp.flags[sp.rank] + slot + peer, seq, peer, 2 + phase);
     }
     __syncthreads();
   }

@@ -7,7 +7,7 @@ def build_model(cfg, batch_size, optimizer=None, seed=0, device=None, backend="a
     """backend: 'fused' (sm_100a kernels, requires a B200), 'torch' (plain PyTorch), 'auto' (fused on CUDA)."""
     import torch
     if backend == "auto":
-        backend = "fused" if (torch.cuda.is_available() and not cfg.batch_norm) else "torch"
+        backend = "fused" if torch.cuda.is_available() else "torch"
     if backend == "fused":
         from .fused import FusedDeepFM
         return FusedDeepFM(cfg, batch_size, optimizer, seed, device, **kw)

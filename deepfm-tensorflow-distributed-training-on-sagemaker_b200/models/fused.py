@@ -62,8 +62,6 @@ class FusedDeepFM:
                  input_slots: int = 2):
         """`global_batch`/`row_offset`: under data parallelism the loss is the mean over the GLOBAL batch and the
         dropout mask of row r is that of global row row_offset+r, so DP-N is comparable to DP-1."""
-        if cfg.batch_norm:
-            raise NotImplementedError("batch_norm=True runs on the torch backend (models/torch_backend.py)")
         _native.require_gpu()
         self.cfg = cfg
         self.B = int(batch_size)
@@ -113,6 +111,11 @@ class FusedDeepFM:
         self.yfm = torch.zeros(B, **f32)
         self.acts = [torch.zeros(B, h, **bf) for h in cfg.deep_layers]
         self.dz = [torch.zeros(B, h, **bf) for h in cfg.deep_layers]
+        self.bn = bool(cfg.batch_norm)
+        if self.bn:  # ReLU outputs (pre-BN) and the saved batch statistics
+            self.zbuf = [torch.zeros(B, h, **bf) for h in cfg.deep_layers]
+            self.bn_mean = [torch.zeros(h, **f32) for h in cfg.deep_layers]
+            self.bn_rstd = [torch.zeros(h, **f32) for h in cfg.deep_layers]
         self.dy = torch.zeros(B, **f32)
         self.prob = torch.zeros(B, **f32)
         self.logit = torch.zeros(B, **f32)
@@ -162,10 +165,15 @@ class FusedDeepFM:
             d_in = x_in.shape[1]
             Wb = self._wb("mlp%d.weight" % i)
             bias = self._w("mlp%d.bias" % i)
-            self.fwd_train.append(K.GemmPlan("fwd", x_in, Wb, self.acts[i], B, h, d_in, bias=bias, relu=True,
-                                             keep_prob=cfg.dropout[i], seed=self.seed, layer=i,
-                                             row_offset=self.row_offset, step_ptr=self.step_t))
-            self.fwd_eval.append(K.GemmPlan("fwd", x_in, Wb, self.acts[i], B, h, d_in, bias=bias, relu=True))
+            if self.bn:  # GEMM epilogue stops at ReLU; BN + dropout run in bn_fwd
+                plan = K.GemmPlan("fwd", x_in, Wb, self.zbuf[i], B, h, d_in, bias=bias, relu=True)
+                self.fwd_train.append(plan)
+                self.fwd_eval.append(plan)
+            else:
+                self.fwd_train.append(K.GemmPlan("fwd", x_in, Wb, self.acts[i], B, h, d_in, bias=bias, relu=True,
+                                                 keep_prob=cfg.dropout[i], seed=self.seed, layer=i,
+                                                 row_offset=self.row_offset, step_ptr=self.step_t))
+                self.fwd_eval.append(K.GemmPlan("fwd", x_in, Wb, self.acts[i], B, h, d_in, bias=bias, relu=True))
             self.wgrad.append(K.GemmPlan("wgrad", self.dz[i], x_in, self._g("mlp%d.weight" % i), h, d_in, B))
             if i == 0:
                 self.dgrad.append(K.GemmPlan("dgrad", self.dz[0], Wb, self.dx0, B, d_in, h))
@@ -191,9 +199,14 @@ class FusedDeepFM:
     def _forward(self, slot, train: bool, rows: Optional[int] = None):
         cfg = self.cfg
         self._emb_forward(slot)
-        for p in (self.fwd_train if train else self.fwd_eval):
+        for i, p in enumerate(self.fwd_train if train else self.fwd_eval):
             p.run()
-        return 1 + self.n_layers
+            if self.bn:
+                K.bn_fwd(self.zbuf[i], self.acts[i], self._w("bn_%d.gamma" % i), self._w("bn_%d.beta" % i),
+                         self._w("bn_%d.moving_mean" % i), self._w("bn_%d.moving_variance" % i), self.bn_mean[i],
+                         self.bn_rstd[i], cfg.batch_norm_decay, train, cfg.dropout[i], self.seed, i, self.row_offset,
+                         self.step_t)
+        return 1 + self.n_layers * (2 if self.bn else 1)
 
     def _train_kernels(self, slot, with_optimizer: bool = True) -> int:
         """Enqueue one full training step on the current stream (+ a forked side branch). Returns #kernels."""
@@ -214,6 +227,10 @@ class FusedDeepFM:
         n += 1
         side = self._side
         for i in range(top, -1, -1):
+            if self.bn:  # dz[i] holds d(BN output); turn it into d(pre-activation) in place (BN + ReLU backward)
+                K.bn_bwd(self.dz[i], self.zbuf[i], self._w("bn_%d.gamma" % i), self.bn_mean[i], self.bn_rstd[i],
+                         self._g("bn_%d.gamma" % i), self._g("bn_%d.beta" % i))
+                n += 1
             # fork: wgrad (+ bias colsum) of layer i only needs dz[i]; the dgrad chain continues on `cur`
             ev = torch.cuda.Event()
             ev.record(cur)

@@ -120,3 +120,20 @@ def flat_opt_step(w, g, s0, s1, opt_name: str, lr: float, beta1: float, beta2: f
 
 def cast_f32_bf16(src: torch.Tensor, dst: torch.Tensor) -> None:
     _lib.check(_lib.load().dfm_cast_f32_bf16(_p(src), _p(dst), c_longlong(src.numel()), _stream()))
+
+
+def bn_fwd(z, out, gamma, beta, mov_mean, mov_var, save_mean, save_rstd, decay: float, train: bool, keep_prob: float = 1.0,
+           seed: int = 0, layer: int = 0, row_offset: int = 0, step_ptr: Optional[torch.Tensor] = None) -> None:
+    """Batch norm after ReLU (+ inverted dropout in training), bf16 in/out, fp32 statistics (csrc/batchnorm.cu)."""
+    B, H = z.shape
+    _lib.check(_lib.load().dfm_bn_fwd(_p(z), c_int(z.stride(0)), _p(out), c_int(out.stride(0)), c_int(B), c_int(H),
+                                      _p(gamma), _p(beta), _p(mov_mean), _p(mov_var), _p(save_mean), _p(save_rstd),
+                                      c_float(decay), c_int(1 if train else 0), c_float(keep_prob), c_uint64(seed),
+                                      c_int(layer), c_int(row_offset), _p(step_ptr), _stream()))
+
+
+def bn_bwd(dy_inout, z, gamma, save_mean, save_rstd, g_gamma, g_beta) -> None:
+    B, H = z.shape
+    _lib.check(_lib.load().dfm_bn_bwd(_p(dy_inout), c_int(dy_inout.stride(0)), _p(z), c_int(z.stride(0)), c_int(B),
+                                      c_int(H), _p(gamma), _p(save_mean), _p(save_rstd), _p(g_gamma), _p(g_beta),
+                                      _stream()))

@@ -231,10 +231,17 @@ class FusedDataParallel(FusedDeepFM):
         dist.barrier(group=self.group)
         n = self.layout.trainable_numel
         if self.rank == src:
+            # parameters: one pass of multicast (NVLS) or per-peer P2P stores from inside a kernel (bcast_state)
+            lib = _nlib.load()
+            n = (self.P.numel() + 3) // 4 * 4
+            _nlib.check(lib.dfm_bcast_f32(self._tables["P"], c_void_p(self.arena.mc("P")), c_longlong(min(n, self.P.numel() // 4 * 4)),
+                                          c_int(self.rank), c_int(self.world), c_int(1 if self.use_nvls else 0),
+                                          c_void_p(torch.cuda.current_stream().cuda_stream)))
             for r in range(self.world):
                 if r == src:
                     continue
-                self.arena.peer_view("P", r).copy_(self.P)
+                if self.P.numel() % 4:
+                    self.arena.peer_view("P", r)[-(self.P.numel() % 4):].copy_(self.P[-(self.P.numel() % 4):])
                 self.arena.peer_view("shadow", r).copy_(self.shadow)
         step = self.step_t.clone()
         dist.broadcast(step, src, group=self.group)

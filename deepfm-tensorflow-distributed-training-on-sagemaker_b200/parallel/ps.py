@@ -63,12 +63,15 @@ class SharedParamStore:
                 f.truncate(self.total * 4)
         self.flat = torch.from_file(path, shared=True, size=self.total, dtype=torch.float32)
         self.pinned = False
+        self.dev_base = 0  # device-visible alias of the store (0 = not mapped)
         if pin and torch.cuda.is_available():
             try:
                 import ctypes
                 from ..ops import lib as _nlib
+                dp = ctypes.c_void_p(0)
                 self.pinned = _nlib.load().dfm_host_register(ctypes.c_void_p(self.flat.data_ptr()),
-                                                             ctypes.c_ulonglong(self.total * 4)) == 0
+                                                             ctypes.c_ulonglong(self.total * 4), ctypes.byref(dp)) == 0
+                self.dev_base = int(dp.value or 0) if self.pinned else 0
             except Exception:
                 self.pinned = False
         if create:
@@ -83,6 +86,10 @@ class SharedParamStore:
         off, shape = self.offsets[name]
         n = int(np.prod(shape))
         return self.flat[off:off + n].view(shape)
+
+    def dev_ptr(self, name: str) -> int:
+        """Device-visible address of a variable inside the mapped store (for the zero-copy gather kernel)."""
+        return self.dev_base + self.offsets[name][0] * 4 if self.dev_base else 0
 
     def slots(self, name: str) -> List[torch.Tensor]:
         return [self.view("%s/%s" % (name, s)) for s in SLOT_SUFFIXES[self.opt.name]]
@@ -174,14 +181,26 @@ class AsyncPSTrainer:
         u, inv = torch.unique(ids_d, return_inverse=True)
         U = int(u.numel())
         u_host = u.cpu()
-        # ---- pull: host gather into pinned staging, H2D on the side stream
-        torch.index_select(st.view("fm_v"), 0, u_host, out=self.h_rows[:U])
-        torch.index_select(st.view("fm_w"), 0, u_host, out=self.h_w[:U])
         for n in self.dense_names:
             self.h_dense[n].copy_(st.view(n))
+        self.side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(self.side):
-            m._w("fm_v")[:U].copy_(self.h_rows[:U], non_blocking=True)
-            m._w("fm_w")[:U].copy_(self.h_w[:U], non_blocking=True)
+            if st.dev_base:
+                # ---- pull: the GPU gathers the touched rows straight out of the mapped host store (zero-copy)
+                import ctypes
+                from ..ops import lib as _nlib
+                lib, sp = _nlib.load(), ctypes.c_void_p(self.side.cuda_stream)
+                K = self.cfg.embedding_size
+                _nlib.check(lib.dfm_ps_gather(ctypes.c_void_p(st.dev_ptr("fm_v")), ctypes.c_void_p(u.data_ptr()),
+                                              ctypes.c_int(U), ctypes.c_int(K), ctypes.c_void_p(m._w("fm_v").data_ptr()), sp))
+                _nlib.check(lib.dfm_ps_gather(ctypes.c_void_p(st.dev_ptr("fm_w")), ctypes.c_void_p(u.data_ptr()),
+                                              ctypes.c_int(U), ctypes.c_int(1), ctypes.c_void_p(m._w("fm_w").data_ptr()), sp))
+            else:
+                # ---- pull: host gather into pinned staging, H2D on the side stream
+                torch.index_select(st.view("fm_v"), 0, u_host, out=self.h_rows[:U])
+                torch.index_select(st.view("fm_w"), 0, u_host, out=self.h_w[:U])
+                m._w("fm_v")[:U].copy_(self.h_rows[:U], non_blocking=True)
+                m._w("fm_w")[:U].copy_(self.h_w[:U], non_blocking=True)
             for n in self.dense_names:
                 m._w(n).copy_(self.h_dense[n], non_blocking=True)
         torch.cuda.current_stream().wait_stream(self.side)

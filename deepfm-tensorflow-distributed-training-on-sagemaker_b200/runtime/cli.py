@@ -42,6 +42,22 @@ def channel_names(env=os.environ) -> List[str]:
     return ["evaluation", "training"]
 
 
+def configure_host_threads(F, env) -> None:
+    """CPU threading knobs of the PS trainer (PS:405-411,428-430; README-EN:18-32): it disables MKL thread binding
+    (`KMP_AFFINITY=verbose,disabled`), sets `OMP_NUM_THREADS` and TF's intra/inter-op pools to the vCPU count. Same idea
+    here for the torch CPU backend and the host side of the loaders: split the vCPUs over the local workers."""
+    import torch
+    per_worker = max(1, int(F.num_CPUs) // max(1, int(F.worker_per_host) if F.worker_per_host > 1 else env.world_size))
+    os.environ.setdefault("KMP_AFFINITY", "verbose,disabled" if os.environ.get("DFM_VERBOSE_THREADS") else "disabled")
+    os.environ.setdefault("KMP_SETTINGS", "0")
+    os.environ.setdefault("OMP_NUM_THREADS", str(per_worker))
+    try:
+        torch.set_num_threads(per_worker)
+        torch.set_num_interop_threads(max(1, min(per_worker, F.num_threads)))
+    except RuntimeError:
+        pass  # inter-op pool already started
+
+
 def main(argv: Optional[List[str]] = None) -> int:
     argv = list(sys.argv[1:] if argv is None else argv)
     if "--help" in argv or "-h" in argv:
@@ -53,6 +69,7 @@ def main(argv: Optional[List[str]] = None) -> int:
     if F.backend == "torch" and F.num_GPUs == 0:
         use_cuda = False
     env = init_from_env(use_cuda)
+    configure_host_threads(F, env)
     if env.is_chief:
         print(sys.argv)
         print_flags(F)

@@ -31,7 +31,7 @@ class Trainer:
         self.world, self.rank = world_size, rank
         self.opt = optimizer or TF1Optimizer("Adam", 5e-4)
         if backend == "auto":
-            backend = "fused" if (torch.cuda.is_available() and not cfg.batch_norm) else "torch"
+            backend = "fused" if torch.cuda.is_available() else "torch"
         self.backend = backend
         self.comm_name = "none"
         gb = batch_size * world_size
@@ -65,6 +65,8 @@ class Trainer:
                 from ..parallel.dp import install_torch_allreduce
                 install_torch_allreduce(self.model, process_group)
                 self.comm_name = "torch.distributed.all_reduce"
+        import os as _os
+        self.nvtx = bool(_os.environ.get("DFM_NVTX"))  # NVTX range per step for nsys/ncu timelines
         self._cuda = self.dev.type == "cuda"
         self._nslots = len(getattr(self.model, "in_slots", [])) or 1
         self._k = 0
@@ -134,6 +136,15 @@ class Trainer:
         return self._train_host(lambda slot: self.model.load_inputs(ids, vals, labels, slot, non_blocking=True))
 
     def _train_host(self, load_fn):
+        if self.nvtx:
+            torch.cuda.nvtx.range_push("deepfm_b200.step")
+        try:
+            return self._train_host_impl(load_fn)
+        finally:
+            if self.nvtx:
+                torch.cuda.nvtx.range_pop()
+
+    def _train_host_impl(self, load_fn):
         main = torch.cuda.current_stream(self.dev)
         slot = self._k % self._nslots
         self._k += 1

@@ -49,6 +49,14 @@ int dfm_logit_loss(const void* x_bf16, int ldx, int H, const float* w_out, const
 /* out[j] += sum_b a[b,j] * (w ? w[b] : 1): bias gradients (w = NULL) and g_w_out = X_top^T dy (w = dy). */
 int dfm_colsum_bf16(const void* a_bf16, int lda, int B, int H, const float* w, float* out, void* stream);
 
+/* ---- batch norm after ReLU (+ dropout) for --batch_norm (batch_norm_layer, PS:288-292; applied at PS:215-218) */
+int dfm_bn_fwd(const void* z_bf16, int ldz, void* out_bf16, int ldo, int B, int H, const float* gamma, const float* beta,
+               float* mov_mean, float* mov_var, float* save_mean, float* save_rstd, float decay, int train,
+               float keep_prob, unsigned long long seed, int layer, int row_offset, const unsigned long long* step_ptr,
+               void* stream);
+int dfm_bn_bwd(void* dy_inout_bf16, int ldd, const void* z_bf16, int ldz, int B, int H, const float* gamma,
+               const float* save_mean, const float* save_rstd, float* g_gamma, float* g_beta, void* stream);
+
 /* ---- streaming AUC histogram (tf.metrics.auc, PS:249-251) ---- */
 int dfm_auc_hist(const float* prob, const float* labels, int B, const float* thr, int T, float* hist, void* stream);
 
@@ -75,6 +83,9 @@ int dfm_allreduce_opt_step(void* const* g_ptrs, void* const* p_ptrs, void* const
                            unsigned long long* step_ptr, float* reg_local, unsigned int* done_counter,
                            unsigned int* seq_ptr, int use_nvls, int grid_blocks, void* stream);
 
+/* ---- state broadcast from one rank into every replica (replaces BroadcastGlobalVariablesHook(0), HVD:372) */
+int dfm_bcast_f32(void* const* ptrs, void* mc, long long n, int rank, int world, int use_nvls, void* stream);
+
 /* ---- row-sharded embedding tables with the all-to-all fused into the kernels (no counterpart in the reference beyond
  * the partitioner advice of PDF p32). Pointer tables: host arrays of `world` device pointers into symmetric
  * memory (table shards v/w, gradient shards gv/gw, touched-row bitmaps, barrier flags of dfm_sharded_flag_words() words).
@@ -97,7 +108,9 @@ int dfm_sparse_row_opt(void* const* v, void* const* w, void* const* gv, void* co
 /* ---- runtime switches / host helpers */
 int dfm_pdl_enabled(void);            /* programmatic dependent launch between the step kernels (default on; DFM_PDL=0) */
 void dfm_set_pdl(int on);
-int dfm_host_register(void* ptr, unsigned long long bytes);   /* page-lock the parameter-server store (HOST pointer) */
+int dfm_host_register(void* ptr, unsigned long long bytes, void** dev_ptr); /* page-lock + map the PS store (HOST pointer) */
+/* zero-copy parameter-server pull: out[i,:] = table[ids[i],:], table = device alias of the host store (X3 / row 11) */
+int dfm_ps_gather(const float* table_dev, const long long* ids, int n, int K, float* out, void* stream);
 int dfm_host_unregister(void* ptr);
 
 /* ---- flat optimizer step that allocates nothing (no counterpart in the reference: TF owns its own allocator).

@@ -78,6 +78,38 @@ def test_fused_grads_match_oracle(cuda_lib):
         assert err < 2e-2, (k, err)
 
 
+def test_fused_batch_norm_grads_and_moving_stats(cuda_lib):
+    """--batch_norm path (BN after ReLU, then dropout): gradients incl. gamma/beta and the moving statistics."""
+    from deepfm_b200.models import DeepFMConfig, init_params
+    from deepfm_b200.models.fused import FusedDeepFM
+    from deepfm_b200.models.oracle import oracle_forward, oracle_grads
+    cfg = DeepFMConfig(field_size=39, feature_size=3000, embedding_size=32, deep_layers=[128, 64], dropout=[0.8, 1.0],
+                       l2_reg=0.0, batch_norm=True, batch_norm_decay=0.9)
+    B = 512
+    params = init_params(cfg, seed=4)
+    for k in params:
+        if k.endswith("gamma"):
+            params[k].uniform_(0.5, 1.5)
+        if k.endswith("beta") or k.endswith("bias"):
+            params[k].normal_(0, 0.1)
+    m = FusedDeepFM(cfg, B, seed=11, params=params, use_graph=False)
+    ids, vals, labels = _mk(cfg, B, seed=2)
+    g = m.compute_grads(ids.cuda(), vals.cuda(), labels.cuda())
+    ref_p = {k: v.clone().cuda() for k, v in params.items()}
+    r = oracle_grads(ref_p, cfg, ids.cuda(), vals.cuda(), labels.cuda(), True, 11, 0, 0, compute_dtype=torch.bfloat16)
+    for k, ref in r["grads"].items():
+        err = float((g[k] - ref).abs().max()) / (float(ref.abs().max()) + 1e-12)
+        assert err < 4e-2, (k, err)
+    got = m.named_parameters()
+    for k, v in r["bn_updates"].items():
+        assert torch.allclose(got[k], v, rtol=2e-2, atol=2e-3), k
+    # inference uses the moving statistics
+    p = m.predict(ids.cuda(), vals.cuda())
+    ref_now = {k: v.clone() for k, v in got.items()}
+    y = oracle_forward(ref_now, cfg, ids.cuda(), vals.cuda(), False, compute_dtype=torch.bfloat16)
+    assert torch.allclose(p, torch.sigmoid(y), atol=5e-3)
+
+
 def test_fused_eval_predict_and_auc(cuda_lib):
     from deepfm_b200.models import DeepFMConfig, init_params
     from deepfm_b200.models.fused import FusedDeepFM
