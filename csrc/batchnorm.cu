@@ -2,6 +2,7 @@
 // `tf.contrib.layers.batch_norm(decay, center, scale, updates_collections=None)` applied after the fully-connected
 // ReLU, PS:215-216, then dropout PS:218). Per replica, like the reference (no cross-rank statistics).
 //
+//   (z = relu(xW+b) is kept in fp32: BN multiplies rounding error of z by rstd, up to 31x at eps = 1e-3)
 //   train:  mu, var = batch moments (biased) of z = relu(xW+b);  y = gamma * (z - mu) * rsqrt(var + eps) + beta
 //           moving_mean/var <- decay * moving + (1 - decay) * batch        (in place: updates_collections=None)
 //           out = dropout(y)  (same Philox stream as the GEMM epilogue)      eps = 0.001 (contrib default)
@@ -32,7 +33,7 @@ __device__ __forceinline__ float2 bn_block_colsum2(float a, float b, float (*sa)
 }
 
 __global__ void __launch_bounds__(kBnThreads)
-bn_fwd_kernel(const __nv_bfloat16* __restrict__ z, int ldz, __nv_bfloat16* __restrict__ out, int ldo, int B, int H,
+bn_fwd_kernel(const float* __restrict__ z, int ldz, __nv_bfloat16* __restrict__ out, int ldo, int B, int H,
               const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ mov_mean,
               float* __restrict__ mov_var, float* __restrict__ save_mean, float* __restrict__ save_rstd, float decay,
               int train, DropoutCfg drop, const unsigned long long* __restrict__ step_ptr) {
@@ -47,7 +48,7 @@ bn_fwd_kernel(const __nv_bfloat16* __restrict__ z, int ldz, __nv_bfloat16* __res
     float s = 0.f, ss = 0.f;
     if (col_ok)
       for (int r = ty; r < B; r += kBnThreads / 32) {
-        const float v = __bfloat162float(z[(size_t)r * ldz + j]);
+        const float v = z[(size_t)r * ldz + j];
         s += v; ss += v * v;
       }
     const float2 t = bn_block_colsum2(s, ss, sa, sb);
@@ -69,7 +70,7 @@ bn_fwd_kernel(const __nv_bfloat16* __restrict__ z, int ldz, __nv_bfloat16* __res
   if (train && drop.enabled && step_ptr) step = *step_ptr;
   drop.step_lo = (uint32_t)step; drop.step_hi = (uint32_t)(step >> 32);
   for (int r = ty; r < B; r += kBnThreads / 32) {
-    float y = g * (__bfloat162float(z[(size_t)r * ldz + j]) - mean) * rstd + b;
+    float y = g * (z[(size_t)r * ldz + j] - mean) * rstd + b;
     if (train && drop.enabled) {
       const uint64_t elem = (uint64_t)(r + drop.row_offset) * (uint64_t)H + (uint64_t)j;
       const uint4 rnd = dropout_words(drop, elem >> 2);
@@ -84,7 +85,7 @@ bn_fwd_kernel(const __nv_bfloat16* __restrict__ z, int ldz, __nv_bfloat16* __res
 // dy: in = gradient w.r.t. the BN output (dropout already applied by the producer); out (in place) = gradient w.r.t.
 // the pre-activation of the fully-connected layer (through BN and ReLU).
 __global__ void __launch_bounds__(kBnThreads)
-bn_bwd_kernel(__nv_bfloat16* __restrict__ dy, int ldd, const __nv_bfloat16* __restrict__ z, int ldz, int B, int H,
+bn_bwd_kernel(__nv_bfloat16* __restrict__ dy, int ldd, const float* __restrict__ z, int ldz, int B, int H,
               const float* __restrict__ gamma, const float* __restrict__ save_mean, const float* __restrict__ save_rstd,
               float* __restrict__ g_gamma, float* __restrict__ g_beta) {
   __shared__ float sa[kBnThreads / 32][33], sb[kBnThreads / 32][33];
@@ -98,7 +99,7 @@ bn_bwd_kernel(__nv_bfloat16* __restrict__ dy, int ldd, const __nv_bfloat16* __re
   if (col_ok)
     for (int r = ty; r < B; r += kBnThreads / 32) {
       const float d = __bfloat162float(dy[(size_t)r * ldd + j]);
-      const float xh = (__bfloat162float(z[(size_t)r * ldz + j]) - mean) * rstd;
+      const float xh = (z[(size_t)r * ldz + j] - mean) * rstd;
       s += d; sx += d * xh;
     }
   const float2 t = bn_block_colsum2(s, sx, sa, sb);
@@ -109,7 +110,7 @@ bn_bwd_kernel(__nv_bfloat16* __restrict__ dy, int ldd, const __nv_bfloat16* __re
   }
   const float g = gamma[j], m1 = t.x / B, m2 = t.y / B;
   for (int r = ty; r < B; r += kBnThreads / 32) {
-    const float zz = __bfloat162float(z[(size_t)r * ldz + j]);
+    const float zz = z[(size_t)r * ldz + j];
     const float xh = (zz - mean) * rstd;
     const float d = __bfloat162float(dy[(size_t)r * ldd + j]);
     const float dz = zz > 0.f ? g * rstd * (d - m1 - xh * m2) : 0.f;
@@ -135,7 +136,7 @@ int dfm_bn_fwd(const void* z, int ldz, void* out, int ldo, int B, int H, const f
   d.seed_lo = (uint32_t)seed; d.seed_hi = (uint32_t)(seed >> 32); d.step_lo = d.step_hi = 0;
   d.layer = (uint32_t)layer; d.row_offset = (uint32_t)row_offset;
   DFM_CHECK(launch_k(bn_fwd_kernel, dim3(ceil_div(H, 32)), dim3(kBnThreads), 0, (cudaStream_t)stream,
-                     (const __nv_bfloat16*)z, ldz, (__nv_bfloat16*)out, ldo, B, H, gamma, beta, mov_mean, mov_var,
+                     (const float*)z, ldz, (__nv_bfloat16*)out, ldo, B, H, gamma, beta, mov_mean, mov_var,
                      save_mean, save_rstd, decay, train, d, step_ptr));
   return DFM_OK;
 }
@@ -144,7 +145,7 @@ int dfm_bn_bwd(void* dy_inout, int ldd, const void* z, int ldz, int B, int H, co
                const float* save_rstd, float* g_gamma, float* g_beta, void* stream) {
   DFM_REQUIRE(B > 0 && H > 0, "bn_bwd: empty problem");
   DFM_CHECK(launch_k(bn_bwd_kernel, dim3(ceil_div(H, 32)), dim3(kBnThreads), 0, (cudaStream_t)stream,
-                     (__nv_bfloat16*)dy_inout, ldd, (const __nv_bfloat16*)z, ldz, B, H, gamma, save_mean, save_rstd,
+                     (__nv_bfloat16*)dy_inout, ldd, (const float*)z, ldz, B, H, gamma, save_mean, save_rstd,
                      g_gamma, g_beta));
   return DFM_OK;
 }

@@ -45,6 +45,7 @@ struct GemmParams {
   const __nv_bfloat16* mask;
   int ldmask;
   float mask_scale;
+  int out_f32;  // EPI_BIAS_ACT only: store fp32 (pre-batch-norm activations must not be rounded to bf16)
 };
 
 template <int BN>
@@ -267,6 +268,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           for (int j = 0; j < 16; ++j)
             if (n + j < p.N) atomicAdd(orow + j, v[j]);
         }
+      } else if (EPI == EPI_BIAS_ACT && p.out_f32) {
+        float* orow = reinterpret_cast<float*>(p.out) + (size_t)row * p.ldo + n;
+        if (full16 && (p.ldo % 4 == 0)) {
+#pragma unroll
+          for (int j = 0; j < 16; j += 4)
+            *reinterpret_cast<float4*>(orow + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (n + j < p.N) orow[j] = v[j];
+        }
       } else {
         __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.ldo + n;
         if (full16 && (p.ldo % 8 == 0)) {
@@ -426,6 +438,7 @@ int dfm_gemm_plan_create(void** plan_out, int mode, const void* A, int lda, cons
   p.drop.step_lo = p.drop.step_hi = 0; p.drop.layer = (uint32_t)layer; p.drop.row_offset = (uint32_t)row_offset;
   p.step_ptr = step_ptr;
   p.mask = reinterpret_cast<const __nv_bfloat16*>(mask); p.ldmask = ldmask; p.mask_scale = mask_scale;
+  p.out_f32 = 0;
   pl->grid = dim3(m_tiles, ceil_div(N, pl->bn), splits);
   *plan_out = pl;
   return DFM_OK;
@@ -434,6 +447,14 @@ int dfm_gemm_plan_create(void** plan_out, int mode, const void* A, int lda, cons
 int dfm_gemm_plan_info(void* plan, int* bn, int* grid_x, int* grid_y, int* grid_z) {
   GemmPlan* pl = reinterpret_cast<GemmPlan*>(plan);
   *bn = pl->bn; *grid_x = pl->grid.x; *grid_y = pl->grid.y; *grid_z = pl->grid.z;
+  return DFM_OK;
+}
+
+// Forward plans only: write the epilogue result as fp32 (ldo then counts fp32 elements). Used by the batch-norm path.
+int dfm_gemm_plan_set_out_f32(void* plan, int on) {
+  GemmPlan* pl = reinterpret_cast<GemmPlan*>(plan);
+  DFM_REQUIRE(pl->mode == 0, "out_f32 applies to forward plans only");
+  pl->p.out_f32 = on ? 1 : 0;
   return DFM_OK;
 }
 

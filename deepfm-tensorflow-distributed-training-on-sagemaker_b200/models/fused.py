@@ -113,7 +113,7 @@ class FusedDeepFM:
         self.dz = [torch.zeros(B, h, **bf) for h in cfg.deep_layers]
         self.bn = bool(cfg.batch_norm)
         if self.bn:  # ReLU outputs (pre-BN) and the saved batch statistics
-            self.zbuf = [torch.zeros(B, h, **bf) for h in cfg.deep_layers]
+            self.zbuf = [torch.zeros(B, h, **f32) for h in cfg.deep_layers]  # fp32: BN amplifies rounding of z
             self.bn_mean = [torch.zeros(h, **f32) for h in cfg.deep_layers]
             self.bn_rstd = [torch.zeros(h, **f32) for h in cfg.deep_layers]
         self.dy = torch.zeros(B, **f32)
@@ -166,7 +166,7 @@ class FusedDeepFM:
             Wb = self._wb("mlp%d.weight" % i)
             bias = self._w("mlp%d.bias" % i)
             if self.bn:  # GEMM epilogue stops at ReLU; BN + dropout run in bn_fwd
-                plan = K.GemmPlan("fwd", x_in, Wb, self.zbuf[i], B, h, d_in, bias=bias, relu=True)
+                plan = K.GemmPlan("fwd", x_in, Wb, self.zbuf[i], B, h, d_in, bias=bias, relu=True).set_out_f32()
                 self.fwd_train.append(plan)
                 self.fwd_eval.append(plan)
             else:

@@ -76,6 +76,10 @@ class GemmPlan:
         _lib.load().dfm_gemm_plan_info(self._h, ctypes.byref(bn), ctypes.byref(gx), ctypes.byref(gy), ctypes.byref(gz))
         return {"bn": bn.value, "grid": (gx.value, gy.value, gz.value)}
 
+    def set_out_f32(self, on: bool = True) -> "GemmPlan":
+        _lib.check(_lib.load().dfm_gemm_plan_set_out_f32(self._h, c_int(1 if on else 0)))
+        return self
+
     def run(self) -> None:
         _lib.check(_lib.load().dfm_gemm_run(self._h, _stream()))
 

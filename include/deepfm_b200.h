@@ -38,6 +38,7 @@ int dfm_gemm_plan_create(void** plan_out, int mode, const void* A, int lda, cons
                          float mask_scale, int split_k);
 int dfm_gemm_plan_info(void* plan, int* bn, int* grid_x, int* grid_y, int* grid_z);
 int dfm_gemm_plan_set_row_offset(void* plan, int row_offset);
+int dfm_gemm_plan_set_out_f32(void* plan, int on); /* forward plans: fp32 output (pre-batch-norm activations) */
 void dfm_gemm_plan_destroy(void* plan);
 int dfm_gemm_run(void* plan, void* stream);
 
@@ -50,11 +51,11 @@ int dfm_logit_loss(const void* x_bf16, int ldx, int H, const float* w_out, const
 int dfm_colsum_bf16(const void* a_bf16, int lda, int B, int H, const float* w, float* out, void* stream);
 
 /* ---- batch norm after ReLU (+ dropout) for --batch_norm (batch_norm_layer, PS:288-292; applied at PS:215-218) */
-int dfm_bn_fwd(const void* z_bf16, int ldz, void* out_bf16, int ldo, int B, int H, const float* gamma, const float* beta,
+int dfm_bn_fwd(const float* z, int ldz, void* out_bf16, int ldo, int B, int H, const float* gamma, const float* beta,
                float* mov_mean, float* mov_var, float* save_mean, float* save_rstd, float decay, int train,
                float keep_prob, unsigned long long seed, int layer, int row_offset, const unsigned long long* step_ptr,
                void* stream);
-int dfm_bn_bwd(void* dy_inout_bf16, int ldd, const void* z_bf16, int ldz, int B, int H, const float* gamma,
+int dfm_bn_bwd(void* dy_inout_bf16, int ldd, const float* z, int ldz, int B, int H, const float* gamma,
                const float* save_mean, const float* save_rstd, float* g_gamma, float* g_beta, void* stream);
 
 /* ---- streaming AUC histogram (tf.metrics.auc, PS:249-251) ---- */
