@@ -33,7 +33,7 @@ template <int G>
 __global__ void __launch_bounds__(kEmbThreads)
 emb_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, const float* __restrict__ fm_w,
                   const float* __restrict__ fm_v, __nv_bfloat16* __restrict__ x0, int ldx, float* __restrict__ S,
-                  float* __restrict__ yfm, int B, int F, int N) {
+                  float* __restrict__ yfm, int B, int F, int N, float* __restrict__ zero_scalars, int n_zero) {
   constexpr int K = 4 * G;
   constexpr int FG = 32 / G;
   const int lane = threadIdx.x & 31;
@@ -41,6 +41,8 @@ emb_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, c
   const int g = lane % G, fg = lane / G;
   pdl_launch_dependents();
   pdl_wait();
+  // first kernel of a training step: also clears the step's loss accumulators (saves a memset node on the chain)
+  if (blockIdx.x == 0 && threadIdx.x < n_zero) zero_scalars[threadIdx.x] = 0.f;
   if (sample >= B) return;  // warp-uniform
   const int* sid = ids + (size_t)sample * F;
   const float* sval = vals + (size_t)sample * F;
@@ -188,9 +190,10 @@ emb_bwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, cons
 
 template <int G>
 static int launch_fwd(const int* ids, const float* vals, const float* fm_w, const float* fm_v, __nv_bfloat16* x0,
-                      int ldx, float* S, float* yfm, int B, int F, int N, cudaStream_t st) {
+                      int ldx, float* S, float* yfm, int B, int F, int N, float* zero_scalars, int n_zero,
+                      cudaStream_t st) {
   DFM_CHECK(launch_k(emb_fm_fwd_kernel<G>, dim3((unsigned)ceil_div(B, kEmbThreads / 32)), dim3(kEmbThreads), 0, st, ids,
-                     vals, fm_w, fm_v, x0, ldx, S, yfm, B, F, N));
+                     vals, fm_w, fm_v, x0, ldx, S, yfm, B, F, N, zero_scalars, n_zero));
   return DFM_OK;
 }
 
@@ -224,11 +227,14 @@ extern "C" {
 
 // ids [B,F] int32, vals [B,F] f32, fm_w [N] f32, fm_v [N,K] f32 (16-byte aligned rows)
 // -> x0 [B, ldx>=F*K] bf16, S [B,K] f32, yfm [B] f32
+// zero_scalars/n_zero (optional): up to 32 floats cleared by the kernel (the step's loss accumulators).
 int dfm_emb_fm_fwd(const int* ids, const float* vals, const float* fm_w, const float* fm_v, void* x0, int ldx, float* S,
-                   float* yfm, int B, int F, int K, int N, void* stream) {
+                   float* yfm, int B, int F, int K, int N, float* zero_scalars, int n_zero, void* stream) {
+  DFM_REQUIRE(n_zero >= 0 && n_zero <= 32, "emb_fm_fwd: n_zero must be in [0,32]");
   DFM_REQUIRE(B > 0 && F > 0 && N > 0, "emb_fm_fwd: empty problem");
   DFM_REQUIRE(ldx >= F * K && ldx % 4 == 0, "emb_fm_fwd: ldx must be >= F*K and a multiple of 4");
-#define CALL(G) launch_fwd<G>(ids, vals, fm_w, fm_v, (__nv_bfloat16*)x0, ldx, S, yfm, B, F, N, (cudaStream_t)stream)
+#define CALL(G) \
+  launch_fwd<G>(ids, vals, fm_w, fm_v, (__nv_bfloat16*)x0, ldx, S, yfm, B, F, N, zero_scalars, n_zero, (cudaStream_t)stream)
   DFM_DISPATCH_G(K, CALL)
 #undef CALL
 }

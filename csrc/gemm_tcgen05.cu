@@ -56,7 +56,7 @@ struct GemmCfg {
   static constexpr int STAGES_RAW = (200 * 1024) / STAGE_BYTES;
   static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
   static constexpr int TMEM_COLS = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + BN * 4 /*bias*/;
 };
 
 template <int BN, bool A_MN, bool B_MN, int EPI>
@@ -73,6 +73,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint64_t* empty_bar = full_bar + Cfg::STAGES;
   uint64_t* tmem_full_bar = empty_bar + Cfg::STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+  float* s_bias = reinterpret_cast<float*>(smem + Cfg::STAGES * Cfg::STAGE_BYTES + 256);  // [BN]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -163,21 +164,68 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int q = warp & 3;
     const int sub = (warp - 2) >> 2;
     const int row = m0 + q * 32 + lane;
-    mbar_wait(tmem_full_bar, 0);
-    tc_fence_after();
     const bool row_ok = row < p.M;
+    constexpr int NCHUNK = BN / 16;
+    constexpr int WPQ = kEpiWarps / 4;
+    constexpr int MYCH = (NCHUNK + WPQ - 1) / WPQ;
+    const bool n_mult4 = (p.N & 3) == 0;
     DropoutCfg drop = p.drop;
+
+    // ---- work that does not need the accumulator runs NOW, while TMA/MMA are still busy: stage the bias tile in shared
+    // memory, draw the dropout keep-bits (Philox) / read the ReLU-dropout mask of the previous layer, 16 bits per chunk
+    uint32_t bits[MYCH];
+    bool fastc[MYCH];
     if constexpr (EPI == EPI_BIAS_ACT) {
+      for (int j = threadIdx.x - 64; j < BN; j += 32 * kEpiWarps)
+        s_bias[j] = (p.bias && n0 + j < p.N) ? __ldg(p.bias + n0 + j) : 0.f;
       if (drop.enabled && p.step_ptr) {
         const unsigned long long step = *p.step_ptr;
         drop.step_lo = (uint32_t)step;
         drop.step_hi = (uint32_t)(step >> 32);
       }
     }
-    const bool n_mult4 = (p.N & 3) == 0;
+#pragma unroll
+    for (int k = 0; k < MYCH; ++k) {
+      const int c = (sub + k * WPQ) * 16;
+      const int n = n0 + c;
+      bits[k] = 0xFFFFu;
+      fastc[k] = (c < BN) && row_ok && (n + 16 <= p.N);
+      if constexpr (EPI == EPI_BIAS_ACT) {
+        fastc[k] = fastc[k] && n_mult4;
+        if (fastc[k] && drop.enabled) {
+          const uint64_t quad0 = ((uint64_t)(row + drop.row_offset) * (uint64_t)p.N + (uint64_t)n) >> 2;
+          uint32_t b = 0;
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            const uint4 r = dropout_words(drop, quad0 + t);
+            b |= (r.x < drop.threshold ? 1u : 0u) << (4 * t) | (r.y < drop.threshold ? 1u : 0u) << (4 * t + 1) |
+                 (r.z < drop.threshold ? 1u : 0u) << (4 * t + 2) | (r.w < drop.threshold ? 1u : 0u) << (4 * t + 3);
+          }
+          bits[k] = b;
+        }
+      } else if constexpr (EPI == EPI_MASK) {
+        fastc[k] = fastc[k] && (p.ldmask % 8 == 0);
+        if (fastc[k] && p.mask) {
+          const uint4* mp = reinterpret_cast<const uint4*>(p.mask + (size_t)row * p.ldmask + n);
+          const uint4 m0v = __ldg(mp), m1v = __ldg(mp + 1);
+          const uint32_t mw[8] = {m0v.x, m0v.y, m0v.z, m0v.w, m1v.x, m1v.y, m1v.z, m1v.w};
+          uint32_t b = 0;
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            b |= ((mw[j] & 0x7FFFu) ? 1u : 0u) << (2 * j) | ((mw[j] & 0x7FFF0000u) ? 1u : 0u) << (2 * j + 1);
+          bits[k] = b;
+        }
+      }
+    }
+    if constexpr (EPI == EPI_BIAS_ACT) asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");  // s_bias ready
 
-#pragma unroll 1
-    for (int c = sub * 16; c < BN; c += 16 * (kEpiWarps / 4)) {
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+
+#pragma unroll
+    for (int k = 0; k < MYCH; ++k) {
+      const int c = (sub + k * WPQ) * 16;
+      if (c >= BN) continue;  // warp-uniform
       float v[16];
       tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
       const int n = n0 + c;
@@ -185,32 +233,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const bool full16 = (n + 16 <= p.N);
 
       if constexpr (EPI == EPI_BIAS_ACT) {
-        if (full16 && n_mult4) {
-          // fast path: vector bias loads, branch-free activation, 4 independent Philox streams
-          if (p.bias) {
-            const float4* bp = reinterpret_cast<const float4*>(p.bias + n);
-            const float4 b0 = __ldg(bp), b1 = __ldg(bp + 1), b2 = __ldg(bp + 2), b3 = __ldg(bp + 3);
-            v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
-            v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
-            v[8] += b2.x; v[9] += b2.y; v[10] += b2.z; v[11] += b2.w;
-            v[12] += b3.x; v[13] += b3.y; v[14] += b3.z; v[15] += b3.w;
-          }
-          if (p.relu) {
+        if (fastc[k]) {
+          const float scale = drop.enabled ? drop.scale : 1.f;
 #pragma unroll
-            for (int j = 0; j < 16; ++j) v[j] = fmaxf(v[j], 0.f);
-          }
-          if (drop.enabled) {
-            const uint64_t quad0 = ((uint64_t)(row + drop.row_offset) * (uint64_t)p.N + (uint64_t)n) >> 2;
-            uint4 r[4];
-#pragma unroll
-            for (int t = 0; t < 4; ++t) r[t] = dropout_words(drop, quad0 + t);
-#pragma unroll
-            for (int t = 0; t < 4; ++t) {
-              v[4 * t + 0] = (r[t].x < drop.threshold) ? v[4 * t + 0] * drop.scale : 0.f;
-              v[4 * t + 1] = (r[t].y < drop.threshold) ? v[4 * t + 1] * drop.scale : 0.f;
-              v[4 * t + 2] = (r[t].z < drop.threshold) ? v[4 * t + 2] * drop.scale : 0.f;
-              v[4 * t + 3] = (r[t].w < drop.threshold) ? v[4 * t + 3] * drop.scale : 0.f;
-            }
+          for (int j = 0; j < 16; ++j) {
+            float x = v[j] + s_bias[c + j];
+            if (p.relu) x = fmaxf(x, 0.f);
+            v[j] = ((bits[k] >> j) & 1u) ? x * scale : 0.f;
           }
         } else {
           uint64_t last_quad = ~0ull;
@@ -220,7 +249,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const int nn = n + j;
             float x = v[j];
             if (nn < p.N) {
-              if (p.bias) x += __ldg(p.bias + nn);
+              x += s_bias[c + j];
               if (p.relu) x = fmaxf(x, 0.f);
               if (drop.enabled) {
                 const uint64_t elem = (uint64_t)(row + drop.row_offset) * (uint64_t)p.N + (uint64_t)nn;
@@ -236,17 +265,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
       } else if constexpr (EPI == EPI_MASK) {
         if (p.mask) {
-          const __nv_bfloat16* mrow = p.mask + (size_t)row * p.ldmask + n;
-          if (full16 && (p.ldmask % 8 == 0)) {
-            const uint4 m0v = __ldg(reinterpret_cast<const uint4*>(mrow));
-            const uint4 m1v = __ldg(reinterpret_cast<const uint4*>(mrow) + 1);
-            const uint32_t mw[8] = {m0v.x, m0v.y, m0v.z, m0v.w, m1v.x, m1v.y, m1v.z, m1v.w};
+          if (fastc[k]) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              v[2 * j] = (mw[j] & 0x7FFFu) ? v[2 * j] * p.mask_scale : 0.f;
-              v[2 * j + 1] = (mw[j] & 0x7FFF0000u) ? v[2 * j + 1] * p.mask_scale : 0.f;
-            }
+            for (int j = 0; j < 16; ++j) v[j] = ((bits[k] >> j) & 1u) ? v[j] * p.mask_scale : 0.f;
           } else {
+            const __nv_bfloat16* mrow = p.mask + (size_t)row * p.ldmask + n;
 #pragma unroll
             for (int j = 0; j < 16; ++j) {
               if (n + j < p.N) {

@@ -188,17 +188,25 @@ class FusedDeepFM:
         K.cast_f32_bf16(self.P[a:b], self.shadow)
 
     # ------------------------------------------------------------------------------------------------ kernels
-    def _emb_forward(self, slot) -> None:
-        K.emb_fm_fwd(slot["ids"], slot["vals"], self._w("fm_w"), self._w("fm_v"), self.x0, self.Ssum, self.yfm)
+    _emb_zeroes_scalars = True  # the replicated emb_fm_fwd clears the step's loss accumulators itself
+
+    def _emb_forward(self, slot, zero_scalars: bool = False) -> None:
+        K.emb_fm_fwd(slot["ids"], slot["vals"], self._w("fm_w"), self._w("fm_v"), self.x0, self.Ssum, self.yfm,
+                     self.scalars if zero_scalars else None)
 
     def _emb_backward(self, slot) -> int:
         K.emb_bwd(slot["ids"], slot["vals"], self._w("fm_v"), self.Ssum, self.dy, self.dx0, self._g("fm_w"),
                   self._g("fm_v"))
         return 1
 
-    def _forward(self, slot, train: bool, rows: Optional[int] = None):
+    def _forward(self, slot, train: bool, rows: Optional[int] = None, zero_scalars: bool = False):
         cfg = self.cfg
-        self._emb_forward(slot)
+        if zero_scalars and self._emb_zeroes_scalars:
+            self._emb_forward(slot, True)
+        else:
+            if zero_scalars:
+                self.scalars.zero_()
+            self._emb_forward(slot)
         for i, p in enumerate(self.fwd_train if train else self.fwd_eval):
             p.run()
             if self.bn:
@@ -213,9 +221,8 @@ class FusedDeepFM:
         cfg, nl = self.cfg, self.n_layers
         cur = torch.cuda.current_stream()
         n = 0
-        self.scalars.zero_()  # loss_sum, reg_loss (one memset node)
         pre = self._pre_step(self._side)
-        n += self._forward(slot, True)
+        n += self._forward(slot, True, zero_scalars=True)  # also clears loss_sum / reg_loss
         if pre:  # join the pre-step branch (e.g. gradient zeroing under data parallelism) before the first grad write
             evp = torch.cuda.Event()
             evp.record(self._side)

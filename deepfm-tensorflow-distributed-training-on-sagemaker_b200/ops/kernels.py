@@ -27,14 +27,15 @@ def _chk_dev(*ts):
 
 
 def emb_fm_fwd(ids: torch.Tensor, vals: torch.Tensor, fm_w: torch.Tensor, fm_v: torch.Tensor, x0: torch.Tensor,
-               S: torch.Tensor, yfm: torch.Tensor) -> None:
+               S: torch.Tensor, yfm: torch.Tensor, zero_scalars: Optional[torch.Tensor] = None) -> None:
     """ids [B,F] int32, vals [B,F] f32, fm_w [N], fm_v [N,K] -> x0 [B, >=F*K] bf16, S [B,K] f32, yfm [B] f32."""
     _chk_dev(ids, vals, fm_w, fm_v, x0, S, yfm)
     assert ids.dtype == torch.int32 and vals.dtype == torch.float32 and x0.dtype == torch.bfloat16
     B, F = ids.shape
     N, K = fm_v.shape
     _lib.check(_lib.load().dfm_emb_fm_fwd(_p(ids), _p(vals), _p(fm_w), _p(fm_v), _p(x0), c_int(x0.stride(0)), _p(S),
-                                          _p(yfm), c_int(B), c_int(F), c_int(K), c_int(N), _stream()))
+                                          _p(yfm), c_int(B), c_int(F), c_int(K), c_int(N), _p(zero_scalars),
+                                          c_int(zero_scalars.numel() if zero_scalars is not None else 0), _stream()))
 
 
 def emb_bwd(ids, vals, fm_v, S, dy, dx0, g_w, g_v) -> None:

@@ -102,6 +102,7 @@ class ShardedDeepFM(FusedDataParallel):
 
     # ---- embedding kernels with the all-to-all fused in
     _train_mode = False
+    _emb_zeroes_scalars = False
 
     def _train_kernels(self, slot, with_optimizer: bool = True) -> int:
         self._train_mode = True  # the forward all-to-all synchronises with the peers only inside a training step
@@ -110,7 +111,7 @@ class ShardedDeepFM(FusedDataParallel):
         finally:
             self._train_mode = False
 
-    def _emb_forward(self, slot) -> None:
+    def _emb_forward(self, slot, zero_scalars: bool = False) -> None:
         cfg, t = self.cfg, self._t
         _nlib.check(_nlib.load().dfm_emb_fm_fwd_a2a(
             t["V"], t["W"], t["GV"], t["GW"], t["bitmap"], t["flags"], c_int(self.rank), c_int(self.world),

@@ -24,7 +24,7 @@ int dfm_device_is_sm100(void);
 
 /* ---- embedding + FM (replaces embedding_lookup x2 + FM reductions, PS:177-187,203) ---- */
 int dfm_emb_fm_fwd(const int* ids, const float* vals, const float* fm_w, const float* fm_v, void* x0_bf16, int ldx,
-                   float* S, float* yfm, int B, int F, int K, int N, void* stream);
+                   float* S, float* yfm, int B, int F, int K, int N, float* zero_scalars, int n_zero, void* stream);
 int dfm_emb_bwd(const int* ids, const float* vals, const float* fm_v, const float* S, const float* dy,
                 const void* dx0_bf16, int ldx, float* g_w, float* g_v, int B, int F, int K, int N, void* stream);
 
