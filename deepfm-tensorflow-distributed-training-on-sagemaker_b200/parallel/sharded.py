@@ -30,7 +30,15 @@ from .symm import SymmArena
 
 class ShardedDeepFM(FusedDataParallel):
     def __init__(self, cfg, batch_size, optimizer, seed, device, world_size, rank, comm: str = "auto",
-                 use_graph: bool = True, params: Optional[Dict[str, torch.Tensor]] = None, process_group=None):
+                 use_graph: bool = True, params: Optional[Dict[str, torch.Tensor]] = None, process_group=None,
+                 a2a_mode: str = "auto"):
+        """a2a_mode: 'pull' (peer loads from the owner's shard; lowest latency, small batches), 'push' (requests out,
+        rows pushed back with P2P stores, gradients pushed into owner inboxes; highest bandwidth, large batches),
+        'auto' = push from 64 Ki lookups per rank per step (env DFM_A2A overrides)."""
+        import os as _os
+        a2a_mode = _os.environ.get("DFM_A2A", a2a_mode)
+        lookups = batch_size * cfg.field_size
+        self.push = a2a_mode == "push" or (a2a_mode == "auto" and lookups >= 65536 and world_size > 1)
         self._table_src = params
         N, K = cfg.feature_size, cfg.embedding_size
         self.rows_local = (N + world_size - 1) // world_size
@@ -60,7 +68,20 @@ class ShardedDeepFM(FusedDataParallel):
         self.e32 = torch.zeros(self.B, cfg.field_size * K, **f32)
         self._fwd_blocks = max(1, min(1184, (self.B + 7) // 8))
         self._opt_blocks = max(1, min(1184, (self.words + 7) // 8))
-        self.comm_name = "sharded-embeddings fused-a2a (P2P) + " + self.comm_name
+        if self.push:
+            cap = self.B * cfg.field_size
+            self.cap = cap
+            Wn = world_size
+            pregions = [("req", Wn * cap * 4, torch.int32), ("req_cnt", 8, torch.int32), ("rows_in", cap * K, torch.float32),
+                        ("wv_in", cap, torch.float32), ("grad_in", Wn * cap * K, torch.float32),
+                        ("gw_in", Wn * cap, torch.float32), ("pflags", lib.dfm_a2a_push_flag_words(), torch.int32)]
+            self.parena = SymmArena(pregions, device, self.group)
+            self._pt = {k: self.parena.ptr_table(k) for k in ("req", "req_cnt", "rows_in", "wv_in", "grad_in", "gw_in", "pflags")}
+            self.cnt_local = torch.zeros(8, device=device, dtype=torch.int32)
+            self.pos_of_pair = torch.zeros(cap, device=device, dtype=torch.int32)
+            self.push_done = torch.zeros(1, device=device, dtype=torch.int32)
+            self._push_blocks = max(1, min(1184, (cap + 63) // 64))
+        self.comm_name = "sharded-embeddings fused-a2a (%s) + %s" % ("P2P push" if self.push else "P2P pull", self.comm_name)
         self._tables_ready = True
         torch.cuda.synchronize(device)
         dist.barrier(group=self.group)
@@ -113,6 +134,18 @@ class ShardedDeepFM(FusedDataParallel):
 
     def _emb_forward(self, slot, zero_scalars: bool = False) -> None:
         cfg, t = self.cfg, self._t
+        if self.push and self._train_mode:
+            pt = self._pt
+            p = lambda x: c_void_p(x.data_ptr())
+            self.cnt_local.zero_()
+            _nlib.check(_nlib.load().dfm_a2a_push_forward(
+                pt["req"], pt["req_cnt"], pt["rows_in"], pt["wv_in"], pt["grad_in"], pt["gw_in"], pt["pflags"],
+                c_int(self.rank), c_int(self.world), c_longlong(self.cap), p(slot["ids"]), p(slot["vals"]), p(self.V),
+                p(self.Wt), p(self.cnt_local), p(self.pos_of_pair), p(self.push_done), p(self.x0), c_void_p(0),
+                c_int(self.x0.stride(0)), p(self.Ssum), p(self.yfm), c_int(self.B), c_int(cfg.field_size),
+                c_int(cfg.embedding_size), c_longlong(cfg.feature_size), p(self.sh_seq), c_int(self._push_blocks),
+                c_void_p(torch.cuda.current_stream().cuda_stream)))
+            return
         _nlib.check(_nlib.load().dfm_emb_fm_fwd_a2a(
             t["V"], t["W"], t["GV"], t["GW"], t["bitmap"], t["flags"], c_int(self.rank), c_int(self.world),
             c_void_p(slot["ids"].data_ptr()), c_void_p(slot["vals"].data_ptr()), c_void_p(self.x0.data_ptr()),
@@ -126,12 +159,30 @@ class ShardedDeepFM(FusedDataParallel):
         cfg, t, o = self.cfg, self._t, self.opt
         lib = _nlib.load()
         st = c_void_p(torch.cuda.current_stream().cuda_stream)
+        if self.push:
+            pt = self._pt
+            q = lambda x: c_void_p(x.data_ptr())
+            _nlib.check(lib.dfm_a2a_push_backward(
+                pt["req"], pt["req_cnt"], pt["rows_in"], pt["wv_in"], pt["grad_in"], pt["gw_in"], pt["pflags"],
+                c_int(self.rank), c_int(self.world), c_longlong(self.cap), q(slot["ids"]), q(slot["vals"]),
+                q(self.pos_of_pair), q(self.e32), q(self.Ssum), q(self.dy), q(self.dx0), c_int(self.dx0.stride(0)),
+                q(self.GV), q(self.GW), q(self.bitmap), c_int(self.B), c_int(cfg.field_size), c_int(cfg.embedding_size),
+                q(self.sh_seq), c_int(self._push_blocks), st))
+        else:
+            self._bwd_pull(slot, st)
+        return self._sparse_opt(st) + (1 if self.push else 0)
+
+    def _bwd_pull(self, slot, st) -> None:
+        cfg, t, lib = self.cfg, self._t, _nlib.load()
         _nlib.check(lib.dfm_emb_bwd_a2a(
             t["V"], t["W"], t["GV"], t["GW"], t["bitmap"], t["flags"], c_int(self.rank), c_int(self.world),
             c_void_p(slot["ids"].data_ptr()), c_void_p(slot["vals"].data_ptr()), c_void_p(self.e32.data_ptr()),
             c_void_p(self.Ssum.data_ptr()), c_void_p(self.dy.data_ptr()), c_void_p(self.dx0.data_ptr()),
             c_int(self.dx0.stride(0)), c_int(self.B), c_int(cfg.field_size), c_int(cfg.embedding_size),
             c_longlong(cfg.feature_size), st))
+
+    def _sparse_opt(self, st) -> int:
+        cfg, t, o, lib = self.cfg, self._t, self.opt, _nlib.load()
         p = lambda x: c_void_p(x.data_ptr())
         z = c_void_p(0)
         _nlib.check(lib.dfm_sparse_row_opt(

@@ -106,6 +106,20 @@ int dfm_sparse_row_opt(void* const* v, void* const* w, void* const* gv, void* co
                        const unsigned long long* step_ptr, int step_offset, unsigned int* seq_ptr,
                        unsigned int* done_counter, float* reg_loss, int grid_blocks, void* stream);
 
+/* push flavour of the fused all-to-all (csrc/sharded_push.cu): requests out, rows pushed back with P2P stores, gradient
+ * rows pushed into owner inboxes. cap = B*F; cnt_local = world ints zeroed per step; grid_blocks identical on all ranks. */
+int dfm_a2a_push_flag_words(void);
+int dfm_a2a_push_forward(void* const* req, void* const* cnt, void* const* rows, void* const* wv, void* const* gin,
+                         void* const* gwin, void* const* fl, int rank, int world, long long cap, const int* ids,
+                         const float* vals, const float* V, const float* Wt, int* cnt_local, int* pos_of_pair,
+                         unsigned int* done_counter, void* x0_bf16, float* e32, int ldx, float* S, float* yfm, int B, int F,
+                         int K, long long N, const unsigned int* seq_ptr, int grid_blocks, void* stream);
+int dfm_a2a_push_backward(void* const* req, void* const* cnt, void* const* rows, void* const* wv, void* const* gin,
+                          void* const* gwin, void* const* fl, int rank, int world, long long cap, const int* ids,
+                          const float* vals, const int* pos_of_pair, const float* e32, const float* S, const float* dy,
+                          const void* dx0_bf16, int ldx, float* GV, float* GW, void* bitmap, int B, int F, int K,
+                          const unsigned int* seq_ptr, int grid_blocks, void* stream);
+
 /* ---- runtime switches / host helpers */
 int dfm_pdl_enabled(void);            /* programmatic dependent launch between the step kernels (default on; DFM_PDL=0) */
 void dfm_set_pdl(int on);

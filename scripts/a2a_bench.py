@@ -24,11 +24,12 @@ def timeit(fn, n=30):
     return float(t)
 
 results = []
-for n_ids in [1024, 16384, 131072, 1048576]:
+for n_ids in [int(x) for x in os.environ.get("A2A_SIZES", "1024,16384,131072,1048576").split(",")]:
     B = max(1, n_ids // F)
     cfg = DeepFMConfig(field_size=F, feature_size=N, embedding_size=K, deep_layers=[64], dropout=[1.0], l2_reg=0.0,
                        l2_mode="touched")
-    m = ShardedDeepFM(cfg, B, TF1Optimizer("Adagrad", 1e-2), 1, dev, world, rank, use_graph=False)
+    m = ShardedDeepFM(cfg, B, TF1Optimizer("Adagrad", 1e-2), 1, dev, world, rank, use_graph=False,
+                      a2a_mode=os.environ.get("A2A_MODE", "auto"))
     g = torch.Generator(device=dev).manual_seed(rank + 1)
     s = m.in_slots[0]
     s["ids"].copy_(torch.randint(0, N, (B, F), device=dev, generator=g, dtype=torch.int32))
@@ -74,7 +75,7 @@ for n_ids in [1024, 16384, 131072, 1048576]:
     t_base = timeit(baseline, n=10)
     bytes_nvl = B * F * K * 4 * 2 * (world - 1) / world   # rows in + grads out, remote fraction
     if rank == 0:
-        r = dict(ids_per_gpu=B * F, world=world, rows=N, K=K, fused_us=t_fused, fused_fwd_us=t_fwd, nccl_torch_us=t_base,
+        r = dict(ids_per_gpu=B * F, world=world, rows=N, K=K, mode="push" if m.push else "pull", fused_us=t_fused, fused_fwd_us=t_fwd, nccl_torch_us=t_base,
                  speedup=t_base / t_fused, nvlink_bytes_per_rank=bytes_nvl,
                  roofline_us_at_770GBs=bytes_nvl / 2 / 770e9 * 1e6, frac_of_roofline=(bytes_nvl / 2 / 770e9 * 1e6) / t_fused)
         results.append(r)
