@@ -371,13 +371,23 @@ struct RawBatch {
 class Loader {
  public:
   Loader(std::vector<std::string> paths, int F, int batch, int shard_n, int shard_i, int epochs, int threads,
-         bool drop_remainder, bool check_crc, uint8_t* slots, int nslots, size_t slot_stride)
+         bool drop_remainder, bool check_crc, uint8_t* slots, int nslots, size_t slot_stride, bool raw = false)
       : paths_(std::move(paths)), F_(F), B_(batch), shard_n_(shard_n < 1 ? 1 : shard_n), shard_i_(shard_i),
         epochs_(epochs), drop_(drop_remainder), crc_(check_crc), slots_(slots), nslots_(nslots),
-        stride_(slot_stride) {
+        stride_(slot_stride), raw_mode_(raw) {
     for (int i = 0; i < nslots_; ++i) free_slots_.push_back(i);
-    reader_ = std::thread([this] { reader_main(); });
-    for (int i = 0; i < (threads < 1 ? 1 : threads); ++i) parsers_.emplace_back([this] { parser_main(); });
+    if (raw_mode_) {
+      // raw mode: slots carry the serialized records themselves (offsets[B+1] | bytes); the GPU parses them
+      // (csrc/parse_gpu.cu), so there are no parser threads and the reader fills the slots directly
+      reader_ = std::thread([this] { reader_main_raw(); });
+    } else {
+      reader_ = std::thread([this] { reader_main(); });
+      for (int i = 0; i < (threads < 1 ? 1 : threads); ++i) parsers_.emplace_back([this] { parser_main(); });
+    }
+  }
+  static size_t raw_slot_bytes(int B, int max_record_bytes) {
+    auto al = [](size_t x) { return (x + 255) & ~size_t(255); };
+    return al((size_t)(B + 1) * 4) + al((size_t)B * max_record_bytes);
   }
   ~Loader() {
     {
@@ -428,6 +438,7 @@ class Loader {
       std::lock_guard<std::mutex> l(mu_);
       free_slots_.push_back(slot);
     }
+    cv_free_.notify_one();
     cv_work_.notify_one();  // parsers wait on cv_work_ for (raw batch AND free slot); one slot -> one parser
   }
   long records_read() const { return records_read_.load(); }
@@ -548,6 +559,114 @@ class Loader {
     cv_done_.notify_all();
   }
 
+  // ---- raw mode -------------------------------------------------------------------------------------------
+  int take_free_slot() {
+    std::unique_lock<std::mutex> l(mu_);
+    cv_free_.wait(l, [this] { return stop_ || !free_slots_.empty(); });
+    if (stop_) return -1;
+    const int s = free_slots_.front();
+    free_slots_.pop_front();
+    return s;
+  }
+  void publish(long seq, int slot, int rows) {
+    {
+      std::lock_guard<std::mutex> l(mu_);
+      done_.push_back(Done{seq, slot, rows});
+    }
+    cv_done_.notify_one();
+  }
+  void reader_main_raw() {
+    const size_t off_bytes = ((size_t)(B_ + 1) * 4 + 255) & ~size_t(255);
+    const size_t cap = stride_ - off_bytes;
+    long seq = 0, rec_idx = 0;
+    int slot = take_free_slot();
+    if (slot < 0) return;
+    int rows = 0;
+    size_t used = 0;
+    auto offs = [&](int s) { return reinterpret_cast<int32_t*>(slots_ + (size_t)s * stride_); };
+    auto bytes = [&](int s) { return slots_ + (size_t)s * stride_ + off_bytes; };
+    auto append = [&](const uint8_t* hdr, const uint8_t* data, size_t n, const uint8_t* tail, const std::string& path) -> bool {
+      if (crc_) {
+        uint32_t hc, dc;
+        memcpy(&hc, hdr + 8, 4);
+        memcpy(&dc, tail, 4);
+        if (mask_crc(crc32c(hdr, 8)) != hc) { fail("corrupted record length CRC in " + path); return false; }
+        if (mask_crc(crc32c(data, n)) != dc) { fail("corrupted record data CRC in " + path); return false; }
+      }
+      if (used + n > cap) { fail("raw slot overflow: raise max_record_bytes"); return false; }
+      offs(slot)[rows] = (int32_t)used;
+      memcpy(bytes(slot) + used, data, n);
+      used += n;
+      ++rows;
+      offs(slot)[rows] = (int32_t)used;
+      if (rows == B_) {
+        records_read_.fetch_add(rows);
+        publish(seq++, slot, rows);
+        slot = take_free_slot();
+        if (slot < 0) return false;
+        rows = 0;
+        used = 0;
+      }
+      return true;
+    };
+    RecordReader rr;
+    std::vector<uint8_t> tmp;
+    for (int ep = 0; ep < epochs_ && !stopped(); ++ep) {
+      for (const auto& path : paths_) {
+        std::shared_ptr<MappedFile> mf;
+        {
+          auto it = maps_.find(path);
+          if (it != maps_.end()) mf = it->second;
+          else if ((mf = MappedFile::open_path(path.c_str()))) maps_[path] = mf;
+        }
+        if (mf) {
+          size_t pos = 0;
+          while (pos < mf->size) {
+            if ((rec_idx & 255) == 0 && stopped()) return;
+            if (pos + 12 > mf->size) { fail("truncated record in " + path); return; }
+            uint64_t n;
+            memcpy(&n, mf->base + pos, 8);
+            if (n > (1ull << 31) || pos + 12 + n + 4 > mf->size) { fail("truncated or corrupted record in " + path); return; }
+            const uint8_t* hdr = mf->base + pos;
+            pos += 12 + n + 4;
+            const bool mine = (rec_idx % shard_n_) == shard_i_;
+            ++rec_idx;
+            if (!mine) continue;
+            if (!append(hdr, hdr + 12, (size_t)n, hdr + 12 + n, path)) return;
+          }
+        } else {
+          if (!rr.open_path(path.c_str())) { fail(g_err); return; }
+          for (;;) {
+            if (stopped()) return;
+            tmp.clear();
+            size_t o, n;
+            const bool mine = (rec_idx % shard_n_) == shard_i_;
+            int r = rr.next(tmp, &o, &n, crc_ && mine);
+            if (r < 0) { fail(std::string(g_err) + " in " + path); return; }
+            if (r == 0) break;
+            ++rec_idx;
+            if (!mine) continue;
+            const bool keep_crc = crc_;
+            crc_ = false;  // already verified by the streaming reader
+            const bool ok = append(nullptr, tmp.data() + o, n, nullptr, path);
+            crc_ = keep_crc;
+            if (!ok) return;
+          }
+        }
+      }
+    }
+    if (rows > 0 && !drop_) {
+      records_read_.fetch_add(rows);
+      publish(seq++, slot, rows);
+    }
+    {
+      std::lock_guard<std::mutex> l(mu_);
+      total_batches_ = seq;
+      reader_finished_ = true;
+    }
+    cv_done_.notify_all();
+  }
+
   bool push_raw(std::unique_ptr<RawBatch> b) {
     std::unique_lock<std::mutex> l(mu_);
     cv_raw_space_.wait(l, [this] { return stop_ || (int)raw_.size() < nslots_ + 2; });
@@ -619,6 +738,7 @@ class Loader {
   uint8_t* slots_;
   int nslots_;
   size_t stride_;
+  bool raw_mode_ = false;
   std::mutex mu_;
   std::condition_variable cv_work_, cv_free_, cv_done_, cv_raw_space_;
   std::deque<std::unique_ptr<RawBatch>> raw_;
@@ -701,6 +821,19 @@ int dfmio_parse_batch(const uint8_t* bytes, const uint64_t* off, const uint64_t*
 
 // ---- prefetching loader
 uint64_t dfmio_loader_slot_bytes(int batch, int F) { return Loader::slot_bytes(batch, F); }
+uint64_t dfmio_loader_raw_slot_bytes(int batch, int max_record_bytes) { return Loader::raw_slot_bytes(batch, max_record_bytes); }
+// Raw mode: slots hold `int32 offsets[batch+1]` followed (256-byte aligned) by the serialized records back to back.
+void* dfmio_loader_create_raw(const char** paths, int npaths, int batch, int shard_n, int shard_i, int epochs,
+                              int drop_remainder, int check_crc, uint8_t* slots, int nslots, uint64_t slot_stride) {
+  if (npaths <= 0 || batch <= 0 || nslots < 2 || !slots || slot_stride < (((uint64_t)(batch + 1) * 4 + 255) & ~255ull) + 256 ||
+      shard_i < 0 || shard_i >= (shard_n < 1 ? 1 : shard_n)) {
+    set_err("loader_create_raw: bad arguments");
+    return nullptr;
+  }
+  std::vector<std::string> p(paths, paths + npaths);
+  return new Loader(std::move(p), 0, batch, shard_n, shard_i, epochs, 0, drop_remainder != 0, check_crc != 0, slots,
+                    nslots, slot_stride, true);
+}
 void* dfmio_loader_create(const char** paths, int npaths, int F, int batch, int shard_n, int shard_i, int epochs,
                           int threads, int drop_remainder, int check_crc, uint8_t* slots, int nslots,
                           uint64_t slot_stride) {

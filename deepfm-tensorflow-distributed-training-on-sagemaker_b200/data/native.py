@@ -52,6 +52,11 @@ def load(build_if_missing: bool = True) -> ctypes.CDLL:
     lib.dfmio_loader_create.restype = c_void_p
     lib.dfmio_loader_create.argtypes = [ctypes.POINTER(c_char_p), c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                         c_int, c_int, c_void_p, c_int, c_uint64]
+    lib.dfmio_loader_raw_slot_bytes.restype = c_uint64
+    lib.dfmio_loader_raw_slot_bytes.argtypes = [c_int, c_int]
+    lib.dfmio_loader_create_raw.restype = c_void_p
+    lib.dfmio_loader_create_raw.argtypes = [ctypes.POINTER(c_char_p), c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                            c_void_p, c_int, c_uint64]
     lib.dfmio_loader_next.argtypes = [c_void_p, ctypes.POINTER(c_int)]
     lib.dfmio_loader_release.argtypes = [c_void_p, c_int]
     lib.dfmio_loader_records.restype = c_long
@@ -192,6 +197,62 @@ class NativeLoader:
 
     def records_read(self) -> int:
         return int(load().dfmio_loader_records(self._h))
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            load().dfmio_loader_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class NativeRawLoader:
+    """Loader in RAW mode: slots carry the serialized Examples themselves — `int32 offsets[B+1]`, then (256-byte
+    aligned) the record bytes back to back — for the GPU parser (csrc/parse_gpu.cu, ops.kernels.example_parse).
+    The host only walks / CRC-checks / copies records; no protobuf parsing on the CPU."""
+
+    def __init__(self, paths: List[str], batch_size: int, shard_n: int = 1, shard_i: int = 0, num_epochs: int = 1,
+                 drop_remainder: bool = True, check_crc: bool = True, nslots: int = 6, pin_memory: bool = False,
+                 max_record_bytes: int = 1024):
+        import torch
+        lib = load()
+        self.B, self.nslots = batch_size, nslots
+        self.stride = int(lib.dfmio_loader_raw_slot_bytes(batch_size, max_record_bytes))
+        self.off_bytes = ((batch_size + 1) * 4 + 255) & ~255
+        self.buf = torch.zeros(self.stride * nslots, dtype=torch.uint8)
+        if pin_memory and torch.cuda.is_available():
+            self.buf = self.buf.pin_memory()
+        arr = (c_char_p * len(paths))(*[p.encode() for p in paths])
+        self._h = lib.dfmio_loader_create_raw(arr, len(paths), batch_size, shard_n, shard_i, num_epochs,
+                                              1 if drop_remainder else 0, 1 if check_crc else 0, self.buf.data_ptr(),
+                                              nslots, self.stride)
+        if not self._h:
+            raise NativeIOError(_err())
+
+    def next(self):
+        slot = c_int(-1)
+        rows = load().dfmio_loader_next(self._h, ctypes.byref(slot))
+        if rows < 0:
+            raise NativeIOError(_err())
+        if rows == 0:
+            return None
+        raw = self.buf[slot.value * self.stride:(slot.value + 1) * self.stride]
+        return slot.value, rows, raw
+
+    def records(self, raw, rows: int) -> List[bytes]:
+        """Host-side view of a raw slot (tests / debugging)."""
+        import torch
+        offs = raw[: (rows + 1) * 4].view(torch.int32).tolist()
+        body = raw[self.off_bytes:].numpy().tobytes()
+        return [body[offs[i]:offs[i + 1]] for i in range(rows)]
+
+    def release(self, slot: int) -> None:
+        if getattr(self, "_h", None):
+            load().dfmio_loader_release(self._h, slot)
 
     def close(self) -> None:
         if getattr(self, "_h", None):

@@ -45,6 +45,7 @@ class Batch:
     vals: torch.Tensor    # [rows, F] f32
     packed: Optional[torch.Tensor] = None  # whole pinned slot (labels|ids|vals) when it came from the native loader
     _release: Optional[Callable[[], None]] = None
+    raw: Optional[torch.Tensor] = None     # whole pinned RAW slot (offsets|record bytes) when gpu_parse is on
 
     def release(self):
         if self._release is not None:
@@ -63,13 +64,17 @@ class InputPipeline:
 
     def __init__(self, sources: Sequence[str], field_size: int, batch_size: int, num_epochs: int = 1,
                  shard: Tuple[int, int] = (1, 0), drop_remainder: bool = True, threads: int = 4, pin_memory: bool = True,
-                 use_native: bool = True, check_crc: bool = True, nslots: int = 8):
+                 use_native: bool = True, check_crc: bool = True, nslots: int = 8, gpu_parse: bool = False,
+                 max_record_bytes: int = 1024):
+        """gpu_parse=True: the host only walks/CRC-checks/copies records into pinned raw slots; the Example protos are
+        decoded on the GPU (`Trainer.train_raw`). Batches then carry `raw` instead of parsed tensors."""
         self.sources = list(sources)
         self.F, self.B = field_size, batch_size
         self.num_epochs = max(1, num_epochs)
         self.shard = shard
         self.drop = drop_remainder
         self.threads, self.pin, self.crc, self.nslots = threads, pin_memory, check_crc, nslots
+        self.gpu_parse, self.max_record_bytes = gpu_parse, max_record_bytes
         self.native = False
         if use_native:
             try:
@@ -81,7 +86,24 @@ class InputPipeline:
     def __iter__(self) -> Iterator[Batch]:
         if not self.sources:
             return iter(())
+        if self.gpu_parse and self.native:
+            return self._iter_raw()
         return self._iter_native() if self.native else self._iter_python()
+
+    def _iter_raw(self) -> Iterator[Batch]:
+        from .native import NativeRawLoader
+        ld = NativeRawLoader(self.sources, self.B, self.shard[0], self.shard[1], self.num_epochs, self.drop, self.crc,
+                             self.nslots, self.pin, self.max_record_bytes)
+        self.raw_off_bytes = ld.off_bytes
+        try:
+            while True:
+                b = ld.next()
+                if b is None:
+                    return
+                slot, rows, raw = b
+                yield Batch(rows, None, None, None, None, (lambda s=slot: ld.release(s)), raw)
+        finally:
+            ld.close()
 
     def _iter_native(self) -> Iterator[Batch]:
         from .native import NativeLoader

@@ -142,3 +142,11 @@ def bn_bwd(dy_inout, z, gamma, save_mean, save_rstd, g_gamma, g_beta) -> None:
     _lib.check(_lib.load().dfm_bn_bwd(_p(dy_inout), c_int(dy_inout.stride(0)), _p(z), c_int(z.stride(0)), c_int(B),
                                       c_int(H), _p(gamma), _p(save_mean), _p(save_rstd), _p(g_gamma), _p(g_beta),
                                       _stream()))
+
+
+def example_parse(blob: torch.Tensor, offsets: torch.Tensor, n: int, field_size: int, labels: torch.Tensor,
+                  ids: torch.Tensor, vals: torch.Tensor, err: torch.Tensor) -> None:
+    """Decode n serialized tf.train.Example protos on the GPU into (labels, ids int32, vals); see csrc/parse_gpu.cu."""
+    _chk_dev(blob, offsets, labels, ids, vals, err)
+    _lib.check(_lib.load().dfm_example_parse(_p(blob), _p(offsets), c_int(n), c_int(field_size), _p(labels), _p(ids),
+                                             _p(vals), _p(err), _stream()))

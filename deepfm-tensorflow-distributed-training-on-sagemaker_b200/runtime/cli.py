@@ -118,7 +118,10 @@ def main(argv: Optional[List[str]] = None) -> int:
     pin = env.device is not None
 
     def input_fn(files, num_epochs=1, shard=(1, 0), drop_remainder=True):
-        return InputPipeline(files, F.field_size, F.batch_size, num_epochs, shard, drop_remainder, F.loader_threads, pin)
+        gpu_parse = bool(F.gpu_parse) and drop_remainder and env.device is not None and F.strategy != "ps" \
+            and F.backend != "torch"
+        return InputPipeline(files, F.field_size, F.batch_size, num_epochs, shard, drop_remainder, F.loader_threads, pin,
+                             gpu_parse=gpu_parse)
 
     names = channel_names()
     metrics = None

@@ -82,7 +82,9 @@ class Estimator:
             if batch.rows != self.B:  # drop_remainder=True upstream; a short batch would change the graph shape
                 batch.release()
                 continue
-            if fused and batch.packed is not None:
+            if fused and batch.raw is not None:
+                ev = tr.train_raw(batch.raw, batch.rows)
+            elif fused and batch.packed is not None:
                 ev = tr.train_packed(batch.packed)
             else:
                 ev = tr.train_batch(batch.ids, batch.vals, batch.labels)

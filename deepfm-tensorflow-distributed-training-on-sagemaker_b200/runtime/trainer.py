@@ -122,6 +122,32 @@ class Trainer:
         pinned async H2D copy on the copy stream, graph replay, async D2H of the loss scalars."""
         return self._train_host(lambda slot: self.model.load_packed(packed, slot, non_blocking=True))
 
+    def train_raw(self, raw: torch.Tensor, rows: int):
+        """One optimizer step on a HOST batch of SERIALIZED Examples (raw loader slot: offsets | record bytes): one pinned
+        H2D copy of the raw bytes, decoded on the GPU by example_parse straight into the input slot, then the step."""
+        from ..ops import kernels as K
+        if rows != self.B:
+            raise ValueError("train_raw needs full batches (drop_remainder=True)")
+        if not hasattr(self, "_raw_dev"):
+            self._raw_dev = [torch.zeros(raw.numel(), dtype=torch.uint8, device=self.dev) for _ in range(self._nslots)]
+            self._parse_err = torch.zeros(1, dtype=torch.int32, device=self.dev)
+            self._raw_off = ((self.B + 1) * 4 + 255) & ~255
+        F = self.cfg.field_size
+
+        def load(slot):
+            d = self._raw_dev[slot]
+            d.copy_(raw, non_blocking=True)
+            s = self.model.in_slots[slot]
+            K.example_parse(d[self._raw_off:], d[: (self.B + 1) * 4].view(torch.int32), self.B, F, s["labels"], s["ids"],
+                            s["vals"], self._parse_err)
+        return self._train_host(load)
+
+    def check_parse_errors(self) -> None:
+        if hasattr(self, "_parse_err"):
+            e = int(self._parse_err.item())
+            if e:
+                raise ValueError("GPU Example parser rejected record %d of a batch (schema mismatch or malformed proto)" % (e - 1))
+
     def train_batch(self, ids, vals, labels):
         """One optimizer step on a HOST batch. On CUDA: pinned-memory async H2D on a side stream into the next input
         slot (overlapping the previous step), graph replay, async D2H of the step's loss scalars."""
@@ -174,6 +200,7 @@ class Trainer:
         """Wait for outstanding steps; return the per-step losses (mean log-loss + L2 terms, PS:244-246)."""
         if self._cuda:
             torch.cuda.synchronize(self.dev)
+            self.check_parse_errors()
             reg_now = None
             if getattr(self.model, "arena", None) is not None and not getattr(self.model, "_nccl", False):
                 reg_now = float(self.model.arena.view("reg_parts").sum())  # L2 terms, gathered by the fused kernel

@@ -120,6 +120,11 @@ int dfm_a2a_push_backward(void* const* req, void* const* cnt, void* const* rows,
                           const void* dx0_bf16, int ldx, float* GV, float* GW, void* bitmap, int B, int F, int K,
                           const unsigned int* seq_ptr, int grid_blocks, void* stream);
 
+/* ---- GPU-side tf.train.Example parser (replaces the ParseExample op, HVD:78-83, when the host parser is the bottleneck):
+ * blob = serialized records back to back, offsets[n+1]; *err = 0 on entry, 1 + index of the first bad record after. */
+int dfm_example_parse(const void* blob, const int* offsets, int n, int F, float* labels, int* ids, float* vals, int* err,
+                      void* stream);
+
 /* ---- runtime switches / host helpers */
 int dfm_pdl_enabled(void);            /* programmatic dependent launch between the step kernels (default on; DFM_PDL=0) */
 void dfm_set_pdl(int on);

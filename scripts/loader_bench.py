@@ -19,6 +19,12 @@ for threads in (1, 2, 4, 8):
             rows += b.rows; b.release()
         dt = time.time() - t0
         print("native loader threads=%d crc=%s: %.2f M records/s (%.0f MB/s)" % (threads, crc, rows / dt / 1e6, size / dt / 1e6))
+for crc in (True, False):
+    t0 = time.time(); rows = 0
+    for b in InputPipeline(paths, F, B, pin_memory=False, check_crc=crc, gpu_parse=True, num_epochs=4):
+        rows += b.rows; b.release()
+    dt = time.time() - t0
+    print("raw loader (records copied for GPU parsing) crc=%s: %.2f M records/s (%.0f MB/s)" % (crc, rows / dt / 1e6, 4 * size / dt / 1e6))
 t0 = time.time(); rows = 0
 for b in InputPipeline(paths[:1], F, B, use_native=False):
     rows += b.rows

@@ -69,6 +69,20 @@ def test_cli_fused_train_eval_infer_export(cuda_lib, data, tmp_path):
     assert tuple(tf_sd["Deep-part/mlp0/weights"].shape) == (F * 32, 128) and "fm_v/Adam_1" in tf_sd
 
 
+def test_cli_gpu_side_example_parsing(cuda_lib, data, tmp_path):
+    """--gpu_parse: raw record bytes go to the GPU and are decoded there; training must behave like the host-parsed run."""
+    runs = {}
+    for mode in ("False", "True"):
+        ckpt = str(tmp_path / ("ckpt_" + mode))
+        out = _run(COMMON + ["--training_data_dir", str(data / "train"), "--val_data_dir", str(data / "val"),
+                             "--model_dir", ckpt, "--task_type", "train", "--num_epochs", "1", "--gpu_parse", mode])
+        ev = [json.loads(l)["eval"] for l in out.splitlines() if l.startswith('{"eval"')][-1]
+        runs[mode] = ev
+        assert ev["global_step"] == 120
+    assert abs(runs["True"]["loss"] - runs["False"]["loss"]) < 5e-3, runs
+    assert abs(runs["True"]["auc"] - runs["False"]["auc"]) < 1e-2 and runs["True"]["auc"] > 0.6, runs
+
+
 @pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
 def test_launcher_two_ranks_fused_dp_and_sharded(cuda_lib, data, tmp_path):
     from deepfm_b200.launch import LocalEstimator

@@ -220,3 +220,46 @@ def test_auc_hist_matches_streaming_auc(cuda_lib):
     ref = StreamingAUC()
     ref.update(labels, prob)
     assert torch.equal(hist.cpu().double(), ref.hist)
+
+
+def test_example_parse_gpu_matches_host_parser(cuda_lib, tmp_path):
+    """GPU protobuf parser == C++/Python host parsers on real loader slots (packed + unpacked encodings, bad record)."""
+    import struct
+    import numpy as np
+    from deepfm_b200.data import native
+    from deepfm_b200.ops import kernels as k
+    from deepfm_b200.utils import tfrecord as T
+    F, B = 39, 256
+    rng = np.random.default_rng(0)
+    path = str(tmp_path / "tr.tfrecords")
+    recs = []
+    with native.NativeRecordWriter(path) as w:
+        for i in range(B):
+            ex = T.make_ctr_example(float(i % 2), rng.integers(0, 2 ** 31 - 1, F).tolist(), rng.random(F).astype(np.float32).tolist())
+            recs.append(ex); w.write(ex)
+    ld = native.NativeRawLoader([path], B, pin_memory=True)
+    slot, rows, raw = ld.next()
+    d = raw.cuda()
+    off = ((B + 1) * 4 + 255) & ~255
+    labels = torch.empty(B, device="cuda"); ids = torch.empty(B, F, device="cuda", dtype=torch.int32)
+    vals = torch.empty(B, F, device="cuda"); err = torch.zeros(1, device="cuda", dtype=torch.int32)
+    k.example_parse(d[off:], d[: (B + 1) * 4].view(torch.int32), B, F, labels, ids, vals, err)
+    torch.cuda.synchronize()
+    l, i, v = T.parse_ctr_batch(recs, F)
+    assert int(err) == 0
+    assert np.array_equal(labels.cpu().numpy(), l) and np.array_equal(ids.cpu().numpy(), i.astype(np.int32))
+    assert np.array_equal(vals.cpu().numpy(), v)
+    ld.release(slot); ld.close()
+    # unpacked repeated fields + a record with the wrong number of ids
+    unpacked = T._ld(1, T._ld(1, T._ld(1, b"values") + T._ld(2, T._ld(2, b"\x0d" + struct.pack("<f", 2.0) + b"\x0d" + struct.pack("<f", 3.0)))) +
+                     T._ld(1, T._ld(1, b"label") + T._ld(2, T._ld(2, b"\x0d" + struct.pack("<f", 1.0)))) +
+                     T._ld(1, T._ld(1, b"ids") + T._ld(2, T._ld(3, b"\x08\x05\x08\x07"))))
+    bad = T.make_ctr_example(1.0, [1, 2, 3], [0.1, 0.2, 0.3])
+    blob = torch.frombuffer(bytearray(unpacked + bad), dtype=torch.uint8).cuda()
+    offs = torch.tensor([0, len(unpacked), len(unpacked) + len(bad)], dtype=torch.int32, device="cuda")
+    labels = torch.empty(2, device="cuda"); ids = torch.empty(2, 2, device="cuda", dtype=torch.int32)
+    vals = torch.empty(2, 2, device="cuda"); err = torch.zeros(1, device="cuda", dtype=torch.int32)
+    k.example_parse(blob, offs, 2, 2, labels, ids, vals, err)
+    torch.cuda.synchronize()
+    assert ids[0].tolist() == [5, 7] and vals[0].tolist() == [2.0, 3.0] and float(labels[0]) == 1.0
+    assert int(err) == 2 and ids[1].tolist() == [0, 0]
