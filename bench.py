@@ -226,7 +226,7 @@ def main():
                        "cuda_graph": not a.no_graph},
             "clocks": clocks,
             "e2e": {"value": e2e, "unit": "samples/s", "ms_per_step": ms_e2e / a.steps,
-                    "h2d_bytes_per_step": bytes_per_batch, "d2h_bytes_per_step": 4,
+                    "h2d_bytes_per_step": bytes_per_batch, "d2h_bytes_per_step": 8,
                     "api": "deepfm_b200.runtime.trainer.Trainer.train_packed (one pinned H2D copy per batch)"},
             "gpu_launches": launches, "kernels_per_step": tr.kernels_per_step,
             "final_loss": final_loss, "e2e_last_loss": losses[-1] if losses else None,

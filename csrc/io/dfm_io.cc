@@ -545,10 +545,15 @@ class Loader {
           }
         }
       }
-    }
-    if (cur->rows > 0 && !drop_) {
-      cur->seq = seq++;
-      if (!push_raw(std::move(cur))) return;
+      // end of one pass over the data: `batch(B, drop_remainder)` comes BEFORE `repeat(num_epochs)` in the reference
+      // (HVD:122-126), so the remainder of every epoch is dropped (or emitted as a short batch), never carried over
+      if (cur->rows > 0) {
+        if (!drop_) {
+          cur->seq = seq++;
+          if (!push_raw(std::move(cur))) return;
+        }
+        cur.reset(new RawBatch());
+      }
     }
     {
       std::lock_guard<std::mutex> l(mu_);
@@ -654,10 +659,16 @@ class Loader {
           }
         }
       }
-    }
-    if (rows > 0 && !drop_) {
-      records_read_.fetch_add(rows);
-      publish(seq++, slot, rows);
+      if (rows > 0) {  // per-epoch remainder: dropped or emitted short, never carried into the next epoch
+        if (!drop_) {
+          records_read_.fetch_add(rows);
+          publish(seq++, slot, rows);
+          slot = take_free_slot();
+          if (slot < 0) return;
+        }
+        rows = 0;
+        used = 0;
+      }
     }
     {
       std::lock_guard<std::mutex> l(mu_);
@@ -810,6 +821,28 @@ long dfmio_reader_next(void* rd, uint8_t* buf, size_t cap, int check_crc) {
   return (long)n;
 }
 void dfmio_reader_close(void* rd) { delete (RecordReader*)rd; }
+
+// ---- record count of a TFRecord file by walking the length headers of a read-only mapping (no payload reads);
+// used to agree on a common step count across ranks before an epoch (uneven shards would otherwise leave one rank
+// waiting in a collective: the Horovod failure mode of PDF p22-23). Returns -1 on error.
+long dfmio_count_records(const char* path) {
+  std::shared_ptr<MappedFile> mf = MappedFile::open_path(path);
+  if (!mf) {
+    set_err("cannot map %s", path);
+    return -1;
+  }
+  long n = 0;
+  size_t pos = 0;
+  while (pos < mf->size) {
+    if (pos + 12 > mf->size) { set_err("truncated record in %s", path); return -1; }
+    uint64_t len;
+    memcpy(&len, mf->base + pos, 8);
+    if (len > (1ull << 31) || pos + 16 + len > mf->size) { set_err("truncated or corrupted record in %s", path); return -1; }
+    pos += 16 + len;
+    ++n;
+  }
+  return n;
+}
 
 // ---- batch parse: `nrec` serialized Examples (concatenated in `bytes`, located by off/len) -> dense arrays
 int dfmio_parse_batch(const uint8_t* bytes, const uint64_t* off, const uint64_t* len, int nrec, int F, float* labels,

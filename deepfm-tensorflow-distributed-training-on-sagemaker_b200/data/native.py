@@ -52,6 +52,8 @@ def load(build_if_missing: bool = True) -> ctypes.CDLL:
     lib.dfmio_loader_create.restype = c_void_p
     lib.dfmio_loader_create.argtypes = [ctypes.POINTER(c_char_p), c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                         c_int, c_int, c_void_p, c_int, c_uint64]
+    lib.dfmio_count_records.restype = c_long
+    lib.dfmio_count_records.argtypes = [c_char_p]
     lib.dfmio_loader_raw_slot_bytes.restype = c_uint64
     lib.dfmio_loader_raw_slot_bytes.argtypes = [c_int, c_int]
     lib.dfmio_loader_create_raw.restype = c_void_p
@@ -85,6 +87,13 @@ def crc32c(data: bytes) -> int:
 
 def masked_crc32c(data: bytes) -> int:
     return int(load().dfmio_masked_crc32c(data, len(data)))
+
+
+def count_records_native(path: str) -> int:
+    n = int(load().dfmio_count_records(path.encode()))
+    if n < 0:
+        raise NativeIOError(_err())
+    return n
 
 
 class NativeRecordWriter:

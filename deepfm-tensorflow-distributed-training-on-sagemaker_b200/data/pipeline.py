@@ -122,9 +122,9 @@ class InputPipeline:
 
     def _iter_python(self) -> Iterator[Batch]:
         n, i = self.shard
-        buf: List[bytes] = []
         idx = 0
         for _ in range(self.num_epochs):
+            buf: List[bytes] = []
             for path in self.sources:
                 for rec in T.read_records(path, self.crc):
                     keep = (idx % n) == i
@@ -135,8 +135,8 @@ class InputPipeline:
                     if len(buf) == self.B:
                         yield self._parse(buf)
                         buf = []
-        if buf and not self.drop:
-            yield self._parse(buf)
+            if buf and not self.drop:  # batch() precedes repeat(): the remainder never crosses an epoch boundary
+                yield self._parse(buf)
 
     def _parse(self, recs: List[bytes]) -> Batch:
         lab, ids, vals = T.parse_ctr_batch(recs, self.F)
@@ -145,10 +145,24 @@ class InputPipeline:
 
 def count_records(paths: Sequence[str]) -> int:
     n = 0
+    try:
+        from .native import available, count_records_native
+        if available():
+            return sum(count_records_native(p) for p in paths)
+    except Exception:
+        pass
     for p in paths:
         for _ in T.read_records(p, check_crc=False):
             n += 1
     return n
+
+
+def local_steps(paths: Sequence[str], batch_size: int, shard: Tuple[int, int], num_epochs: int = 1) -> int:
+    """Number of full batches this worker will get from `paths` under `dataset.shard(n, i).batch(B, drop_remainder)`."""
+    total = count_records(paths)
+    n, i = shard
+    mine = (total - i + n - 1) // n if total > i else 0
+    return (mine // batch_size) * num_epochs
 
 
 # ---------------------------------------------------------------------------------------------- binary cache

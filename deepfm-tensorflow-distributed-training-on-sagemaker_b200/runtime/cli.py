@@ -73,6 +73,7 @@ def main(argv: Optional[List[str]] = None) -> int:
     if env.is_chief:
         print(sys.argv)
         print_flags(F)
+        print("strategy %s on %d worker(s), backend %s" % (F.strategy, env.world_size, env.backend))
     if F.field_size <= 0 or F.feature_size <= 0:
         raise SystemExit("--field_size and --feature_size are required")
 
@@ -127,8 +128,14 @@ def main(argv: Optional[List[str]] = None) -> int:
     metrics = None
     if F.task_type == "train":
         if not pipe:
+            hint = None
+            if env.world_size > 1 and F.strategy != "ps":
+                # synchronous strategies: every rank must run the same number of steps or one of them ends up waiting
+                # in a collective (PDF p22-23); agree on min over ranks of the local full-batch count
+                from ..data.pipeline import local_steps
+                hint = local_steps(tr_files, F.batch_size, train_shard, 1)
             for _ in range(F.num_epochs):  # HVD:391-394
-                est.train(lambda: input_fn(tr_files, 1, train_shard), max_steps=F.max_steps)
+                est.train(lambda: input_fn(tr_files, 1, train_shard), max_steps=F.max_steps, steps_hint=hint)
                 if env.is_chief and va_files:
                     metrics = est.evaluate(lambda: input_fn(va_files, 1, (1, 0), False))
                 barrier(env)

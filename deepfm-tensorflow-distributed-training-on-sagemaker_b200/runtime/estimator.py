@@ -41,6 +41,8 @@ class Estimator:
         else:
             self.trainer = Trainer(cfg, batch_size, optimizer, seed, self.env.device, backend, self.env.world_size,
                                    self.env.rank, comm=comm, strategy=strategy)
+        if self.env.is_chief:  # the transport actually selected (reference: NCCL_DEBUG=INFO in the launcher, NB-HVD:90)
+            print("INFO:deepfm_b200:communication: %s" % getattr(self.trainer, "comm_name", "none"), file=out)
         gb = batch_size * self.env.world_size
         mf = metrics_file or (os.path.join(model_dir, "metrics.jsonl") if model_dir else None)
         self.log = LoggingHook(log_steps, gb, mf if self.env.is_chief else None, out, enabled=self.env.is_chief)

@@ -111,7 +111,7 @@ def test_native_loader_shard_batch_epochs(tmp_path):
         rows += n
         ld.release(slot)
     ld.close()
-    assert rows == (2 * 500) // 128 * 128  # shard -> repeat -> batch(drop_remainder) like HVD:98,122-126
+    assert rows == 2 * (500 // 128 * 128)  # shard -> batch(drop_remainder) -> repeat, like HVD:98,122-126
     la, ia, va = T.parse_ctr_batch(recs[1:256:2], 39)
     assert (first[0].numpy() == la).all() and (first[1].numpy() == ia).all() and (first[2].numpy() == va).all()
 
@@ -244,5 +244,20 @@ def test_raw_loader_slots_hold_the_serialized_records(tmp_path):
         ld.release(slot)
     ld.close()
     mine = recs[0::2]
-    want = (mine + mine)[: (2 * len(mine)) // 64 * 64]
+    per_epoch = mine[: len(mine) // 64 * 64]
+    want = per_epoch + per_epoch
     assert batches == len(want) // 64 and got == want
+
+
+def test_count_records_and_local_steps(tmp_path):
+    from deepfm_b200.data.native import count_records_native
+    from deepfm_b200.data.pipeline import InputPipeline, local_steps
+    p, recs = _write(tmp_path, 777)
+    assert count_records_native(p) == 777
+    for shard in [(1, 0), (2, 1), (3, 2)]:
+        want = 0
+        for b in InputPipeline([p], 39, 32, 2, shard, pin_memory=False):
+            want += 1
+            b.release()
+        # repeat(num_epochs) happens AFTER batch in the reference (HVD:122-126): per-epoch remainders are dropped
+        assert want == 2 * local_steps([p], 32, shard, 1) == local_steps([p], 32, shard, 2)
