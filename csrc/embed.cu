@@ -135,8 +135,11 @@ emb_bwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, cons
   const float4* sp = reinterpret_cast<const float4*>(S + (size_t)b * K);
   const uint2* dxp = reinterpret_cast<const uint2*>(dx0 + (size_t)b * ldx + (size_t)f * K);
 
+  // the row's G 16-byte chunks are split over gridDim.y CTAs (shorter serial chain per thread, 4x the threads)
+  const int g_per = (G + (int)gridDim.y - 1) / (int)gridDim.y;
+  const int g_begin = (int)blockIdx.y * g_per, g_end = min(G, g_begin + g_per);
 #pragma unroll 2
-  for (int g = 0; g < G; ++g) {
+  for (int g = g_begin; g < g_end; ++g) {
     float4 gr = make_float4(0.f, 0.f, 0.f, 0.f);
     if (valid) {
       const float4 row = __ldg(rowp + g);
@@ -169,7 +172,8 @@ emb_bwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, cons
       if (lane == leader && valid) red_add_f32x4(g_v + (size_t)id * K + 4 * g, acc.x, acc.y, acc.z, acc.w);
     }
   }
-  // first-order weights: same aggregation on the scalar dy*val
+  // first-order weights: same aggregation on the scalar dy*val (first chunk-slice only)
+  if (blockIdx.y != 0) return;  // CTA-uniform
   float gw = valid ? d * v : 0.f;
   if (mask == 0xffffffffu) {
     gw = warp_sum(gw);
@@ -201,8 +205,12 @@ template <int G>
 static int launch_bwd(const int* ids, const float* vals, const float* fm_v, const float* S, const float* dy,
                       const __nv_bfloat16* dx0, int ldx, float* g_w, float* g_v, int B, int F, int N, cudaStream_t st) {
   const long long threads = (long long)B * F;
-  DFM_CHECK(launch_k(emb_bwd_kernel<G>, dim3((unsigned)ceil_div_ll(threads, kEmbThreads)), dim3(kEmbThreads), 0, st, ids,
-                     vals, fm_v, S, dy, dx0, ldx, g_w, g_v, B, F, N));
+  const unsigned xblocks = (unsigned)ceil_div_ll(threads, kEmbThreads);
+  // split the K/4 chunks over up to 4 CTAs in y while the grid stays under ~8 CTAs per SM
+  unsigned ysplit = 1;
+  while (ysplit < 4 && ysplit * 2 <= (unsigned)G && (unsigned long long)xblocks * ysplit * 2 <= 148ull * 8) ysplit *= 2;
+  DFM_CHECK(launch_k(emb_bwd_kernel<G>, dim3(xblocks, ysplit), dim3(kEmbThreads), 0, st, ids, vals, fm_v, S, dy, dx0, ldx,
+                     g_w, g_v, B, F, N));
   return DFM_OK;
 }
 

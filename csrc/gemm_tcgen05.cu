@@ -389,15 +389,18 @@ static int launch_gemm(const GemmPlan& pl, cudaStream_t stream) {
   return DFM_OK;
 }
 
-static int pick_bn(int N, const int* cands, int ncand, int m_tiles) {
+static int pick_bn(int N, const int* cands, int ncand, int m_tiles, bool prefer_wide = false) {
   int best = cands[0];
   long best_cost = -1;
   for (int i = 0; i < ncand; ++i) {
     const int bn = cands[i];
     const int tiles = ceil_div(N, bn);
     // cost ~ padded columns (+ a small per-tile overhead); when few CTAs would result prefer more, smaller tiles
-    long cost = (long)tiles * bn * 8 + tiles * 64;
-    if ((long)tiles * m_tiles < 148) cost += (long)bn;  // tie-break toward smaller tiles on small problems
+    // cost ~ padded columns; a per-tile overhead only once the grid exceeds one wave — below that, more (smaller) tiles
+    // mean more SMs working and a shorter epilogue per CTA
+    long cost = (long)tiles * bn * 8;
+    if (prefer_wide || (long)tiles * m_tiles > 148) cost += (long)tiles * 64;  // wgrad fills the SMs with split-K instead
+    else cost += (long)bn / 8;
     if (best_cost < 0 || cost < best_cost) { best_cost = cost; best = bn; }
   }
   return best;
@@ -425,7 +428,7 @@ int dfm_gemm_plan_create(void** plan_out, int mode, const void* A, int lda, cons
   const int m_tiles = ceil_div(M, BM);
   static const int kk_cands[] = {32, 64, 80, 96, 128, 256};
   static const int mn_cands[] = {64, 128, 256};
-  pl->bn = mode == 0 ? pick_bn(N, kk_cands, 6, m_tiles) : pick_bn(N, mn_cands, 3, m_tiles);
+  pl->bn = mode == 0 ? pick_bn(N, kk_cands, 6, m_tiles) : pick_bn(N, mn_cands, 3, m_tiles, mode == 2);
   int rc;
   if (mode == 0) {  // A [M,K] K-major, B [N,K] K-major
     rc = make_tmap(&pl->tmA, A, M, K, lda, BM);
