@@ -229,6 +229,7 @@ def main():
                     "h2d_bytes_per_step": bytes_per_batch, "d2h_bytes_per_step": 8,
                     "api": "deepfm_b200.runtime.trainer.Trainer.train_packed (one pinned H2D copy per batch)"},
             "gpu_launches": launches, "kernels_per_step": tr.kernels_per_step,
+            "l2_persist_bytes": int(getattr(getattr(tr, "model", None), "l2_persist_bytes", 0) or 0),
             "final_loss": final_loss, "e2e_last_loss": losses[-1] if losses else None,
         }
         print(json.dumps(out))

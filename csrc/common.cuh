@@ -33,6 +33,9 @@ extern "C" void dfm_set_error(const char* fmt, ...);
   } while (0)
 
 extern "C" int dfm_pdl_enabled();
+// Optional persisting-L2 window (parameters + gradients + optimizer slots, re-read every step): set once by
+// dfm_set_l2_persist(); launch_k attaches it to every launch so it is captured into the CUDA graph's kernel nodes.
+extern "C" const cudaAccessPolicyWindow* dfm_l2_window();
 
 namespace dfm {
 
@@ -51,11 +54,17 @@ inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_
   cfg.blockDim = block;
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
+  int na = dfm_pdl_enabled() ? 1 : 0;
+  if (const cudaAccessPolicyWindow* w = dfm_l2_window()) {
+    attr[na].id = cudaLaunchAttributeAccessPolicyWindow;
+    attr[na].val.accessPolicyWindow = *w;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = dfm_pdl_enabled() ? 1 : 0;
+  cfg.numAttrs = na;
   return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
 }
 

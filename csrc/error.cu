@@ -61,3 +61,29 @@ extern "C" int dfm_host_unregister(void* ptr) {
   if (e != cudaSuccess) cudaGetLastError();
   return e == cudaSuccess ? 0 : 1;
 }
+
+// Persisting-L2 window over the training state (the 126 MB L2 makes keeping the optimizer state resident pay).
+static cudaAccessPolicyWindow g_l2w;
+static int g_l2w_on = 0;
+extern "C" const cudaAccessPolicyWindow* dfm_l2_window() { return g_l2w_on ? &g_l2w : nullptr; }
+// Returns the number of bytes the device agreed to set aside (0 = unsupported / disabled); bytes == 0 turns it off.
+extern "C" long long dfm_set_l2_persist(void* base, unsigned long long bytes) {
+  g_l2w_on = 0;
+  if (!base || bytes == 0) return 0;
+  int dev = 0, max_persist = 0, max_window = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, dev);
+  cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, dev);
+  if (max_persist <= 0 || max_window <= 0) { cudaGetLastError(); return 0; }
+  unsigned long long set_aside = bytes < (unsigned long long)max_persist ? bytes : (unsigned long long)max_persist;
+  if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, set_aside) != cudaSuccess) { cudaGetLastError(); return 0; }
+  unsigned long long win = bytes < (unsigned long long)max_window ? bytes : (unsigned long long)max_window;
+  g_l2w.base_ptr = base;
+  g_l2w.num_bytes = win;
+  g_l2w.hitRatio = (float)((double)set_aside / (double)win);
+  if (g_l2w.hitRatio > 1.f) g_l2w.hitRatio = 1.f;
+  g_l2w.hitProp = cudaAccessPropertyPersisting;
+  g_l2w.missProp = cudaAccessPropertyStreaming;
+  g_l2w_on = 1;
+  return (long long)set_aside;
+}

@@ -78,6 +78,13 @@ class FusedDeepFM:
         f32 = dict(device=dev, dtype=torch.float32)
 
         # ---- parameters / grads / slots (flat) ------------------------------------------------------------
+        # P, G and the optimizer slots are carved from ONE allocation so a single persisting-L2 window can cover them
+        nsl = len(SLOT_INIT[self.opt.name])
+        self._state_arena = None
+        self._state_off = 0
+        if type(self)._alloc is FusedDeepFM._alloc:
+            self._state_arena = torch.zeros(2 * L.total_numel + nsl * self._slot_numel() + 256, device=dev,
+                                            dtype=torch.float32)
         self.P = self._alloc("P", L.total_numel, torch.float32)
         self.G = self._alloc("G", L.total_numel, torch.float32)
         inits = SLOT_INIT[self.opt.name]
@@ -127,6 +134,7 @@ class FusedDeepFM:
         self._graphs: Dict[int, torch.cuda.CUDAGraph] = {}
         self.kernels_per_step = 0
         self.host_step = 0
+        self.l2_persist_bytes = self.enable_l2_persistence()
 
     # ------------------------------------------------------------------------------------------------ allocation
     def _make_layout(self, cfg) -> FlatLayout:
@@ -137,7 +145,22 @@ class FusedDeepFM:
 
     def _alloc(self, name: str, numel: int, dtype) -> torch.Tensor:
         """Persistent buffer allocation; parallel/dp.py overrides this to place P/G/shadow/slots in symmetric memory."""
+        if name in ("P", "G", "S0", "S1") and getattr(self, "_state_arena", None) is not None:
+            o = self._state_off
+            self._state_off = (o + numel + 63) // 64 * 64
+            return self._state_arena[o:o + numel]
         return torch.zeros(numel, device=self.dev, dtype=dtype)
+
+    def enable_l2_persistence(self) -> int:
+        """Ask the device to keep the training state (parameters, gradients, optimizer slots — re-read every step) in
+        the persisting part of the 126 MB L2. Returns the bytes set aside (0 = unsupported or switched off)."""
+        import ctypes, os
+        if os.environ.get("DFM_L2_PERSIST", "1") == "0" or self._state_arena is None:
+            return 0
+        lib = _native.load()
+        lib.dfm_set_l2_persist.restype = ctypes.c_longlong
+        return int(lib.dfm_set_l2_persist(ctypes.c_void_p(self._state_arena.data_ptr()),
+                                          ctypes.c_ulonglong(self._state_off * 4)))
 
     def _slot_numel(self) -> int:
         return self.layout.trainable_numel

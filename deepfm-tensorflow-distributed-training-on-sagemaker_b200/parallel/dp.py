@@ -104,6 +104,11 @@ class FusedDataParallel(FusedDeepFM):
         import os as _os
         if _os.environ.get("DFM_AR_BLOCKS"):  # tuning knob: must be set identically on every rank
             self._grid_blocks = max(1, min(lib.dfm_allreduce_opt_max_blocks(), int(_os.environ["DFM_AR_BLOCKS"])))
+        import ctypes as _ct, os as _os2
+        if _os2.environ.get("DFM_L2_PERSIST", "1") != "0":  # the symmetric arena (P | G | shadow | slot slices) is contiguous
+            lib.dfm_set_l2_persist.restype = _ct.c_longlong
+            self.l2_persist_bytes = int(lib.dfm_set_l2_persist(_ct.c_void_p(self.arena.buf.data_ptr()),
+                                                               _ct.c_ulonglong(self.arena.nbytes)))
         torch.cuda.synchronize(device)
         dist.barrier(group=self.group)
 

@@ -128,6 +128,8 @@ int dfm_example_parse(const void* blob, const int* offsets, int n, int F, float*
 /* ---- runtime switches / host helpers */
 int dfm_pdl_enabled(void);            /* programmatic dependent launch between the step kernels (default on; DFM_PDL=0) */
 void dfm_set_pdl(int on);
+long long dfm_set_l2_persist(void* base, unsigned long long bytes); /* persisting-L2 window over the training state;
+                                                                         returns bytes set aside, 0 = off/unsupported */
 int dfm_host_register(void* ptr, unsigned long long bytes, void** dev_ptr); /* page-lock + map the PS store (HOST pointer) */
 /* zero-copy parameter-server pull: out[i,:] = table[ids[i],:], table = device alias of the host store (X3 / row 11) */
 int dfm_ps_gather(const float* table_dev, const long long* ids, int n, int K, float* out, void* stream);
