@@ -100,6 +100,11 @@ class FusedDataParallel(FusedDeepFM):
         self.comm_name = "nccl-allreduce+flat_opt (baseline)" if self._nccl else \
             ("fused-nvls-multimem" if self.use_nvls else "fused-p2p")
         blocks = (chunk // 4 + 511) // 512  # two float4 per thread per trip
+        if self.use_nvls:
+            # NVLS: ~4 trips per thread instead of 1. With a single wave every CTA reduces, then every CTA broadcasts, and
+            # the link runs one direction at a time; a few trips per thread let the multimem.st of trip k overlap the
+            # multimem.ld_reduce of trip k+1 (measured at 8 ranks: 287 CTAs 69.7 us, 74 CTAs 58.3 us, 37 CTAs 67.0 us)
+            blocks = max(32, (chunk // 4 + 2047) // 2048)
         self._grid_blocks = max(1, min(lib.dfm_allreduce_opt_max_blocks(), blocks))
         import os as _os
         if _os.environ.get("DFM_AR_BLOCKS"):  # tuning knob: must be set identically on every rank

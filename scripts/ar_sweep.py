@@ -18,10 +18,10 @@ def timeit(fn, n=200):
     e1.record(); torch.cuda.synchronize()
     t = torch.tensor([e0.elapsed_time(e1) * 1e3 / n], device=dev); dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t)
-for feat in (117581, 2000):
+for feat in [int(x) for x in os.environ.get("AR_FEATS", "117581,2000").split(",")]:
     cfg = DeepFMConfig(field_size=39, feature_size=feat, embedding_size=32, deep_layers=[400, 400, 400], dropout=[0.5] * 3)
-    for comm in ("p2p", "nvls"):
-        for blocks in (296, 148, 64, 16):
+    for comm in os.environ.get("AR_COMMS", "p2p,nvls").split(","):
+        for blocks in [int(x) for x in os.environ.get("AR_BLOCKS", "296,148,64,16").split(",")]:
             os.environ["DFM_AR_BLOCKS"] = str(blocks)
             try:
                 m = FusedDataParallel(cfg, 1024, TF1Optimizer("Adam", 5e-4), 1, dev, world, rank, comm=comm, use_graph=False)
