@@ -15,6 +15,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
 #include <unistd.h>
 
 #include <atomic>
@@ -336,6 +337,9 @@ struct MappedFile {
     if (base) munmap(const_cast<uint8_t*>(base), size);
   }
   static std::shared_ptr<MappedFile> open_path(const char* path) {
+    struct stat pre;
+    // never open() a FIFO here: opening and closing its read end would break the writer feeding it (pipe mode)
+    if (::stat(path, &pre) != 0 || !S_ISREG(pre.st_mode) || pre.st_size == 0) return nullptr;
     int fd = ::open(path, O_RDONLY);
     if (fd < 0) return nullptr;
     struct stat st;
@@ -376,6 +380,18 @@ class Loader {
         epochs_(epochs), drop_(drop_remainder), crc_(check_crc), slots_(slots), nslots_(nslots),
         stride_(slot_stride), raw_mode_(raw) {
     for (int i = 0; i < nslots_; ++i) free_slots_.push_back(i);
+    const char* no_index = getenv("DFM_LOADER_INDEXED");
+    if (!(no_index && no_index[0] == '0') && build_index()) {
+      // indexed mode (regular files only): record boundaries are walked ONCE; afterwards batch k of the sharded record
+      // sequence is an O(1) lookup, so `threads` workers build batches fully in parallel — no serial reader stage
+      indexed_ = true;
+      const long full = (long)(index_.size() / (size_t)B_);
+      per_epoch_batches_ = full + ((!drop_ && index_.size() % (size_t)B_) ? 1 : 0);
+      total_batches_ = per_epoch_batches_ * epochs_;
+      reader_finished_ = true;
+      for (int i = 0; i < (threads < 1 ? 1 : threads); ++i) parsers_.emplace_back([this] { indexed_worker(); });
+      return;
+    }
     if (raw_mode_) {
       // raw mode: slots carry the serialized records themselves (offsets[B+1] | bytes); the GPU parses them
       // (csrc/parse_gpu.cu), so there are no parser threads and the reader fills the slots directly
@@ -564,6 +580,108 @@ class Loader {
     cv_done_.notify_all();
   }
 
+  // ---- indexed mode ---------------------------------------------------------------------------------------
+  struct RecRef {
+    const uint8_t* ptr;
+    uint32_t len;
+  };
+  bool build_index() {
+    std::vector<std::shared_ptr<MappedFile>> maps;
+    for (const auto& path : paths_) {
+      std::shared_ptr<MappedFile> mf = MappedFile::open_path(path.c_str());
+      if (!mf) return false;  // FIFO / pipe / empty file: use the streaming reader
+      maps.push_back(mf);
+    }
+    long rec_idx = 0;
+    for (size_t fi = 0; fi < maps.size(); ++fi) {
+      const MappedFile& mf = *maps[fi];
+      size_t pos = 0;
+      while (pos < mf.size) {
+        if (pos + 12 > mf.size) return false;  // let the streaming path report the corruption with context
+        uint64_t n;
+        memcpy(&n, mf.base + pos, 8);
+        if (n > (1ull << 31) || pos + 16 + n > mf.size) return false;
+        if ((rec_idx % shard_n_) == shard_i_) index_.push_back(RecRef{mf.base + pos + 12, (uint32_t)n});
+        ++rec_idx;
+        pos += 16 + n;
+      }
+    }
+    for (size_t fi = 0; fi < maps.size(); ++fi) maps_[paths_[fi]] = maps[fi];
+    return true;
+  }
+  bool check_record_crc(const RecRef& r) const {
+    uint32_t hc, dc;
+    memcpy(&hc, r.ptr - 4, 4);
+    memcpy(&dc, r.ptr + r.len, 4);
+    return mask_crc(crc32c(r.ptr - 12, 8)) == hc && mask_crc(crc32c(r.ptr, r.len)) == dc;
+  }
+  void indexed_worker() {
+    const size_t off_bytes = ((size_t)(B_ + 1) * 4 + 255) & ~size_t(255);
+    for (;;) {
+      long k;
+      int slot;
+      {
+        // a batch number is handed out only together with a free slot, so the oldest outstanding batch always owns a
+        // slot and in-order delivery cannot deadlock
+        std::unique_lock<std::mutex> l(mu_);
+        cv_free_.wait(l, [this] { return stop_ || !err_.empty() || next_batch_ >= total_batches_ || !free_slots_.empty(); });
+        if (stop_ || !err_.empty() || next_batch_ >= total_batches_) return;
+        slot = free_slots_.front();
+        free_slots_.pop_front();
+        k = next_batch_++;
+      }
+      const size_t first = (size_t)(k % per_epoch_batches_) * (size_t)B_;
+      const int rows = (int)std::min<size_t>((size_t)B_, index_.size() - first);
+      bool bad = false;
+      if (raw_mode_) {
+        int32_t* offs = reinterpret_cast<int32_t*>(slots_ + (size_t)slot * stride_);
+        uint8_t* bytes = slots_ + (size_t)slot * stride_ + off_bytes;
+        const size_t cap = stride_ - off_bytes;
+        size_t used = 0;
+        for (int r = 0; r < rows && !bad; ++r) {
+          const RecRef& rr = index_[first + r];
+          if (r + 6 < rows) {
+            const RecRef& pf = index_[first + r + 6];
+            for (uint32_t o = 0; o < pf.len + 4; o += 64) __builtin_prefetch(pf.ptr - 12 + o, 0, 0);
+          }
+          if (crc_ && !check_record_crc(rr)) { set_err("corrupted record CRC"); bad = true; break; }
+          if (used + rr.len > cap) { set_err("raw slot overflow: raise max_record_bytes"); bad = true; break; }
+          offs[r] = (int32_t)used;
+          memcpy(bytes + used, rr.ptr, rr.len);
+          used += rr.len;
+          offs[r + 1] = (int32_t)used;
+        }
+      } else {
+        float* lab = slot_labels(slot);
+        int32_t* ids = slot_ids(slot);
+        float* vals = slot_vals(slot);
+        for (int r = 0; r < rows && !bad; ++r) {
+          const RecRef& rr = index_[first + r];
+          if (r + 6 < rows) {  // records stream from DRAM exactly once: fetch a few records ahead of the parser
+            const RecRef& pf = index_[first + r + 6];
+            for (uint32_t o = 0; o < pf.len + 4; o += 64) __builtin_prefetch(pf.ptr - 12 + o, 0, 0);
+          }
+          if (crc_ && !check_record_crc(rr)) { set_err("corrupted record CRC"); bad = true; break; }
+          if (parse_example(rr.ptr, rr.len, F_, lab + r, ids + (size_t)r * F_, vals + (size_t)r * F_)) bad = true;
+        }
+      }
+      if (bad) {
+        fail(g_err);
+        cv_free_.notify_all();
+        return;
+      }
+      records_read_.fetch_add(rows);
+      {
+        std::lock_guard<std::mutex> l(mu_);
+        Done d{k, slot, rows};
+        auto it = done_.begin();
+        while (it != done_.end() && it->seq < d.seq) ++it;
+        done_.insert(it, d);
+      }
+      cv_done_.notify_one();
+    }
+  }
+
   // ---- raw mode -------------------------------------------------------------------------------------------
   int take_free_slot() {
     std::unique_lock<std::mutex> l(mu_);
@@ -750,6 +868,9 @@ class Loader {
   int nslots_;
   size_t stride_;
   bool raw_mode_ = false;
+  bool indexed_ = false;
+  std::vector<RecRef> index_;
+  long per_epoch_batches_ = 0, next_batch_ = 0;
   std::mutex mu_;
   std::condition_variable cv_work_, cv_free_, cv_done_, cv_raw_space_;
   std::deque<std::unique_ptr<RawBatch>> raw_;
