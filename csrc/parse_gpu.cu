@@ -1,6 +1,6 @@
 // example_parse_gpu (replaces the CPU ParseExample op, N2, when the host parser is the
 // bottleneck): a batch of serialized `tf.train.Example` protos is copied to the GPU as raw bytes and decoded there,
-// one thread per record, straight into the packed input slot (labels | ids | vals) the training step reads.
+// one thread per record (records staged in shared memory per CTA), straight into the packed input slot (labels | ids | vals) the training step reads.
 // Fixed schema (TOOL:25-32, HVD:78-83): "label" float x1, "ids" int64 xF, "values" float xF; packed and unpacked
 // repeated encodings, any map order, unknown features skipped. Errors (missing feature, wrong count, id > int32,
 // malformed varint) set *err to 1 + record index of the first failure and leave the record zero-filled.
@@ -170,15 +170,42 @@ __device__ bool parse_example_dev(const uint8_t* p, int len, int F, float* label
   return got_l && got_i && got_v;
 }
 
-__global__ void __launch_bounds__(128)
+constexpr int kParseThreads = 64;         // records per CTA
+constexpr int kParseStage = 40 * 1024;    // staged bytes per CTA (64 records x ~400 B at F = 39; longer spans parse from global)
+
+// Parsing is a chain of dependent byte loads (every varint byte decides where the next one is), ~0.5 us each from
+// global memory. The records of one CTA are contiguous in the blob, so the CTA first copies their span into shared
+// memory with coalesced 16-byte loads (bytewise head/tail: nothing outside [begin, end) is ever read) and the threads
+// then walk their records there.
+__global__ void __launch_bounds__(kParseThreads)
 example_parse_kernel(const uint8_t* __restrict__ blob, const int* __restrict__ offsets, int n, int F,
                      float* __restrict__ labels, int* __restrict__ ids, float* __restrict__ vals, int* __restrict__ err) {
-  const int r = blockIdx.x * 128 + threadIdx.x;
+  __shared__ __align__(16) uint8_t stage[kParseStage];
+  const int r0 = blockIdx.x * kParseThreads;
+  const int r1 = min(n, r0 + kParseThreads);
+  const int o_begin = offsets[r0], o_end = offsets[r1];
+  const uint8_t* src = blob + o_begin;
+  const int span = o_end - o_begin;
+  const int mis = (int)(reinterpret_cast<uintptr_t>(src) & 15);  // stage[mis + k] holds src[k]: 16-byte chunks stay aligned
+  const bool staged = span >= 0 && span + mis <= kParseStage;    // CTA-uniform
+  if (staged) {
+    const int head = min(span, (16 - mis) & 15);           // bytes before the first 16-byte boundary
+    const int nvec = (span - head) >> 4;                   // whole 16-byte chunks
+    const int tail0 = head + (nvec << 4);
+    for (int k = threadIdx.x; k < head; k += kParseThreads) stage[mis + k] = src[k];
+    const uint4* vsrc = reinterpret_cast<const uint4*>(src + head);
+    uint4* vdst = reinterpret_cast<uint4*>(stage + mis + head);
+    for (int k = threadIdx.x; k < nvec; k += kParseThreads) vdst[k] = __ldg(vsrc + k);
+    for (int k = tail0 + threadIdx.x; k < span; k += kParseThreads) stage[mis + k] = src[k];
+  }
+  __syncthreads();
+  const int r = r0 + threadIdx.x;
   if (r >= n) return;
   const int o = offsets[r], len = offsets[r + 1] - o;
+  const uint8_t* rec = staged ? stage + mis + (o - o_begin) : blob + o;
   float* v = vals + (size_t)r * F;
   int* d = ids + (size_t)r * F;
-  if (!parse_example_dev(blob + o, len, F, labels + r, d, v)) {
+  if (len < 0 || !parse_example_dev(rec, len, F, labels + r, d, v)) {
     atomicCAS(err, 0, r + 1);
     labels[r] = 0.f;
     for (int f = 0; f < F; ++f) { d[f] = 0; v[f] = 0.f; }
@@ -196,7 +223,7 @@ extern "C" {
 int dfm_example_parse(const void* blob, const int* offsets, int n, int F, float* labels, int* ids, float* vals, int* err,
                       void* stream) {
   DFM_REQUIRE(n > 0 && F > 0, "example_parse: empty batch");
-  example_parse_kernel<<<ceil_div(n, 128), 128, 0, (cudaStream_t)stream>>>((const uint8_t*)blob, offsets, n, F, labels,
+  example_parse_kernel<<<ceil_div(n, kParseThreads), kParseThreads, 0, (cudaStream_t)stream>>>((const uint8_t*)blob, offsets, n, F, labels,
                                                                             ids, vals, err);
   DFM_CHECK(cudaGetLastError());
   return DFM_OK;

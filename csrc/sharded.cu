@@ -176,8 +176,11 @@ emb_bwd_a2a_kernel(const ShardPtrs sp, const int* __restrict__ ids, const float*
   const float4* ep = reinterpret_cast<const float4*>(e32 + (size_t)b * ldx + (size_t)f * K);
   const float4* spp = reinterpret_cast<const float4*>(S + (size_t)b * K);
   const uint2* dxp = reinterpret_cast<const uint2*>(dx0 + (size_t)b * ldx + (size_t)f * K);
+  // the row's G 16-byte chunks are split over gridDim.y CTAs (shorter serial chain per thread), as in emb_bwd
+  const int g_per = (G + (int)gridDim.y - 1) / (int)gridDim.y;
+  const int g_begin = (int)blockIdx.y * g_per, g_end = min(G, g_begin + g_per);
 #pragma unroll 2
-  for (int g = 0; g < G; ++g) {
+  for (int g = g_begin; g < g_end; ++g) {
     float4 gr = make_float4(0.f, 0.f, 0.f, 0.f);
     if (valid) {
       const float4 e = __ldg(ep + g);
@@ -207,6 +210,7 @@ emb_bwd_a2a_kernel(const ShardPtrs sp, const int* __restrict__ ids, const float*
     }
     if (is_leader) red_add_f32x4(gdst + 4 * g, gr.x, gr.y, gr.z, gr.w);  // remote reduction over NVLink
   }
+  if (blockIdx.y != 0) return;  // CTA-uniform: first-order gradient and touched bit once per pair
   float gw = valid ? d * v : 0.f;
   if (mask == 0xffffffffu) {
     gw = warp_sum(gw);
@@ -240,12 +244,64 @@ struct SparseOptArgs {
   float* reg_loss;
 };
 
+// Row update of one touched row by the G lanes of a sub-group: loads first (all independent), then math, then stores.
+template <int G>
+struct RowState {
+  float4 gr, w, s0, s1;
+  float gw1, w1, t0, t1;
+};
+
+template <int G>
+__device__ __forceinline__ void row_load(const SparseOptArgs& a, long long row, int g, int nslots, RowState<G>& r) {
+  constexpr int K = 4 * G;
+  r.gr = reinterpret_cast<const float4*>(a.gv + row * K)[g];
+  r.w = reinterpret_cast<const float4*>(a.v + row * K)[g];
+  r.s0 = nslots > 0 ? reinterpret_cast<const float4*>(a.v_s0 + row * K)[g] : make_float4(0, 0, 0, 0);
+  r.s1 = nslots > 1 ? reinterpret_cast<const float4*>(a.v_s1 + row * K)[g] : make_float4(0, 0, 0, 0);
+  if (g == 0) {  // first-order weight of the same row
+    r.gw1 = a.gw[row]; r.w1 = a.w[row];
+    r.t0 = nslots > 0 ? a.w_s0[row] : 0.f;
+    r.t1 = nslots > 1 ? a.w_s1[row] : 0.f;
+  }
+}
+
+template <int G>
+__device__ __forceinline__ float row_update_store(const SparseOptArgs& a, long long row, int g, int nslots, float lr_t,
+                                                  RowState<G>& r) {
+  constexpr int K = 4 * G;
+  float reg = r.w.x * r.w.x + r.w.y * r.w.y + r.w.z * r.w.z + r.w.w * r.w.w;
+  r.gr.x += a.l2 * r.w.x; r.gr.y += a.l2 * r.w.y; r.gr.z += a.l2 * r.w.z; r.gr.w += a.l2 * r.w.w;
+  opt_update(a.h, lr_t, r.gr.x, r.w.x, r.s0.x, r.s1.x);
+  opt_update(a.h, lr_t, r.gr.y, r.w.y, r.s0.y, r.s1.y);
+  opt_update(a.h, lr_t, r.gr.z, r.w.z, r.s0.z, r.s1.z);
+  opt_update(a.h, lr_t, r.gr.w, r.w.w, r.s0.w, r.s1.w);
+  reinterpret_cast<float4*>(a.v + row * K)[g] = r.w;
+  reinterpret_cast<float4*>(a.gv + row * K)[g] = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (nslots > 0) reinterpret_cast<float4*>(a.v_s0 + row * K)[g] = r.s0;
+  if (nslots > 1) reinterpret_cast<float4*>(a.v_s1 + row * K)[g] = r.s1;
+  if (g == 0) {
+    reg += r.w1 * r.w1;
+    r.gw1 += a.l2 * r.w1;
+    opt_update(a.h, lr_t, r.gw1, r.w1, r.t0, r.t1);
+    a.w[row] = r.w1;
+    a.gw[row] = 0.f;
+    if (nslots > 0) a.w_s0[row] = r.t0;
+    if (nslots > 1) a.w_s1[row] = r.t1;
+  }
+  return reg;
+}
+
+// The bitmap is read `wpt` words per warp trip with ONE coalesced load (lane l < wpt takes word base + l); the set bits
+// of the trip are expanded into a per-warp row list in shared memory (warp scan of the popcounts), and the list is then
+// consumed 2 * (32 / G) rows at a time with every load of a trip in flight before the first update. `wpt` is the largest
+// power of two that still gives at least half of the resident warps a trip, so a 1 %-dense bitmap over 4 Mi rows is one
+// bitmap load + ~1 row trip per warp instead of a 14-deep chain of dependent word loads (59 -> see profiles/).
 template <int G>
 __global__ void __launch_bounds__(kShThreads)
 sparse_row_opt_kernel(const ShardPtrs sp, const SparseOptArgs a) {
-  constexpr int K = 4 * G;
   constexpr int RPW = 32 / G;  // rows processed in parallel by one warp
   __shared__ float s_lr;
+  __shared__ unsigned short s_rows[kShThreads / 32][32 * 32];  // offset of a touched row inside the trip (< 1024)
   const uint32_t seq = *a.seq_ptr + 1u;
   cross_rank_barrier(sp, 1, seq);
   const unsigned long long t = *a.step_ptr + (unsigned long long)a.step_offset;
@@ -253,63 +309,57 @@ sparse_row_opt_kernel(const ShardPtrs sp, const SparseOptArgs a) {
   __syncthreads();
   const float lr_t = s_lr;
   const int nslots = opt_num_slots(a.h.opt);
-  const int lane = threadIdx.x & 31;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int g = lane % G, sub = lane / G;
   const long long nwords = (a.rows_local + 31) >> 5;
-  const long long warp_global = (long long)blockIdx.x * (kShThreads / 32) + (threadIdx.x >> 5);
+  const long long warp_global = (long long)blockIdx.x * (kShThreads / 32) + wib;
   const long long nwarps = (long long)gridDim.x * (kShThreads / 32);
+  int wpt = 32;
+  while (wpt > 1 && 2 * (nwords / wpt) < nwarps) wpt >>= 1;
+  unsigned short* rows = s_rows[wib];
   float reg = 0.f;
-  for (long long wd = warp_global; wd < nwords; wd += nwarps) {
-    uint32_t bits = a.bitmap[wd];
-    if (bits == 0u) continue;  // warp-uniform
-    if (lane == 0) a.bitmap[wd] = 0u;
-    while (bits) {
-      // pick up to RPW rows for this trip: sub-group `sub` takes the sub-th set bit
-      uint32_t tmp = bits;
-      int mybit = -1;
+  for (long long base = warp_global * wpt; base < nwords; base += nwarps * wpt) {
+    const long long wd = base + lane;
+    uint32_t bits = (lane < wpt && wd < nwords) ? a.bitmap[wd] : 0u;
+    if (bits) a.bitmap[wd] = 0u;
+    // exclusive warp scan of the popcounts -> slot of this lane's first row in the list
+    const int cnt = __popc(bits);
+    int incl = cnt;
 #pragma unroll
-      for (int k = 0; k < RPW; ++k) {
-        const int bpos = tmp ? __ffs(tmp) - 1 : -1;
-        if (k == sub) mybit = bpos;
-        if (tmp) tmp &= tmp - 1;
-      }
-      bits = tmp;
-      if (mybit >= 0) {
-        const long long row = (wd << 5) + mybit;
-        float4 gr = reinterpret_cast<float4*>(a.gv + row * K)[g];
-        float4 w = reinterpret_cast<float4*>(a.v + row * K)[g];
-        float4 s0 = nslots > 0 ? reinterpret_cast<float4*>(a.v_s0 + row * K)[g] : make_float4(0, 0, 0, 0);
-        float4 s1 = nslots > 1 ? reinterpret_cast<float4*>(a.v_s1 + row * K)[g] : make_float4(0, 0, 0, 0);
-        reg += w.x * w.x + w.y * w.y + w.z * w.z + w.w * w.w;
-        gr.x += a.l2 * w.x; gr.y += a.l2 * w.y; gr.z += a.l2 * w.z; gr.w += a.l2 * w.w;
-        opt_update(a.h, lr_t, gr.x, w.x, s0.x, s1.x);
-        opt_update(a.h, lr_t, gr.y, w.y, s0.y, s1.y);
-        opt_update(a.h, lr_t, gr.z, w.z, s0.z, s1.z);
-        opt_update(a.h, lr_t, gr.w, w.w, s0.w, s1.w);
-        reinterpret_cast<float4*>(a.v + row * K)[g] = w;
-        reinterpret_cast<float4*>(a.gv + row * K)[g] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (nslots > 0) reinterpret_cast<float4*>(a.v_s0 + row * K)[g] = s0;
-        if (nslots > 1) reinterpret_cast<float4*>(a.v_s1 + row * K)[g] = s1;
-        if (g == 0) {  // first-order weight of the same row
-          float gw1 = a.gw[row], w1 = a.w[row];
-          float t0 = nslots > 0 ? a.w_s0[row] : 0.f, t1 = nslots > 1 ? a.w_s1[row] : 0.f;
-          reg += w1 * w1;
-          gw1 += a.l2 * w1;
-          opt_update(a.h, lr_t, gw1, w1, t0, t1);
-          a.w[row] = w1;
-          a.gw[row] = 0.f;
-          if (nslots > 0) a.w_s0[row] = t0;
-          if (nslots > 1) a.w_s1[row] = t1;
-        }
-      }
+    for (int o = 1; o < 32; o <<= 1) {
+      const int up = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += up;
     }
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    if (total == 0) continue;  // warp-uniform
+    int slot = incl - cnt;
+    while (bits) {
+      rows[slot++] = (unsigned short)((lane << 5) + (__ffs(bits) - 1));  // offset inside the trip: word * 32 + bit
+      bits &= bits - 1;
+    }
+    __syncwarp();
+    for (int q = sub; q < total; q += 2 * RPW) {
+      const long long r0 = (base << 5) + rows[q];
+      const bool two = q + RPW < total;
+      const long long r1 = two ? (base << 5) + rows[q + RPW] : r0;
+      RowState<G> A, Bq;
+      row_load<G>(a, r0, g, nslots, A);
+      if (two) row_load<G>(a, r1, g, nslots, Bq);
+      reg += row_update_store<G>(a, r0, g, nslots, lr_t, A);
+      if (two) reg += row_update_store<G>(a, r1, g, nslots, lr_t, Bq);
+    }
+    __syncwarp();  // the list is rewritten by the next trip
   }
   reg = warp_sum(reg);
   if (lane == 0 && reg != 0.f && a.reg_loss) atomicAdd(a.reg_loss, 0.5f * a.l2 * reg);
-  __threadfence_system();  // updated rows visible to peers before the next forward's barrier
+  // Updated rows must be visible to peers before the next forward's barrier. One gpu-scope fence per CTA (thread 0, after
+  // the CTA barrier: cumulative over the CTA's stores) chained through the done counter, and ONE system-scope fence in
+  // the last CTA - a fence.sys per thread (303 K of them) was most of this kernel's 59 us (profiles/kernels_ncu.md).
   __syncthreads();
   if (threadIdx.x == 0) {
+    __threadfence();
     if (atomicAdd(a.done_counter, 1u) == gridDim.x - 1) {
+      __threadfence_system();
       *a.done_counter = 0u;
       *a.seq_ptr = seq;
     }
@@ -368,7 +418,11 @@ int dfm_emb_bwd_a2a(void* const* v, void* const* w, void* const* gv, void* const
   int rc = fill_ptrs(sp, v, w, gv, gw, bm, fl, rank, world);
   if (rc) return rc;
   const unsigned blocks = (unsigned)ceil_div_ll((long long)B * F, kShThreads);
-#define CALL(G) emb_bwd_a2a_kernel<G><<<blocks, kShThreads, 0, (cudaStream_t)stream>>>( \
+  // split the K/4 chunks over up to 4 CTAs in y while the grid stays under ~8 CTAs per SM
+  const int Gk = K / 4;
+  unsigned ysplit = 1;
+  while (ysplit < 4 && ysplit * 2 <= (unsigned)Gk && (unsigned long long)blocks * ysplit * 2 <= 148ull * 8) ysplit *= 2;
+#define CALL(G) emb_bwd_a2a_kernel<G><<<dim3(blocks, ysplit), kShThreads, 0, (cudaStream_t)stream>>>( \
       sp, ids, vals, e32, S, dy, (const __nv_bfloat16*)dx0, ldx, B, F, N)
   DFM_SH_DISPATCH(K, CALL)
 #undef CALL

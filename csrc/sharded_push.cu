@@ -86,9 +86,11 @@ a2a_dispatch_kernel(const PushPtrs pp, const int* __restrict__ ids, const float*
   }
   // last CTA publishes the per-owner request counts into the owners' inboxes
   __shared__ bool s_last;
-  __threadfence();
   __syncthreads();
-  if (threadIdx.x == 0) s_last = (atomicAdd(done_counter, 1u) == gridDim.x - 1);
+  if (threadIdx.x == 0) {
+    __threadfence();  // one fence per CTA, cumulative over the CTA's request stores (ordered by the barrier above)
+    s_last = (atomicAdd(done_counter, 1u) == gridDim.x - 1);
+  }
   __syncthreads();
   if (s_last) {
     __threadfence();
@@ -128,6 +130,8 @@ a2a_serve_kernel(const PushPtrs pp, const float* __restrict__ V, const float* __
 }
 
 // ------------------------------------------------------------------------------------------------ combine
+constexpr int kCombineUnroll = 4;
+
 template <int G>
 __global__ void __launch_bounds__(kPsThreads)
 a2a_combine_kernel(const PushPtrs pp, const int* __restrict__ pos_of_pair, const float* __restrict__ rows,
@@ -140,17 +144,33 @@ a2a_combine_kernel(const PushPtrs pp, const int* __restrict__ pos_of_pair, const
   const int g = lane % G, fg = lane / G;
   for (int sample = blockIdx.x * (kPsThreads / 32) + (threadIdx.x >> 5); sample < B; sample += gridDim.x * (kPsThreads / 32)) {
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f), ss = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int f = fg; f < F; f += FG) {
-      const long long p = (long long)f * B + sample;
-      float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (pos_of_pair[p] >= 0) e = *reinterpret_cast<const float4*>(rows + (size_t)p * K + 4 * g);
-      s.x += e.x; s.y += e.y; s.z += e.z; s.w += e.w;
-      ss.x += e.x * e.x; ss.y += e.y * e.y; ss.z += e.z * e.z; ss.w += e.w * e.w;
-      uint2 pk;
-      pk.x = pack_bf16x2(e.x, e.y);
-      pk.y = pack_bf16x2(e.z, e.w);
-      *reinterpret_cast<uint2*>(x0 + (size_t)sample * ldx + (size_t)f * K + 4 * g) = pk;
-      if (e32) *reinterpret_cast<float4*>(e32 + (size_t)sample * ldx + (size_t)f * K + 4 * g) = e;
+    for (int f0 = fg; f0 < F; f0 += FG * kCombineUnroll) {  // kCombineUnroll rows in flight per sub-group
+      bool have[kCombineUnroll];
+      float4 row[kCombineUnroll];
+#pragma unroll
+      for (int u = 0; u < kCombineUnroll; ++u) {
+        const int f = f0 + u * FG;
+        have[u] = f < F && pos_of_pair[(long long)f * B + sample] >= 0;
+      }
+#pragma unroll
+      for (int u = 0; u < kCombineUnroll; ++u) {
+        const long long p = (long long)(f0 + u * FG) * B + sample;
+        row[u] = have[u] ? *reinterpret_cast<const float4*>(rows + (size_t)p * K + 4 * g) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int u = 0; u < kCombineUnroll; ++u) {
+        const int f = f0 + u * FG;
+        if (f < F) {
+          const float4 e = row[u];
+          s.x += e.x; s.y += e.y; s.z += e.z; s.w += e.w;
+          ss.x += e.x * e.x; ss.y += e.y * e.y; ss.z += e.z * e.z; ss.w += e.w * e.w;
+          uint2 pk;
+          pk.x = pack_bf16x2(e.x, e.y);
+          pk.y = pack_bf16x2(e.z, e.w);
+          *reinterpret_cast<uint2*>(x0 + (size_t)sample * ldx + (size_t)f * K + 4 * g) = pk;
+          if (e32) *reinterpret_cast<float4*>(e32 + (size_t)sample * ldx + (size_t)f * K + 4 * g) = e;
+        }
+      }
     }
 #pragma unroll
     for (int o = G; o < 32; o <<= 1) {
@@ -201,27 +221,72 @@ a2a_grad_push_kernel(const PushPtrs pp, const int* __restrict__ ids, const float
 }
 
 // ------------------------------------------------------------------------------------------------ gradient apply
+// A warp takes 32 consecutive inbox entries; its 32 / G sub-groups each walk G of them in order and MERGE RUNS of equal
+// rows in registers before the red.add (dispatch numbers the requests of one requester warp consecutively and pairs are
+// field-major, so a hot row - Criteo's numeric fields use one id for every sample - arrives as runs of up to 32 equal
+// entries: same-address L2 atomics, which serialise at ~10 ns each, drop by the run length). Loads go 4 entries at a time
+// in front of the (fire-and-forget) reductions. First-order gradients and bitmap bits are merged with match_any.
 template <int G>
 __global__ void __launch_bounds__(kPsThreads)
 a2a_grad_apply_kernel(const PushPtrs pp, float* __restrict__ GV, float* __restrict__ GW, uint32_t* __restrict__ bitmap,
                       const unsigned int* __restrict__ seq_ptr) {
   constexpr int K = 4 * G;
+  constexpr int U = G < 4 ? G : 4;
   push_barrier(pp, 2, *seq_ptr + 1u);  // every rank's gradient rows have arrived
-  const int g = threadIdx.x % G;
-  const long long group = ((long long)blockIdx.x * kPsThreads + threadIdx.x) / G;
-  const long long ngroups = (long long)gridDim.x * kPsThreads / G;
+  const int lane = threadIdx.x & 31;
+  const int g = lane % G, sub = lane / G;
+  const long long warp_global = (long long)blockIdx.x * (kPsThreads / 32) + (threadIdx.x >> 5);
+  const long long nwarps = (long long)gridDim.x * (kPsThreads / 32);
   for (int src = 0; src < pp.world; ++src) {
     const int n = pp.req_cnt[pp.rank][src];
     const Req* inbox = pp.req[pp.rank] + (size_t)src * pp.cap;
     const float* gin = pp.grad_in[pp.rank] + (size_t)src * pp.cap * K;
     const float* gwin = pp.gw_in[pp.rank] + (size_t)src * pp.cap;
-    for (long long e = group; e < n; e += ngroups) {
-      const int lrow = inbox[e].lrow;
-      const float4 gr = *reinterpret_cast<const float4*>(gin + (size_t)e * K + 4 * g);
-      red_add_f32x4(GV + (size_t)lrow * K + 4 * g, gr.x, gr.y, gr.z, gr.w);  // local segment-sum
-      if (g == 0) {
-        atomicAdd(GW + lrow, gwin[e]);
-        atomicOr(bitmap + (lrow >> 5), 1u << (lrow & 31));
+    for (long long e0 = warp_global * 32; e0 < n; e0 += nwarps * 32) {
+      const bool has = e0 + lane < n;
+      const int my_row = has ? inbox[e0 + lane].lrow : -1;
+      float my_gw = has ? gwin[e0 + lane] : 0.f;
+      // ---- embedding rows: sub-group `sub` owns entries [sub * G, sub * G + G) of this trip
+      const float* gsub = gin + (size_t)(e0 + sub * G) * K + 4 * g;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      int cur = -1;
+#pragma unroll
+      for (int i0 = 0; i0 < G; i0 += U) {
+        int r[U];
+        float4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) r[u] = __shfl_sync(0xffffffffu, my_row, sub * G + i0 + u);
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          v[u] = r[u] >= 0 ? *reinterpret_cast<const float4*>(gsub + (size_t)(i0 + u) * K) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          if (r[u] != cur) {
+            if (cur >= 0) red_add_f32x4(GV + (size_t)cur * K + 4 * g, acc.x, acc.y, acc.z, acc.w);  // local segment-sum
+            acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            cur = r[u];
+          }
+          acc.x += v[u].x; acc.y += v[u].y; acc.z += v[u].z; acc.w += v[u].w;
+        }
+      }
+      if (cur >= 0) red_add_f32x4(GV + (size_t)cur * K + 4 * g, acc.x, acc.y, acc.z, acc.w);
+      // ---- first-order gradient + touched bit: one atomic per distinct row of the trip
+      const unsigned key = has ? (unsigned)my_row : (0x80000000u | (unsigned)lane);
+      const unsigned mask = __match_any_sync(0xffffffffu, key);
+      const int leader = __ffs(mask) - 1;
+      if (__popc(mask) > 1) {
+        float sum = my_gw;
+        unsigned rem = mask & ~(1u << leader);
+        while (rem) {
+          const int srcl = __ffs(rem) - 1;
+          rem &= rem - 1;
+          sum += __shfl_sync(mask, my_gw, srcl);
+        }
+        my_gw = sum;
+      }
+      if (has && lane == leader) {
+        atomicAdd(GW + my_row, my_gw);
+        atomicOr(bitmap + (my_row >> 5), 1u << (my_row & 31));
       }
     }
   }

@@ -27,12 +27,13 @@ def batch(cfg, B, seed):
     labels = (torch.rand(B, generator=g) < 0.3).float()
     return ids, vals, labels
 
-for K, opt in [(32, "Adagrad"), (64, "Adam"), (32, "GD")]:
+for K, opt, mode in [(32, "Adagrad", "pull"), (64, "Adam", "pull"), (32, "GD", "pull"), (64, "GD", "push"),
+                     (32, "Adam", "push")]:
     cfg = DeepFMConfig(field_size=39, feature_size=5003, embedding_size=K, deep_layers=[400, 400, 400],
                        dropout=[0.5, 0.8, 1.0], l2_reg=1e-4, l2_mode="touched")
     Bl = 256; GB = Bl * world
     params = init_params(cfg, seed=3)
-    m = ShardedDeepFM(cfg, Bl, TF1Optimizer(opt, 1e-2), 77, dev, world, rank, params=params)
+    m = ShardedDeepFM(cfg, Bl, TF1Optimizer(opt, 1e-2), 77, dev, world, rank, params=params, a2a_mode=mode)
     ref_p = {k: v.clone().to(dev) for k, v in params.items()}
     ref_opt = TF1Optimizer(opt, 1e-2)
     ref_slots = ref_opt.init_slots(ref_p)
@@ -57,10 +58,10 @@ for K, opt in [(32, "Adagrad"), (64, "Adam"), (32, "GD")]:
         scale = float(b.abs().max()) + 1e-8
         if opt == "GD":
             err = float((a - b).abs().max()) / scale; worst = max(worst, err)
-            check(err < 3e-2, "K%d %s %s err %.3e" % (K, opt, k, err))
+            check(err < 3e-2, "K%d %s %s %s err %.3e" % (K, opt, mode, k, err))
         else:
             frac = float(((a - b).abs() > 3e-2 * scale).float().mean()); worst = max(worst, frac)
-            check(frac < 0.20, "K%d %s %s frac_bad %.3f" % (K, opt, k, frac))
+            check(frac < 0.20, "K%d %s %s %s frac_bad %.3f" % (K, opt, mode, k, frac))
     # untouched rows must be bit-identical to the initial table (lazy update)
     all_ids = torch.cat([batch(cfg, GB, s)[0].reshape(-1) for s in range(3)]).unique().to(dev)
     untouched = torch.ones(cfg.feature_size, dtype=torch.bool, device=dev); untouched[all_ids] = False
@@ -76,7 +77,7 @@ for K, opt in [(32, "Adagrad"), (64, "Adam"), (32, "GD")]:
     e1.record(); torch.cuda.synchronize()
     tt = torch.tensor([e0.elapsed_time(e1) * 10.0], device=dev); dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     if rank == 0:
-        print("sharded K=%d opt=%-7s world=%d worst=%.3e us/step=%.1f loss=%.4f (%s)" % (K, opt, world, worst, float(tt), float(m.last_loss()), m.comm_name), flush=True)
+        print("sharded K=%d opt=%-7s a2a=%s world=%d worst=%.3e us/step=%.1f loss=%.4f (%s)" % (K, opt, mode, world, worst, float(tt), float(m.last_loss()), m.comm_name), flush=True)
     del m
     torch.cuda.synchronize(); dist.barrier()
 flag = torch.tensor([1 if ok else 0], device=dev); dist.all_reduce(flag, op=dist.ReduceOp.MIN)
