@@ -291,17 +291,18 @@ __device__ __forceinline__ float row_update_store(const SparseOptArgs& a, long l
   return reg;
 }
 
-// The bitmap is read `wpt` words per warp trip with ONE coalesced load (lane l < wpt takes word base + l); the set bits
-// of the trip are expanded into a per-warp row list in shared memory (warp scan of the popcounts), and the list is then
-// consumed 2 * (32 / G) rows at a time with every load of a trip in flight before the first update. `wpt` is the largest
-// power of two that still gives at least half of the resident warps a trip, so a 1 %-dense bitmap over 4 Mi rows is one
-// bitmap load + ~1 row trip per warp instead of a 14-deep chain of dependent word loads (59 -> see profiles/).
+// Bitmap words are dealt to warps round-robin (word wd belongs to warp wd % nwarps): hot ids are small ids inside each
+// field's range, so touched rows cluster, and a contiguous split left a few warps with hundreds of rows while 60 % of the
+// SM cycles idled (ncu: 63 us, mostly stall_barrier). A warp reads up to 32 of its words with ONE load instruction,
+// expands the set bits into a per-warp row list in shared memory (warp scan of the popcounts) and consumes the list
+// 2 * (32 / G) rows at a time with every load of a trip in flight before the first update - instead of a chain of
+// ~14 dependent word loads, each followed by its own dependent row loads.
 template <int G>
-__global__ void __launch_bounds__(kShThreads)
+__global__ void __launch_bounds__(kShThreads, 4)
 sparse_row_opt_kernel(const ShardPtrs sp, const SparseOptArgs a) {
   constexpr int RPW = 32 / G;  // rows processed in parallel by one warp
   __shared__ float s_lr;
-  __shared__ unsigned short s_rows[kShThreads / 32][32 * 32];  // offset of a touched row inside the trip (< 1024)
+  __shared__ unsigned short s_rows[kShThreads / 32][32 * 32];  // (word slot in the trip) * 32 + bit
   const uint32_t seq = *a.seq_ptr + 1u;
   cross_rank_barrier(sp, 1, seq);
   const unsigned long long t = *a.step_ptr + (unsigned long long)a.step_offset;
@@ -314,13 +315,11 @@ sparse_row_opt_kernel(const ShardPtrs sp, const SparseOptArgs a) {
   const long long nwords = (a.rows_local + 31) >> 5;
   const long long warp_global = (long long)blockIdx.x * (kShThreads / 32) + wib;
   const long long nwarps = (long long)gridDim.x * (kShThreads / 32);
-  int wpt = 32;
-  while (wpt > 1 && 2 * (nwords / wpt) < nwarps) wpt >>= 1;
   unsigned short* rows = s_rows[wib];
   float reg = 0.f;
-  for (long long base = warp_global * wpt; base < nwords; base += nwarps * wpt) {
-    const long long wd = base + lane;
-    uint32_t bits = (lane < wpt && wd < nwords) ? a.bitmap[wd] : 0u;
+  for (long long k0 = 0; k0 * nwarps + warp_global < nwords; k0 += 32) {  // warp-uniform
+    const long long wd = (k0 + lane) * nwarps + warp_global;
+    uint32_t bits = wd < nwords ? a.bitmap[wd] : 0u;
     if (bits) a.bitmap[wd] = 0u;
     // exclusive warp scan of the popcounts -> slot of this lane's first row in the list
     const int cnt = __popc(bits);
@@ -334,14 +333,16 @@ sparse_row_opt_kernel(const ShardPtrs sp, const SparseOptArgs a) {
     if (total == 0) continue;  // warp-uniform
     int slot = incl - cnt;
     while (bits) {
-      rows[slot++] = (unsigned short)((lane << 5) + (__ffs(bits) - 1));  // offset inside the trip: word * 32 + bit
+      rows[slot++] = (unsigned short)((lane << 5) + (__ffs(bits) - 1));
       bits &= bits - 1;
     }
     __syncwarp();
     for (int q = sub; q < total; q += 2 * RPW) {
-      const long long r0 = (base << 5) + rows[q];
+      const int c0 = rows[q];
+      const long long r0 = (((k0 + (c0 >> 5)) * nwarps + warp_global) << 5) + (c0 & 31);
       const bool two = q + RPW < total;
-      const long long r1 = two ? (base << 5) + rows[q + RPW] : r0;
+      const int c1 = two ? rows[q + RPW] : c0;
+      const long long r1 = (((k0 + (c1 >> 5)) * nwarps + warp_global) << 5) + (c1 & 31);
       RowState<G> A, Bq;
       row_load<G>(a, r0, g, nslots, A);
       if (two) row_load<G>(a, r1, g, nslots, Bq);

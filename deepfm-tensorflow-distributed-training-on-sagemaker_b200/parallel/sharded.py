@@ -67,7 +67,10 @@ class ShardedDeepFM(FusedDataParallel):
         self.sh_done = torch.zeros(1, device=device, dtype=torch.int32)
         self.e32 = torch.zeros(self.B, cfg.field_size * K, **f32)
         self._fwd_blocks = max(1, min(1184, (self.B + 7) // 8))
-        self._opt_blocks = max(1, min(1184, (self.words + 7) // 8))
+        # sparse_row_opt: a warp takes up to 32 bitmap words per trip and ~4 rows per inner iteration. Enough warps for
+        # ~8 touched rows each (at most B*F*W / W lookups land on this shard), one wave of 4 CTAs/SM (64 registers).
+        want_warps = max(self.words // 32, min(R, self.B * cfg.field_size) // 8, 1)
+        self._opt_blocks = int(_os.environ.get("DFM_SPARSE_OPT_BLOCKS", max(1, min(592, (want_warps + 7) // 8))))
         if self.push:
             cap = self.B * cfg.field_size
             self.cap = cap
