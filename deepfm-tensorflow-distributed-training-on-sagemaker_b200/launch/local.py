@@ -21,6 +21,7 @@ import subprocess
 import sys
 import tempfile
 import threading
+import time
 from typing import Dict, List, Optional
 
 
@@ -43,7 +44,8 @@ def hyperparameters_to_argv(hp: Dict[str, object]) -> List[str]:
 class LocalEstimator:
     def __init__(self, hyperparameters: Dict[str, object], distribution: Optional[dict] = None, input_mode: str = "File",
                  instance_count: int = 1, entry_module: str = "deepfm_b200", python: str = sys.executable,
-                 env: Optional[Dict[str, str]] = None, cwd: Optional[str] = None):
+                 env: Optional[Dict[str, str]] = None, cwd: Optional[str] = None, max_restarts: int = 0,
+                 grace_secs: float = 10.0):
         self.hp = dict(hyperparameters)
         self.dist = distribution or {}
         self.input_mode = input_mode
@@ -58,6 +60,7 @@ class LocalEstimator:
         if ps.get("enabled"):
             self.hp.setdefault("strategy", "ps")
         self.returncodes: List[int] = []
+        self.max_restarts, self.grace_secs, self.restarts = int(max_restarts), float(grace_secs), 0
 
     def fit(self, inputs: Dict[str, str], wait: bool = True, timeout: Optional[float] = None) -> List[int]:
         pipe = self.input_mode.lower() == "pipe"
@@ -84,6 +87,26 @@ class LocalEstimator:
             if "evaluation" in inputs:
                 hp.setdefault("val_data_dir", inputs["evaluation"])
         argv = hyperparameters_to_argv(hp)
+        attempt = 0
+        while True:
+            procs = self._spawn(argv, inputs)
+            if not wait:
+                self._procs = procs
+                return []
+            self.returncodes = self._supervise(procs, timeout)
+            if not any(self.returncodes):
+                return self.returncodes
+            # A failed attempt is restarted like an interrupted (spot) SageMaker job: same model_dir, so the chief
+            # restores the latest checkpoint (Estimator semantics). Pipe mode cannot be replayed (the
+            # FIFOs of the failed attempt are consumed), so only File mode restarts.
+            if attempt >= self.max_restarts or pipe:
+                raise RuntimeError("training job failed: return codes %s" % self.returncodes)
+            attempt += 1
+            self.restarts = attempt
+            print("INFO:deepfm_b200.launch: attempt %d failed with return codes %s; restarting (%d/%d)"
+                  % (attempt, self.returncodes, attempt, self.max_restarts), flush=True)
+
+    def _spawn(self, argv: List[str], inputs: Dict[str, str]) -> List[subprocess.Popen]:
         port = _free_port()
         procs = []
         for r in range(self.nproc):
@@ -95,20 +118,39 @@ class LocalEstimator:
             for ch, src in inputs.items():
                 env["SM_CHANNEL_%s" % ch.upper().replace("-", "_")] = src
             procs.append(subprocess.Popen([self.python, "-m", self.entry] + argv, env=env, cwd=self.cwd))
-        if not wait:
-            self._procs = procs
-            return []
-        self.returncodes = []
-        for p in procs:
-            try:
-                self.returncodes.append(p.wait(timeout=timeout))
-            except subprocess.TimeoutExpired:
-                for q in procs:
-                    q.kill()
-                raise
-        if any(self.returncodes):
-            raise RuntimeError("training job failed: return codes %s" % self.returncodes)
-        return self.returncodes
+        return procs
+
+    def _supervise(self, procs: List[subprocess.Popen], timeout: Optional[float]) -> List[int]:
+        """Failure detection (the reference relies on Horovod's 'shut down because a rank exited' error, PDF p22): poll
+        every worker; when one exits non-zero the survivors - which would otherwise sit in a collective until the
+        device-side watchdog fires - get `grace_secs` to notice by themselves and are then terminated."""
+        t0 = time.time()
+        failed_at: Optional[float] = None
+        while True:
+            codes = [p.poll() for p in procs]
+            if all(c is not None for c in codes):
+                return [int(c) for c in codes]
+            now = time.time()
+            if failed_at is None and any(c not in (None, 0) for c in codes):
+                failed_at = now
+            if failed_at is not None and now - failed_at > self.grace_secs:
+                for p in procs:
+                    if p.poll() is None:
+                        p.terminate()
+                deadline = time.time() + 5.0
+                for p in procs:
+                    try:
+                        p.wait(timeout=max(0.1, deadline - time.time()))
+                    except subprocess.TimeoutExpired:
+                        p.kill()
+                        p.wait()
+                return [int(p.returncode) for p in procs]
+            if timeout is not None and now - t0 > timeout:
+                for p in procs:
+                    if p.poll() is None:
+                        p.kill()
+                raise subprocess.TimeoutExpired(cmd="%s -m %s" % (self.python, self.entry), timeout=timeout)
+            time.sleep(0.05)
 
 
 def _feed_fifo(fifo: str, src: str) -> None:
@@ -141,6 +183,8 @@ def main(argv=None) -> int:
     ap.add_argument("--pipe", action="store_true", help="Pipe input mode")
     ap.add_argument("--training", default="")
     ap.add_argument("--evaluation", default="")
+    ap.add_argument("--max_restarts", type=int, default=0,
+                    help="restart a failed File-mode job from its latest checkpoint up to this many times")
     a = ap.parse_args(argv)
     hp: Dict[str, object] = {}
     k = None
@@ -158,7 +202,7 @@ def main(argv=None) -> int:
         inputs["training"] = a.training
     if a.evaluation:
         inputs["evaluation"] = a.evaluation
-    LocalEstimator(hp, dist, "Pipe" if a.pipe else "File").fit(inputs)
+    LocalEstimator(hp, dist, "Pipe" if a.pipe else "File", max_restarts=a.max_restarts).fit(inputs)
     return 0
 
 

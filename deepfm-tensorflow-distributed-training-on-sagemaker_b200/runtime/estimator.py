@@ -21,6 +21,33 @@ from .hooks import CheckpointSaverHook, LoggingHook
 from .trainer import Trainer
 
 
+def _parse_fault(spec: str, rank: int):
+    """Fault injection for the failure-detection / resume tests (the reference has none).
+    DFM_FAULT_INJECT="<rank>:<step>[:<marker file>]": that rank dies with exit code 17 right after optimizer step
+    <step>. With a marker file the fault fires once per job: the file is created first, and a process that finds it
+    (the restarted attempt) runs normally."""
+    if not spec:
+        return None
+    parts = spec.split(":", 2)
+    try:
+        r, step = int(parts[0]), int(parts[1])
+    except (ValueError, IndexError):
+        raise SystemExit("DFM_FAULT_INJECT must be <rank>:<step>[:<marker file>], got %r" % spec)
+    marker = parts[2] if len(parts) > 2 else ""
+    if r != rank or (marker and os.path.exists(marker)):
+        return None
+    return (step, marker)
+
+
+def _fire_fault(fault, step: int, rank: int) -> None:
+    if fault[1]:
+        with open(fault[1], "w") as f:
+            f.write("rank %d died at step %d\n" % (rank, step))
+    sys.stderr.write("ERROR:deepfm_b200: injected fault: rank %d exits at step %d\n" % (rank, step))
+    sys.stderr.flush()
+    os._exit(17)
+
+
 class Estimator:
     def __init__(self, cfg: DeepFMConfig, batch_size: int, optimizer: TF1Optimizer, model_dir: Optional[str],
                  env: Optional[DistEnv] = None, backend: str = "auto", seed: int = 0, log_steps: int = 100,
@@ -49,6 +76,7 @@ class Estimator:
         self.saver = CheckpointSaverHook(self.model_dir or "", save_checkpoints_secs, save_checkpoints_steps,
                                          keep_checkpoint_max, enabled=self.env.is_chief and bool(model_dir))
         self._restored = False
+        self._fault = _parse_fault(os.environ.get("DFM_FAULT_INJECT", ""), self.env.rank)
 
     # ------------------------------------------------------------------------------------------ state
     def restore_latest(self) -> Optional[str]:
@@ -98,6 +126,8 @@ class Estimator:
                 b.release()
             step += 1
             n_local += 1
+            if self._fault is not None and step >= self._fault[0]:
+                _fire_fault(self._fault, step, self.env.rank)
             self.log.after_step(step, lambda: self._current_loss())
             if self.saver.due(step):
                 self.saver.save(tr, self.out)

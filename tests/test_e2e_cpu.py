@@ -126,3 +126,34 @@ def test_pipe_mode_training(data, tmp_path):
         {"training": str(data / "train"), "evaluation": str(data / "val")}, timeout=600)
     from deepfm_b200.utils.checkpoint import latest_checkpoint
     assert latest_checkpoint(str(tmp_path / "pm")).endswith("model.ckpt-80")  # 2 epochs x 2560 rows / 64
+
+
+def test_failure_detection_and_restart_from_checkpoint(data, tmp_path):
+    """a worker that dies mid-epoch must fail the job promptly (no hang in a collective), and a restart
+    of the same job resumes from the chief's latest checkpoint. Fault injection: DFM_FAULT_INJECT=<rank>:<step>."""
+    import time
+    from deepfm_b200.launch import LocalEstimator
+    from deepfm_b200.utils.checkpoint import all_checkpoints, latest_checkpoint
+    from deepfm_b200.utils.tf_bundle import read_bundle
+    hp = dict(field_size=F, feature_size=N, embedding_size=8, deep_layers="16", dropout="1.0", batch_size=32,
+              backend="torch", task_type="train", num_epochs=1, log_steps=1000, loader_threads=1,
+              save_checkpoints_steps=10)
+    inputs = {"training": str(data / "train"), "evaluation": str(data / "val")}
+    env = {"PYTHONPATH": REPO, "CUDA_VISIBLE_DEVICES": ""}
+    # (a) no restarts allowed: the job fails with the dead worker's exit code instead of hanging
+    d0 = str(tmp_path / "f0")
+    est = LocalEstimator(dict(hp, model_dir=d0), env=dict(env, DFM_FAULT_INJECT="0:13"), cwd=REPO)
+    t0 = time.time()
+    with pytest.raises(RuntimeError, match="17"):
+        est.fit(inputs, timeout=300)
+    assert time.time() - t0 < 200
+    assert all_checkpoints(d0) == [10]  # the checkpoint before the fault survived
+    # (b) two ranks, rank 1 dies after step 25 (once); the launcher tears the job down and restarts it
+    d1 = str(tmp_path / "f1")
+    marker = str(tmp_path / "fault.marker")
+    est = LocalEstimator(dict(hp, model_dir=d1), {"mpi": {"enabled": True, "processes_per_host": 2}},
+                         env=dict(env, DFM_FAULT_INJECT="1:25:" + marker), cwd=REPO, max_restarts=1, grace_secs=3.0)
+    est.fit(inputs, timeout=600)
+    assert est.restarts == 1 and os.path.exists(marker)
+    # first attempt checkpointed at 10 and 20; the second resumed from 20 and ran its 40-step epoch
+    assert int(read_bundle(latest_checkpoint(d1))["global_step"]) == 60
