@@ -54,7 +54,7 @@ def main() -> int:
     print("REDG = red.global.add (v4.f32 in the gradient kernels), LDGMC = NVLS multimem.ld_reduce, UCGABAR = cluster barrier")
     print("(barrier.cluster arrive/wait around the DSMEM exchange), MEMBAR.SYS = system-scope fences, MATCH = match.any,")
     print("STG.SYS = system-scope vector stores (multimem.st compiles to STG.E.128.STRONG.SYS on the multicast address; the")
-    print("P2P flavour uses the same opcode on peer addresses).\n")
+    print("P2P flavour stores to peer addresses with plain STG.E.128 and orders them with the final MEMBAR.SYS).\n")
     print("```")
     for mangled, nice in zip(per, names):
         c = per[mangled]
