@@ -157,3 +157,30 @@ def test_failure_detection_and_restart_from_checkpoint(data, tmp_path):
     assert est.restarts == 1 and os.path.exists(marker)
     # first attempt checkpointed at 10 and 20; the second resumed from 20 and ran its 40-step epoch
     assert int(read_bundle(latest_checkpoint(d1))["global_step"]) == 60
+
+
+def test_example_notebooks_and_scripts_use_known_flags():
+    """The launcher notebooks / example scripts (stand-ins for NB-PS / NB-HVD) must stay in sync with the flag table."""
+    import ast
+    import glob
+    import json
+    from deepfm_b200.runtime.flags import flag_definitions
+    known = {n for n, _, _, _ in flag_definitions({})}
+    sources = []
+    for nb in sorted(glob.glob(os.path.join(REPO, "examples", "notebooks", "*.ipynb"))):
+        doc = json.load(open(nb))
+        assert doc["nbformat"] == 4
+        sources += [("%s[%d]" % (os.path.basename(nb), i), "".join(c["source"]))
+                    for i, c in enumerate(doc["cells"]) if c["cell_type"] == "code"]
+    for py in sorted(glob.glob(os.path.join(REPO, "examples", "*.py"))):
+        sources.append((os.path.basename(py), open(py).read()))
+    assert len(sources) >= 9
+    seen = set()
+    for name, src in sources:
+        tree = ast.parse(src, name)  # every cell compiles
+        for node in ast.walk(tree):
+            if isinstance(node, ast.Assign) and any(getattr(t, "id", "") == "hyperparameters" for t in node.targets):
+                keys = {k.value for k in node.value.keys if isinstance(k, ast.Constant)}
+                assert keys <= known, (name, keys - known)
+                seen |= keys
+    assert {"task_type", "field_size", "feature_size", "worker_per_host", "enable_data_multi_path"} <= seen
