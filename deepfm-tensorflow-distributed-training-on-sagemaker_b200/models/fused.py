@@ -15,7 +15,7 @@ Layout: models/layout.py. Numerics oracle: models/oracle.py. Kernel ABI: include
 from __future__ import annotations
 
 from collections import OrderedDict
-from typing import Callable, Dict, List, Optional
+from typing import Dict, Optional
 
 import torch
 

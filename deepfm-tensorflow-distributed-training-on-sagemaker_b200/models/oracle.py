@@ -14,9 +14,8 @@ The MLP `weights_regularizer` is registered but never added to the loss in the r
 """
 from __future__ import annotations
 
-from typing import Dict, List, Optional
+from typing import Dict, Optional
 
-import numpy as np
 import torch
 import torch.nn.functional as F
 

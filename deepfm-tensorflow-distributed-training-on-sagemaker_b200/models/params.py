@@ -11,7 +11,7 @@ Native layout vs the reference's TF variables:
 from __future__ import annotations
 
 from collections import OrderedDict
-from typing import Dict, Iterator, Tuple
+from typing import Tuple
 
 import torch
 

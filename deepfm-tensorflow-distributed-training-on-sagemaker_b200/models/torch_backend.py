@@ -6,14 +6,13 @@ numerical referee of FusedDeepFM. Same public interface as FusedDeepFM.
 from __future__ import annotations
 
 from collections import OrderedDict
-from typing import Dict, List, Optional
+from typing import Dict, Optional
 
 import torch
 
 from ..optim.tf1 import SLOT_SUFFIXES, TF1Optimizer
-from ..utils.auc import StreamingAUC
 from .config import DeepFMConfig
-from .oracle import oracle_forward, oracle_grads, oracle_loss
+from .oracle import oracle_forward, oracle_grads
 from .params import init_params
 
 

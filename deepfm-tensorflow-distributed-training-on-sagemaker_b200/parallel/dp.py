@@ -19,7 +19,7 @@ a batch equals DP-1 on the concatenated batch (tests/test_dp_cpu.py, tests/test_
 """
 from __future__ import annotations
 
-from typing import Dict, Optional
+from typing import Dict
 
 import torch
 import torch.distributed as dist
@@ -165,10 +165,6 @@ class FusedDataParallel(FusedDeepFM):
             c_void_p(self.step_t.data_ptr()), c_void_p(self.reg_local.data_ptr()), c_void_p(self.done_counter.data_ptr()),
             c_void_p(self.seq.data_ptr()), c_int(1 if self.use_nvls else 0), c_int(self._grid_blocks), st))
         return 1
-
-    def _snapshot(self):
-        snap = super()._snapshot()
-        return snap
 
     def _restore(self, snap):
         super()._restore(snap)

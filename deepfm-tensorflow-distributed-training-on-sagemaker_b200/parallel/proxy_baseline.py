@@ -9,7 +9,6 @@ Horovod's fusion buffer, HVD:262). Same Trainer interface as the fused engine so
 from __future__ import annotations
 
 from collections import OrderedDict
-from typing import Optional
 
 import torch
 import torch.distributed as dist

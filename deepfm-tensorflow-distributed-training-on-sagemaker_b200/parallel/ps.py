@@ -23,7 +23,6 @@ from __future__ import annotations
 import os
 import queue
 import threading
-import time
 from collections import OrderedDict
 from typing import Dict, Iterable, List, Optional
 
@@ -36,7 +35,7 @@ from ..models.config import DeepFMConfig as _Cfg
 from ..models.oracle import oracle_forward, oracle_grads
 from ..models.params import init_params, native_names
 from ..optim.tf1 import SLOT_INIT, SLOT_SUFFIXES, TF1Optimizer
-from ..utils.auc import StreamingAUC, auc_from_hist
+from ..utils.auc import StreamingAUC
 
 
 class SharedParamStore:
@@ -170,7 +169,6 @@ class AsyncPSTrainer:
         self.h_rows, self.h_w = pin(self.umax, K), pin(self.umax)
         self.h_grows, self.h_gw = pin(self.umax, K), pin(self.umax)
         L = self.model.layout
-        self.dense_span = (0, L.segments["fm_w"].offset), (L.segments["mlp0.weight"].offset, L.trainable_numel)
         self.h_dense = {n: torch.zeros(L.segments[n].shape).pin_memory() for n in self.dense_names}
         self.h_gdense = {n: torch.zeros(L.segments[n].shape).pin_memory() for n in self.dense_names}
         self._graph = None

@@ -23,7 +23,7 @@ import torch.distributed as dist
 
 from ..models.layout import FlatLayout
 from ..ops import lib as _nlib
-from ..optim.tf1 import OPT_IDS, SLOT_INIT, SLOT_SUFFIXES
+from ..optim.tf1 import OPT_IDS, SLOT_INIT
 from .dp import FusedDataParallel
 from .symm import SymmArena
 

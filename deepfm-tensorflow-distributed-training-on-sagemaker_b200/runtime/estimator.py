@@ -6,16 +6,13 @@ from __future__ import annotations
 
 import collections
 import os
-import shutil
 import sys
 import time
 from typing import Callable, Iterable, Optional
 
-import torch
-
 from ..models import DeepFMConfig
 from ..optim.tf1 import TF1Optimizer
-from ..parallel.dist import DistEnv, agree_min, barrier
+from ..parallel.dist import DistEnv, agree_min
 from ..utils.checkpoint import latest_checkpoint, load_checkpoint
 from .hooks import CheckpointSaverHook, LoggingHook
 from .trainer import Trainer
