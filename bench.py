@@ -8,8 +8,9 @@ feature 117581, emb 32, MLP 400-400-400, Adam, bf16 compute, replicated embeddin
 
 Prints ONE JSON line on rank 0. `value` = device-timed (CUDA events, max over ranks) whole-job samples/s with
 device-resident input batches rotated through a pool larger than L2; `e2e.value` = the same metric through the
-public API `Trainer.train_batch` with, every step, the H2D copy of that step's batch from pinned host memory and
-a D2H read of the step's loss.
+public API `Trainer.train_packed` with, every step, the H2D copy of that step's batch from pinned host memory and
+a D2H read of the step's loss (8 bytes: stored into a pinned host ring by the optimizer kernel on one GPU, copied
+with cudaMemcpyAsync under dp / sharded).
 """
 from __future__ import annotations
 
@@ -196,8 +197,10 @@ def main():
     barrier()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
+    t_issue = time.perf_counter()
     for s in range(a.steps):
         step_host(*host_pool[(a.warmup + s) % pool])
+    t_issue = time.perf_counter() - t_issue  # host time to ISSUE the steps (the GPU is still running them)
     losses = tr.drain()
     f1.record()
     barrier()
@@ -227,6 +230,10 @@ def main():
             "clocks": clocks,
             "e2e": {"value": e2e, "unit": "samples/s", "ms_per_step": ms_e2e / a.steps,
                     "h2d_bytes_per_step": bytes_per_batch, "d2h_bytes_per_step": 8,
+                    "host_issue_us_per_step": t_issue / a.steps * 1e6,
+                    "native_step_driver": int(getattr(tr, "native_steps", 0)) > 0,
+                    "d2h_mode": ("optimizer kernel stores the step's 8 result bytes into the pinned host ring"
+                                 if getattr(tr, "_publish", False) else "cudaMemcpyAsync D2H of the result scalars"),
                     "api": "deepfm_b200.runtime.trainer.Trainer.train_packed (one pinned H2D copy per batch)"},
             "gpu_launches": launches, "kernels_per_step": tr.kernels_per_step,
             "l2_persist_bytes": int(getattr(getattr(tr, "model", None), "l2_persist_bytes", 0) or 0),

@@ -28,6 +28,11 @@ struct FlatOptArgs {
   unsigned long long* step_ptr;
   float* reg_loss;
   unsigned int* done_counter;  // scratch: CTA completion counter, self-resetting
+  // optional result publication (dfm_flat_opt_step_pub): the last CTA stores pub_n floats from pub_src into record
+  // (t - 1) % pub_ring of a host-mapped ring, so the step's result reaches the host without a D2H copy in the stream
+  const float* pub_src;
+  float* pub_dst;
+  int pub_n, pub_ring;
 };
 
 constexpr int kOptThreads = 256;
@@ -85,6 +90,13 @@ __global__ void __launch_bounds__(kOptThreads) flat_opt_kernel(const FlatOptArgs
     if (done == gridDim.x - 1) {  // every CTA has read the step by now
       *a.step_ptr = t;
       *a.done_counter = 0u;
+      if (a.pub_dst) {  // every CTA's reg_loss atomic happened before its done-counter increment (fence above)
+        __threadfence();
+        float* rec = a.pub_dst + ((t - 1ull) % (unsigned long long)a.pub_ring) * (unsigned long long)a.pub_n;
+        for (int i = 0; i < a.pub_n; ++i) rec[i] = __ldcg(a.pub_src + i);
+        // no fence.sys here: it would hold the kernel (and the next step) for a PCIe round trip (~2.7 us measured);
+        // the host reads the ring only after a stream / device synchronisation, which orders these stores
+      }
     }
   }
 }
@@ -101,10 +113,13 @@ using namespace dfm;
 extern "C" {
 
 // All ranges in elements and multiples of 4; buffers 16-byte aligned. `done_counter` = 4 bytes of zeroed scratch.
-int dfm_flat_opt_step(float* w, float* g, float* s0, float* s1, long long n, int opt, float lr, float beta1, float beta2,
-                      float eps, float momentum, float grad_scale, long long decay_begin, long long decay_end, float l2,
-                      long long shadow_begin, long long shadow_end, void* shadow, unsigned long long* step_ptr,
-                      float* reg_loss, unsigned int* done_counter, void* stream) {
+int dfm_flat_opt_step_pub(float* w, float* g, float* s0, float* s1, long long n, int opt, float lr, float beta1,
+                          float beta2, float eps, float momentum, float grad_scale, long long decay_begin,
+                          long long decay_end, float l2, long long shadow_begin, long long shadow_end, void* shadow,
+                          unsigned long long* step_ptr, float* reg_loss, unsigned int* done_counter,
+                          const float* pub_src, int pub_n, float* pub_ring, int pub_ring_len, void* stream) {
+  DFM_REQUIRE((pub_ring == nullptr) || (pub_src != nullptr && pub_n >= 1 && pub_n <= 16 && pub_ring_len >= 1),
+              "flat_opt_pub: publication needs a source, 1..16 floats per record and a ring length >= 1");
   DFM_REQUIRE(n > 0 && n % 4 == 0, "flat_opt: n must be a positive multiple of 4");
   DFM_REQUIRE(decay_begin % 4 == 0 && decay_end % 4 == 0 && shadow_begin % 4 == 0 && shadow_end % 4 == 0,
               "flat_opt: ranges must be multiples of 4");
@@ -115,10 +130,20 @@ int dfm_flat_opt_step(float* w, float* g, float* s0, float* s1, long long n, int
   a.grad_scale = grad_scale; a.decay_begin = decay_begin; a.decay_end = decay_end; a.l2 = l2;
   a.shadow_begin = shadow_begin; a.shadow_end = shadow_end; a.shadow = (__nv_bfloat16*)shadow;
   a.step_ptr = step_ptr; a.reg_loss = reg_loss; a.done_counter = done_counter;
+  a.pub_src = pub_src; a.pub_dst = pub_ring; a.pub_n = pub_n; a.pub_ring = pub_ring_len;
   long long blocks = ceil_div_ll(n / 4, kOptThreads);
   if (blocks > 148 * 8) blocks = 148 * 8;
   DFM_CHECK(launch_k(flat_opt_kernel, dim3((unsigned)blocks), dim3(kOptThreads), 0, (cudaStream_t)stream, a));
   return DFM_OK;
+}
+
+int dfm_flat_opt_step(float* w, float* g, float* s0, float* s1, long long n, int opt, float lr, float beta1, float beta2,
+                      float eps, float momentum, float grad_scale, long long decay_begin, long long decay_end, float l2,
+                      long long shadow_begin, long long shadow_end, void* shadow, unsigned long long* step_ptr,
+                      float* reg_loss, unsigned int* done_counter, void* stream) {
+  return dfm_flat_opt_step_pub(w, g, s0, s1, n, opt, lr, beta1, beta2, eps, momentum, grad_scale, decay_begin, decay_end,
+                               l2, shadow_begin, shadow_end, shadow, step_ptr, reg_loss, done_counter, nullptr, 0, nullptr,
+                               0, stream);
 }
 
 int dfm_cast_f32_bf16(const float* in, void* out, long long n, void* stream) {

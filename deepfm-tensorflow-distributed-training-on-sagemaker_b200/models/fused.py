@@ -297,10 +297,21 @@ class FusedDeepFM:
         o, L = self.opt, self.layout
         lt = L.trainable_numel
         decay = L.decay_range if self.cfg.l2_reg > 0 else (0, 0)
+        ring = getattr(self, "_result_ring", None)
         K.flat_opt_step(self.P[:lt], self.G[:lt], self.S0, self.S1, o.name, o.lr, o.beta1, o.beta2, o.eps, o.momentum,
                         1.0, decay, self.cfg.l2_reg, L.shadow_range, self.shadow, self.step_t, self.reg_loss,
-                        self.done_counter)
+                        self.done_counter, publish=(self.scalars, ring) if ring is not None else None)
         return 1
+
+    def set_result_ring(self, ring: Optional[torch.Tensor]) -> bool:
+        """Have the optimizer kernel store each step's (loss sum, L2 term) into `ring[(step - 1) % len(ring)]`, a pinned
+        HOST tensor [R, 2] - the per-step result read-back then needs no D2H copy in the stream. Must be called before
+        the first training step (the pointer is baked into the captured graphs). Returns False where the step does not
+        end with the local flat optimizer (dp / sharded subclasses publish through their own D2H copy)."""
+        if type(self)._optimizer_kernels is not FusedDeepFM._optimizer_kernels or self._graphs:
+            return False
+        self._result_ring = ring
+        return ring is not None
 
     # ------------------------------------------------------------------------------------------------ public API
     def load_inputs(self, ids: torch.Tensor, vals: torch.Tensor, labels: Optional[torch.Tensor], slot_idx: int = 0,

@@ -115,12 +115,20 @@ def auc_hist(prob: torch.Tensor, labels: torch.Tensor, thr: torch.Tensor, hist: 
 
 def flat_opt_step(w, g, s0, s1, opt_name: str, lr: float, beta1: float, beta2: float, eps: float, momentum: float,
                   grad_scale: float, decay_range, l2: float, shadow_range, shadow, step_ptr, reg_loss,
-                  done_counter) -> None:
-    _lib.check(_lib.load().dfm_flat_opt_step(
+                  done_counter, publish=None) -> None:
+    """publish = (scalars [n] device f32, ring [R, n] PINNED HOST f32): the kernel's last CTA stores the scalars into
+    ring[(step - 1) % R] directly (page-locked host memory is device-addressable under UVA)."""
+    if publish is None:
+        pub = (None, c_int(0), None, c_int(0))
+    else:
+        src, ring = publish
+        assert src.is_cuda and ring.is_pinned() and ring.dtype == torch.float32 and ring.shape[1] == src.numel()
+        pub = (_p(src), c_int(src.numel()), c_void_p(ring.data_ptr()), c_int(ring.shape[0]))
+    _lib.check(_lib.load().dfm_flat_opt_step_pub(
         _p(w), _p(g), _p(s0), _p(s1), c_longlong(w.numel()), c_int(OPT_IDS[opt_name]), c_float(lr), c_float(beta1),
         c_float(beta2), c_float(eps), c_float(momentum), c_float(grad_scale), c_longlong(decay_range[0]),
         c_longlong(decay_range[1]), c_float(l2), c_longlong(shadow_range[0]), c_longlong(shadow_range[1]), _p(shadow),
-        _p(step_ptr), _p(reg_loss), _p(done_counter), _stream()))
+        _p(step_ptr), _p(reg_loss), _p(done_counter), pub[0], pub[1], pub[2], pub[3], _stream()))
 
 
 def cast_f32_bf16(src: torch.Tensor, dst: torch.Tensor) -> None:

@@ -22,6 +22,22 @@ from ..optim.tf1 import TF1Optimizer
 from ..utils.auc import StreamingAUC, auc_from_hist
 
 
+class _CopyTicket:
+    """What `train_packed` returns on the native step path: completes when the pinned source buffer of that step has
+    been copied out (same `query()` / `synchronize()` surface as the torch Event of the Python path)."""
+    __slots__ = ("_lib", "_h", "_slot")
+
+    def __init__(self, lib, handle, slot):
+        self._lib, self._h, self._slot = lib, handle, slot
+
+    def query(self) -> bool:
+        return self._lib.dfm_driver_copy_done(self._h, self._slot) != 0
+
+    def synchronize(self) -> None:
+        from ..ops import lib as _nlib
+        _nlib.check(self._lib.dfm_driver_copy_wait(self._h, self._slot))
+
+
 class Trainer:
     def __init__(self, cfg: DeepFMConfig, batch_size: int, optimizer: Optional[TF1Optimizer] = None, seed: int = 0,
                  device=None, backend: str = "auto", world_size: int = 1, rank: int = 0, use_graph: bool = True,
@@ -78,6 +94,77 @@ class Trainer:
             self._ring = torch.zeros(self._ring_n, 2, dtype=torch.float32).pin_memory()
             self._ring_pos = 0
         self._host_losses: List[float] = []
+        # result publication: the optimizer kernel stores (loss sum, L2 term) of step t into ring[(t - 1) % ring_n]
+        # itself, so the per-step D2H read-back is 8 bytes written by the kernel instead of a copy op between two graph
+        # launches (which cost ~10 us/step of engine hand-offs). _pending then holds the model's step index at issue.
+        self._publish = False
+        if self._cuda and backend == "fused" and _os.environ.get("DFM_PUBLISH", "1") != "0" \
+                and hasattr(self.model, "set_result_ring"):
+            self._publish = bool(self.model.set_result_ring(self._ring))
+        # native step driver (csrc/step_driver.cu): one C call per host-fed step once the slot's graph exists
+        self._drv = None
+        self.native_steps = 0
+        if self._cuda and backend == "fused" and _os.environ.get("DFM_NATIVE_STEP", "1") != "0" \
+                and getattr(self.model, "use_graph", False):
+            import ctypes
+            from ..ops import lib as _nlib
+            lib = _nlib.load()
+            lib.dfm_driver_steps.restype = ctypes.c_ulonglong
+            h = ctypes.c_void_p()
+            _nlib.check(lib.dfm_driver_create(ctypes.byref(h), ctypes.c_int(self._nslots)))
+            self._drv = (lib, h)
+
+    def close(self) -> None:
+        if self._drv is not None:
+            if self._cuda:
+                torch.cuda.synchronize(self.dev)
+            lib, h = self._drv
+            self._drv = None
+            lib.dfm_driver_destroy(h)
+        if hasattr(self.model, "close"):
+            self.model.close()
+
+    def _graph_exec(self, slot: int, g) -> int:
+        cache = self.__dict__.setdefault("_exec_cache", {})
+        e = cache.get(slot)
+        if e is None or e[0] is not g:
+            e = cache[slot] = (g, int(g.raw_cuda_graph_exec()))
+        return e[1]
+
+    def _native_step(self, packed: torch.Tensor):
+        """train_packed through dfm_driver_step; None if this step has to take the Python path (graph not captured yet,
+        pageable source, ring full)."""
+        import ctypes
+        m = self.model
+        slot = self._k % self._nslots
+        g = m._graphs.get(slot)
+        if g is None or not packed.is_pinned() or self._ring_pos == self._ring_n:
+            return None
+        lib, h = self._drv
+        dst = m.in_slots[slot]["packed"]
+        nbytes = packed.numel() * packed.element_size()
+        if nbytes != dst.numel() * dst.element_size() or not packed.is_contiguous():
+            raise ValueError("train_packed: buffer does not match the packed slot layout (%d bytes)" % nbytes)
+        cs = self._copy_stream
+        if self._slot_free[slot] is not None:  # the slot was last used through the Python path
+            cs.wait_event(self._slot_free[slot])
+            self._slot_free[slot] = None
+        main = torch.cuda.current_stream(self.dev)
+        ring = self._ring[self._ring_pos]
+        sc = m.scalars
+        nscal = 0 if self._publish else min(sc.numel(), ring.numel()) * 4
+        from ..ops import lib as _nlib
+        _nlib.check(lib.dfm_driver_step(
+            h, ctypes.c_int(slot), ctypes.c_void_p(packed.data_ptr()), ctypes.c_void_p(dst.data_ptr()),
+            ctypes.c_ulonglong(nbytes), ctypes.c_void_p(self._graph_exec(slot, g)), ctypes.c_void_p(cs.cuda_stream),
+            ctypes.c_void_p(main.cuda_stream), ctypes.c_void_p(sc.data_ptr()), ctypes.c_void_p(ring.data_ptr()),
+            ctypes.c_ulonglong(nscal)))
+        self._k += 1
+        self._pending.append(m.host_step if self._publish else 0)
+        m.host_step += 1
+        self._ring_pos += 1
+        self.native_steps += 1
+        return _CopyTicket(lib, h, slot)
 
     @staticmethod
     def _ensure_group(world_size: int, rank: int):
@@ -120,6 +207,10 @@ class Trainer:
     def train_packed(self, packed: torch.Tensor):
         """One optimizer step on a HOST batch in packed slot layout (what the native loader produces): a single
         pinned async H2D copy on the copy stream, graph replay, async D2H of the loss scalars."""
+        if self._drv is not None and not self.nvtx:
+            t = self._native_step(packed)
+            if t is not None:
+                return t
         return self._train_host(lambda slot: self.model.load_packed(packed, slot, non_blocking=True))
 
     def train_raw(self, raw: torch.Tensor, rows: int):
@@ -175,18 +266,27 @@ class Trainer:
         slot = self._k % self._nslots
         self._k += 1
         cs = self._copy_stream
+        if self._publish and self._ring_pos == self._ring_n:
+            self.drain(keep=True)  # before issuing: the new step's record would land on the oldest unread one
         if self._slot_free[slot] is not None:
             cs.wait_event(self._slot_free[slot])  # the step that last read this slot has finished
+        elif self.native_steps:
+            cs.wait_stream(main)  # the slot's last reader was issued by the native driver (its events live there)
         with torch.cuda.stream(cs):
             load_fn(slot)
             ev = torch.cuda.Event()
             ev.record(cs)
         main.wait_event(ev)
+        issued = getattr(self.model, "host_step", 0)
         self.model.train_step_slot(slot)
         done = torch.cuda.Event()
         done.record(main)
         self._slot_free[slot] = done
-        self._push_loss(self.model.scalars, already_mean=False)
+        if self._publish:
+            self._pending.append(issued)
+            self._ring_pos += 1
+        else:
+            self._push_loss(self.model.scalars, already_mean=False)
         return ev  # completes when the host buffer has been copied out (the caller may then reuse it)
 
     def _push_loss(self, scalars: torch.Tensor, already_mean: bool):
@@ -204,8 +304,15 @@ class Trainer:
             reg_now = None
             if getattr(self.model, "arena", None) is not None and not getattr(self.model, "_nccl", False):
                 reg_now = float(self.model.arena.view("reg_parts").sum())  # L2 terms, gathered by the fused kernel
+            # published results sit at ring[(t - 1) % n] for optimizer step t = step index at issue + 1 + (device step
+            # counter - host step count), the last term being the global_step restored from a checkpoint
+            shift = (self.model.global_step - self.model.host_step) if (self._publish and self._pending) else 0
             for i, mean_flag in enumerate(self._pending):
-                a, b = float(self._ring[i, 0]), float(self._ring[i, 1])
+                if self._publish:
+                    pos = (mean_flag + shift) % self._ring_n
+                    a, b, mean_flag = float(self._ring[pos, 0]), float(self._ring[pos, 1]), 0
+                else:
+                    a, b = float(self._ring[i, 0]), float(self._ring[i, 1])
                 if reg_now is not None:
                     b = reg_now
                 # fused: (local sum of log-loss, L2 term). Under DP the local sum is scaled to the local batch (an

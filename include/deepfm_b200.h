@@ -67,6 +67,14 @@ int dfm_flat_opt_step(float* w, float* g, float* s0, float* s1, long long n, int
                       float eps, float momentum, float grad_scale, long long decay_begin, long long decay_end, float l2,
                       long long shadow_begin, long long shadow_end, void* shadow_bf16, unsigned long long* step_ptr,
                       float* reg_loss, unsigned int* done_counter, void* stream);
+/* Same sweep; additionally the last CTA stores `pub_n` floats read from `pub_src` (device) into record (step - 1) %
+ * pub_ring_len of `pub_ring`, a device-visible alias of page-locked HOST memory: the step's result (loss sum, L2 term)
+ * reaches the host with no D2H copy operation in the stream. pub_ring == NULL disables it. */
+int dfm_flat_opt_step_pub(float* w, float* g, float* s0, float* s1, long long n, int opt, float lr, float beta1,
+                          float beta2, float eps, float momentum, float grad_scale, long long decay_begin,
+                          long long decay_end, float l2, long long shadow_begin, long long shadow_end, void* shadow,
+                          unsigned long long* step_ptr, float* reg_loss, unsigned int* done_counter,
+                          const float* pub_src, int pub_n, float* pub_ring, int pub_ring_len, void* stream);
 int dfm_cast_f32_bf16(const float* in, void* out_bf16, long long n, void* stream);
 
 /* ---- gradient all-reduce fused with the optimizer step over NVLink peer memory (replaces Horovod's NCCL all-reduce
@@ -134,6 +142,19 @@ int dfm_host_register(void* ptr, unsigned long long bytes, void** dev_ptr); /* p
 /* zero-copy parameter-server pull: out[i,:] = table[ids[i],:], table = device alias of the host store (X3 / row 11) */
 int dfm_ps_gather(const float* table_dev, const long long* ids, int n, int K, float* out, void* stream);
 int dfm_host_unregister(void* ptr);
+
+/* ---- host-side step driver (csrc/step_driver.cu): one call issues a whole host-fed step - pinned H2D copy into input slot
+ * `slot` on copy_stream (after the slot's previous reader), compute_stream waits for it, cudaGraphLaunch of the step's
+ * graph, D2H of the result scalars. Asynchronous; host_src must be page-locked. copy_done: 1 = the last copy into the slot
+ * has completed (source buffer reusable), 0 = in flight. */
+int dfm_driver_create(void** handle, int nslots);
+int dfm_driver_destroy(void* handle);
+int dfm_driver_step(void* handle, int slot, const void* host_src, void* dev_dst, unsigned long long bytes,
+                    void* graph_exec, void* copy_stream, void* compute_stream, const void* dev_scalars,
+                    void* host_scalars, unsigned long long scalar_bytes);
+int dfm_driver_copy_done(void* handle, int slot);
+int dfm_driver_copy_wait(void* handle, int slot);
+unsigned long long dfm_driver_steps(void* handle);
 
 /* ---- flat optimizer step that allocates nothing (no counterpart in the reference: TF owns its own allocator).
  * Same update as dfm_flat_opt_step, but the scratch it needs sits in a static device array inside the library

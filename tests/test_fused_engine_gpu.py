@@ -153,3 +153,45 @@ def test_fused_training_reduces_loss(cuda_lib):
     last = float(m.last_loss().item())
     assert 0.55 < first < 0.85, first   # ~ln 2 at init (reference log: loss = 0.69646865 at step 1, PDF p34)
     assert last < first - 0.05, (first, last)
+
+
+def test_native_step_driver_matches_python_step_path(cuda_lib, monkeypatch):
+    """Trainer.train_packed through the C++ step driver (one call: H2D + graph launch + D2H) == the Python-issued path."""
+    from deepfm_b200.data.synthetic import SyntheticCTR
+    from deepfm_b200.models import DeepFMConfig
+    from deepfm_b200.models.fused import pack_batch
+    from deepfm_b200.optim import TF1Optimizer
+    from deepfm_b200.runtime.trainer import Trainer
+    cfg = DeepFMConfig(field_size=39, feature_size=5000, embedding_size=16, deep_layers=[64, 32], dropout=[0.8, 1.0],
+                       l2_reg=1e-4)
+    B, steps = 256, 40
+    data = SyntheticCTR(cfg.field_size, cfg.feature_size, seed=0)
+    batches = [pack_batch(*data.batch(B, i), pin=True) for i in range(steps)]
+
+    def run(native: bool, publish: bool = True):
+        monkeypatch.setenv("DFM_NATIVE_STEP", "1" if native else "0")
+        monkeypatch.setenv("DFM_PUBLISH", "1" if publish else "0")
+        tr = Trainer(cfg, B, TF1Optimizer("Momentum", 1e-2), seed=3, backend="fused")
+        assert tr._publish == publish
+        tickets = [tr.train_packed(b) for b in batches]
+        for t in tickets[-2:]:
+            t.synchronize()
+            assert t.query()
+        losses = tr.drain()
+        params = {k: v.clone() for k, v in tr.model.named_parameters().items()}
+        n_native, gs = tr.native_steps, tr.global_step
+        tr.close()
+        return losses, params, n_native, gs
+
+    l_py, p_py, n_py, gs_py = run(False, publish=False)  # Python-issued step, D2H copy of the scalars every step
+    l_nat, p_nat, n_nat, gs_nat = run(True)              # C++ step driver, results published by the optimizer kernel
+    l_mix, _, _, _ = run(False, publish=True)
+    assert len(l_mix) == steps and all(abs(a - b) < 1e-3 * max(1.0, abs(a)) for a, b in zip(l_py, l_mix))
+    assert n_py == 0 and n_nat >= steps - 4, (n_py, n_nat)  # every step after the per-slot graph captures is native
+    assert gs_py == gs_nat == steps and len(l_py) == len(l_nat) == steps
+    assert l_nat[0] > l_nat[-1]
+    for a, b in zip(l_py, l_nat):
+        assert abs(a - b) < 1e-3 * max(1.0, abs(a)), (a, b)
+    for k in p_py:  # same kernels, same inputs: only atomic summation order differs
+        scale = float(p_py[k].abs().max()) + 1e-8
+        assert float((p_py[k] - p_nat[k]).abs().max()) / scale < 2e-2, k
