@@ -1,0 +1,72 @@
+/* C ABI of the host IO library (data/_lib/libdeepfm_io.so, sources in csrc/io/): TFRecord framing with hardware CRC32C,
+ * fixed-schema tf.train.Example batch parser, prefetching loader (streaming / indexed / raw / FIFO), TensorFlow
+ * tensor-bundle (checkpoint) writer and reader. Host code only, no CUDA dependency. The reference gets all of this from
+ * TensorFlow's C++ runtime; there is no counterpart source in the reference tree.
+ *
+ * Conventions: functions returning pointers return NULL on failure, functions returning int return 0 on success (or a
+ * count where stated) and a negative value on failure; dfmio_last_error() / dfmio_bundle_last_error() hold the message.
+ */
+#ifndef DEEPFM_IO_H_
+#define DEEPFM_IO_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* dfmio_last_error(void);
+
+/* ---- CRC32C (Castagnoli), TFRecord masking: ((crc >> 15) | (crc << 17)) + 0xa282ead8 */
+uint32_t dfmio_crc32c(const uint8_t* p, size_t n);
+uint32_t dfmio_masked_crc32c(const uint8_t* p, size_t n);
+
+/* ---- TFRecord writer / reader: u64 length | u32 masked crc(length) | payload | u32 masked crc(payload) */
+void* dfmio_writer_open(const char* path);
+int dfmio_writer_write(void* writer, const uint8_t* data, uint64_t n);
+int dfmio_writer_close(void* writer);
+void* dfmio_reader_open(const char* path); /* regular file (memory-mapped) or FIFO (buffered reads, never probed) */
+/* next record into buf: returns its length, -1 at end of stream, -2 on corruption / IO error, -3 if cap is too small */
+long dfmio_reader_next(void* reader, uint8_t* buf, size_t cap, int check_crc);
+void dfmio_reader_close(void* reader);
+long dfmio_count_records(const char* path); /* walks the length fields only */
+
+/* ---- fixed-schema Example parser: label float x1, ids int64 xF (stored as int32), values float xF */
+int dfmio_parse_batch(const uint8_t* bytes, const uint64_t* off, const uint64_t* len, int nrec, int F, float* labels,
+                      int32_t* ids, float* vals);
+
+/* ---- prefetching loader. The caller owns `slots` (nslots x slot_stride bytes, ideally page-locked); a parsed slot is
+ * laid out labels[batch] f32 | ids[batch*F] i32 | vals[batch*F] f32 (256-byte aligned sections) so that ONE copy moves a
+ * batch to the GPU; a raw slot is offsets[batch+1] i32 | serialized records (for the GPU-side parser).
+ * Records are sharded as record_index % shard_n == shard_i; `epochs` <= 0 repeats forever. */
+uint64_t dfmio_loader_slot_bytes(int batch, int F);
+uint64_t dfmio_loader_raw_slot_bytes(int batch, int max_record_bytes);
+void* dfmio_loader_create(const char** paths, int npaths, int F, int batch, int shard_n, int shard_i, int epochs,
+                          int threads, int drop_remainder, int check_crc, uint8_t* slots, int nslots,
+                          uint64_t slot_stride);
+void* dfmio_loader_create_raw(const char** paths, int npaths, int batch, int shard_n, int shard_i, int epochs,
+                              int drop_remainder, int check_crc, uint8_t* slots, int nslots, uint64_t slot_stride);
+int dfmio_loader_next(void* loader, int* slot); /* rows in the slot (> 0), 0 at end of data, < 0 on error; blocks */
+void dfmio_loader_release(void* loader, int slot);
+long dfmio_loader_records(void* loader);
+void dfmio_loader_destroy(void* loader);
+
+/* ---- TensorFlow tensor bundle (checkpoint V2): <prefix>.index (SSTable) + <prefix>.data-00000-of-00001.
+ * dtype is TensorFlow's DataType enum (1 float32, 3 int32, 9 int64); dims holds up to 8 entries. */
+const char* dfmio_bundle_last_error(void);
+void* dfmio_bundle_writer_create(const char* prefix);
+int dfmio_bundle_writer_add(void* writer, const char* name, int dtype, int ndim, const int64_t* dims, const void* bytes,
+                            uint64_t nbytes);
+int dfmio_bundle_writer_finish(void* writer); /* sorts the keys, writes both files, frees the writer */
+void* dfmio_bundle_reader_open(const char* prefix);
+int dfmio_bundle_reader_count(void* reader);
+int dfmio_bundle_reader_entry(void* reader, int i, char* name, int cap, int* dtype, int* ndim, int64_t* dims,
+                              uint64_t* nbytes);
+int dfmio_bundle_reader_read(void* reader, int i, void* dst, uint64_t cap, int verify_crc);
+void dfmio_bundle_reader_close(void* reader);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DEEPFM_IO_H_ */

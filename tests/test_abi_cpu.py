@@ -1,0 +1,53 @@
+"""The C ABI is what other code links against: the header and the built libraries must agree."""
+import os
+import re
+import subprocess
+
+import pytest
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(REPO, "deepfm-tensorflow-distributed-training-on-sagemaker_b200")
+HEADER = os.path.join(REPO, "include", "deepfm_b200.h")
+IO_HEADER = os.path.join(REPO, "include", "deepfm_io.h")
+
+
+def _exported(lib, prefix):
+    out = subprocess.run(["nm", "-D", "--defined-only", lib], capture_output=True, text=True, check=True).stdout
+    return {ln.split()[-1] for ln in out.splitlines() if ln.split() and ln.split()[-1].startswith(prefix)
+            and ln.split()[-2] in ("T", "t")}
+
+
+def _declared(header=HEADER):
+    src = open(header).read()
+    src = re.sub(r"/\*.*?\*/", " ", src, flags=re.S)
+    src = re.sub(r"//[^\n]*", " ", src)
+    return set(re.findall(r"\b(dfm_[a-z0-9_]+)\s*\(", src)), set(re.findall(r"\b(dfmio_[a-z0-9_]+)\s*\(", src))
+
+
+def test_every_exported_cuda_entry_point_is_declared_in_the_header():
+    lib = os.path.join(PKG, "ops", "_lib", "libdeepfm_b200.so")
+    if not os.path.exists(lib):
+        pytest.skip("CUDA library not built")
+    declared, _ = _declared()
+    exported = _exported(lib, "dfm_")
+    internal = {"dfm_set_error", "dfm_l2_window"}  # shared between translation units, not part of the public surface
+    assert exported - internal <= declared, sorted(exported - internal - declared)
+    assert declared <= exported, sorted(declared - exported)
+
+
+def test_every_exported_io_entry_point_is_declared_in_the_io_header():
+    lib = os.path.join(PKG, "data", "_lib", "libdeepfm_io.so")
+    if not os.path.exists(lib):
+        pytest.skip("IO library not built")
+    _, declared = _declared(IO_HEADER)
+    exported = _exported(lib, "dfmio_")
+    assert exported == declared, (sorted(exported - declared), sorted(declared - exported))
+
+
+def test_header_is_valid_c_and_cxx(tmp_path):
+    for comp, ext in (("gcc", "c"), ("g++", "cc")):
+        src = tmp_path / ("t." + ext)
+        src.write_text('#include "deepfm_b200.h"\n#include "deepfm_io.h"\nint main(void) { return 0; }\n')
+        r = subprocess.run([comp, "-fsyntax-only", "-Wall", "-Werror", "-I", os.path.join(REPO, "include"), str(src)],
+                           capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
