@@ -77,8 +77,11 @@ def latest_checkpoint(model_dir: str) -> Optional[str]:
                 p = p if os.path.isabs(p) else os.path.join(model_dir, p)
                 if os.path.exists(p + ".index"):
                     return p
-    steps = all_checkpoints(model_dir)
-    return os.path.join(model_dir, "model.ckpt-%d" % steps[-1]) if steps else None
+    for step in reversed(all_checkpoints(model_dir)):  # no usable state file: newest checkpoint with both files present
+        p = os.path.join(model_dir, "model.ckpt-%d" % step)
+        if os.path.exists(p + ".data-00000-of-00001"):
+            return p
+    return None
 
 
 def save_checkpoint(model_dir: str, state_dict: Dict[str, torch.Tensor], opt, keep: int = 5) -> str:
@@ -90,7 +93,11 @@ def save_checkpoint(model_dir: str, state_dict: Dict[str, torch.Tensor], opt, ke
         tf_sd = native_to_tf(state_dict, opt.name, opt.scalar_state())
     finally:
         opt.step = saved_step
-    write_bundle(prefix, tf_sd)
+    # atomic publication, like TF's Saver: a crash while writing never leaves a half-written "latest" checkpoint
+    tmp = prefix + ".tmp-%d" % os.getpid()
+    write_bundle(tmp, tf_sd)
+    for ext in (".data-00000-of-00001", ".index"):  # the index last: its presence marks the checkpoint complete
+        os.replace(tmp + ext, prefix + ext)
     steps = all_checkpoints(model_dir)
     for old in steps[:-keep] if keep > 0 else []:
         for ext in (".index", ".data-00000-of-00001"):
@@ -99,10 +106,12 @@ def save_checkpoint(model_dir: str, state_dict: Dict[str, torch.Tensor], opt, ke
             except OSError:
                 pass
     steps = all_checkpoints(model_dir)
-    with open(os.path.join(model_dir, "checkpoint"), "w") as f:
+    state = os.path.join(model_dir, "checkpoint")
+    with open(state + ".tmp", "w") as f:
         f.write('model_checkpoint_path: "model.ckpt-%d"\n' % step)
         for s in steps:
             f.write('all_model_checkpoint_paths: "model.ckpt-%d"\n' % s)
+    os.replace(state + ".tmp", state)
     return prefix
 
 

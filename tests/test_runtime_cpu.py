@@ -1,0 +1,90 @@
+"""Runtime plumbing that the reference gets from tf.estimator: hooks, checkpoint rotation, atomic
+checkpoint publication, fault-injection spec parsing."""
+import io
+import json
+import os
+
+import pytest
+import torch
+
+
+def _state(step):
+    return {"fm_bias": torch.tensor([0.5]), "fm_w": torch.arange(4.0), "global_step": torch.tensor(step)}
+
+
+def test_checkpoint_rotation_state_file_and_atomic_publication(tmp_path):
+    from deepfm_b200.optim import TF1Optimizer
+    from deepfm_b200.utils.checkpoint import all_checkpoints, latest_checkpoint, save_checkpoint
+    d = str(tmp_path / "ck")
+    opt = TF1Optimizer("GD", 0.1)
+    for step in (10, 20, 30, 40):
+        save_checkpoint(d, _state(step), opt, keep=2)
+    assert all_checkpoints(d) == [30, 40]                               # keep_checkpoint_max
+    assert latest_checkpoint(d).endswith("model.ckpt-40")
+    state = open(os.path.join(d, "checkpoint")).read()
+    assert 'model_checkpoint_path: "model.ckpt-40"' in state and state.count("all_model_checkpoint_paths") == 2
+    assert not [f for f in os.listdir(d) if ".tmp" in f]                # nothing half-written left behind
+    # a crash that left only an index (no data file) and no state file must not be picked up as "latest"
+    os.remove(os.path.join(d, "checkpoint"))
+    open(os.path.join(d, "model.ckpt-50.index"), "wb").write(b"partial")
+    assert latest_checkpoint(d).endswith("model.ckpt-40")
+    # a state file that points at a vanished checkpoint falls back to the newest complete one
+    open(os.path.join(d, "checkpoint"), "w").write('model_checkpoint_path: "model.ckpt-99"\n')
+    assert latest_checkpoint(d).endswith("model.ckpt-40")
+    assert latest_checkpoint(str(tmp_path / "nothing")) is None
+
+
+def test_logging_hook_honours_log_steps_and_writes_jsonl(tmp_path):
+    from deepfm_b200.runtime.hooks import LoggingHook
+    out, mf = io.StringIO(), str(tmp_path / "m" / "metrics.jsonl")
+    calls = []
+    hook = LoggingHook(every_steps=5, global_batch=64, metrics_file=mf, out=out)
+    hook.begin(0)
+    for step in range(1, 13):
+        hook.after_step(step, lambda: calls.append(1) or 0.25)
+    assert len(calls) == 2                                              # the loss is read (device sync) only when due
+    lines = [json.loads(x) for x in open(mf)]
+    assert [x["step"] for x in lines] == [5, 10] and all(x["loss"] == 0.25 for x in lines)
+    assert all(abs(x["examples_per_sec"] - 64 * x["steps_per_sec"]) < 1e-6 * x["examples_per_sec"] for x in lines)
+    assert "loss = 0.25, step = 5" in out.getvalue() and "global_step/sec" in out.getvalue()
+    hook.log_eval({"auc": 0.7, "loss": 0.4, "global_step": 10})
+    assert json.loads(open(mf).read().splitlines()[-1])["eval"] is True
+    silent = LoggingHook(1, 64, None, out=io.StringIO(), enabled=False)    # non-chief ranks log nothing
+    silent.after_step(1, lambda: pytest.fail("must not read the loss"))
+
+
+def test_checkpoint_saver_hook_periods(tmp_path):
+    from deepfm_b200.optim import TF1Optimizer
+    from deepfm_b200.runtime.hooks import CheckpointSaverHook
+
+    class FakeTrainer:
+        opt = TF1Optimizer("GD", 0.1)
+        step = 0
+
+        def state_dict(self):
+            return _state(self.step)
+
+    tr, d = FakeTrainer(), str(tmp_path / "ck")
+    by_steps = CheckpointSaverHook(d, save_secs=600, save_steps=3, keep=5)
+    saved = []
+    for step in range(1, 10):
+        tr.step = step
+        if by_steps.due(step):
+            saved.append(os.path.basename(by_steps.save(tr, out=io.StringIO())))
+    assert saved == ["model.ckpt-3", "model.ckpt-6", "model.ckpt-9"]
+    assert by_steps.save(tr, out=io.StringIO()) is None                 # same step twice: no duplicate write
+    by_secs = CheckpointSaverHook(d, save_secs=600, save_steps=0)
+    assert not by_secs.due(1)
+    by_secs._last_t -= 601
+    assert by_secs.due(1)
+    assert not CheckpointSaverHook(d, enabled=False).due(3) and not CheckpointSaverHook("", save_steps=1).due(1)
+
+
+def test_fault_injection_spec():
+    from deepfm_b200.runtime.estimator import _parse_fault
+    assert _parse_fault("", 0) is None
+    assert _parse_fault("1:25", 0) is None and _parse_fault("1:25", 1) == (25, "")
+    assert _parse_fault("0:7:/tmp/some:marker", 0) == (7, "/tmp/some:marker")
+    assert _parse_fault("0:7:" + __file__, 0) is None                   # marker exists: the fault already fired
+    with pytest.raises(SystemExit):
+        _parse_fault("zero:seven", 0)
