@@ -104,8 +104,10 @@ class Trainer:
         # native step driver (csrc/step_driver.cu): one C call per host-fed step once the slot's graph exists
         self._drv = None
         self.native_steps = 0
-        if self._cuda and backend == "fused" and _os.environ.get("DFM_NATIVE_STEP", "1") != "0" \
-                and getattr(self.model, "use_graph", False):
+        # default: on for single-GPU trainers (validated on a B200 this round); multi-rank trainers keep the Python-issued
+        # sequence unless DFM_NATIVE_STEP=1 asks for it (same code path, not yet re-measured at 2-8 ranks)
+        want = _os.environ.get("DFM_NATIVE_STEP", "1" if world_size == 1 else "0")
+        if self._cuda and backend == "fused" and want != "0" and getattr(self.model, "use_graph", False):
             import ctypes
             from ..ops import lib as _nlib
             lib = _nlib.load()
