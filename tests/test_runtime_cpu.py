@@ -88,3 +88,25 @@ def test_fault_injection_spec():
     assert _parse_fault("0:7:" + __file__, 0) is None                   # marker exists: the fault already fired
     with pytest.raises(SystemExit):
         _parse_fault("zero:seven", 0)
+
+
+def test_inspect_checkpoint_lists_tf_names_for_model_dir_and_servable(tmp_path):
+    from deepfm_b200.models import DeepFMConfig, init_params
+    from deepfm_b200.optim import TF1Optimizer
+    from deepfm_b200.serving.export import export_servable
+    from deepfm_b200.utils.checkpoint import save_checkpoint
+    from deepfm_b200.utils.inspect_checkpoint import main
+    cfg = DeepFMConfig(field_size=4, feature_size=50, embedding_size=4, deep_layers=[8], dropout=[1.0])
+    params = init_params(cfg, seed=1)
+    sd = dict(params, global_step=torch.tensor(12))
+    save_checkpoint(str(tmp_path / "ck"), sd, TF1Optimizer("GD", 0.1))
+    out = io.StringIO()
+    assert main([str(tmp_path / "ck"), "--stats"], out=out) == 0
+    text = out.getvalue()
+    for name in ("fm_bias", "fm_w", "fm_v", "Deep-part/mlp0/weights", "Deep-part/deep_out/biases", "global_step"):
+        assert name in text
+    assert "model.ckpt-12" in text and "= 12" in text and "l2" in text
+    export_servable(str(tmp_path / "model"), cfg, params, global_step=12)
+    out = io.StringIO()
+    assert main([str(tmp_path / "model"), "--tensor", "fm_w"], out=out) == 0 and "(50,)" in out.getvalue()
+    assert main([str(tmp_path / "nothing")], out=io.StringIO()) == 1
