@@ -20,7 +20,9 @@
 
 #include <atomic>
 #include <condition_variable>
+#include <algorithm>
 #include <deque>
+#include <functional>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -352,7 +354,7 @@ struct MappedFile {
     void* p = mmap(nullptr, (size_t)st.st_size, PROT_READ, MAP_PRIVATE | MAP_POPULATE, fd, 0);
     ::close(fd);
     if (p == MAP_FAILED) return nullptr;
-    madvise(p, (size_t)st.st_size, MADV_SEQUENTIAL | MADV_WILLNEED);
+    madvise(p, (size_t)st.st_size, MADV_WILLNEED);  // (advice values are not flags: one call per advice)
     auto m = std::make_shared<MappedFile>();
     m->base = (const uint8_t*)p;
     m->size = (size_t)st.st_size;
@@ -389,7 +391,9 @@ class Loader {
       per_epoch_batches_ = full + ((!drop_ && index_.size() % (size_t)B_) ? 1 : 0);
       total_batches_ = per_epoch_batches_ * epochs_;
       reader_finished_ = true;
-      for (int i = 0; i < (threads < 1 ? 1 : threads); ++i) parsers_.emplace_back([this] { indexed_worker(); });
+      // raw mode only copies bytes (one worker moves ~3.5 GB/s): two workers by default, `threads` if given
+      const int workers = threads >= 1 ? threads : (raw_mode_ ? 2 : 1);
+      for (int i = 0; i < workers; ++i) parsers_.emplace_back([this] { indexed_worker(); });
       return;
     }
     if (raw_mode_) {
@@ -585,28 +589,60 @@ class Loader {
     const uint8_t* ptr;
     uint32_t len;
   };
+  // Files are scanned in parallel (one task per file: map + populate + walk the length fields); the walk keeps only the
+  // record lengths (4 bytes each), from which the second, arithmetic-only pass places every record of THIS shard at its
+  // final position - global record numbers, and hence shard membership, are known once the per-file counts are.
   bool build_index() {
-    std::vector<std::shared_ptr<MappedFile>> maps;
-    for (const auto& path : paths_) {
-      std::shared_ptr<MappedFile> mf = MappedFile::open_path(path.c_str());
-      if (!mf) return false;  // FIFO / pipe / empty file: use the streaming reader
-      maps.push_back(mf);
-    }
-    long rec_idx = 0;
-    for (size_t fi = 0; fi < maps.size(); ++fi) {
-      const MappedFile& mf = *maps[fi];
+    const int nf = (int)paths_.size();
+    std::vector<std::shared_ptr<MappedFile>> maps((size_t)nf);
+    std::vector<std::vector<uint32_t>> lens((size_t)nf);
+    std::atomic<bool> ok{true};
+    auto scan = [&](int fi) {
+      std::shared_ptr<MappedFile> mf = MappedFile::open_path(paths_[(size_t)fi].c_str());
+      if (!mf) { ok.store(false); return; }  // FIFO / pipe / empty file: use the streaming reader
+      maps[(size_t)fi] = mf;
+      std::vector<uint32_t>& out = lens[(size_t)fi];
+      out.reserve(mf->size / 256 + 16);
       size_t pos = 0;
-      while (pos < mf.size) {
-        if (pos + 12 > mf.size) return false;  // let the streaming path report the corruption with context
+      while (pos < mf->size) {
+        if (pos + 12 > mf->size) { ok.store(false); return; }  // the streaming path reports corruption with context
         uint64_t n;
-        memcpy(&n, mf.base + pos, 8);
-        if (n > (1ull << 31) || pos + 16 + n > mf.size) return false;
-        if ((rec_idx % shard_n_) == shard_i_) index_.push_back(RecRef{mf.base + pos + 12, (uint32_t)n});
-        ++rec_idx;
+        memcpy(&n, mf->base + pos, 8);
+        if (n > (1ull << 31) || pos + 16 + n > mf->size) { ok.store(false); return; }
+        out.push_back((uint32_t)n);
         pos += 16 + n;
       }
-    }
-    for (size_t fi = 0; fi < maps.size(); ++fi) maps_[paths_[fi]] = maps[fi];
+    };
+    unsigned hw = std::thread::hardware_concurrency();
+    const int T = std::max(1, std::min({nf, (int)(hw ? hw : 4), 16}));
+    auto run_parallel = [&](const std::function<void(int)>& fn) {
+      if (T == 1) {
+        for (int fi = 0; fi < nf; ++fi) fn(fi);
+        return;
+      }
+      std::vector<std::thread> th;
+      for (int t = 0; t < T; ++t)
+        th.emplace_back([&, t] { for (int fi = t; fi < nf && ok.load(); fi += T) fn(fi); });
+      for (auto& x : th) x.join();
+    };
+    run_parallel(scan);
+    if (!ok.load()) return false;
+    const long n = shard_n_, sidx = shard_i_;
+    auto sel_before = [&](long b) { return b > sidx ? (b - sidx + n - 1) / n : 0L; };  // #{i < b : i % n == sidx}
+    std::vector<long> base((size_t)nf + 1, 0);
+    for (int fi = 0; fi < nf; ++fi) base[(size_t)fi + 1] = base[(size_t)fi] + (long)lens[(size_t)fi].size();
+    index_.resize((size_t)sel_before(base[(size_t)nf]));
+    run_parallel([&](int fi) {
+      const uint8_t* p = maps[(size_t)fi]->base;
+      long idx = base[(size_t)fi];
+      size_t out = (size_t)sel_before(idx), pos = 0;
+      for (uint32_t len : lens[(size_t)fi]) {
+        if (idx % n == sidx) index_[out++] = RecRef{p + pos + 12, len};
+        ++idx;
+        pos += 16 + (size_t)len;
+      }
+    });
+    for (int fi = 0; fi < nf; ++fi) maps_[paths_[(size_t)fi]] = maps[(size_t)fi];
     return true;
   }
   bool check_record_crc(const RecRef& r) const {
