@@ -64,8 +64,51 @@ def load(build_if_missing: bool = True) -> ctypes.CDLL:
     lib.dfmio_loader_records.restype = c_long
     lib.dfmio_loader_records.argtypes = [c_void_p]
     lib.dfmio_loader_destroy.argtypes = [c_void_p]
+    c_ll, c_f = ctypes.c_longlong, ctypes.c_float
+    lib.dfmio_sparse_opt_apply.argtypes = [c_void_p, c_void_p, c_void_p, c_ll, c_int, c_void_p, c_ll, c_void_p, c_int,
+                                           c_f, c_f, c_f, c_f, c_f, c_f, c_ll, c_int]
+    lib.dfmio_dense_opt_apply.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_int, c_f, c_f, c_f, c_f, c_f,
+                                          c_f, c_ll, c_int]
     _lib = lib
     return lib
+
+
+def _slot_ptrs(slots):
+    p = [s.data_ptr() if s is not None else None for s in slots] + [None, None]
+    return p[0], p[1]
+
+
+def sparse_opt_apply(table, slots, rows, grads, opt, l2: float, step: int, threads: int = 4) -> None:
+    """In-place TF-1 optimizer update of the rows `rows` (unique int64 [n]) of a HOST table [N, K] (or [N]) with dense
+    per-row gradients `grads` [n, K]; `g + l2 * w` is formed per element inside the same pass (csrc/io/host_optim.cc)."""
+    from ..optim.tf1 import OPT_IDS
+    import torch
+    assert table.device.type == "cpu" and table.is_contiguous() and table.dtype == torch.float32
+    N = table.shape[0]
+    K = table.numel() // max(N, 1)
+    rows = rows.to(torch.int64).contiguous()
+    grads = grads.to(torch.float32).contiguous()
+    assert grads.numel() == rows.numel() * K and all(s.is_contiguous() and s.shape == table.shape for s in slots)
+    s0, s1 = _slot_ptrs(slots)
+    rc = load().dfmio_sparse_opt_apply(table.data_ptr(), s0, s1, N, K, rows.data_ptr(), rows.numel(), grads.data_ptr(),
+                                       OPT_IDS[opt.name], opt.lr, opt.beta1, opt.beta2, opt.eps, opt.momentum, float(l2),
+                                       int(step), int(threads))
+    if rc != 0:
+        raise NativeIOError("sparse_opt_apply: bad arguments (row index out of range or missing slot table)")
+
+
+def dense_opt_apply(w, slots, g, opt, l2: float, step: int, threads: int = 4) -> None:
+    """In-place TF-1 optimizer update of a whole HOST variable."""
+    from ..optim.tf1 import OPT_IDS
+    import torch
+    assert w.device.type == "cpu" and w.is_contiguous() and w.dtype == torch.float32
+    g = g.to(torch.float32).contiguous()
+    assert g.numel() == w.numel() and all(s.is_contiguous() and s.numel() == w.numel() for s in slots)
+    s0, s1 = _slot_ptrs(slots)
+    rc = load().dfmio_dense_opt_apply(w.data_ptr(), s0, s1, g.data_ptr(), w.numel(), OPT_IDS[opt.name], opt.lr, opt.beta1,
+                                      opt.beta2, opt.eps, opt.momentum, float(l2), int(step), int(threads))
+    if rc != 0:
+        raise NativeIOError("dense_opt_apply: bad arguments")
 
 
 def available() -> bool:

@@ -143,6 +143,15 @@ class AsyncPSTrainer:
             self.store = SharedParamStore(cfg, optimizer, path, False, seed, pin=self.cuda)
         self.names = [n for n, _, _ in native_names(cfg)]
         self.dense_names = [n for n in self.names if n not in ("fm_w", "fm_v")]
+        # pushes are applied by the C++ host optimizer unless DFM_PS_NATIVE_APPLY=0 (then: the torch-op reference path)
+        self._native_apply = os.environ.get("DFM_PS_NATIVE_APPLY", "1") != "0"
+        self._apply_threads = max(1, min(8, (os.cpu_count() or 4) // max(1, self.world)))
+        if self._native_apply:
+            try:
+                from ..data import native as _nio
+                _nio.load()
+            except Exception:
+                self._native_apply = False
         self._q: "queue.Queue" = queue.Queue()
         self._applier = threading.Thread(target=self._apply_loop, daemon=True)
         self._applier.start()
@@ -258,6 +267,15 @@ class AsyncPSTrainer:
         st, o, l2 = self.store, self.opt, self.cfg.l2_reg
         t = st.bump_step()
         rows = push["rows"]
+        if self._native_apply:  # one fused pass per row / per variable in C++ (csrc/io/host_optim.cc)
+            from ..data import native as _nio
+            for name in ("fm_w", "fm_v"):
+                _nio.sparse_opt_apply(st.view(name), st.slots(name), rows, push[name], o, l2, t, self._apply_threads)
+            for name, g in push["dense"].items():
+                _nio.dense_opt_apply(st.view(name), st.slots(name), g, o, 0.0, t, self._apply_threads)
+            for name, v in push.get("bn", {}).items():
+                st.view(name).copy_(v)
+            return
         for name in ("fm_w", "fm_v"):
             tab, slots = st.view(name), st.slots(name)
             w = tab[rows]

@@ -52,6 +52,15 @@ void dfmio_loader_release(void* loader, int slot);
 long dfmio_loader_records(void* loader);
 void dfmio_loader_destroy(void* loader);
 
+/* ---- host-side optimizer application for the asynchronous parameter-server store (csrc/io/host_optim.cc): TF-1 rules
+ * (opt: 0 Adam, 1 Adagrad, 2 Momentum, 3 FTRL, 4 SGD), `g + l2 * w` formed in the same pass, `step` = 1-based update index,
+ * work split over `threads` threads, no locking (Hogwild). s0 / s1 = slot tables (NULL where the rule has fewer slots). */
+int dfmio_sparse_opt_apply(float* table, float* s0, float* s1, long long N, int K, const long long* rows, long long nrows,
+                           const float* grads, int opt, float lr, float beta1, float beta2, float eps, float momentum,
+                           float l2, long long step, int threads);
+int dfmio_dense_opt_apply(float* w, float* s0, float* s1, const float* g, long long n, int opt, float lr, float beta1,
+                          float beta2, float eps, float momentum, float l2, long long step, int threads);
+
 /* ---- TensorFlow tensor bundle (checkpoint V2): <prefix>.index (SSTable) + <prefix>.data-00000-of-00001.
  * dtype is TensorFlow's DataType enum (1 float32, 3 int32, 9 int64); dims holds up to 8 entries. */
 const char* dfmio_bundle_last_error(void);

@@ -70,3 +70,45 @@ def test_two_worker_ps_over_gloo(tmp_path):
     m = [json.loads(l) for l in open(tmp_path / "ck" / "metrics.jsonl")]
     evs = [x for x in m if x.get("eval")]
     assert len(evs) == 3 and evs[-1]["auc"] > 0.55 and evs[-1]["loss"] < evs[0]["loss"] + 0.02
+
+
+@pytest.mark.parametrize("opt_name", ["Adam", "Adagrad", "Momentum", "ftrl", "GD"])
+def test_native_host_optimizer_matches_tf1_reference_rules(opt_name):
+    """csrc/io/host_optim.cc (what the PS applier runs) == optim/tf1.py on touched rows and on dense variables."""
+    from deepfm_b200.data import native
+    from deepfm_b200.optim import SLOT_INIT, TF1Optimizer
+    g = torch.Generator().manual_seed(3)
+    N, K, n = 500, 16, 137
+    opt = TF1Optimizer(opt_name, 1e-2)
+    table = torch.randn(N, K, generator=g)
+    slots = [torch.full((N, K), v) + 0.01 * torch.rand(N, K, generator=g) for v in SLOT_INIT[opt.name]]
+    ref_t, ref_s = table.clone(), [s.clone() for s in slots]
+    for step in (1, 2, 7):
+        rows = torch.randperm(N, generator=g)[:n]
+        grads = torch.randn(n, K, generator=g) * 0.1
+        native.sparse_opt_apply(table, slots, rows, grads, opt, 1e-3, step, threads=3)
+        w = ref_t[rows]
+        sl = [s[rows] for s in ref_s]
+        opt.apply_dense(w, grads + 1e-3 * w, sl, step)
+        ref_t[rows] = w
+        for s, v in zip(ref_s, sl):
+            s[rows] = v
+        assert torch.allclose(table, ref_t, rtol=2e-5, atol=1e-6), (opt_name, step)
+        for a, b in zip(slots, ref_s):
+            assert torch.allclose(a, b, rtol=1e-4, atol=2e-6)  # FTRL's linear slot cancels (g - sigma * w)
+    # dense variable, 1-D first-order table and argument checking
+    w = torch.randn(70001, generator=g)
+    sl = [torch.full_like(w, v) for v in SLOT_INIT[opt.name]]
+    w_ref, sl_ref = w.clone(), [s.clone() for s in sl]
+    gd = torch.randn(70001, generator=g) * 0.1
+    native.dense_opt_apply(w, sl, gd, opt, 0.0, 5, threads=4)
+    opt.apply_dense(w_ref, gd, sl_ref, 5)
+    assert torch.allclose(w, w_ref, rtol=2e-5, atol=1e-6)
+    fm_w = torch.randn(N, generator=g)
+    sl1 = [torch.full((N,), v) for v in SLOT_INIT[opt.name]]
+    before = fm_w.clone()
+    native.sparse_opt_apply(fm_w, sl1, torch.tensor([3, 9]), torch.tensor([0.5, -0.5]), opt, 0.0, 1)
+    changed = (fm_w != before).nonzero().reshape(-1).tolist()
+    assert changed == [3, 9]
+    with pytest.raises(IOError):
+        native.sparse_opt_apply(fm_w, sl1, torch.tensor([N]), torch.tensor([0.5]), opt, 0.0, 1)
