@@ -110,3 +110,15 @@ def test_inspect_checkpoint_lists_tf_names_for_model_dir_and_servable(tmp_path):
     out = io.StringIO()
     assert main([str(tmp_path / "model"), "--tensor", "fm_w"], out=out) == 0 and "(50,)" in out.getvalue()
     assert main([str(tmp_path / "nothing")], out=io.StringIO()) == 1
+
+
+def test_bench_reference_arm_reports_unavailable():
+    """bench.py contract: `--impl reference` prints one JSON line and exits 0 when the reference cannot be installed."""
+    import subprocess
+    import sys
+    repo = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(repo, "bench.py"), "--impl", "reference", "--gpus", "1", "--steps", "5",
+                        "--warmup", "3"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and isinstance(line["unavailable"], str) and line["unavailable"]
