@@ -69,7 +69,8 @@ class Estimator:
             print("INFO:deepfm_b200:communication: %s" % getattr(self.trainer, "comm_name", "none"), file=out)
         gb = batch_size * self.env.world_size
         mf = metrics_file or (os.path.join(model_dir, "metrics.jsonl") if model_dir else None)
-        self.log = LoggingHook(log_steps, gb, mf if self.env.is_chief else None, out, enabled=self.env.is_chief)
+        self.log = LoggingHook(log_steps, gb, mf if self.env.is_chief else None, out, enabled=self.env.is_chief,
+                               event_dir=model_dir if self.env.is_chief else None)
         self.saver = CheckpointSaverHook(self.model_dir or "", save_checkpoints_secs, save_checkpoints_steps,
                                          keep_checkpoint_max, enabled=self.env.is_chief and bool(model_dir))
         self._restored = False

@@ -12,15 +12,37 @@ from typing import Optional
 
 class LoggingHook:
     def __init__(self, every_steps: int, global_batch: int, metrics_file: Optional[str] = None, out=sys.stdout,
-                 enabled: bool = True):
+                 enabled: bool = True, event_dir: Optional[str] = None):
+        """`event_dir`: also write TensorBoard event files the way the Estimator does - training scalars into
+        `<event_dir>/events.out.tfevents.*`, evaluation metrics into `<event_dir>/eval/` (utils/tfevents.py)."""
         self.every = max(1, int(every_steps))
         self.gb = global_batch
         self.out, self.enabled = out, enabled
         self.metrics_file = metrics_file
+        self.event_dir = event_dir if enabled else None
+        self._ev_train = self._ev_eval = None
         self._t0 = None
         self._s0 = 0
         if metrics_file and enabled:
             os.makedirs(os.path.dirname(os.path.abspath(metrics_file)), exist_ok=True)
+
+    def _events(self, which: str):
+        if not self.event_dir:
+            return None
+        from ..utils.tfevents import EventFileWriter
+        if which == "train":
+            if self._ev_train is None:
+                self._ev_train = EventFileWriter(self.event_dir)
+            return self._ev_train
+        if self._ev_eval is None:
+            self._ev_eval = EventFileWriter(os.path.join(self.event_dir, "eval"))
+        return self._ev_eval
+
+    def close(self):
+        for w in (self._ev_train, self._ev_eval):
+            if w is not None:
+                w.close()
+        self._ev_train = self._ev_eval = None
 
     def begin(self, step: int):
         self._t0, self._s0 = time.time(), step
@@ -40,6 +62,10 @@ class LoggingHook:
             with open(self.metrics_file, "a") as f:
                 f.write(json.dumps({"step": step, "loss": loss, "steps_per_sec": sps, "examples_per_sec": sps * self.gb,
                                     "step_time_ms": 1e3 / max(sps, 1e-9), "time": now}) + "\n")
+        ev = self._events("train")
+        if ev is not None:
+            ev.add_scalars({"loss": loss, "global_step/sec": sps, "examples/sec": sps * self.gb}, step, now)
+            ev.flush()
         self._t0, self._s0 = now, step
 
     def log_eval(self, metrics: dict):
@@ -52,6 +78,11 @@ class LoggingHook:
         if self.metrics_file:
             with open(self.metrics_file, "a") as f:
                 f.write(json.dumps(dict(metrics, eval=True, time=time.time())) + "\n")
+        ev = self._events("eval")
+        if ev is not None:
+            ev.add_scalars({k: float(v) for k, v in metrics.items() if k in ("auc", "loss")},
+                           int(metrics.get("global_step", 0)))
+            ev.flush()
 
 
 class CheckpointSaverHook:

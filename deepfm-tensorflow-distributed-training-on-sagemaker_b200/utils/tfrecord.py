@@ -78,6 +78,9 @@ class TFRecordWriter:
     def write(self, data: bytes) -> None:
         self._f.write(frame_record(data))
 
+    def flush(self) -> None:
+        self._f.flush()
+
     def close(self) -> None:
         if self._own:
             self._f.close()
