@@ -19,6 +19,7 @@
 #include <unistd.h>
 
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <algorithm>
 #include <deque>
@@ -375,6 +376,8 @@ struct RawBatch {
 };
 
 class Loader {
+  static constexpr std::chrono::microseconds kSlotPoll{100};
+
  public:
   Loader(std::vector<std::string> paths, int F, int batch, int shard_n, int shard_i, int epochs, int threads,
          bool drop_remainder, bool check_crc, uint8_t* slots, int nslots, size_t slot_stride, bool raw = false)
@@ -458,8 +461,13 @@ class Loader {
       std::lock_guard<std::mutex> l(mu_);
       free_slots_.push_back(slot);
     }
-    cv_free_.notify_one();
-    cv_work_.notify_one();  // parsers wait on cv_work_ for (raw batch AND free slot); one slot -> one parser
+    // No notification by default: two futex wake-ups per batch cost the CONSUMER thread (the training loop) 16-25 us
+    // per step. Threads that wait for a free slot poll with a timed wait (kSlotPoll) instead; a freed slot is picked up
+    // at most that much later, which the depth of the slot ring hides. DFM_LOADER_NOTIFY=1 restores the wake-ups.
+    if (notify_on_release_) {
+      cv_free_.notify_one();
+      cv_work_.notify_one();
+    }
   }
   long records_read() const { return records_read_.load(); }
 
@@ -660,7 +668,7 @@ class Loader {
         // a batch number is handed out only together with a free slot, so the oldest outstanding batch always owns a
         // slot and in-order delivery cannot deadlock
         std::unique_lock<std::mutex> l(mu_);
-        cv_free_.wait(l, [this] { return stop_ || !err_.empty() || next_batch_ >= total_batches_ || !free_slots_.empty(); });
+        while (!(stop_ || !err_.empty() || next_batch_ >= total_batches_ || !free_slots_.empty())) cv_free_.wait_for(l, kSlotPoll);
         if (stop_ || !err_.empty() || next_batch_ >= total_batches_) return;
         slot = free_slots_.front();
         free_slots_.pop_front();
@@ -721,7 +729,7 @@ class Loader {
   // ---- raw mode -------------------------------------------------------------------------------------------
   int take_free_slot() {
     std::unique_lock<std::mutex> l(mu_);
-    cv_free_.wait(l, [this] { return stop_ || !free_slots_.empty(); });
+    while (!(stop_ || !free_slots_.empty())) cv_free_.wait_for(l, kSlotPoll);
     if (stop_) return -1;
     const int s = free_slots_.front();
     free_slots_.pop_front();
@@ -849,7 +857,8 @@ class Loader {
       {
         std::unique_lock<std::mutex> l(mu_);
         // take work only when a slot is free; the OLDEST raw batch always gets the next free slot (no deadlock)
-        cv_work_.wait(l, [this] { return stop_ || !err_.empty() || (!raw_.empty() && !free_slots_.empty()) || (reader_finished_ && raw_.empty()); });
+        while (!(stop_ || !err_.empty() || (!raw_.empty() && !free_slots_.empty()) || (reader_finished_ && raw_.empty())))
+          cv_work_.wait_for(l, kSlotPoll);  // woken by the reader for new work; slot frees are found by polling
         if (stop_ || !err_.empty() || (raw_.empty() && reader_finished_)) return;
         b = std::move(raw_.front());
         raw_.pop_front();
@@ -909,6 +918,7 @@ class Loader {
   long per_epoch_batches_ = 0, next_batch_ = 0;
   std::mutex mu_;
   std::condition_variable cv_work_, cv_free_, cv_done_, cv_raw_space_;
+  const bool notify_on_release_ = [] { const char* e = getenv("DFM_LOADER_NOTIFY"); return e && e[0] == '1'; }();
   std::deque<std::unique_ptr<RawBatch>> raw_;
   std::deque<int> free_slots_;
   std::deque<Done> done_;

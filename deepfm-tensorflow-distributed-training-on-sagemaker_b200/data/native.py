@@ -223,6 +223,10 @@ class NativeLoader:
         al = lambda x: (x + 255) & ~255
         self._o_ids = al(batch_size * 4)
         self._o_vals = self._o_ids + al(batch_size * field_size * 4)
+        self._slot = c_int(-1)
+        self._slot_ref = ctypes.byref(self._slot)
+        self._next = lib.dfmio_loader_next
+        self._full_views = {}
 
     def slot_views(self, slot: int, rows: int):
         import torch
@@ -233,15 +237,27 @@ class NativeLoader:
         vals = self.buf[base + self._o_vals:base + self._o_vals + B * F * 4].view(torch.float32).view(B, F)[:rows]
         return lab, ids, vals
 
+    def full_views(self, slot: int):
+        """(labels, ids, vals, packed) views of a FULL batch in `slot`, built once per slot: creating the dozen tensor
+        views per batch cost ~35 us, a third of a 0.1 ms training step."""
+        v = self._full_views.get(slot)
+        if v is None:
+            lab, ids, vals = self.slot_views(slot, self.B)
+            v = self._full_views[slot] = (lab, ids, vals, self.buf[slot * self.stride:(slot + 1) * self.stride])
+        return v
+
     def next(self):
-        slot = c_int(-1)
-        rows = load().dfmio_loader_next(self._h, ctypes.byref(slot))
+        rows = self._next(self._h, self._slot_ref)
         if rows < 0:
             raise NativeIOError(_err())
         if rows == 0:
             return None
-        lab, ids, vals = self.slot_views(slot.value, rows)
-        return slot.value, rows, lab, ids, vals
+        s = self._slot.value
+        if rows == self.B:
+            lab, ids, vals, _ = self.full_views(s)
+        else:
+            lab, ids, vals = self.slot_views(s, rows)
+        return s, rows, lab, ids, vals
 
     def release(self, slot: int) -> None:
         if getattr(self, "_h", None):  # releasing into a closed loader is a no-op

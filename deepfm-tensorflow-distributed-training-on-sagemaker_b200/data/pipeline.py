@@ -115,7 +115,7 @@ class InputPipeline:
                 if b is None:
                     return
                 slot, rows, lab, ids, vals = b
-                packed = ld.buf[slot * ld.stride:(slot + 1) * ld.stride] if rows == self.B else None
+                packed = ld.full_views(slot)[3] if rows == self.B else None
                 yield Batch(rows, lab, ids, vals, packed, (lambda s=slot: ld.release(s)))
         finally:
             ld.close()
