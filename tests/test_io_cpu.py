@@ -261,3 +261,43 @@ def test_count_records_and_local_steps(tmp_path):
             b.release()
         # repeat(num_epochs) happens AFTER batch in the reference (HVD:122-126): per-epoch remainders are dropped
         assert want == 2 * local_steps([p], 32, shard, 1) == local_steps([p], 32, shard, 2)
+
+
+def test_loader_survives_slow_out_of_order_consumers(tmp_path):
+    """Slots are handed back late and out of order (as CUDA-event driven releases are): delivery stays in record order,
+    nothing deadlocks with the smallest legal ring, in parsed and in raw mode."""
+    import random
+    from deepfm_b200.data import native
+    from deepfm_b200.utils import tfrecord as T
+    F, B, n = 3, 8, 8 * 37
+    path = str(tmp_path / "tr.tfrecords")
+    with native.NativeRecordWriter(path) as w:
+        for i in range(n):
+            w.write(T.make_ctr_example(float(i % 2), [i, i + 1, i + 2], [1.0, 0.5, 0.25]))
+    rng = random.Random(0)
+    for mode in ("parsed", "raw"):
+        if mode == "parsed":
+            ld = native.NativeLoader([path], F, B, num_epochs=3, threads=3, nslots=2)
+        else:
+            ld = native.NativeRawLoader([path], B, num_epochs=3, nslots=2, max_record_bytes=256)
+        held, first_ids = [], []
+        while True:
+            item = ld.next()
+            if item is None:
+                break
+            if mode == "parsed":
+                slot, rows, lab, ids, vals = item
+                first_ids.append(int(ids[0, 0]))
+            else:
+                slot, rows, raw = item
+                first_ids.append(int(T.parse_ctr_batch(ld.records(raw, rows)[:1], F)[1][0, 0]))
+            assert rows == B
+            held.append(slot)
+            if len(held) == 2 or rng.random() < 0.5:      # hold up to the whole ring, release in random order
+                rng.shuffle(held)
+                while held:
+                    ld.release(held.pop())
+        for s in held:
+            ld.release(s)
+        ld.close()
+        assert first_ids == [B * k for k in range(n // B)] * 3, mode
