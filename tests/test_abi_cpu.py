@@ -51,3 +51,13 @@ def test_header_is_valid_c_and_cxx(tmp_path):
         r = subprocess.run([comp, "-fsyntax-only", "-Wall", "-Werror", "-I", os.path.join(REPO, "include"), str(src)],
                            capture_output=True, text=True)
         assert r.returncode == 0, r.stderr
+
+
+def test_c_abi_example_compiles_against_the_header():
+    """examples/c_abi_example.c is the documented way in for non-Python callers: it must at least type-check."""
+    cuda_inc = "/usr/local/cuda/include"
+    if not os.path.exists(os.path.join(cuda_inc, "cuda_runtime.h")):
+        pytest.skip("CUDA toolkit headers not installed")
+    r = subprocess.run(["gcc", "-fsyntax-only", "-Wall", "-Werror", "-I", os.path.join(REPO, "include"), "-I", cuda_inc,
+                        os.path.join(REPO, "examples", "c_abi_example.c")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
