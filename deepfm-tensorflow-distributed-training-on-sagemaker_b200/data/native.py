@@ -69,8 +69,22 @@ def load(build_if_missing: bool = True) -> ctypes.CDLL:
                                            c_f, c_f, c_f, c_f, c_f, c_f, c_ll, c_int]
     lib.dfmio_dense_opt_apply.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_int, c_f, c_f, c_f, c_f, c_f,
                                           c_f, c_ll, c_int]
+    lib.dfmio_libsvm_last_error.restype = c_char_p
+    lib.dfmio_libsvm_convert.restype = c_ll
+    lib.dfmio_libsvm_convert.argtypes = [c_char_p, c_char_p, c_int, c_ll, c_int]
     _lib = lib
     return lib
+
+
+def libsvm_convert_native(input_filename: str, output_filename: str, field_size: Optional[int] = None, pad_id: int = 0,
+                          threads: int = 0) -> int:
+    """libsvm text -> TFRecord file of CTR Examples, multi-threaded (csrc/io/libsvm_convert.cc); returns the row count."""
+    lib = load()
+    n = lib.dfmio_libsvm_convert(input_filename.encode(), output_filename.encode(), int(field_size or 0), int(pad_id),
+                                 int(threads))
+    if n < 0:
+        raise ValueError((lib.dfmio_libsvm_last_error() or b"libsvm conversion failed").decode())
+    return int(n)
 
 
 def _slot_ptrs(slots):

@@ -53,8 +53,16 @@ def convert_lines(lines: Iterable[str], writer: TFRecordWriter, field_size: Opti
 
 
 def convert_tfrecords(input_filename: str, output_filename: str, field_size: Optional[int] = None,
-                      pad_id: int = 0) -> int:
-    """Same name and positional arguments as the reference function (TOOL:5)."""
+                      pad_id: int = 0, use_native: bool = True, threads: int = 0) -> int:
+    """Same name and positional arguments as the reference function (TOOL:5). With the host IO library built, the
+    multi-threaded C++ converter does the work (byte-identical output, ~100x the rate of the Python loop below)."""
+    if use_native:
+        try:
+            from ..data import native
+            if native.available():
+                return native.libsvm_convert_native(input_filename, output_filename, field_size, pad_id, threads)
+        except (ImportError, OSError):
+            pass
     with open(input_filename, "r") as fin, TFRecordWriter(output_filename) as w:
         return convert_lines(fin, w, field_size, pad_id)
 
@@ -66,8 +74,10 @@ def main(argv=None) -> int:
     ap.add_argument("--field_size", type=int, default=None,
                     help="pad/truncate every row to exactly this many id:value pairs")
     ap.add_argument("--pad_id", type=int, default=0)
+    ap.add_argument("--python", action="store_true", help="use the pure-Python converter")
+    ap.add_argument("--threads", type=int, default=0, help="converter threads (0 = one per hardware thread)")
     a = ap.parse_args(argv)
-    n = convert_tfrecords(a.input, a.output, a.field_size, a.pad_id)
+    n = convert_tfrecords(a.input, a.output, a.field_size, a.pad_id, not a.python, a.threads)
     print("converted %d rows: %s -> %s" % (n, a.input, a.output))
     return 0
 

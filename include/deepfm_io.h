@@ -52,6 +52,12 @@ void dfmio_loader_release(void* loader, int slot);
 long dfmio_loader_records(void* loader);
 void dfmio_loader_destroy(void* loader);
 
+/* ---- libsvm text ("label id:val id:val ...") -> TFRecord file of Examples {ids, label, values}, multi-threaded, record
+ * order = line order, rows padded with (pad_id, 0) / truncated to field_size when field_size > 0. Returns the number of
+ * rows, -1 on error (dfmio_libsvm_last_error()). threads <= 0: one per hardware thread. */
+const char* dfmio_libsvm_last_error(void);
+long long dfmio_libsvm_convert(const char* input, const char* output, int field_size, long long pad_id, int threads);
+
 /* ---- host-side optimizer application for the asynchronous parameter-server store (csrc/io/host_optim.cc): TF-1 rules
  * (opt: 0 Adam, 1 Adagrad, 2 Momentum, 3 FTRL, 4 SGD), `g + l2 * w` formed in the same pass, `step` = 1-based update index,
  * work split over `threads` threads, no locking (Hogwild). s0 / s1 = slot tables (NULL where the rule has fewer slots). */

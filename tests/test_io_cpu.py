@@ -301,3 +301,35 @@ def test_loader_survives_slow_out_of_order_consumers(tmp_path):
             ld.release(s)
         ld.close()
         assert first_ids == [B * k for k in range(n // B)] * 3, mode
+
+
+def test_native_libsvm_converter_is_byte_identical_to_the_python_one(tmp_path):
+    """C1: the multi-threaded C++ converter writes exactly the bytes utils/libsvm.py writes (record order = line order,
+    padding / truncation, blank lines, CRLF, exponents, missing final newline), and names the line it cannot parse."""
+    import random
+    from deepfm_b200.data import native
+    from deepfm_b200.utils.libsvm import convert_tfrecords
+    rng = random.Random(7)
+    lines = ["1 5:1 7:0.5 11:2.25", "0 3:1e-3 4:+2 9:.5 12:-0.125 13:7 14:8", "", "   ", "1 1:1\r", "0", "1 0:0 0:0 0:0 0:0 0:0"]
+    for i in range(3000):
+        k = rng.choice([1, 3, 4, 5, 9])
+        lines.append("%d %s" % (i % 2, " ".join("%d:%r" % (rng.randrange(1 << 40), rng.uniform(-3, 3)) for _ in range(k))))
+    src = tmp_path / "in.libsvm"
+    src.write_text("\n".join(lines))  # no trailing newline on purpose
+    for field_size in (4, None):
+        a, b = str(tmp_path / "py.tfrecords"), str(tmp_path / "cc.tfrecords")
+        n_py = convert_tfrecords(str(src), a, field_size, pad_id=2, use_native=False)
+        for threads in (1, 3, 0):
+            n_cc = native.libsvm_convert_native(str(src), b, field_size, 2, threads)
+            assert n_cc == n_py == len(lines) - 2
+            assert open(a, "rb").read() == open(b, "rb").read(), (field_size, threads)
+    assert convert_tfrecords(str(src), b, 4, pad_id=2) == n_py          # default path = native
+    bad = tmp_path / "bad.libsvm"
+    bad.write_text("1 1:1\n0 2:x\n1 3:1\n")
+    with pytest.raises(ValueError, match="line 2"):
+        native.libsvm_convert_native(str(bad), b, 4)
+    with pytest.raises(ValueError, match="cannot open"):
+        native.libsvm_convert_native(str(tmp_path / "missing"), b, 4)
+    empty = tmp_path / "empty.libsvm"
+    empty.write_text("")
+    assert native.libsvm_convert_native(str(empty), b, 4) == 0
