@@ -70,6 +70,8 @@ struct Scratch {
   std::string packed, entries, example, t1, t2;
 };
 
+void emit_record(double label, Scratch& s, std::string& out);
+
 // Converts one line [p, e) (no newline) and appends the framed record to `out`. Returns false on a malformed line.
 bool convert_line(const char* p, const char* e, int field_size, int64_t pad_id, Scratch& s, std::string& out) {
   while (e > p && (e[-1] == '\r' || e[-1] == '\n')) --e;
@@ -93,6 +95,12 @@ bool convert_line(const char* p, const char* e, int field_size, int64_t pad_id, 
     s.ids.resize((size_t)field_size, pad_id);  // truncates or pads
     s.vals.resize((size_t)field_size, 0.0f);
   }
+  emit_record(label, s, out);
+  return true;
+}
+
+// Appends the framed record of Example{ids = s.ids, label, values = s.vals} to `out`.
+void emit_record(double label, Scratch& s, std::string& out) {
   s.entries.clear();
   s.packed.clear();
   for (int64_t id : s.ids) put_varint(s.packed, (uint64_t)id);
@@ -111,7 +119,6 @@ bool convert_line(const char* p, const char* e, int field_size, int64_t pad_id, 
   out.append((const char*)&c1, 4);
   out += s.example;
   out.append((const char*)&c2, 4);
-  return true;
 }
 
 bool blank(const char* p, const char* e) {
@@ -125,6 +132,24 @@ bool blank(const char* p, const char* e) {
 extern "C" {
 
 const char* dfmio_libsvm_last_error() { return g_cerr; }
+
+// Dense arrays -> framed TFRecord bytes of n Examples (labels [n] f32, ids [n, F] i64, vals [n, F] f32), for writers that
+// already hold columns (synthetic data, parquet / numpy sources). Returns the number of bytes the n records take; they are
+// written to `out` only if they fit in `cap` (call with out = NULL to size the buffer).
+unsigned long long dfmio_encode_ctr_batch(const float* labels, const int64_t* ids, const float* vals, long long n, int F,
+                                          uint8_t* out, unsigned long long cap) {
+  if (!labels || !ids || !vals || n < 0 || F <= 0) return 0;
+  Scratch s;
+  std::string buf;
+  buf.reserve((size_t)n * (size_t)(64 + 14 * F));
+  for (long long r = 0; r < n; ++r) {
+    s.ids.assign(ids + (size_t)r * F, ids + (size_t)(r + 1) * F);
+    s.vals.assign(vals + (size_t)r * F, vals + (size_t)(r + 1) * F);
+    emit_record((double)labels[r], s, buf);
+  }
+  if (out && buf.size() <= cap) memcpy(out, buf.data(), buf.size());
+  return buf.size();
+}
 
 // Returns the number of rows written, or -1 (message in dfmio_libsvm_last_error()). field_size <= 0: rows keep the number
 // of id:value pairs they have. threads <= 0: one per hardware thread (at most 16).

@@ -69,11 +69,32 @@ def load(build_if_missing: bool = True) -> ctypes.CDLL:
                                            c_f, c_f, c_f, c_f, c_f, c_f, c_ll, c_int]
     lib.dfmio_dense_opt_apply.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_int, c_f, c_f, c_f, c_f, c_f,
                                           c_f, c_ll, c_int]
+    lib.dfmio_encode_ctr_batch.restype = c_uint64
+    lib.dfmio_encode_ctr_batch.argtypes = [c_void_p, c_void_p, c_void_p, c_ll, c_int, c_void_p, c_uint64]
     lib.dfmio_libsvm_last_error.restype = c_char_p
     lib.dfmio_libsvm_convert.restype = c_ll
     lib.dfmio_libsvm_convert.argtypes = [c_char_p, c_char_p, c_int, c_ll, c_int]
     _lib = lib
     return lib
+
+
+def encode_ctr_batch(labels, ids, vals) -> bytes:
+    """numpy columns (labels [n], ids [n, F], vals [n, F]) -> the bytes of n framed TFRecord Examples, ready to append to
+    a .tfrecords file (same bytes as utils/tfrecord.py::make_ctr_example + frame_record per row)."""
+    labels = np.ascontiguousarray(labels, dtype=np.float32)
+    ids = np.ascontiguousarray(ids, dtype=np.int64)
+    vals = np.ascontiguousarray(vals, dtype=np.float32)
+    n, F = ids.shape
+    assert labels.shape == (n,) and vals.shape == (n, F)
+    lib = load()
+    cap = n * (64 + 14 * F)
+    while True:
+        buf = np.empty(cap, dtype=np.uint8)
+        need = int(lib.dfmio_encode_ctr_batch(labels.ctypes.data, ids.ctypes.data, vals.ctypes.data, n, F,
+                                              buf.ctypes.data, cap))
+        if need <= cap:
+            return buf[:need].tobytes()
+        cap = need
 
 
 def libsvm_convert_native(input_filename: str, output_filename: str, field_size: Optional[int] = None, pad_id: int = 0,

@@ -68,20 +68,25 @@ def write_synthetic_tfrecords(out_dir: str, prefix: str, num_files: int, rows_pe
     os.makedirs(out_dir, exist_ok=True)
     gen = SyntheticCTR(field_size, feature_size, seed=seed)
     paths = []
-    writer_cls = TFRecordWriter
+    encode = None
     if native:
         try:
-            from .native import NativeRecordWriter, available
+            from .native import available, encode_ctr_batch
             if available():
-                writer_cls = NativeRecordWriter
+                encode = encode_ctr_batch
         except Exception:
             pass
+    import zlib
     for fi in range(num_files):
         path = os.path.join(out_dir, "%s%03d.tfrecords" % (prefix, fi))
-        import zlib
         ids, vals, labels = gen.numpy_batch(rows_per_file, zlib.crc32(("%s/%d" % (prefix, fi)).encode()))
-        with writer_cls(path) as w:
-            for r in range(rows_per_file):
-                w.write(make_ctr_example(float(labels[r]), ids[r].tolist(), vals[r].tolist()))
+        if encode is not None:  # columns -> framed records in one native call per 64 Ki rows
+            with open(path, "wb") as f:
+                for r0 in range(0, rows_per_file, 65536):
+                    f.write(encode(labels[r0:r0 + 65536], ids[r0:r0 + 65536], vals[r0:r0 + 65536]))
+        else:
+            with TFRecordWriter(path) as w:
+                for r in range(rows_per_file):
+                    w.write(make_ctr_example(float(labels[r]), ids[r].tolist(), vals[r].tolist()))
         paths.append(path)
     return paths

@@ -57,6 +57,9 @@ void dfmio_loader_destroy(void* loader);
  * rows, -1 on error (dfmio_libsvm_last_error()). threads <= 0: one per hardware thread. */
 const char* dfmio_libsvm_last_error(void);
 long long dfmio_libsvm_convert(const char* input, const char* output, int field_size, long long pad_id, int threads);
+/* columns -> framed TFRecord bytes of n Examples; returns the byte count, writes to out only if it fits in cap */
+unsigned long long dfmio_encode_ctr_batch(const float* labels, const int64_t* ids, const float* vals, long long n, int F,
+                                          uint8_t* out, unsigned long long cap);
 
 /* ---- host-side optimizer application for the asynchronous parameter-server store (csrc/io/host_optim.cc): TF-1 rules
  * (opt: 0 Adam, 1 Adagrad, 2 Momentum, 3 FTRL, 4 SGD), `g + l2 * w` formed in the same pass, `step` = 1-based update index,
