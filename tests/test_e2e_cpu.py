@@ -184,3 +184,20 @@ def test_example_notebooks_and_scripts_use_known_flags():
                 assert keys <= known, (name, keys - known)
                 seen |= keys
     assert {"task_type", "field_size", "feature_size", "worker_per_host", "enable_data_multi_path"} <= seen
+
+
+def test_uneven_shards_do_not_deadlock_the_job(data, tmp_path):
+    """Horovod's failure mode with unequal per-rank data (PDF p22-23): 383 records over 2 ranks = 192 vs 191, i.e. 6 vs 5
+    full batches of 32. The ranks agree on 5 steps before the epoch, so nobody waits in a collective for a 6th."""
+    from deepfm_b200.data.synthetic import write_synthetic_tfrecords
+    from deepfm_b200.launch import LocalEstimator
+    from deepfm_b200.utils.checkpoint import latest_checkpoint
+    from deepfm_b200.utils.tf_bundle import read_bundle
+    write_synthetic_tfrecords(str(tmp_path / "train"), "tr", 1, 383, F, N, seed=4)
+    hp = dict(field_size=F, feature_size=N, embedding_size=8, deep_layers="16", dropout="1.0", batch_size=32,
+              backend="torch", task_type="train", num_epochs=2, log_steps=1000, loader_threads=1,
+              model_dir=str(tmp_path / "ck"))
+    LocalEstimator(hp, {"mpi": {"enabled": True, "processes_per_host": 2}},
+                   env={"PYTHONPATH": REPO, "CUDA_VISIBLE_DEVICES": ""}, cwd=REPO).fit(
+        {"training": str(tmp_path / "train"), "evaluation": str(data / "val")}, timeout=240)
+    assert int(read_bundle(latest_checkpoint(str(tmp_path / "ck")))["global_step"]) == 10   # 2 epochs x min(6, 5)
