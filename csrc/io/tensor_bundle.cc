@@ -67,6 +67,7 @@ struct Entry {
   std::vector<int64_t> dims;
   uint64_t offset = 0, size = 0;
   uint32_t crc = 0;  // masked
+  int shard = 0;     // which <prefix>.data-SSSSS-of-NNNNN file holds the bytes
 };
 
 std::string encode_entry(const Entry& e) {
@@ -85,7 +86,10 @@ std::string encode_entry(const Entry& e) {
   s.push_back((char)((2 << 3) | 2));
   put_varint(s, shape.size());
   s += shape;
-  // shard_id (3) = 0 omitted (proto3 default)
+  if (e.shard) {  // shard_id (3); 0 is omitted (proto3 default)
+    s.push_back((char)((3 << 3) | 0));
+    put_varint(s, (uint64_t)e.shard);
+  }
   if (e.offset) {
     s.push_back((char)((4 << 3) | 0));
     put_varint(s, e.offset);
@@ -97,10 +101,10 @@ std::string encode_entry(const Entry& e) {
   return s;
 }
 
-std::string encode_header() {
+std::string encode_header(int num_shards) {
   std::string s;
   s.push_back((char)((1 << 3) | 0));
-  put_varint(s, 1);  // num_shards
+  put_varint(s, (uint64_t)num_shards);
   // endianness (2) = LITTLE = 0 omitted
   std::string ver;
   ver.push_back((char)((1 << 3) | 0));
@@ -120,6 +124,7 @@ bool decode_entry(const uint8_t* p, const uint8_t* e, Entry* out) {
       uint64_t v;
       if (!get_varint(p, e, &v)) return false;
       if (f == 1) out->dtype = (int)v;
+      else if (f == 3) out->shard = (int)v;
       else if (f == 4) out->offset = v;
       else if (f == 5) out->size = v;
     } else if (wt == 5) {
@@ -218,15 +223,22 @@ Handle write_block(FILE* f, const std::string& block, uint64_t* pos) {
   return h;
 }
 
+std::string shard_path(const std::string& prefix, int shard, int num_shards) {
+  char suffix[64];
+  snprintf(suffix, sizeof(suffix), ".data-%05d-of-%05d", shard, num_shards);
+  return prefix + suffix;
+}
+
 struct Writer {
   std::string prefix;
-  FILE* data = nullptr;
-  uint64_t data_pos = 0;
+  std::vector<FILE*> data;         // one file per shard; variables are dealt round-robin, as TF's
+  std::vector<uint64_t> data_pos;  // replica_device_setter deals them to parameter-server tasks
   std::vector<Entry> entries;
 };
 
 struct Reader {
   std::string prefix;
+  int num_shards = 1;
   std::vector<Entry> entries;
 };
 
@@ -298,18 +310,31 @@ extern "C" {
 
 const char* dfmio_bundle_last_error() { return g_berr; }
 
-void* dfmio_bundle_writer_create(const char* prefix) {
+// num_shards data files (an Estimator's Saver is sharded: one file per parameter-server task in the reference's PS mode,
+// one file otherwise); variable k goes to shard k % num_shards.
+void* dfmio_bundle_writer_create_sharded(const char* prefix, int num_shards) {
+  if (num_shards < 1 || num_shards > 99999) {
+    berr("bundle writer: num_shards out of range");
+    return nullptr;
+  }
   Writer* w = new Writer();
   w->prefix = prefix;
-  const std::string dp = w->prefix + ".data-00000-of-00001";
-  w->data = fopen(dp.c_str(), "wb");
-  if (!w->data) {
-    berr("cannot open %s for writing", dp.c_str());
-    delete w;
-    return nullptr;
+  for (int sidx = 0; sidx < num_shards; ++sidx) {
+    const std::string dp = shard_path(w->prefix, sidx, num_shards);
+    FILE* f = fopen(dp.c_str(), "wb");
+    if (!f) {
+      berr("cannot open %s for writing", dp.c_str());
+      for (FILE* g : w->data) fclose(g);
+      delete w;
+      return nullptr;
+    }
+    w->data.push_back(f);
+    w->data_pos.push_back(0);
   }
   return w;
 }
+
+void* dfmio_bundle_writer_create(const char* prefix) { return dfmio_bundle_writer_create_sharded(prefix, 1); }
 
 // dtype: TF DataType enum (1 float32, 3 int32, 9 int64). Bytes are host memory, little-endian.
 int dfmio_bundle_writer_add(void* wh, const char* name, int dtype, int ndim, const int64_t* dims, const void* bytes,
@@ -319,23 +344,24 @@ int dfmio_bundle_writer_add(void* wh, const char* name, int dtype, int ndim, con
   e.name = name;
   e.dtype = dtype;
   e.dims.assign(dims, dims + ndim);
-  e.offset = w->data_pos;
+  e.shard = (int)(w->entries.size() % w->data.size());
+  e.offset = w->data_pos[(size_t)e.shard];
   e.size = nbytes;
   e.crc = mask_crc(dfmio::crc32c((const uint8_t*)bytes, nbytes));
-  if (nbytes && fwrite(bytes, 1, nbytes, w->data) != nbytes) {
+  if (nbytes && fwrite(bytes, 1, nbytes, w->data[(size_t)e.shard]) != nbytes) {
     berr("write failed for %s", name);
     return -1;
   }
-  w->data_pos += nbytes;
+  w->data_pos[(size_t)e.shard] += nbytes;
   w->entries.push_back(std::move(e));
   return 0;
 }
 
 int dfmio_bundle_writer_finish(void* wh) {
   Writer* w = (Writer*)wh;
-  fclose(w->data);
+  for (FILE* f : w->data) fclose(f);
   std::map<std::string, std::string> kv;
-  kv[""] = encode_header();
+  kv[""] = encode_header((int)w->data.size());
   for (const Entry& e : w->entries) kv[e.name] = encode_entry(e);
   const std::string ip = w->prefix + ".index";
   FILE* f = fopen(ip.c_str(), "wb");
@@ -407,7 +433,16 @@ void* dfmio_bundle_reader_open(const char* prefix) {
     const uint8_t *db, *de;
     if (!check_block(file, dh, &db, &de)) return false;
     return iterate_block(db, de, [&](const std::string& key, const uint8_t* ev, const uint8_t* eve) {
-      if (key.empty()) return true;  // header
+      if (key.empty()) {  // BundleHeaderProto: num_shards = field 1
+        const uint8_t* hp = ev;
+        uint64_t tag, v;
+        while (hp < eve && get_varint(hp, eve, &tag)) {
+          if ((tag & 7) != 0) break;  // later fields (endianness, version) are not needed
+          if (!get_varint(hp, eve, &v)) break;
+          if ((tag >> 3) == 1 && v >= 1) r->num_shards = (int)v;
+        }
+        return true;
+      }
       Entry en;
       en.name = key;
       if (!decode_entry(ev, eve, &en)) {
@@ -450,7 +485,11 @@ int dfmio_bundle_reader_read(void* rh, int i, void* dst, uint64_t cap, int verif
     berr("destination too small for %s", e.name.c_str());
     return -1;
   }
-  const std::string dp = r->prefix + ".data-00000-of-00001";
+  if (e.shard < 0 || e.shard >= r->num_shards) {
+    berr("%s lives in shard %d of %d", e.name.c_str(), e.shard, r->num_shards);
+    return -1;
+  }
+  const std::string dp = shard_path(r->prefix, e.shard, r->num_shards);
   FILE* f = fopen(dp.c_str(), "rb");
   if (!f) {
     berr("cannot open %s", dp.c_str());

@@ -10,6 +10,7 @@ and transposed to the native `[out,in]` on load.
 """
 from __future__ import annotations
 
+import glob
 import os
 import re
 from typing import Dict, List, Optional
@@ -79,7 +80,7 @@ def latest_checkpoint(model_dir: str) -> Optional[str]:
                     return p
     for step in reversed(all_checkpoints(model_dir)):  # no usable state file: newest checkpoint with both files present
         p = os.path.join(model_dir, "model.ckpt-%d" % step)
-        if os.path.exists(p + ".data-00000-of-00001"):
+        if glob.glob(glob.escape(p) + ".data-*"):  # one data file, or several behind a sharded (PS-style) index
             return p
     return None
 
@@ -100,9 +101,10 @@ def save_checkpoint(model_dir: str, state_dict: Dict[str, torch.Tensor], opt, ke
         os.replace(tmp + ext, prefix + ext)
     steps = all_checkpoints(model_dir)
     for old in steps[:-keep] if keep > 0 else []:
-        for ext in (".index", ".data-00000-of-00001"):
+        stem = os.path.join(model_dir, "model.ckpt-%d" % old)
+        for path in [stem + ".index"] + glob.glob(glob.escape(stem) + ".data-*"):
             try:
-                os.remove(os.path.join(model_dir, "model.ckpt-%d%s" % (old, ext)))
+                os.remove(path)
             except OSError:
                 pass
     steps = all_checkpoints(model_dir)

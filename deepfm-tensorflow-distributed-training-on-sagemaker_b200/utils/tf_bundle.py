@@ -21,6 +21,8 @@ def _lib():
         lib.dfmio_bundle_last_error.restype = c_char_p
         lib.dfmio_bundle_writer_create.restype = c_void_p
         lib.dfmio_bundle_writer_create.argtypes = [c_char_p]
+        lib.dfmio_bundle_writer_create_sharded.restype = c_void_p
+        lib.dfmio_bundle_writer_create_sharded.argtypes = [c_char_p, c_int]
         lib.dfmio_bundle_writer_add.argtypes = [c_void_p, c_char_p, c_int, c_int, c_void_p, c_void_p, c_uint64]
         lib.dfmio_bundle_writer_finish.argtypes = [c_void_p]
         lib.dfmio_bundle_reader_open.restype = c_void_p
@@ -38,10 +40,12 @@ def _err(lib):
     return m.decode() if m else "?"
 
 
-def write_bundle(prefix: str, tensors: Dict[str, torch.Tensor]) -> None:
-    """Write `<prefix>.index` + `<prefix>.data-00000-of-00001` holding `tensors` (keys = TF variable names)."""
+def write_bundle(prefix: str, tensors: Dict[str, torch.Tensor], num_shards: int = 1) -> None:
+    """Write `<prefix>.index` + `<prefix>.data-SSSSS-of-NNNNN` holding `tensors` (keys = TF variable names).
+    `num_shards` > 1 spreads the variables round-robin over that many data files - the layout the reference's
+    parameter-server jobs leave behind (sharded Saver, one file per PS task); `read_bundle` reads any shard count."""
     lib = _lib()
-    h = lib.dfmio_bundle_writer_create(prefix.encode())
+    h = lib.dfmio_bundle_writer_create_sharded(prefix.encode(), int(num_shards))
     if not h:
         raise IOError(_err(lib))
     for name in sorted(tensors):

@@ -74,6 +74,9 @@ int dfmio_dense_opt_apply(float* w, float* s0, float* s1, const float* g, long l
  * dtype is TensorFlow's DataType enum (1 float32, 3 int32, 9 int64); dims holds up to 8 entries. */
 const char* dfmio_bundle_last_error(void);
 void* dfmio_bundle_writer_create(const char* prefix);
+/* num_shards data files (<prefix>.data-SSSSS-of-NNNNN), variable k in shard k % num_shards: the layout a sharded TF Saver
+ * produces with one parameter-server task per shard; the reader handles any number of shards */
+void* dfmio_bundle_writer_create_sharded(const char* prefix, int num_shards);
 int dfmio_bundle_writer_add(void* writer, const char* name, int dtype, int ndim, const int64_t* dims, const void* bytes,
                             uint64_t nbytes);
 int dfmio_bundle_writer_finish(void* writer); /* sorts the keys, writes both files, frees the writer */

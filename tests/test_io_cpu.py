@@ -333,3 +333,29 @@ def test_native_libsvm_converter_is_byte_identical_to_the_python_one(tmp_path):
     empty = tmp_path / "empty.libsvm"
     empty.write_text("")
     assert native.libsvm_convert_native(str(empty), b, 4) == 0
+
+
+def test_sharded_tensor_bundles_like_a_parameter_server_checkpoint(tmp_path):
+    """The reference's PS jobs save through a sharded Saver: several `.data-SSSSS-of-NNNNN` files behind one index. The
+    reader follows BundleEntryProto.shard_id / BundleHeaderProto.num_shards; a missing shard is reported, not misread."""
+    import os
+    from deepfm_b200.utils.tf_bundle import read_bundle, write_bundle
+    g = torch.Generator().manual_seed(0)
+    tensors = {"fm_w": torch.randn(50, generator=g), "fm_v": torch.randn(50, 8, generator=g),
+               "Deep-part/mlp0/weights": torch.randn(32, 16, generator=g), "Deep-part/mlp0/biases": torch.zeros(16),
+               "fm_bias": torch.tensor([0.25]), "global_step": torch.tensor(123)}
+    prefix = str(tmp_path / "model.ckpt-123")
+    write_bundle(prefix, tensors, num_shards=3)
+    files = sorted(f for f in os.listdir(tmp_path) if ".data-" in f)
+    assert files == ["model.ckpt-123.data-0000%d-of-00003" % i for i in range(3)]
+    assert all(os.path.getsize(tmp_path / f) > 0 for f in files)
+    back = read_bundle(prefix)
+    assert set(back) == set(tensors)
+    for k, v in tensors.items():
+        assert torch.equal(back[k], v) and back[k].shape == v.shape, k
+    one = str(tmp_path / "single")
+    write_bundle(one, tensors)                                   # default layout unchanged: one data file
+    assert os.path.exists(one + ".data-00000-of-00001") and torch.equal(read_bundle(one)["fm_v"], tensors["fm_v"])
+    os.remove(tmp_path / files[1])
+    with pytest.raises(IOError, match="cannot open"):
+        read_bundle(prefix)
