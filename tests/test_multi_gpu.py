@@ -49,11 +49,14 @@ def test_ps_fused_worker_converges(cuda_lib, tmp_path):
                         store_path=str(tmp_path / "s.bin"))
     assert tr.use_fused
     data = SyntheticCTR(39, 20000, seed=0)
+    held_out = [data.batch(1024, 5000 + i, ids_dtype=torch.int64) for i in range(4)]
+    before = tr.evaluate(held_out)
     for s in range(200):
         tr.train_batch(*data.batch(512, s))
     losses = tr.drain()
-    assert sum(losses[:10]) / 10 > sum(losses[-10:]) / 10 + 0.03, (losses[:3], losses[-3:])
+    assert len(losses) == 200 and all(l == l for l in losses)
     assert tr.max_observed_staleness <= 2 and tr.kernels_per_step > 10
-    ev = tr.evaluate([data.batch(1024, 5000 + i, ids_dtype=torch.int64) for i in range(4)])
+    ev = tr.evaluate(held_out)
+    assert ev["loss"] < before["loss"] - 0.02, (before, ev)  # held-out loss: robust to asynchronous update order
     assert ev["auc"] > 0.6
     tr.close()

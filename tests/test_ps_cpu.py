@@ -35,13 +35,18 @@ def test_single_worker_ps_converges_and_bounds_staleness(tmp_path):
     tr = AsyncPSTrainer(cfg, 64, TF1Optimizer("Adagrad", 0.05), 0, DistEnv(), backend="torch", staleness=2,
                         store_path=str(tmp_path / "store.bin"))
     data = SyntheticCTR(F, N, seed=0)
+    held_out = [data.batch(512, 1000 + i, ids_dtype=torch.int64) for i in range(4)]
+    before = tr.evaluate(held_out)
     for s in range(150):
         tr.train_batch(*data.batch(64, s, ids_dtype=torch.int64))
     losses = tr.drain()
-    assert sum(losses[:10]) / 10 > sum(losses[-10:]) / 10 + 0.03
+    assert len(losses) == 150 and all(l == l for l in losses)
     assert tr.max_observed_staleness <= 2
     assert tr.global_step == 150
-    ev = tr.evaluate([data.batch(512, 1000 + i, ids_dtype=torch.int64) for i in range(4)])
+    ev = tr.evaluate(held_out)
+    # convergence on HELD-OUT data (0.68 -> 0.49 here): per-batch training losses of an asynchronous run at batch 64 are
+    # too noisy for a fixed margin (their 10-step means moved by 0.03-0.12 from run to run)
+    assert ev["loss"] < before["loss"] - 0.1, (before, ev)
     assert ev["auc"] > 0.6 and ev["examples"] == 2048
     sd = tr.state_dict()
     assert "fm_v/Adagrad" in sd and sd["fm_v"].shape == (N, 8) and int(sd["global_step"]) == 150
