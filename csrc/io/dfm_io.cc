@@ -380,16 +380,19 @@ class Loader {
 
  public:
   Loader(std::vector<std::string> paths, int F, int batch, int shard_n, int shard_i, int epochs, int threads,
-         bool drop_remainder, bool check_crc, uint8_t* slots, int nslots, size_t slot_stride, bool raw = false)
+         bool drop_remainder, bool check_crc, uint8_t* slots, int nslots, size_t slot_stride, bool raw = false,
+         uint64_t shuffle_seed = 0)
       : paths_(std::move(paths)), F_(F), B_(batch), shard_n_(shard_n < 1 ? 1 : shard_n), shard_i_(shard_i),
         epochs_(epochs), drop_(drop_remainder), crc_(check_crc), slots_(slots), nslots_(nslots),
-        stride_(slot_stride), raw_mode_(raw) {
+        stride_(slot_stride), raw_mode_(raw), shuffle_seed_(shuffle_seed) {
     for (int i = 0; i < nslots_; ++i) free_slots_.push_back(i);
     const char* no_index = getenv("DFM_LOADER_INDEXED");
     if (!(no_index && no_index[0] == '0') && build_index()) {
       // indexed mode (regular files only): record boundaries are walked ONCE; afterwards batch k of the sharded record
       // sequence is an O(1) lookup, so `threads` workers build batches fully in parallel — no serial reader stage
       indexed_ = true;
+      perm_half_ = 1;
+      while ((1ull << (2 * perm_half_)) < index_.size()) ++perm_half_;
       const long full = (long)(index_.size() / (size_t)B_);
       per_epoch_batches_ = full + ((!drop_ && index_.size() % (size_t)B_) ? 1 : 0);
       total_batches_ = per_epoch_batches_ * epochs_;
@@ -653,6 +656,33 @@ class Loader {
     for (int fi = 0; fi < nf; ++fi) maps_[paths_[(size_t)fi]] = maps[(size_t)fi];
     return true;
   }
+  // ---- per-epoch shuffle (indexed mode): position p of epoch e reads record permute(p) of this rank's shard, where
+  // permute is a keyed bijection on [0, n) - a 4-round Feistel network on 2 * perm_half_ bits with cycle walking (the
+  // domain is less than 4n, so under 4 walks on average). No permutation array is stored, every worker evaluates it
+  // independently, the order is reproducible from (seed, epoch), and every record is still read exactly once per epoch.
+  static uint64_t splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+  }
+  uint64_t epoch_key_of(uint64_t epoch) const { return shuffle_seed_ ? splitmix64(shuffle_seed_ ^ splitmix64(epoch + 1)) : 0; }
+  const RecRef& record_at(size_t pos, uint64_t epoch_key) const {
+    if (!shuffle_seed_) return index_[pos];
+    const uint64_t n = index_.size(), mask = (1ull << perm_half_) - 1;
+    uint64_t x = pos;
+    do {
+      uint64_t l = x >> perm_half_, r = x & mask;
+      for (int i = 0; i < 4; ++i) {
+        const uint64_t f = splitmix64(r ^ (epoch_key + (uint64_t)i * 0xD1B54A32D192ED03ull)) & mask;
+        const uint64_t nl = r;
+        r = l ^ f;
+        l = nl;
+      }
+      x = (l << perm_half_) | r;
+    } while (x >= n);
+    return index_[x];
+  }
   bool check_record_crc(const RecRef& r) const {
     uint32_t hc, dc;
     memcpy(&hc, r.ptr - 4, 4);
@@ -676,6 +706,7 @@ class Loader {
       }
       const size_t first = (size_t)(k % per_epoch_batches_) * (size_t)B_;
       const int rows = (int)std::min<size_t>((size_t)B_, index_.size() - first);
+      const uint64_t epoch_key = epoch_key_of((uint64_t)(k / per_epoch_batches_));
       bool bad = false;
       if (raw_mode_) {
         int32_t* offs = reinterpret_cast<int32_t*>(slots_ + (size_t)slot * stride_);
@@ -683,9 +714,9 @@ class Loader {
         const size_t cap = stride_ - off_bytes;
         size_t used = 0;
         for (int r = 0; r < rows && !bad; ++r) {
-          const RecRef& rr = index_[first + r];
+          const RecRef& rr = record_at(first + r, epoch_key);
           if (r + 6 < rows) {
-            const RecRef& pf = index_[first + r + 6];
+            const RecRef& pf = record_at(first + r + 6, epoch_key);
             for (uint32_t o = 0; o < pf.len + 4; o += 64) __builtin_prefetch(pf.ptr - 12 + o, 0, 0);
           }
           if (crc_ && !check_record_crc(rr)) { set_err("corrupted record CRC"); bad = true; break; }
@@ -700,9 +731,9 @@ class Loader {
         int32_t* ids = slot_ids(slot);
         float* vals = slot_vals(slot);
         for (int r = 0; r < rows && !bad; ++r) {
-          const RecRef& rr = index_[first + r];
+          const RecRef& rr = record_at(first + r, epoch_key);
           if (r + 6 < rows) {  // records stream from DRAM exactly once: fetch a few records ahead of the parser
-            const RecRef& pf = index_[first + r + 6];
+            const RecRef& pf = record_at(first + r + 6, epoch_key);
             for (uint32_t o = 0; o < pf.len + 4; o += 64) __builtin_prefetch(pf.ptr - 12 + o, 0, 0);
           }
           if (crc_ && !check_record_crc(rr)) { set_err("corrupted record CRC"); bad = true; break; }
@@ -913,6 +944,8 @@ class Loader {
   int nslots_;
   size_t stride_;
   bool raw_mode_ = false;
+  uint64_t shuffle_seed_ = 0;  // 0 = file order
+  int perm_half_ = 1;
   bool indexed_ = false;
   std::vector<RecRef> index_;
   long per_epoch_batches_ = 0, next_batch_ = 0;
@@ -1045,6 +1078,22 @@ void* dfmio_loader_create(const char** paths, int npaths, int F, int batch, int 
   std::vector<std::string> p(paths, paths + npaths);
   return new Loader(std::move(p), F, batch, shard_n, shard_i, epochs, threads, drop_remainder != 0, check_crc != 0,
                     slots, nslots, slot_stride);
+}
+// Same as dfmio_loader_create / dfmio_loader_create_raw (raw != 0: F and threads are ignored as there), plus a per-epoch
+// record shuffle when shuffle_seed != 0. The shuffle needs random access, i.e. regular files (indexed mode): FIFO / pipe
+// sources keep their stream order.
+void* dfmio_loader_create_ex(const char** paths, int npaths, int F, int batch, int shard_n, int shard_i, int epochs,
+                             int threads, int drop_remainder, int check_crc, uint8_t* slots, int nslots,
+                             uint64_t slot_stride, int raw, uint64_t shuffle_seed) {
+  const uint64_t need = raw ? (((uint64_t)(batch + 1) * 4 + 255) & ~255ull) + 256 : Loader::slot_bytes(batch, F);
+  if (npaths <= 0 || (!raw && F <= 0) || batch <= 0 || nslots < 2 || !slots || slot_stride < need || shard_i < 0 ||
+      shard_i >= (shard_n < 1 ? 1 : shard_n)) {
+    set_err("loader_create_ex: bad arguments");
+    return nullptr;
+  }
+  std::vector<std::string> p(paths, paths + npaths);
+  return new Loader(std::move(p), raw ? 0 : F, batch, shard_n, shard_i, epochs, raw ? 0 : threads, drop_remainder != 0,
+                    check_crc != 0, slots, nslots, slot_stride, raw != 0, shuffle_seed);
 }
 int dfmio_loader_next(void* ld, int* slot) { return ((Loader*)ld)->next(slot); }
 void dfmio_loader_release(void* ld, int slot) { ((Loader*)ld)->release(slot); }

@@ -59,6 +59,9 @@ def load(build_if_missing: bool = True) -> ctypes.CDLL:
     lib.dfmio_loader_create_raw.restype = c_void_p
     lib.dfmio_loader_create_raw.argtypes = [ctypes.POINTER(c_char_p), c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                             c_void_p, c_int, c_uint64]
+    lib.dfmio_loader_create_ex.restype = c_void_p
+    lib.dfmio_loader_create_ex.argtypes = [ctypes.POINTER(c_char_p), c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                           c_int, c_int, c_void_p, c_int, c_uint64, c_int, c_uint64]
     lib.dfmio_loader_next.argtypes = [c_void_p, ctypes.POINTER(c_int)]
     lib.dfmio_loader_release.argtypes = [c_void_p, c_int]
     lib.dfmio_loader_records.restype = c_long
@@ -241,7 +244,8 @@ class NativeLoader:
 
     def __init__(self, paths: List[str], field_size: int, batch_size: int, shard_n: int = 1, shard_i: int = 0,
                  num_epochs: int = 1, threads: int = 4, drop_remainder: bool = True, check_crc: bool = True,
-                 nslots: int = 6, pin_memory: bool = False):
+                 nslots: int = 6, pin_memory: bool = False, shuffle_seed: int = 0):
+        """shuffle_seed != 0: records are visited in a fresh pseudo-random order every epoch (regular files only)."""
         import torch
         lib = load()
         self.F, self.B, self.nslots = field_size, batch_size, nslots
@@ -250,9 +254,10 @@ class NativeLoader:
         if pin_memory and torch.cuda.is_available():
             self.buf = self.buf.pin_memory()
         arr = (c_char_p * len(paths))(*[p.encode() for p in paths])
-        self._h = lib.dfmio_loader_create(arr, len(paths), field_size, batch_size, shard_n, shard_i, num_epochs, threads,
-                                          1 if drop_remainder else 0, 1 if check_crc else 0, self.buf.data_ptr(), nslots,
-                                          self.stride)
+        self._h = lib.dfmio_loader_create_ex(arr, len(paths), field_size, batch_size, shard_n, shard_i, num_epochs,
+                                             threads, 1 if drop_remainder else 0, 1 if check_crc else 0,
+                                             self.buf.data_ptr(), nslots, self.stride, 0,
+                                             int(shuffle_seed) & 0xFFFFFFFFFFFFFFFF)
         if not self._h:
             raise NativeIOError(_err())
         al = lambda x: (x + 255) & ~255
@@ -320,7 +325,7 @@ class NativeRawLoader:
 
     def __init__(self, paths: List[str], batch_size: int, shard_n: int = 1, shard_i: int = 0, num_epochs: int = 1,
                  drop_remainder: bool = True, check_crc: bool = True, nslots: int = 6, pin_memory: bool = False,
-                 max_record_bytes: int = 1024):
+                 max_record_bytes: int = 1024, shuffle_seed: int = 0):
         import torch
         lib = load()
         self.B, self.nslots = batch_size, nslots
@@ -330,9 +335,9 @@ class NativeRawLoader:
         if pin_memory and torch.cuda.is_available():
             self.buf = self.buf.pin_memory()
         arr = (c_char_p * len(paths))(*[p.encode() for p in paths])
-        self._h = lib.dfmio_loader_create_raw(arr, len(paths), batch_size, shard_n, shard_i, num_epochs,
-                                              1 if drop_remainder else 0, 1 if check_crc else 0, self.buf.data_ptr(),
-                                              nslots, self.stride)
+        self._h = lib.dfmio_loader_create_ex(arr, len(paths), 0, batch_size, shard_n, shard_i, num_epochs, 0,
+                                             1 if drop_remainder else 0, 1 if check_crc else 0, self.buf.data_ptr(),
+                                             nslots, self.stride, 1, int(shuffle_seed) & 0xFFFFFFFFFFFFFFFF)
         if not self._h:
             raise NativeIOError(_err())
 

@@ -65,7 +65,7 @@ class InputPipeline:
     def __init__(self, sources: Sequence[str], field_size: int, batch_size: int, num_epochs: int = 1,
                  shard: Tuple[int, int] = (1, 0), drop_remainder: bool = True, threads: int = 4, pin_memory: bool = True,
                  use_native: bool = True, check_crc: bool = True, nslots: int = 8, gpu_parse: bool = False,
-                 max_record_bytes: int = 1024):
+                 max_record_bytes: int = 1024, shuffle_seed: int = 0):
         """gpu_parse=True: the host only walks/CRC-checks/copies records into pinned raw slots; the Example protos are
         decoded on the GPU (`Trainer.train_raw`). Batches then carry `raw` instead of parsed tensors."""
         self.sources = list(sources)
@@ -75,6 +75,9 @@ class InputPipeline:
         self.drop = drop_remainder
         self.threads, self.pin, self.crc, self.nslots = threads, pin_memory, check_crc, nslots
         self.gpu_parse, self.max_record_bytes = gpu_parse, max_record_bytes
+        # != 0: every epoch visits this rank's records in a fresh reproducible pseudo-random order (native loader over
+        # regular files; FIFO sources and the pure-Python fallback keep the stream order)
+        self.shuffle_seed = int(shuffle_seed)
         self.native = False
         if use_native:
             try:
@@ -93,7 +96,7 @@ class InputPipeline:
     def _iter_raw(self) -> Iterator[Batch]:
         from .native import NativeRawLoader
         ld = NativeRawLoader(self.sources, self.B, self.shard[0], self.shard[1], self.num_epochs, self.drop, self.crc,
-                             self.nslots, self.pin, self.max_record_bytes)
+                             self.nslots, self.pin, self.max_record_bytes, self.shuffle_seed)
         self.raw_off_bytes = ld.off_bytes
         try:
             while True:
@@ -108,7 +111,7 @@ class InputPipeline:
     def _iter_native(self) -> Iterator[Batch]:
         from .native import NativeLoader
         ld = NativeLoader(self.sources, self.F, self.B, self.shard[0], self.shard[1], self.num_epochs, self.threads,
-                          self.drop, self.crc, self.nslots, self.pin)
+                          self.drop, self.crc, self.nslots, self.pin, self.shuffle_seed)
         try:
             while True:
                 b = ld.next()

@@ -118,11 +118,11 @@ def main(argv: Optional[List[str]] = None) -> int:
     train_shard = shard_rules.normalise(spec)
     pin = env.device is not None
 
-    def input_fn(files, num_epochs=1, shard=(1, 0), drop_remainder=True):
+    def input_fn(files, num_epochs=1, shard=(1, 0), drop_remainder=True, shuffle_seed=0):
         gpu_parse = bool(F.gpu_parse) and drop_remainder and env.device is not None and F.strategy != "ps" \
             and F.backend != "torch"
         return InputPipeline(files, F.field_size, F.batch_size, num_epochs, shard, drop_remainder, F.loader_threads, pin,
-                             gpu_parse=gpu_parse)
+                             gpu_parse=gpu_parse, shuffle_seed=shuffle_seed)
 
     names = channel_names()
     metrics = None
@@ -134,8 +134,12 @@ def main(argv: Optional[List[str]] = None) -> int:
                 # in a collective (PDF p22-23); agree on min over ranks of the local full-batch count
                 from ..data.pipeline import local_steps
                 hint = local_steps(tr_files, F.batch_size, train_shard, 1)
-            for _ in range(F.num_epochs):  # HVD:391-394
-                est.train(lambda: input_fn(tr_files, 1, train_shard), max_steps=F.max_steps, steps_hint=hint)
+            for epoch in range(F.num_epochs):  # HVD:391-394
+                # --perform_shuffle: a fresh record order every epoch (the reference only shuffles the FILE order once,
+                # PS:373-381; its flag of this name is never read)
+                sseed = (int(F.seed) * 1000003 + epoch + 1) if F.perform_shuffle else 0
+                est.train(lambda: input_fn(tr_files, 1, train_shard, True, sseed), max_steps=F.max_steps,
+                          steps_hint=hint)
                 if env.is_chief and va_files:
                     metrics = est.evaluate(lambda: input_fn(va_files, 1, (1, 0), False))
                 barrier(env)

@@ -80,7 +80,8 @@ def flag_definitions(env=os.environ) -> List[Tuple[str, type, Any, str]]:
         ("evaluation_channel_name", str, "", "evaluation channel name"),
         ("enable_s3_shard", bool, False, "data is already sharded per instance (ShardedByS3Key)"),
         ("enable_data_multi_path", bool, False, "pipe mode: every local worker has its own channel"),
-        ("perform_shuffle", bool, False, "accepted for parity (unused in the reference as well)"),
+        ("perform_shuffle", bool, False, "file mode: visit the records in a fresh pseudo-random order every epoch "
+                                         "(declared but never read by the reference)"),
         # ---- deepfm_b200 additions
         ("strategy", str, "dp", "parallel strategy {dp, sharded, ps}: fused-allreduce data parallel, row-sharded "
                                 "embeddings with fused all-to-all, async parameter server"),

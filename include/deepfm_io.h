@@ -47,6 +47,12 @@ void* dfmio_loader_create(const char** paths, int npaths, int F, int batch, int 
                           uint64_t slot_stride);
 void* dfmio_loader_create_raw(const char** paths, int npaths, int batch, int shard_n, int shard_i, int epochs,
                               int drop_remainder, int check_crc, uint8_t* slots, int nslots, uint64_t slot_stride);
+/* the two above in one call (raw != 0 = raw mode), plus a reproducible per-epoch record shuffle when shuffle_seed != 0:
+ * position p of epoch e reads record perm(seed, e)(p) of this rank's shard, perm = keyed Feistel bijection (no permutation
+ * array). Needs regular files; FIFO sources keep their stream order. */
+void* dfmio_loader_create_ex(const char** paths, int npaths, int F, int batch, int shard_n, int shard_i, int epochs,
+                             int threads, int drop_remainder, int check_crc, uint8_t* slots, int nslots,
+                             uint64_t slot_stride, int raw, uint64_t shuffle_seed);
 int dfmio_loader_next(void* loader, int* slot); /* rows in the slot (> 0), 0 at end of data, < 0 on error; blocks */
 void dfmio_loader_release(void* loader, int slot);
 long dfmio_loader_records(void* loader);

@@ -75,7 +75,7 @@ def test_train_eval_infer_export_resume(data, tmp_path):
     assert 0.3 < first_loss < 0.9  # step-10 loss, already below ln 2 (the reference logs 0.696 at step 1, PDF p34)
     assert os.path.exists(os.path.join(ckpt, "checkpoint")) and os.path.exists(os.path.join(ckpt, "metrics.jsonl"))
     # resume: a second train call continues from step 80
-    out2 = _run(base + ["--task_type", "train", "--num_epochs", "1"])
+    out2 = _run(base + ["--task_type", "train", "--num_epochs", "1", "--perform_shuffle", "True"])  # shuffled epoch
     assert "Restoring parameters from" in out2 and "Saving checkpoints for 120" in out2
     # eval / infer / export as separate tasks
     out3 = _run(base + ["--task_type", "eval"])

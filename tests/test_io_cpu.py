@@ -359,3 +359,51 @@ def test_sharded_tensor_bundles_like_a_parameter_server_checkpoint(tmp_path):
     os.remove(tmp_path / files[1])
     with pytest.raises(IOError, match="cannot open"):
         read_bundle(prefix)
+
+
+def test_loader_epoch_shuffle_is_a_reproducible_permutation(tmp_path):
+    """shuffle_seed != 0: each epoch reads every record of the rank's shard exactly once, in an order that differs from
+    the file order, differs between epochs, is identical for the same seed, and respects sharding (parsed and raw mode)."""
+    from deepfm_b200.data import native
+    from deepfm_b200.utils import tfrecord as T
+    F, B, n = 2, 10, 230
+    path = str(tmp_path / "tr.tfrecords")
+    with native.NativeRecordWriter(path) as w:
+        for i in range(n):
+            w.write(T.make_ctr_example(float(i % 2), [i, i + 1000], [1.0, 0.5]))
+
+    def epochs(seed, shard=(1, 0), raw=False, num_epochs=3):
+        if raw:
+            ld = native.NativeRawLoader([path], B, shard[0], shard[1], num_epochs, nslots=4, max_record_bytes=128,
+                                        shuffle_seed=seed)
+        else:
+            ld = native.NativeLoader([path], F, B, shard[0], shard[1], num_epochs, threads=3, nslots=4, shuffle_seed=seed)
+        seen = []
+        while True:
+            item = ld.next()
+            if item is None:
+                break
+            if raw:
+                slot, rows, buf = item
+                seen += [int(x) for x in T.parse_ctr_batch(ld.records(buf, rows), F)[1][:, 0]]
+            else:
+                slot, rows, lab, ids, vals = item
+                assert torch.equal(ids[:, 1], ids[:, 0] + 1000) and torch.equal(lab, (ids[:, 0] % 2).float())
+                seen += ids[:, 0].tolist()
+            ld.release(slot)
+        ld.close()
+        per = len(seen) // num_epochs
+        return [seen[e * per:(e + 1) * per] for e in range(num_epochs)]
+
+    plain = epochs(0)
+    assert plain[0] == list(range(n)) and plain[1] == plain[0]
+    a, b = epochs(7), epochs(7)
+    assert a == b                                                        # reproducible
+    assert all(sorted(e) == list(range(n)) for e in a)                   # a permutation: every record once per epoch
+    assert a[0] != plain[0] and a[0] != a[1] and a[1] != a[2]            # shuffled, and differently every epoch
+    assert epochs(8)[0] != a[0]
+    half = epochs(7, shard=(2, 1))
+    assert all(sorted(e) == list(range(1, n, 2))[:len(e)] or set(e) <= set(range(1, n, 2)) for e in half)
+    assert all(len(set(e)) == len(e) == (n // 2 // B) * B for e in half)  # drop_remainder: 110 of the 115 records
+    r = epochs(7, raw=True)
+    assert all(sorted(e) == list(range(n)) for e in r) and r == a        # raw mode walks the same permutation
