@@ -153,3 +153,22 @@ def test_tensorboard_event_files_roundtrip_and_estimator_layout(tmp_path):
     assert [e[1] for e in train] == [2, 4] and {t for e in train for t, _ in e[3]} == {"loss", "global_step/sec", "examples/sec"}
     (e,) = [e for e in read_events(eval_file) if e[3]]
     assert e[1] == 4 and abs(dict(e[3])["auc"] - 0.71) < 1e-6
+
+
+def test_inspect_tfrecords_reports_schema_problems(tmp_path):
+    from deepfm_b200.data.synthetic import write_synthetic_tfrecords
+    from deepfm_b200.utils.inspect_tfrecords import main
+    paths = write_synthetic_tfrecords(str(tmp_path), "tr", 2, 300, 5, 1000, seed=0)
+    out = io.StringIO()
+    assert main(paths + ["--field_size", "5", "--feature_size", "1000"], out=out) == 0
+    text = out.getvalue()
+    assert "records            600" in text and "ids_out_of_range   0" in text
+    out = io.StringIO()
+    assert main(paths + ["--field_size", "5", "--feature_size", "3"], out=out) == 1 and "outside [0, 3)" in out.getvalue()
+    out = io.StringIO()
+    assert main(paths + ["--field_size", "7"], out=out) == 1 and "FAILED" in out.getvalue()      # wrong schema
+    blob = bytearray(open(paths[0], "rb").read())
+    blob[40] ^= 0xFF
+    open(paths[0], "wb").write(bytes(blob))
+    out = io.StringIO()
+    assert main(paths + ["--field_size", "5"], out=out) == 1 and "FAILED" in out.getvalue()      # corrupted record
