@@ -45,6 +45,8 @@ def parse_args():
                     help="dp = BASELINE config 2 (headline); sharded = config 3 (use --feature_size 33554432 "
                          "--embedding_size 64); ps = config 4 (async PS, use --batch_size 8192 for the 64K global batch)")
     ap.add_argument("--l2_reg", type=float, default=1e-4)
+    ap.add_argument("--proxy_graph", action="store_true",
+                    help="--impl proxy only: capture the proxy step in a CUDA graph (experimental, see proxy_baseline.py)")
     return ap.parse_args()
 
 
@@ -133,6 +135,8 @@ def main():
     # reference scales LR by world size (HVD:149)
     opt = TF1Optimizer(a.optimizer, 5e-4 * world)
     backend = "proxy" if a.impl == "proxy" else "fused"
+    if a.proxy_graph:
+        os.environ["DFM_PROXY_GRAPH"] = "1"
     if a.strategy == "ps":
         from deepfm_b200.parallel.dist import DistEnv
         from deepfm_b200.parallel.ps import AsyncPSTrainer
@@ -219,7 +223,7 @@ def main():
             "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic Criteo-shaped (random-init weights)",
-            "impl": a.impl,
+            "impl": a.impl + ("+cudagraph" if (a.impl == "proxy" and a.proxy_graph) else ""),
             "config": {"model": "DeepFM field39 feat117581 emb%d mlp%s %s" % (a.embedding_size, a.deep_layers, a.optimizer),
                        "global_batch": gb, "per_gpu_batch": B, "seq_len": a.field_size,
                        "parallelism": ("dp%d" % world) if a.strategy == "dp" else ("%s%d" % (a.strategy, world)),

@@ -53,15 +53,24 @@ class _Net(nn.Module):
 
 class ProxyDeepFM:
     def __init__(self, cfg: DeepFMConfig, batch_size: int, optimizer, seed: int, device, world_size: int = 1,
-                 rank: int = 0):
+                 rank: int = 0, use_graph: bool = False):
+        """use_graph (or DFM_PROXY_GRAPH=1; `bench.py --impl proxy --proxy_graph`): capture the whole proxy step -
+        forward, backward, NCCL all-reduce, optimizer - in one CUDA graph, the stock PyTorch recipe. That removes the
+        eager launch overhead and is the closer stand-in for a TF-1 graph-mode step. EXPERIMENTAL: written after this
+        round's GPU budget was spent, not yet run on a GPU; the default (eager) proxy is the one every published ratio
+        uses. Adam and SGD only (the optimizers torch can capture)."""
+        import os
         self.cfg, self.B, self.dev = cfg, batch_size, device
+        self._use_graph = bool(use_graph or os.environ.get("DFM_PROXY_GRAPH") == "1") and optimizer.name in ("Adam", "GD",
+                                                                                                          "Momentum")
+        self._graph = None
         self.world, self.rank = world_size, rank
         torch.manual_seed(seed + rank)
         self.net = _Net(cfg, init_params(cfg, seed)).to(device)
         name = optimizer.name
         ps = list(self.net.parameters())
         if name == "Adam":
-            self.optim = torch.optim.Adam(ps, lr=optimizer.lr, eps=1e-8)
+            self.optim = torch.optim.Adam(ps, lr=optimizer.lr, eps=1e-8, capturable=self._use_graph)
         elif name == "Adagrad":
             self.optim = torch.optim.Adagrad(ps, lr=optimizer.lr, initial_accumulator_value=1e-8, eps=0.0)
         elif name == "Momentum":
@@ -73,9 +82,51 @@ class ProxyDeepFM:
         self._step = 0
         self.scalars = torch.zeros(2, device=device)
 
-    def train_step(self, ids, vals, labels, slot_idx: int = 0):
-        ids = ids.long()
+    def _capture(self):
+        """Whole-network capture as in the PyTorch CUDA-graphs notes: warm up on a side stream (on a state snapshot that
+        is restored afterwards), then record one step over static input buffers."""
+        F_ = self.cfg.field_size
+        self._sids = torch.zeros(self.B, F_, dtype=torch.long, device=self.dev)
+        self._svals = torch.zeros(self.B, F_, device=self.dev)
+        self._slabels = torch.zeros(self.B, device=self.dev)
+        snap = {k: v.clone() for k, v in self.net.state_dict().items()}
+        side = torch.cuda.Stream(device=self.dev)
+        side.wait_stream(torch.cuda.current_stream(self.dev))
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                self._eager_step(self._sids, self._svals, self._slabels)
+        torch.cuda.current_stream(self.dev).wait_stream(side)
+        torch.cuda.synchronize(self.dev)
+        self.net.load_state_dict(snap)
+        for st in self.optim.state.values():  # moments back to zero, step counters back to the start
+            for k, v in st.items():
+                if torch.is_tensor(v):
+                    v.zero_()
         self.optim.zero_grad(set_to_none=True)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._graph_loss = self._eager_step(self._sids, self._svals, self._slabels, zero=False)
+        self._graph = g
+
+    def train_step(self, ids, vals, labels, slot_idx: int = 0):
+        if self._use_graph:
+            if self._graph is None:
+                self._capture()
+            self._sids.copy_(ids)
+            self._svals.copy_(vals)
+            self._slabels.copy_(labels.reshape(-1))
+            self._graph.replay()
+            self._loss = self._graph_loss
+            self._step += 1
+            return self._loss
+        loss = self._eager_step(ids, vals, labels)
+        self._step += 1
+        return loss
+
+    def _eager_step(self, ids, vals, labels, zero: bool = True):
+        ids = ids.long()
+        if zero:
+            self.optim.zero_grad(set_to_none=True)
         y = self.net(ids, vals, True)
         data = F.binary_cross_entropy_with_logits(y, labels.reshape(-1))
         loss = data + 0.5 * self.cfg.l2_reg * (self.net.fm_w.pow(2).sum() + self.net.fm_v.pow(2).sum())
@@ -89,7 +140,6 @@ class ProxyDeepFM:
                 g.copy_(f)
         self.optim.step()
         self._loss = loss.detach()
-        self._step += 1
         return self._loss
 
     def last_loss(self):
