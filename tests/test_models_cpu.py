@@ -135,3 +135,28 @@ def test_torch_backend_global_batch_scaling_matches_concat():
             tot = tot + cfg.l2_reg * p[k]
         want = (p[k] - full.params[k]) / 0.1
         assert torch.allclose(tot, want, rtol=1e-4, atol=1e-6), k
+
+
+def test_proxy_baseline_is_the_same_model():
+    """The NCCL + cuBLAS proxy that stands in for the reference in bench.py must compute the reference's model: its logits
+    equal the oracle's on the same parameters, and its first GD step equals the oracle-gradient step (exact L2 mode)."""
+    from deepfm_b200.models import DeepFMConfig, init_params
+    from deepfm_b200.models.oracle import oracle_forward, oracle_grads
+    from deepfm_b200.optim import TF1Optimizer
+    from deepfm_b200.parallel.proxy_baseline import ProxyDeepFM
+    cfg = DeepFMConfig(field_size=6, feature_size=200, embedding_size=8, deep_layers=[16, 8], dropout=[1.0, 1.0], l2_reg=1e-3)
+    g = torch.Generator().manual_seed(0)
+    ids = torch.randint(0, 200, (32, 6), generator=g)
+    vals = torch.rand(32, 6, generator=g)
+    labels = (torch.rand(32, generator=g) < 0.4).float()
+    params = init_params(cfg, seed=0)
+    m = ProxyDeepFM(cfg, 32, TF1Optimizer("GD", 0.1), 0, torch.device("cpu"))
+    with torch.no_grad():
+        y = m.net(ids, vals, False)
+    assert torch.allclose(y, oracle_forward(params, cfg, ids, vals, False), rtol=1e-5, atol=1e-6)
+    ref = oracle_grads({k: v.clone() for k, v in params.items()}, cfg, ids, vals, labels, True, 0, 0, 0)
+    loss = m.train_step(ids, vals, labels)
+    assert abs(float(loss) - float(ref["loss"])) < 1e-5 and m.global_step == 1
+    assert torch.allclose(m.net.fm_v.detach(), params["fm_v"] - 0.1 * ref["grads"]["fm_v"], rtol=1e-4, atol=1e-6)
+    assert torch.allclose(m.net.mlp[0].weight.detach(), params["mlp0.weight"] - 0.1 * ref["grads"]["mlp0.weight"],
+                          rtol=1e-4, atol=1e-6)
