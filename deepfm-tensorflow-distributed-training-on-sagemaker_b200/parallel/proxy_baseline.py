@@ -1,6 +1,6 @@
 """NCCL + cuBLAS + torch.optim PROXY of the reference's Horovod trainer (2-hvd-gpu) — the baseline, never the product.
 
-The reference itself (TF 1.14/1.15 + Horovod + OpenMPI) cannot be installed offline here (DESIGN.md section 4), so the
+The reference itself (TF 1.14/1.15 + Horovod + OpenMPI) cannot be installed offline here (DESIGN.md section 7), so the
 bar is this stand-in: the same model, built from stock PyTorch ops — `F.embedding`, `nn.Linear` (cuBLAS)
 under bf16 autocast, stock dropout, `binary_cross_entropy_with_logits`, explicit whole-table L2 terms, autograd,
 `torch.optim.Adam` — one process per GPU, gradients averaged with ONE flat NCCL all-reduce per step (the analogue of
