@@ -73,7 +73,7 @@ def build_cuda(force: bool = False, verbose: bool = False) -> str:
 
 
 def build_io(force: bool = False) -> str:
-    srcs = sorted(glob.glob(os.path.join(CSRC, "io", "*.cc")))
+    srcs = sorted(f for f in glob.glob(os.path.join(CSRC, "io", "*.cc")) if not f.endswith("fuzz_main.cc"))
     hdrs = sorted(glob.glob(os.path.join(CSRC, "io", "*.h")) + glob.glob(os.path.join(INC, "*.h")))
     if not srcs:
         return ""

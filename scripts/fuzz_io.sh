@@ -1,0 +1,11 @@
+#!/bin/bash
+# Build the host IO library's sources together with csrc/io/fuzz_main.cc under AddressSanitizer + UBSan and run the
+# mutation fuzzer. Usage: scripts/fuzz_io.sh [iterations] [seed]
+set -euo pipefail
+cd "$(dirname "$0")/.."
+out=$(mktemp -d)
+trap 'rm -rf "$out"' EXIT
+g++ -O1 -g -std=c++17 -msse4.2 -pthread -fsanitize=address,undefined -fno-sanitize-recover=undefined -fno-omit-frame-pointer \
+    -Iinclude -Icsrc -o "$out/fuzz_io" csrc/io/dfm_io.cc csrc/io/tensor_bundle.cc csrc/io/host_optim.cc \
+    csrc/io/libsvm_convert.cc csrc/io/fuzz_main.cc
+ASAN_OPTIONS=detect_leaks=1:abort_on_error=1 UBSAN_OPTIONS=print_stacktrace=1 "$out/fuzz_io" "${1:-300}" "${2:-1}" "$out"
