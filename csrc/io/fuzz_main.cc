@@ -137,6 +137,33 @@ int main(int argc, char** argv) {
         file_err++;
       }
     }
+    // (2b) every 8th round, on the VALID file: many workers, several epochs, shuffle, parsed and raw mode, slots released
+    // late - the configuration a training job uses, for the thread sanitizer's benefit - and the threaded host optimizer
+    if (it % 8 == 0) {
+      write_file(rec_path, framed);
+      const char* paths[1] = {rec_path.c_str()};
+      for (int raw = 0; raw < 2; ++raw) {
+        const uint64_t stride = raw ? dfmio_loader_raw_slot_bytes(4, 512) : dfmio_loader_slot_bytes(4, F);
+        slots.assign((size_t)stride * 4, 0);
+        void* ld = dfmio_loader_create_ex(paths, 1, F, 4, 1, 0, 5, 4, 1, 1, slots.data(), 4, stride, raw, 3);
+        if (!ld) { fprintf(stderr, "stress loader: %s\n", dfmio_last_error()); return 1; }
+        int slot, rows, held[3], nheld = 0;
+        long total = 0;
+        while ((rows = dfmio_loader_next(ld, &slot)) > 0) {
+          total += rows;
+          held[nheld++] = slot;
+          if (nheld == 3) { while (nheld) dfmio_loader_release(ld, held[--nheld]); }
+        }
+        while (nheld) dfmio_loader_release(ld, held[--nheld]);
+        dfmio_loader_destroy(ld);
+        if (rows != 0 || total != 5 * (n / 4) * 4) { fprintf(stderr, "stress loader: %ld rows, rc %d\n", total, rows); return 1; }
+      }
+      std::vector<float> tab(4096 * 8, 0.5f), m(4096 * 8, 0.f), v(4096 * 8, 0.f), g(1024 * 8, 0.01f);
+      std::vector<long long> rows_idx(1024);
+      for (int i = 0; i < 1024; ++i) rows_idx[(size_t)i] = 4 * i + 1;
+      if (dfmio_sparse_opt_apply(tab.data(), m.data(), v.data(), 4096, 8, rows_idx.data(), 1024, g.data(), 0, 1e-3f, 0.9f,
+                                 0.999f, 1e-8f, 0.95f, 1e-4f, 1 + it, 4) != 0) return 1;
+    }
     // (3) checkpoint index with corruptions
     {
       write_file(bprefix + ".index", it % 4 == 0 ? index_ok : mutate(index_ok));

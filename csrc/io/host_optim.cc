@@ -30,7 +30,9 @@ struct Hyper {
 // each loop is straight-line code the compiler vectorises (vsqrtps / vdivps are IEEE-exact: results do not depend on the
 // vector width); target_clones emits an AVX2 and a baseline SSE version and picks one at load time, so the library still
 // runs on any x86-64 host it is copied to.
+#if !defined(__SANITIZE_THREAD__)  // the ifunc resolver of a multiversioned function runs before TSan's runtime is up
 __attribute__((target_clones("avx2", "default")))
+#endif
 void apply_span(const Hyper& h, float* __restrict__ w, float* __restrict__ s0, float* __restrict__ s1,
                 const float* __restrict__ g, float l2, long long n) {
   switch (h.opt) {

@@ -1,6 +1,7 @@
 #!/bin/bash
 # Build the host IO library's sources together with csrc/io/fuzz_main.cc under AddressSanitizer + UBSan and run the
-# mutation fuzzer. Usage: scripts/fuzz_io.sh [iterations] [seed]
+# mutation fuzzer; then the same program under ThreadSanitizer (loader worker threads, converter threads, threaded host
+# optimizer) for a tenth of the iterations. Usage: scripts/fuzz_io.sh [iterations] [seed]
 set -euo pipefail
 cd "$(dirname "$0")/.."
 out=$(mktemp -d)
@@ -9,3 +10,8 @@ g++ -O1 -g -std=c++17 -msse4.2 -pthread -fsanitize=address,undefined -fno-saniti
     -Iinclude -Icsrc -o "$out/fuzz_io" csrc/io/dfm_io.cc csrc/io/tensor_bundle.cc csrc/io/host_optim.cc \
     csrc/io/libsvm_convert.cc csrc/io/fuzz_main.cc
 ASAN_OPTIONS=detect_leaks=1:abort_on_error=1 UBSAN_OPTIONS=print_stacktrace=1 "$out/fuzz_io" "${1:-300}" "${2:-1}" "$out"
+if [ "${DFM_FUZZ_TSAN:-1}" = "1" ]; then
+  g++ -O1 -g -std=c++17 -msse4.2 -pthread -fsanitize=thread -Iinclude -Icsrc -o "$out/fuzz_tsan" csrc/io/dfm_io.cc \
+      csrc/io/tensor_bundle.cc csrc/io/host_optim.cc csrc/io/libsvm_convert.cc csrc/io/fuzz_main.cc
+  TSAN_OPTIONS=halt_on_error=1 "$out/fuzz_tsan" "$(( (${1:-300} + 9) / 10 ))" "${2:-1}" "$out"
+fi

@@ -409,7 +409,7 @@ def test_loader_epoch_shuffle_is_a_reproducible_permutation(tmp_path):
     assert all(sorted(e) == list(range(n)) for e in r) and r == a        # raw mode walks the same permutation
 
 
-def test_host_io_library_survives_fuzzing_under_asan_and_ubsan():
+def test_host_io_library_survives_fuzzing_under_asan_ubsan_and_tsan():
     """SURVEY 5.2 (sanitizers): the parsers that read untrusted bytes - TFRecord framing, Example protos, checkpoint
     indexes, libsvm text - are rebuilt with AddressSanitizer + UBSan and fed corrupted inputs (scripts/fuzz_io.sh)."""
     import shutil
@@ -424,4 +424,4 @@ def test_host_io_library_survives_fuzzing_under_asan_and_ubsan():
     r = subprocess.run([os.path.join(repo, "scripts", "fuzz_io.sh"), "150", "11"], capture_output=True, text=True,
                        timeout=600)
     assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-4000:])
-    assert "fuzz_io: 150 iterations" in r.stdout
+    assert "fuzz_io: 150 iterations" in r.stdout and "fuzz_io: 15 iterations" in r.stdout  # ASan/UBSan pass, TSan pass
