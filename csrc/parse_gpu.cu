@@ -205,7 +205,9 @@ example_parse_kernel(const uint8_t* __restrict__ blob, const int* __restrict__ o
   const uint8_t* rec = staged ? stage + mis + (o - o_begin) : blob + o;
   float* v = vals + (size_t)r * F;
   int* d = ids + (size_t)r * F;
-  if (len < 0 || !parse_example_dev(rec, len, F, labels + r, d, v)) {
+  // offsets are produced by the host loader; a non-monotonic table must not steer the staged pointer outside the span
+  const bool inside = len >= 0 && o >= o_begin && o + len <= o_end;
+  if (!inside || !parse_example_dev(rec, len, F, labels + r, d, v)) {
     atomicCAS(err, 0, r + 1);
     labels[r] = 0.f;
     for (int f = 0; f < F; ++f) { d[f] = 0; v[f] = 0.f; }
