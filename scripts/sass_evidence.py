@@ -62,6 +62,27 @@ def main() -> int:
             continue
         short = re.sub(r"\(.*", "", nice).replace("void ", "").replace("dfm::", "").replace("(anonymous namespace)::", "")
         print("%-46s %s" % (short[:46], "  ".join("%s=%d" % (k, c[k]) for k, _ in GROUPS if c[k])))
+    print("```\n")
+    # ---- static resources per kernel (cuobjdump -res-usage): registers, spill stack, static shared memory
+    res = subprocess.run(["cuobjdump", "-res-usage", LIB], capture_output=True, text=True, check=True).stdout
+    rows, fn = [], None
+    for line in res.splitlines():
+        m = re.search(r"Function (\S+):", line)
+        if m:
+            fn = m.group(1)
+            continue
+        m = re.search(r"REG:(\d+) STACK:(\d+) SHARED:(\d+) LOCAL:(\d+)", line)
+        if m and fn:
+            rows.append((fn,) + tuple(int(x) for x in m.groups()))
+            fn = None
+    nice = subprocess.run(["c++filt"], input="\n".join(r[0] for r in rows), capture_output=True, text=True).stdout.splitlines()
+    print("Static resources (`cuobjdump -res-usage`; STACK > 0 = spill / local arrays, SHARED = static shared memory, the GEMMs")
+    print("add 189-200 KB of dynamic shared memory at launch):\n")
+    print("```")
+    print("%-46s %5s %6s %7s %6s" % ("kernel", "REG", "STACK", "SHARED", "LOCAL"))
+    for r, n in zip(rows, nice):
+        short = re.sub(r"\(.*", "", n).replace("void ", "").replace("dfm::", "").replace("(anonymous namespace)::", "")
+        print("%-46s %5d %6d %7d %6d" % (short[:46], r[1], r[2], r[3], r[4]))
     print("```\n\nSample lines:\n```")
     for s, lines in samples.items():
         for ln in lines:
