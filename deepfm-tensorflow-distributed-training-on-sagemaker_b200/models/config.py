@@ -40,6 +40,28 @@ class DeepFMConfig:
             raise ValueError("need one dropout keep-prob per deep layer")
         if self.l2_mode not in ("exact", "touched"):
             raise ValueError("l2_mode must be 'exact' or 'touched'")
+        if self.field_size <= 0 or self.feature_size <= 0 or self.embedding_size <= 0:
+            raise ValueError("field_size, feature_size and embedding_size must be positive (got %d, %d, %d)"
+                             % (self.field_size, self.feature_size, self.embedding_size))
+        if not self.deep_layers or min(self.deep_layers) <= 0:
+            raise ValueError("deep_layers needs at least one positive width, got %r" % (self.deep_layers,))
+        if any(not (0.0 < p <= 1.0) for p in self.dropout):
+            raise ValueError("dropout holds KEEP probabilities in (0, 1], got %r" % (self.dropout,))
+        if not (0.0 <= self.batch_norm_decay < 1.0) or self.l2_reg < 0:
+            raise ValueError("batch_norm_decay must be in [0, 1) and l2_reg >= 0")
+
+    def fused_constraints(self) -> List[str]:
+        """Why this configuration cannot run on the fused sm_100a kernels ([] = it can). The kernels move bf16 rows with
+        TMA (16-byte row strides) and embedding rows with 128-bit accesses; the torch backend has no such limits."""
+        problems = []
+        if self.embedding_size not in (4, 8, 16, 32, 64, 128):
+            problems.append("embedding_size must be one of 4, 8, 16, 32, 64, 128 (got %d)" % self.embedding_size)
+        if self.deep_input_dim % 8:
+            problems.append("field_size * embedding_size must be a multiple of 8 (got %d)" % self.deep_input_dim)
+        bad = [h for h in self.deep_layers if h % 8]
+        if bad:
+            problems.append("deep layer widths must be multiples of 8 (got %r)" % (bad,))
+        return problems
 
     @property
     def deep_input_dim(self) -> int:

@@ -62,6 +62,9 @@ class FusedDeepFM:
                  input_slots: int = 2):
         """`global_batch`/`row_offset`: under data parallelism the loss is the mean over the GLOBAL batch and the
         dropout mask of row r is that of global row row_offset+r, so DP-N is comparable to DP-1."""
+        problems = cfg.fused_constraints()
+        if problems:
+            raise ValueError("this model cannot use the fused kernels (use --backend torch): " + "; ".join(problems))
         _native.require_gpu()
         self.cfg = cfg
         self.B = int(batch_size)

@@ -160,3 +160,17 @@ def test_proxy_baseline_is_the_same_model():
     assert torch.allclose(m.net.fm_v.detach(), params["fm_v"] - 0.1 * ref["grads"]["fm_v"], rtol=1e-4, atol=1e-6)
     assert torch.allclose(m.net.mlp[0].weight.detach(), params["mlp0.weight"] - 0.1 * ref["grads"]["mlp0.weight"],
                           rtol=1e-4, atol=1e-6)
+
+
+def test_config_validation_and_fused_constraints():
+    from deepfm_b200.models import DeepFMConfig
+    ok = DeepFMConfig(field_size=39, feature_size=117581, embedding_size=32, deep_layers="400,400,400", dropout="0.5,0.5,0.5")
+    assert ok.fused_constraints() == [] and ok.deep_layers == [400, 400, 400] and ok.num_parameters() == 4700975
+    assert DeepFMConfig(deep_layers="128,64,32").fused_constraints() == []          # the notebooks' configuration
+    for bad in (dict(dropout="0.5,0.0,0.5"), dict(dropout="1.5,1,1"), dict(deep_layers=""), dict(field_size=0),
+                dict(l2_mode="lazy"), dict(deep_layers="8,8,8,8"), dict(batch_norm_decay=1.0)):
+        with pytest.raises(ValueError):
+            DeepFMConfig(**bad)
+    odd = DeepFMConfig(field_size=13, feature_size=100, embedding_size=12, deep_layers=[30, 8], dropout=[1.0, 1.0])
+    msgs = " ".join(odd.fused_constraints())
+    assert "embedding_size" in msgs and "multiples of 8" in msgs and "field_size * embedding_size" in msgs
