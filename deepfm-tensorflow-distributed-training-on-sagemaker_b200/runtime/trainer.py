@@ -48,6 +48,11 @@ class Trainer:
         self.opt = optimizer or TF1Optimizer("Adam", 5e-4)
         if backend == "auto":
             backend = "fused" if torch.cuda.is_available() else "torch"
+            why_not = cfg.fused_constraints() if backend == "fused" else []
+            if why_not:  # shapes the sm_100a kernels do not take: run the same model on stock torch ops instead
+                import sys as _sys
+                print("WARNING:deepfm_b200: --backend auto falls back to torch ops: " + "; ".join(why_not), file=_sys.stderr)
+                backend = "torch"
         self.backend = backend
         self.comm_name = "none"
         gb = batch_size * world_size
