@@ -26,7 +26,8 @@ from .export import latest_export
 class Predictor:
     def __init__(self, cfg: DeepFMConfig, params: Dict[str, torch.Tensor], max_batch: int = 4096, backend: str = "auto"):
         self.cfg, self.max_batch = cfg, max_batch
-        use_fused = backend == "fused" or (backend == "auto" and torch.cuda.is_available() and not cfg.batch_norm)
+        use_fused = backend == "fused" or (backend == "auto" and torch.cuda.is_available() and not cfg.batch_norm
+                                           and not cfg.fused_constraints())
         if use_fused:
             from ..models.fused import FusedDeepFM
             self.model = FusedDeepFM(cfg, max_batch, params=params, use_graph=False, input_slots=1)
