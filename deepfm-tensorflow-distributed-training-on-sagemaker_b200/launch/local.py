@@ -93,7 +93,13 @@ class LocalEstimator:
             if not wait:
                 self._procs = procs
                 return []
-            self.returncodes = self._supervise(procs, timeout)
+            try:
+                self.returncodes = self._supervise(procs, timeout)
+            except BaseException:  # Ctrl-C, timeout, ...: never leave workers (and their GPUs) behind
+                for p in procs:
+                    if p.poll() is None:
+                        p.kill()
+                raise
             if not any(self.returncodes):
                 return self.returncodes
             # A failed attempt is restarted like an interrupted (spot) SageMaker job: same model_dir, so the chief
