@@ -46,8 +46,53 @@ def parse_args():
                          "--embedding_size 64); ps = config 4 (async PS, use --batch_size 8192 for the 64K global batch)")
     ap.add_argument("--l2_reg", type=float, default=1e-4)
     ap.add_argument("--proxy_graph", action="store_true",
-                    help="--impl proxy only: capture the proxy step in a CUDA graph (experimental, see proxy_baseline.py)")
+                    help="--impl proxy only: capture the proxy step in a CUDA graph (see proxy_baseline.py)")
+    ap.add_argument("--no_baseline", action="store_true",
+                    help="skip the in-process baseline arm (graph-captured stock-PyTorch NCCL+cuBLAS proxy) that fills "
+                         "vs_baseline for --impl ours --strategy dp")
     return ap.parse_args()
+
+
+def time_proxy_baseline(a, cfg, world, rank, dev, gen, pool):
+    """The bar the default run is compared against (the reference itself cannot be installed): the
+    same model / config / data as a graph-captured stock-PyTorch step (cuBLAS bf16 autocast + F.embedding + fused Adam +
+    one NCCL all-reduce), same pool size, same warm-up and step counts, device-timed, max over ranks. Runs BEFORE our
+    engine is built so it sees the whole L2 (our trainer sets a persisting window)."""
+    import torch
+    import torch.distributed as dist
+    from deepfm_b200.optim import TF1Optimizer
+    from deepfm_b200.parallel.proxy_baseline import ProxyDeepFM
+    B = a.batch_size
+    out = {"what": "stock PyTorch proxy of 2-hvd-gpu: F.embedding + nn.Linear (cuBLAS, bf16 autocast) + fused Adam + "
+                   "one flat NCCL all-reduce, whole step in ONE CUDA graph", "ms_per_step": None, "value": None}
+    try:
+        m = ProxyDeepFM(cfg, B, TF1Optimizer(a.optimizer, 5e-4 * world), 1234, dev, world, rank, use_graph=True)
+        dpool = [tuple(t.to(dev) for t in gen.batch(B, i)) for i in range(pool)]
+        torch.cuda.synchronize()
+        for s in range(max(3, a.warmup)):
+            m.train_step(*dpool[s % pool])
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for s in range(a.steps):
+            m.train_step(*dpool[(a.warmup + s) % pool])
+        e1.record()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+        out.update(ms_per_step=ms / a.steps, value=B * world * a.steps / (ms / 1e3), final_loss=float(m.last_loss()),
+                   cuda_graph=bool(m._graph is not None))
+        del m, dpool
+        torch.cuda.empty_cache()
+    except Exception as e:  # the baseline must never take the measurement down with it
+        out["error"] = "%s: %s" % (type(e).__name__, str(e)[:300])
+    return out
 
 
 class ClockSampler:
@@ -137,6 +182,12 @@ def main():
     backend = "proxy" if a.impl == "proxy" else "fused"
     if a.proxy_graph:
         os.environ["DFM_PROXY_GRAPH"] = "1"
+    gen = SyntheticCTR(a.field_size, a.feature_size, seed=rank)
+    bytes_per_batch = B * a.field_size * 8 + B * 4  # int32 ids + f32 vals + f32 labels
+    pool = a.pool or max(8, int(140e6 // bytes_per_batch) + 1)
+    baseline = None
+    if a.impl == "ours" and a.strategy == "dp" and not a.no_baseline:
+        baseline = time_proxy_baseline(a, cfg, world, rank, dev, gen, pool)
     if a.strategy == "ps":
         from deepfm_b200.parallel.dist import DistEnv
         from deepfm_b200.parallel.ps import AsyncPSTrainer
@@ -148,9 +199,6 @@ def main():
                      use_graph=not a.no_graph, comm=a.comm, strategy=a.strategy)
 
     # ---- input pool: distinct batches, total bytes > L2 (126 MB) so no step re-reads a cached batch
-    bytes_per_batch = B * a.field_size * 8 + B * 4  # int32 ids + f32 vals + f32 labels
-    pool = a.pool or max(8, int(140e6 // bytes_per_batch) + 1)
-    gen = SyntheticCTR(a.field_size, a.feature_size, seed=rank)
     fused = backend == "fused" and a.strategy != "ps"
     if fused:
         from deepfm_b200.models.fused import pack_batch
@@ -222,7 +270,8 @@ def main():
         out = {
             "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "bf16", "data": "synthetic Criteo-shaped (random-init weights)",
+            "vs_baseline": (value / baseline["value"]) if (baseline and baseline.get("value")) else None,
+            "baseline": baseline, "dtype": "bf16", "data": "synthetic Criteo-shaped (random-init weights)",
             "impl": a.impl + ("+cudagraph" if (a.impl == "proxy" and a.proxy_graph) else ""),
             "config": {"model": "DeepFM field39 feat117581 emb%d mlp%s %s" % (a.embedding_size, a.deep_layers, a.optimizer),
                        "global_batch": gb, "per_gpu_batch": B, "seq_len": a.field_size,

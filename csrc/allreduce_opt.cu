@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
   if (threadIdx.x == 0) s_lr = opt_step_lr(a.h, t);
 
   // barrier A ran in the preceding 1-CTA kernel (ar_barrier_kernel): every rank's gradients are complete and visible
-  pdl_wait();
+  pdl_wait(TR_ALLREDUCE);
   __syncthreads();
   const float lr_t = s_lr;
   const int nslots = opt_num_slots(a.h.opt);

@@ -39,13 +39,61 @@ extern "C" const cudaAccessPolicyWindow* dfm_l2_window();
 
 namespace dfm {
 
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// ---- kernel timeline (trace build only: `python -m deepfm_b200.build --trace` -> libdeepfm_b200_trace.so, -DDFM_KTRACE
+// -rdc=true; scripts/step_trace.py). ncu serialises kernels, so it cannot show what overlaps what inside a step that runs
+// on three graph branches (and across GPUs); %globaltimer stamps can. Per trace id: [0] first CTA entered the kernel,
+// [1] first CTA got past griddepcontrol.wait (= every prerequisite grid has finished), [2] last CTA reached trace_end(),
+// [3] free phase stamp (max). Ids: see scripts/step_trace.py. The normal build compiles all of this away.
+enum { TR_EMB_FWD = 0, TR_FWD0 = 1, TR_LOSS = 4, TR_DGRAD0 = 5, TR_WGRAD0 = 8, TR_EMB_BWD = 11, TR_OPT = 12, TR_BITMAP = 13,
+       TR_SWEEP = 14, TR_COLSUM = 15, TR_BAR_A = 16, TR_ALLREDUCE = 17, TR_BM_XCHG = 18, TR_AR_DENSE = 20, TR_AR_ROWS = 21,
+       TR_AR_FENCE = 22, TR_OPT_DENSE = 24, TR_OPT_ROWS = 25, TR_OPT_FINAL = 26, TR_MAX = 32 };
+#ifdef DFM_KTRACE
+extern __device__ unsigned long long g_dfm_trace[4 * TR_MAX];
+__device__ __forceinline__ void trace_min(int id, int slot) {
+  if (id >= 0 && threadIdx.x == 0) atomicMin(&g_dfm_trace[4 * id + slot], global_timer_ns());
+}
+__device__ __forceinline__ void trace_max(int id, int slot) {
+  if (id >= 0 && threadIdx.x == 0) atomicMax(&g_dfm_trace[4 * id + slot], global_timer_ns());
+}
+#else
+__device__ __forceinline__ void trace_min(int, int) {}
+__device__ __forceinline__ void trace_max(int, int) {}
+#endif
+__device__ __forceinline__ void trace_end(int id) { trace_max(id, 2); }
+
 // ---- programmatic dependent launch (PDL): a kernel launched with the attribute may begin while its predecessor in the
 // stream is still running; pdl_wait() blocks until every prerequisite grid has completed and flushed, so everything
 // before it (barrier init, TMEM allocation, descriptor prefetch, index math) overlaps the predecessor's tail.
 // Without the launch attribute both instructions are no-ops. EVERY kernel launched through launch_k calls pdl_wait()
 // before touching global data, which keeps the ordering transitive along the chain.
-__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait(int trace_id = -1) {
+  trace_min(trace_id, 0);
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  trace_min(trace_id, 1);
+}
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// Kernels that run BESIDE the tcgen05 GEMMs on another graph branch (the untouched-row sweep, the bitmap kernels) ask for
+// the LARGEST shared-memory carve-out although they need ~1 KB. An SM changes its L1/shared split only when it is empty:
+// with the default preference such a kernel put its SMs into a small-carve-out configuration and every GEMM CTA (100+ KB of
+// stages) waited until those SMs had drained — measured with scripts/step_trace.py: mlp_fwd0 started 26 us late behind a
+// 148-CTA sweep. (Not applied to every kernel: gathers and epilogues lose L1 hit rate with a 28 KB L1, +10-30 % each.)
+inline void dfm_prefer_max_shared(const void* fn) {
+  constexpr int kCap = 256;
+  static const void* seen[kCap];
+  static int nseen = 0;
+  for (int i = 0; i < nseen; ++i)
+    if (seen[i] == fn) return;  // racy read of an append-only table: worst case the attribute is set twice
+  cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared);
+  cudaGetLastError();
+  if (nseen < kCap) seen[nseen++] = fn;
+}
 
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
@@ -205,11 +253,6 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, int a_mn_ma
 #ifndef DFM_FLAG_TIMEOUT_NS
 #define DFM_FLAG_TIMEOUT_NS 20000000000ull
 #endif
-__device__ __forceinline__ unsigned long long global_timer_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
 __device__ __forceinline__ void wait_flag_geq(const uint32_t* flag, uint32_t seq, int peer, int what) {
   unsigned long long t0 = 0;
   unsigned int spins = 0;

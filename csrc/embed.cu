@@ -40,7 +40,7 @@ emb_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, c
   const int sample = blockIdx.x * (kEmbThreads / 32) + (threadIdx.x >> 5);
   const int g = lane % G, fg = lane / G;
   pdl_launch_dependents();
-  pdl_wait();
+  pdl_wait(TR_EMB_FWD);
   // first kernel of a training step: also clears the step's loss accumulators (saves a memset node on the chain)
   if (blockIdx.x == 0 && threadIdx.x < n_zero) zero_scalars[threadIdx.x] = 0.f;
   if (sample >= B) return;  // warp-uniform
@@ -98,6 +98,7 @@ emb_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, c
   }
   acc = warp_sum(acc);
   if (lane == 0) yfm[sample] = acc;
+  trace_end(TR_EMB_FWD);
 }
 
 // One LANE per (field, sample) pair, pairs in field-major order, so a warp holds 32 samples of the SAME field.
@@ -119,8 +120,7 @@ emb_bwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, cons
   const int b = active ? (int)(p % B) : 0;
   int id = 0;
   float v = 0.f;
-  pdl_launch_dependents();
-  pdl_wait();
+  pdl_wait(TR_EMB_BWD);
   if (active) {
     id = __ldg(ids + (size_t)b * F + f);
     v = __ldg(vals + (size_t)b * F + f);
@@ -173,6 +173,8 @@ emb_bwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, cons
     }
   }
   // first-order weights: same aggregation on the scalar dy*val (first chunk-slice only)
+  pdl_launch_dependents();  // late: the optimizer's CTAs must not sit resident beside this kernel and the wgrad branch
+  trace_end(TR_EMB_BWD);
   if (blockIdx.y != 0) return;  // CTA-uniform
   float gw = valid ? d * v : 0.f;
   if (mask == 0xffffffffu) {

@@ -87,3 +87,38 @@ extern "C" long long dfm_set_l2_persist(void* base, unsigned long long bytes) {
   g_l2w_on = 1;
   return (long long)set_aside;
 }
+
+// ---- kernel timeline buffer (trace build only, see common.cuh). The entry points exist in both builds so the ABI is the
+// same; in the normal build dfm_trace_enabled() returns 0 and the others do nothing.
+#ifdef DFM_KTRACE
+namespace dfm { enum { kTraceWords = 4 * 32 }; __device__ unsigned long long g_dfm_trace[kTraceWords]; }
+#endif
+extern "C" int dfm_trace_enabled() {
+#ifdef DFM_KTRACE
+  return 1;
+#else
+  return 0;
+#endif
+}
+extern "C" int dfm_trace_words() { return 4 * 32; }
+// Slots [0],[1] of every id are minima (reset to ~0), [2],[3] maxima (reset to 0).
+extern "C" int dfm_trace_reset() {
+#ifdef DFM_KTRACE
+  unsigned long long h[dfm::kTraceWords];
+  for (int i = 0; i < dfm::kTraceWords; ++i) h[i] = (i & 3) < 2 ? ~0ull : 0ull;
+  if (cudaMemcpyToSymbol(dfm::g_dfm_trace, h, sizeof(h)) != cudaSuccess) { cudaGetLastError(); return 1; }
+#endif
+  return 0;
+}
+extern "C" int dfm_trace_read(unsigned long long* out) {
+#ifdef DFM_KTRACE
+  if (cudaMemcpyFromSymbol(out, dfm::g_dfm_trace, sizeof(unsigned long long) * dfm::kTraceWords) != cudaSuccess) {
+    cudaGetLastError();
+    return 1;
+  }
+  return 0;
+#else
+  (void)out;
+  return 1;
+#endif
+}

@@ -46,15 +46,28 @@ struct GemmParams {
   int ldmask;
   float mask_scale;
   int out_f32;  // EPI_BIAS_ACT only: store fp32 (pre-batch-norm activations must not be rounded to bf16)
+  int trace_id; // timeline id (trace build only; -1 = none)
+  int overwrite;  // EPI_ACCUM_F32 only: plain stores instead of red.add (needs a single K split)
+  float* colsum;  // EPI_MASK only: colsum[n] += sum over rows of the (masked, scaled) output = the bias gradient of the
+                  // layer that produced the mask (reference: BiasAddGrad); null = off
 };
 
-template <int BN>
+// Shared-memory budget per pass (the rest of the step decides it, not the GEMM itself — scripts/step_trace.py):
+//   forward  runs alone on the chain: the whole SM (~200 KB, up to 7 stages). With 20 k-blocks of 26 KB behind a ~1.2 us
+//            TMA round trip, the bytes in flight are the throughput: 4 stages made mlp_fwd0 1.3 us slower than 7.
+//   dgrad    ~124 KB   and   wgrad ~98 KB: one CTA of each fits on an SM TOGETHER. With ~200 KB each (the first version)
+//            the wgrad branch queued for whole SMs behind the dgrad chain, whose programmatic dependent launches keep the
+//            next kernel's CTAs resident while they wait: wgrad2 took 23 us beside the chain, 2.3 us alone.
+template <int EPI>
+struct GemmBudget { static constexpr int BYTES = EPI == 0 ? 200 * 1024 : (EPI == 1 ? 124 * 1024 : 98 * 1024); };
+
+template <int BN, int EPI>
 struct GemmCfg {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES_RAW = (200 * 1024) / STAGE_BYTES;
-  static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
+  static constexpr int STAGES_RAW = GemmBudget<EPI>::BYTES / STAGE_BYTES;
+  static constexpr int STAGES = STAGES_RAW > 8 ? 8 : (STAGES_RAW < 2 ? 2 : STAGES_RAW);
   static constexpr int TMEM_COLS = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + BN * 4 /*bias*/;
 };
@@ -63,7 +76,7 @@ template <int BN, bool A_MN, bool B_MN, int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const GemmParams p) {
-  using Cfg = GemmCfg<BN>;
+  using Cfg = GemmCfg<BN, EPI>;
   static_assert(BN % 16 == 0 && BN >= 16 && BN <= 256, "UMMA N for M=128 must be a multiple of 16 in [16,256]");
   static_assert(!B_MN || BN % 64 == 0, "MN-major B tiles are built from 64-wide 128B-swizzle atoms");
 
@@ -101,9 +114,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  // PDL: everything above (barrier init, descriptor prefetch, TMEM allocation) overlapped the previous kernel's tail
-  pdl_launch_dependents();
-  pdl_wait();
+  // PDL: everything above (barrier init, descriptor prefetch, TMEM allocation) overlapped the previous kernel's tail.
+  // The NEXT kernel is released late, when this CTA's accumulator is complete (see the epilogue): released at entry, its
+  // CTAs sat resident for this kernel's whole run and kept registers and thread slots from the wgrad branch.
+  pdl_wait(p.trace_id);
 
   if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer
@@ -221,6 +235,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
     mbar_wait(tmem_full_bar, 0);
     tc_fence_after();
+    pdl_launch_dependents();  // one arrival per CTA is what counts; the dependents still wait for this grid to finish
 
 #pragma unroll
     for (int k = 0; k < MYCH; ++k) {
@@ -229,8 +244,38 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       float v[16];
       tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
       const int n = n0 + c;
-      if (!row_ok || n >= p.N) continue;
+      if (n >= p.N) continue;  // warp-uniform
       const bool full16 = (n + 16 <= p.N);
+      if constexpr (EPI == EPI_MASK) {
+        if (p.colsum) {  // warp-uniform: every lane takes part in the shuffles below, rows past M contribute zeros
+          float m[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            bool keep = row_ok && (n + j < p.N);
+            if (p.mask && keep) {
+              if (fastc[k]) keep = (bits[k] >> j) & 1u;
+              else keep = __bfloat162float(p.mask[(size_t)row * p.ldmask + n + j]) != 0.f;
+            }
+            m[j] = keep ? v[j] * (p.mask ? p.mask_scale : 1.f) : 0.f;
+          }
+          // transpose-reduce over the warp's 32 rows: each step halves the columns a lane still carries
+#pragma unroll
+          for (int h = 8, o = 16; h >= 1; h >>= 1, o >>= 1) {
+            const bool upper = (lane & o) != 0;
+#pragma unroll
+            for (int j = 0; j < h; ++j) {
+              const float send = upper ? m[j] : m[j + h];
+              const float recv = __shfl_xor_sync(0xffffffffu, send, o);
+              m[j] = (upper ? m[j + h] : m[j]) + recv;
+            }
+          }
+          m[0] += __shfl_xor_sync(0xffffffffu, m[0], 1);
+          // lane bits 4..1 select the column: bit4 -> +8, bit3 -> +4, bit2 -> +2, bit1 -> +1
+          const int col = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+          if ((lane & 1) == 0 && n + col < p.N) atomicAdd(p.colsum + n + col, m[0]);
+        }
+      }
+      if (!row_ok) continue;
 
       if constexpr (EPI == EPI_BIAS_ACT) {
         if (fastc[k]) {
@@ -283,7 +328,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
       if constexpr (EPI == EPI_ACCUM_F32) {
         float* orow = reinterpret_cast<float*>(p.out) + (size_t)row * p.ldo + n;
-        if (full16 && (p.ldo % 4 == 0)) {
+        if (p.overwrite) {
+          if (full16 && (p.ldo % 4 == 0)) {
+#pragma unroll
+            for (int j = 0; j < 16; j += 4)
+              *reinterpret_cast<float4*>(orow + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (n + j < p.N) orow[j] = v[j];
+          }
+        } else if (full16 && (p.ldo % 4 == 0)) {
 #pragma unroll
           for (int j = 0; j < 16; j += 4) red_add_f32x4(orow + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
         } else {
@@ -323,6 +378,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   tc_fence_before();
   __syncthreads();
+  trace_end(p.trace_id);
   if (warp == 0) tmem_dealloc<Cfg::TMEM_COLS>(tmem_base);
 }
 
@@ -376,13 +432,15 @@ struct GemmPlan {
 
 template <int BN, bool A_MN, bool B_MN, int EPI>
 static int launch_gemm(const GemmPlan& pl, cudaStream_t stream) {
-  using Cfg = GemmCfg<BN>;
+  using Cfg = GemmCfg<BN, EPI>;
   auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, EPI>;
   static bool attr_set[64] = {false};
   int dev = 0;
   DFM_CHECK(cudaGetDevice(&dev));
   if (dev < 64 && !attr_set[dev]) {
     DFM_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    // largest carve-out, so a dgrad CTA and a wgrad CTA (two kernels, 124 + 98 KB) can share an SM
+    DFM_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
     attr_set[dev] = true;
   }
   DFM_CHECK(launch_k(kern, pl.grid, dim3(kGemmThreads), (size_t)Cfg::SMEM_BYTES, stream, pl.tmA, pl.tmB, pl.p));
@@ -429,6 +487,7 @@ int dfm_gemm_plan_create(void** plan_out, int mode, const void* A, int lda, cons
   static const int kk_cands[] = {32, 64, 80, 96, 128, 256};
   static const int mn_cands[] = {64, 128, 256};
   pl->bn = mode == 0 ? pick_bn(N, kk_cands, 6, m_tiles) : pick_bn(N, mn_cands, 3, m_tiles, mode == 2);
+  if (mode == 2 && split_k == 1) pl->bn = 64;  // one K split: narrow tiles are the only source of CTAs
   int rc;
   if (mode == 0) {  // A [M,K] K-major, B [N,K] K-major
     rc = make_tmap(&pl->tmA, A, M, K, lda, BM);
@@ -465,6 +524,9 @@ int dfm_gemm_plan_create(void** plan_out, int mode, const void* A, int lda, cons
   p.step_ptr = step_ptr;
   p.mask = reinterpret_cast<const __nv_bfloat16*>(mask); p.ldmask = ldmask; p.mask_scale = mask_scale;
   p.out_f32 = 0;
+  p.trace_id = -1;
+  p.colsum = nullptr;
+  p.overwrite = 0;
   pl->grid = dim3(m_tiles, ceil_div(N, pl->bn), splits);
   *plan_out = pl;
   return DFM_OK;
@@ -481,6 +543,31 @@ int dfm_gemm_plan_set_out_f32(void* plan, int on) {
   GemmPlan* pl = reinterpret_cast<GemmPlan*>(plan);
   DFM_REQUIRE(pl->mode == 0, "out_f32 applies to forward plans only");
   pl->p.out_f32 = on ? 1 : 0;
+  return DFM_OK;
+}
+
+// wgrad plans created with split_k = 1: out = A^T B with plain stores instead of out += with red.add. In the training
+// step the split-K atomics of three wgrads (~1.2 M vector reds) queued in L2 beside emb_bwd's and delayed every kernel
+// boundary after them (scripts/step_trace.py); one split per tile needs none and leaves most SMs to the dgrad chain.
+int dfm_gemm_plan_set_overwrite(void* plan, int on) {
+  GemmPlan* pl = reinterpret_cast<GemmPlan*>(plan);
+  DFM_REQUIRE(pl->mode == 2, "overwrite applies to wgrad plans only");
+  DFM_REQUIRE(!on || pl->grid.z == 1, "overwrite needs a single K split (create the plan with split_k = 1)");
+  pl->p.overwrite = on ? 1 : 0;
+  return DFM_OK;
+}
+
+// dgrad plans: also accumulate the column sums of the output (= bias gradient of the layer below) into colsum[N] (fp32).
+int dfm_gemm_plan_set_colsum(void* plan, float* colsum) {
+  GemmPlan* pl = reinterpret_cast<GemmPlan*>(plan);
+  DFM_REQUIRE(pl->mode == 1, "colsum applies to dgrad plans only");
+  pl->p.colsum = colsum;
+  return DFM_OK;
+}
+
+// Timeline id of this plan's launches (trace build, scripts/step_trace.py); ignored by the normal build.
+int dfm_gemm_plan_set_trace_id(void* plan, int id) {
+  reinterpret_cast<GemmPlan*>(plan)->p.trace_id = id;
   return DFM_OK;
 }
 

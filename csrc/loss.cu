@@ -24,13 +24,23 @@ logit_loss_kernel(const __nv_bfloat16* __restrict__ x, int ldx, int H, const flo
                   const float* __restrict__ labels, int B, float inv_batch, float mask_scale, int train,
                   float* __restrict__ prob, float* __restrict__ logit, float* __restrict__ dy,
                   __nv_bfloat16* __restrict__ dz, int lddz, float* __restrict__ loss_sum,
-                  float* __restrict__ g_b_out, float* __restrict__ g_fm_bias) {
+                  float* __restrict__ g_b_out, float* __restrict__ g_fm_bias, float* __restrict__ g_b_top,
+                  float* __restrict__ g_w_out) {
   __shared__ float s_scalar[2];  // loss, sum dy
+  // optional column accumulators (train mode, both pointers given): s_col[0][j] = sum_b dZ[b,j] (bias gradient of the
+  // last hidden layer), s_col[1][j] = sum_b dy[b] x[b,j] (gradient of deep_out.weight). One shared-memory atomic per
+  // element here replaces two colsum_bf16 launches that re-read dZ and X from global memory.
+  extern __shared__ float s_col[];  // [kLossWarps][2][H]: every warp owns a row pair, every lane its columns: no atomics
+  const bool cols = train && g_b_top != nullptr && g_w_out != nullptr;
   if (threadIdx.x < 2) s_scalar[threadIdx.x] = 0.f;
+  if (cols)
+    for (int j = threadIdx.x; j < 2 * H * kLossWarps; j += kLossThreads) s_col[j] = 0.f;
   pdl_launch_dependents();
-  pdl_wait();
+  pdl_wait(TR_LOSS);
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* c0 = s_col + (size_t)warp * 2 * H;  // colsum(dZ) partial of this warp
+  float* c1 = c0 + H;                        // X^T dy partial of this warp
   const float bias = __ldg(b_out) + __ldg(fm_bias);
   float loss_acc = 0.f, dy_acc = 0.f;
   for (int b = blockIdx.x * kLossWarps + warp; b < B; b += gridDim.x * kLossWarps) {
@@ -65,9 +75,15 @@ logit_loss_kernel(const __nv_bfloat16* __restrict__ x, int ldx, int H, const flo
         const float z0 = (u & 0x7FFFu) ? d * __ldg(w_out + j) * mask_scale : 0.f;
         const float z1 = (u & 0x7FFF0000u) ? d * __ldg(w_out + j + 1) * mask_scale : 0.f;
         *reinterpret_cast<uint32_t*>(dzr + j) = pack_bf16x2(z0, z1);
+        if (cols) {
+          c0[j] += z0; c0[j + 1] += z1;
+          c1[j] += d * bf16_lo(u); c1[j + 1] += d * bf16_hi(u);
+        }
       } else {
         const float x0 = __bfloat162float(xr[j]);
-        dzr[j] = __float2bfloat16(x0 != 0.f ? d * __ldg(w_out + j) * mask_scale : 0.f);
+        const float z0 = x0 != 0.f ? d * __ldg(w_out + j) * mask_scale : 0.f;
+        dzr[j] = __float2bfloat16(z0);
+        if (cols) { c0[j] += z0; c1[j] += d * x0; }
       }
     }
   }
@@ -84,6 +100,15 @@ logit_loss_kernel(const __nv_bfloat16* __restrict__ x, int ldx, int H, const flo
       atomicAdd(g_fm_bias, s_scalar[1]);
     }
   }
+  if (cols)
+    for (int j = threadIdx.x; j < H; j += kLossThreads) {
+      float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+      for (int w = 0; w < kLossWarps; ++w) { a0 += s_col[(size_t)w * 2 * H + j]; a1 += s_col[(size_t)w * 2 * H + H + j]; }
+      if (a0 != 0.f) atomicAdd(g_b_top + j, a0);
+      if (a1 != 0.f) atomicAdd(g_w_out + j, a1);
+    }
+  trace_end(TR_LOSS);
 }
 
 // Weighted column sums of a bf16 [B,H] matrix: out[j] += sum_b a[b,j] * (w ? w[b] : 1).
@@ -95,7 +120,7 @@ __global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* _
   __shared__ float s_part[8][64];
   const int lane = threadIdx.x & 31, ty = threadIdx.x >> 5;
   pdl_launch_dependents();
-  pdl_wait();
+  pdl_wait(TR_COLSUM);
   const int j = blockIdx.x * 64 + lane * 2;
   const int r0 = blockIdx.y * kColsumRows;
   float a0 = 0.f, a1 = 0.f;
@@ -170,18 +195,38 @@ using namespace dfm;
 extern "C" {
 
 // labels == NULL -> predict mode (only prob/logit written). train == 0 -> eval (loss only, no gradients).
+// g_b_top / g_w_out (both or neither; train mode): additionally g_b_top[j] += sum_b dZ[b,j] and g_w_out[j] += sum_b dy[b]
+// x[b,j], the two column sums that otherwise need dfm_colsum_bf16 launches.
+int dfm_logit_loss_cols(const void* x, int ldx, int H, const float* w_out, const float* b_out, const float* fm_bias,
+                        const float* yfm, const float* labels, int B, float inv_batch, float mask_scale, int train,
+                        float* prob, float* logit, float* dy, void* dz, int lddz, float* loss_sum, float* g_b_out,
+                        float* g_fm_bias, float* g_b_top, float* g_w_out, void* stream) {
+  DFM_REQUIRE(B > 0 && H > 0, "logit_loss: empty problem");
+  DFM_REQUIRE(ldx % 2 == 0 && (!train || lddz % 2 == 0), "logit_loss: leading dimensions must be even");
+  DFM_REQUIRE((g_b_top == nullptr) == (g_w_out == nullptr), "logit_loss: give both column-sum outputs or neither");
+  DFM_REQUIRE(g_b_top == nullptr || H <= 1024, "logit_loss: column sums need H <= 1024 (shared-memory accumulators)");
+  int blocks = ceil_div(B, kLossWarps);
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  const size_t smem = (g_b_top && train) ? 2 * (size_t)H * kLossWarps * sizeof(float) : 0;
+  if (smem > 48 * 1024) {
+    static bool big_smem_set = false;
+    if (!big_smem_set) {
+      DFM_CHECK(cudaFuncSetAttribute(logit_loss_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+      big_smem_set = true;
+    }
+  }
+  DFM_CHECK(launch_k(logit_loss_kernel, dim3(blocks), dim3(kLossThreads), smem, (cudaStream_t)stream,
+                     (const __nv_bfloat16*)x, ldx, H, w_out, b_out, fm_bias, yfm, labels, B, inv_batch, mask_scale, train,
+                     prob, logit, dy, (__nv_bfloat16*)dz, lddz, loss_sum, g_b_out, g_fm_bias, g_b_top, g_w_out));
+  return DFM_OK;
+}
+
 int dfm_logit_loss(const void* x, int ldx, int H, const float* w_out, const float* b_out, const float* fm_bias,
                    const float* yfm, const float* labels, int B, float inv_batch, float mask_scale, int train,
                    float* prob, float* logit, float* dy, void* dz, int lddz, float* loss_sum, float* g_b_out,
                    float* g_fm_bias, void* stream) {
-  DFM_REQUIRE(B > 0 && H > 0, "logit_loss: empty problem");
-  DFM_REQUIRE(ldx % 2 == 0 && (!train || lddz % 2 == 0), "logit_loss: leading dimensions must be even");
-  int blocks = ceil_div(B, kLossWarps);
-  if (blocks > 148 * 4) blocks = 148 * 4;
-  DFM_CHECK(launch_k(logit_loss_kernel, dim3(blocks), dim3(kLossThreads), 0, (cudaStream_t)stream,
-                     (const __nv_bfloat16*)x, ldx, H, w_out, b_out, fm_bias, yfm, labels, B, inv_batch, mask_scale, train,
-                     prob, logit, dy, (__nv_bfloat16*)dz, lddz, loss_sum, g_b_out, g_fm_bias));
-  return DFM_OK;
+  return dfm_logit_loss_cols(x, ldx, H, w_out, b_out, fm_bias, yfm, labels, B, inv_batch, mask_scale, train, prob, logit,
+                             dy, dz, lddz, loss_sum, g_b_out, g_fm_bias, nullptr, nullptr, stream);
 }
 
 // out[j] += sum_b a[b,j] * (w ? w[b] : 1)

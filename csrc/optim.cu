@@ -41,7 +41,7 @@ __global__ void __launch_bounds__(kOptThreads) flat_opt_kernel(const FlatOptArgs
   __shared__ float s_lr;
   __shared__ float s_red[kOptThreads / 32];
   pdl_launch_dependents();
-  pdl_wait();
+  pdl_wait(TR_OPT);
   const unsigned long long t = *a.step_ptr + 1ull;
   if (threadIdx.x == 0) s_lr = opt_step_lr(a.h, t);
   __syncthreads();
@@ -86,6 +86,7 @@ __global__ void __launch_bounds__(kOptThreads) flat_opt_kernel(const FlatOptArgs
     for (int i = 0; i < kOptThreads / 32; ++i) tot += s_red[i];
     if (a.reg_loss && tot != 0.f) atomicAdd(a.reg_loss, 0.5f * a.l2 * tot);
     __threadfence();
+    trace_end(TR_OPT);
     const unsigned int done = atomicAdd(a.done_counter, 1u);
     if (done == gridDim.x - 1) {  // every CTA has read the step by now
       *a.step_ptr = t;

@@ -23,6 +23,7 @@ REPO = os.path.dirname(_HERE)
 CSRC = os.path.join(REPO, "csrc")
 INC = os.path.join(REPO, "include")
 CUDA_LIB = os.path.join(_HERE, "ops", "_lib", "libdeepfm_b200.so")
+TRACE_LIB = os.path.join(_HERE, "ops", "_lib", "libdeepfm_b200_trace.so")  # -DDFM_KTRACE: kernel timeline stamps
 IO_LIB = os.path.join(_HERE, "data", "_lib", "libdeepfm_io.so")
 OBJ_DIR = os.path.join(REPO, "build", "obj")
 
@@ -49,27 +50,33 @@ def _run(cmd):
     return r.stdout + r.stderr
 
 
-def build_cuda(force: bool = False, verbose: bool = False) -> str:
+def build_cuda(force: bool = False, verbose: bool = False, trace: bool = False) -> str:
+    """trace=True builds the timeline variant (csrc/common.cuh: %globaltimer stamps per kernel; relocatable device code so
+    every translation unit shares one trace buffer) next to the normal library; DFM_KTRACE=1 makes ops/lib.py load it."""
     srcs = sorted(glob.glob(os.path.join(CSRC, "*.cu")))
     hdrs = sorted(glob.glob(os.path.join(CSRC, "*.cuh")) + glob.glob(os.path.join(INC, "*.h")))
-    if not force and _newer(CUDA_LIB, srcs + hdrs):
-        return CUDA_LIB
-    os.makedirs(OBJ_DIR, exist_ok=True)
-    os.makedirs(os.path.dirname(CUDA_LIB), exist_ok=True)
+    out_lib = TRACE_LIB if trace else CUDA_LIB
+    obj_dir = OBJ_DIR + ("_trace" if trace else "")
+    extra = ["-DDFM_KTRACE", "-rdc=true"] if trace else []
+    if not force and _newer(out_lib, srcs + hdrs):
+        return out_lib
+    os.makedirs(obj_dir, exist_ok=True)
+    os.makedirs(os.path.dirname(out_lib), exist_ok=True)
     objs = []
 
     def compile_one(src):
-        obj = os.path.join(OBJ_DIR, os.path.basename(src) + ".o")
+        obj = os.path.join(obj_dir, os.path.basename(src) + ".o")
         if force or not _newer(obj, [src] + hdrs):
-            out = _run([_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj])
+            out = _run([_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj])
             if verbose:
                 print(out)
         return obj
 
     with cf.ThreadPoolExecutor(max_workers=min(8, len(srcs) or 1)) as ex:
         objs = list(ex.map(compile_one, srcs))
-    _run([_nvcc(), "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", CUDA_LIB] + objs)
-    return CUDA_LIB
+    _run([_nvcc(), "-shared", "-gencode", "arch=compute_100a,code=sm_100a"] + (["-rdc=true"] if trace else []) +
+         ["-o", out_lib] + objs)
+    return out_lib
 
 
 def build_io(force: bool = False) -> str:
@@ -90,4 +97,6 @@ def build_all(force: bool = False, verbose: bool = False):
 
 if __name__ == "__main__":
     libs = build_all(force="--force" in sys.argv, verbose="-v" in sys.argv)
+    if "--trace" in sys.argv:
+        libs = libs + (build_cuda(force="--force" in sys.argv, trace=True),)
     print("built:", libs)

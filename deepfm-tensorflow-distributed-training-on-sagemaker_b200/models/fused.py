@@ -133,6 +133,8 @@ class FusedDeepFM:
         self.auc_hist = torch.zeros(2, NUM_THRESHOLDS + 1, **f32)
 
         self._side = torch.cuda.Stream(device=dev)
+        self._side2 = torch.cuda.Stream(device=dev)
+        self._setup_split_optimizer()
         self._build_plans()
         self._graphs: Dict[int, torch.cuda.CUDAGraph] = {}
         self.kernels_per_step = 0
@@ -168,6 +170,43 @@ class FusedDeepFM:
     def _slot_numel(self) -> int:
         return self.layout.trainable_numel
 
+    def _want_split(self) -> bool:
+        """Split dense optimizer (csrc/split_opt.cu): needs the tables in the flat buffer; DFM_SPLIT_OPT=0 keeps the
+        single fused sweep (flat_opt) at the end of the step."""
+        import os
+        return self.layout.include_embeddings and os.environ.get("DFM_SPLIT_OPT", "1") != "0" \
+            and type(self)._optimizer_kernels is FusedDeepFM._optimizer_kernels
+
+    def _setup_split_optimizer(self) -> None:
+        self.split = None
+        if not self._want_split():
+            return
+        words = K.bitmap_words(self.cfg.feature_size)
+        dev = self.dev
+        self.bm_own = torch.zeros(words, device=dev, dtype=torch.int32)
+        self.bm_union = torch.zeros(words, device=dev, dtype=torch.int32)
+        self.reg_acc = torch.zeros(1, device=dev, dtype=torch.float32)
+        lt = self.layout.trainable_numel
+        self.split = K.SplitOptimizer(self.layout, self.cfg, self.opt, self.P[:lt], self.G[:lt], self.S0, self.S1,
+                                      self.shadow, self.step_t, self.reg_acc, self.reg_loss, self.done_counter,
+                                      self.bm_union, [self.bm_own], True, self.loss_sum,
+                                      sweep_blocks=self._sweep_blocks())
+
+    @staticmethod
+    def _sweep_blocks() -> int:
+        """Grid of the untouched-row sweep: one 8-warp CTA per SM. It runs beside the forward/backward kernels for most of
+        the step and must leave each SM's registers, warps and bandwidth mostly to them (measured: with ~3 CTAs per SM the
+        GEMM CTAs, one per SM by shared memory, queued behind it and the step got SLOWER than the single sweep)."""
+        import os
+        return int(os.environ.get("DFM_SWEEP_BLOCKS", "148"))
+
+    def _split_side_kernels(self, slot) -> int:
+        """Side branch of a split-optimizer step (forked at step start, joined before the tail): mark the rows this batch
+        looks up, then update every other table row while forward/backward run."""
+        K.touched_bitmap(slot["ids"], self.cfg.feature_size, self.bm_own)
+        self.split.sweep()
+        return 2
+
     def _pre_step(self, side) -> int:
         """Hook at the start of a step (runs inside graph capture); returns #kernels it launched."""
         return 0
@@ -186,6 +225,8 @@ class FusedDeepFM:
         cfg, B = self.cfg, self.B
         nl = len(cfg.deep_layers)
         self.fwd_train, self.fwd_eval, self.wgrad, self.dgrad = [], [], [], []
+        # bias / head-weight gradients are column sums of dZ and X: produced inside the kernels that write dZ
+        self._fold_cols = (not self.bn) and cfg.deep_layers[-1] <= 1024
         x_in = self.x0
         for i, h in enumerate(cfg.deep_layers):
             d_in = x_in.shape[1]
@@ -200,13 +241,25 @@ class FusedDeepFM:
                                                  keep_prob=cfg.dropout[i], seed=self.seed, layer=i,
                                                  row_offset=self.row_offset, step_ptr=self.step_t))
                 self.fwd_eval.append(K.GemmPlan("fwd", x_in, Wb, self.acts[i], B, h, d_in, bias=bias, relu=True))
-            self.wgrad.append(K.GemmPlan("wgrad", self.dz[i], x_in, self._g("mlp%d.weight" % i), h, d_in, B))
+            import os as _os
+            if _os.environ.get("DFM_WGRAD_SPLITK", "0") == "1":  # split-K with red.add (fills the SMs; atomics)
+                self.wgrad.append(K.GemmPlan("wgrad", self.dz[i], x_in, self._g("mlp%d.weight" % i), h, d_in, B))
+            else:  # one K split per tile, plain stores: the weight gradient is written, not accumulated
+                self.wgrad.append(K.GemmPlan("wgrad", self.dz[i], x_in, self._g("mlp%d.weight" % i), h, d_in, B,
+                                             split_k=1).set_overwrite(True))
             if i == 0:
                 self.dgrad.append(K.GemmPlan("dgrad", self.dz[0], Wb, self.dx0, B, d_in, h))
             else:
                 self.dgrad.append(K.GemmPlan("dgrad", self.dz[i], Wb, self.dz[i - 1], B, d_in, h,
                                              mask=self.acts[i - 1], mask_scale=1.0 / cfg.dropout[i - 1]))
+                if self._fold_cols:  # bias gradient of layer i-1 = column sums of dZ_{i-1}: folded into this epilogue
+                    self.dgrad[i].set_colsum(self._g("mlp%d.bias" % (i - 1)))
             x_in = self.acts[i]
+            # timeline ids (csrc/common.cuh TR_*): forward 1+i, dgrad 5+i, wgrad 8+i
+            if i < 3:
+                self.fwd_train[i].set_trace_id(1 + i)
+                self.dgrad[i].set_trace_id(5 + i)
+                self.wgrad[i].set_trace_id(8 + i)
         self.n_layers = nl
 
     def refresh_shadow(self):
@@ -248,6 +301,13 @@ class FusedDeepFM:
         cur = torch.cuda.current_stream()
         n = 0
         pre = self._pre_step(self._side)
+        split = self.split is not None and with_optimizer
+        if split:  # fork: touched-row bitmap + sweep of the untouched table rows overlap the whole forward/backward
+            ev0 = torch.cuda.Event()
+            ev0.record(cur)
+            self._side2.wait_event(ev0)
+            with torch.cuda.stream(self._side2):
+                n += self._split_side_kernels(slot)
         n += self._forward(slot, True, zero_scalars=True)  # also clears loss_sum / reg_loss
         if pre:  # join the pre-step branch (e.g. gradient zeroing under data parallelism) before the first grad write
             evp = torch.cuda.Event()
@@ -256,7 +316,9 @@ class FusedDeepFM:
         top = nl - 1
         K.logit_loss(self.acts[top], self._w("deep_out.weight"), self._w("deep_out.bias"), self._w("fm_bias"), self.yfm,
                      slot["labels"], 1.0 / self.global_batch, 1.0 / cfg.dropout[top], True, self.prob, self.logit,
-                     self.dy, self.dz[top], self.loss_sum, self._g("deep_out.bias"), self._g("fm_bias"))
+                     self.dy, self.dz[top], self.loss_sum, self._g("deep_out.bias"), self._g("fm_bias"),
+                     None if not self._fold_cols else self._g("mlp%d.bias" % top),
+                     None if not self._fold_cols else self._g("deep_out.weight"))
         n += 1
         side = self._side
         for i in range(top, -1, -1):
@@ -270,17 +332,23 @@ class FusedDeepFM:
             side.wait_event(ev)
             with torch.cuda.stream(side):
                 self.wgrad[i].run()
-                K.colsum_bf16(self.dz[i], self._g("mlp%d.bias" % i))
-                n += 2
-                if i == top:  # g_w_out = X_top^T dy
-                    K.colsum_bf16(self.acts[top], self._g("deep_out.weight"), self.dy)
+                n += 1
+                if not self._fold_cols:  # batch-norm path (bn_bwd rewrites dz[i]) / very wide top layer: own pass
+                    K.colsum_bf16(self.dz[i], self._g("mlp%d.bias" % i))
                     n += 1
+                    if i == top:  # g_w_out = X_top^T dy
+                        K.colsum_bf16(self.acts[top], self._g("deep_out.weight"), self.dy)
+                        n += 1
             self.dgrad[i].run()
             n += 1
         n += self._emb_backward(slot)
         ev = torch.cuda.Event()
         ev.record(side)
         cur.wait_event(ev)  # join
+        if split:
+            ev2 = torch.cuda.Event()
+            ev2.record(self._side2)
+            cur.wait_event(ev2)
         if with_optimizer:
             n += self._optimizer_kernels()
         return n
@@ -301,6 +369,9 @@ class FusedDeepFM:
         lt = L.trainable_numel
         decay = L.decay_range if self.cfg.l2_reg > 0 else (0, 0)
         ring = getattr(self, "_result_ring", None)
+        if self.split is not None:
+            self.split.tail(publish=(self.scalars, ring) if ring is not None else None)
+            return 1
         K.flat_opt_step(self.P[:lt], self.G[:lt], self.S0, self.S1, o.name, o.lr, o.beta1, o.beta2, o.eps, o.momentum,
                         1.0, decay, self.cfg.l2_reg, L.shadow_range, self.shadow, self.step_t, self.reg_loss,
                         self.done_counter, publish=(self.scalars, ring) if ring is not None else None)
@@ -351,7 +422,11 @@ class FusedDeepFM:
                 torch.cuda.synchronize()
                 self._restore(snap)
                 g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g):
+                # capture on a high-priority stream: the kernel nodes of the critical chain inherit it, the forked side
+                # branches (wgrad, untouched-row sweep) keep the default priority and yield SMs to the chain
+                if getattr(self, "_cap_stream", None) is None:
+                    self._cap_stream = torch.cuda.Stream(device=self.dev, priority=-1)
+                with torch.cuda.graph(g, stream=self._cap_stream):
                     self.kernels_per_step = self._train_kernels(self.in_slots[slot_idx])
                 self._graphs[slot_idx] = g
             g.replay()
@@ -369,6 +444,9 @@ class FusedDeepFM:
                 dst.copy_(src)
         self.G.zero_()
         self.done_counter.zero_()
+        if self.split is not None:
+            self.bm_own.zero_()
+            self.reg_acc.zero_()
         torch.cuda.synchronize()
 
     def train_step(self, ids, vals, labels, slot_idx: int = 0) -> torch.Tensor:

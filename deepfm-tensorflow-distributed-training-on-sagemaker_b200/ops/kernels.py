@@ -77,6 +77,22 @@ class GemmPlan:
         _lib.load().dfm_gemm_plan_info(self._h, ctypes.byref(bn), ctypes.byref(gx), ctypes.byref(gy), ctypes.byref(gz))
         return {"bn": bn.value, "grid": (gx.value, gy.value, gz.value)}
 
+    def set_overwrite(self, on: bool = True) -> "GemmPlan":
+        """wgrad plans created with split_k=1: out = A^T B (plain stores) instead of out += (split-K atomics)."""
+        _lib.check(_lib.load().dfm_gemm_plan_set_overwrite(self._h, c_int(1 if on else 0)))
+        return self
+
+    def set_colsum(self, out: Optional[torch.Tensor]) -> "GemmPlan":
+        """dgrad plans: out[n] += sum_m result[m,n] in the epilogue (the bias gradient of the layer below)."""
+        self._keep = self._keep + (out,)
+        _lib.check(_lib.load().dfm_gemm_plan_set_colsum(self._h, _p(out)))
+        return self
+
+    def set_trace_id(self, tid: int) -> "GemmPlan":
+        """Timeline id of this plan's launches (only the trace build records anything; scripts/step_trace.py)."""
+        _lib.check(_lib.load().dfm_gemm_plan_set_trace_id(self._h, c_int(tid)))
+        return self
+
     def set_out_f32(self, on: bool = True) -> "GemmPlan":
         _lib.check(_lib.load().dfm_gemm_plan_set_out_f32(self._h, c_int(1 if on else 0)))
         return self
@@ -94,12 +110,15 @@ class GemmPlan:
 
 
 def logit_loss(x, w_out, b_out, fm_bias, yfm, labels, inv_batch: float, mask_scale: float, train: bool,
-               prob=None, logit=None, dy=None, dz=None, loss_sum=None, g_b_out=None, g_fm_bias=None) -> None:
+               prob=None, logit=None, dy=None, dz=None, loss_sum=None, g_b_out=None, g_fm_bias=None, g_b_top=None,
+               g_w_out=None) -> None:
+    """g_b_top / g_w_out (train): also accumulate colsum(dZ) and X^T dy here instead of two colsum_bf16 launches."""
     B, H = x.shape
-    _lib.check(_lib.load().dfm_logit_loss(
+    _lib.check(_lib.load().dfm_logit_loss_cols(
         _p(x), c_int(x.stride(0)), c_int(H), _p(w_out), _p(b_out), _p(fm_bias), _p(yfm), _p(labels), c_int(B),
         c_float(inv_batch), c_float(mask_scale), c_int(1 if train else 0), _p(prob), _p(logit), _p(dy), _p(dz),
-        c_int(dz.stride(0) if dz is not None else 0), _p(loss_sum), _p(g_b_out), _p(g_fm_bias), _stream()))
+        c_int(dz.stride(0) if dz is not None else 0), _p(loss_sum), _p(g_b_out), _p(g_fm_bias), _p(g_b_top), _p(g_w_out),
+        _stream()))
 
 
 def colsum_bf16(a: torch.Tensor, out: torch.Tensor, w: Optional[torch.Tensor] = None) -> None:
@@ -158,3 +177,65 @@ def example_parse(blob: torch.Tensor, offsets: torch.Tensor, n: int, field_size:
     _chk_dev(blob, offsets, labels, ids, vals, err)
     _lib.check(_lib.load().dfm_example_parse(_p(blob), _p(offsets), c_int(n), c_int(field_size), _p(labels), _p(ids),
                                              _p(vals), _p(err), _stream()))
+
+
+# ---------------------------------------------------------------------------------------------- split optimizer
+def bitmap_words(N: int) -> int:
+    return (N + 31) // 32
+
+
+def touched_bitmap(ids: torch.Tensor, N: int, bitmap: torch.Tensor) -> None:
+    """bitmap[id >> 5] |= 1 << (id & 31) for every in-range id (int32 [B,F]); bitmap int32 [ceil(N/32)]."""
+    B, F = ids.shape
+    _lib.check(_lib.load().dfm_touched_bitmap(_p(ids), c_int(B), c_int(F), c_int(N), _p(bitmap), _stream()))
+
+
+class SplitOptimizer:
+    """Bound arguments of the split dense optimizer (csrc/split_opt.cu) over one flat (w, g, s0, s1) buffer set:
+    `sweep()` = every table row NOT in the touched bitmap (side stream, concurrent with forward/backward),
+    `tail()`  = touched rows + fm_bias block + MLP block, then step counter / L2 loss value / result publication."""
+
+    def __init__(self, layout, cfg, opt, w, g, s0, s1, shadow, step_ptr, reg_acc, reg_loss, done_counter, bm_union,
+                 bm_in, clear_inputs: bool, loss_sum, loss_parts=None, world: int = 1, sweep_blocks: int = 0):
+        seg_w, seg_v = layout.segments["fm_w"], layout.segments["fm_v"]
+        self.o, self.cfg, self.L = opt, cfg, layout
+        self.w, self.g, self.s0, self.s1, self.shadow = w, g, s0, s1, shadow
+        self.step_ptr, self.reg_acc, self.reg_loss, self.done = step_ptr, reg_acc, reg_loss, done_counter
+        self.bm_union, self.loss_sum, self.loss_parts, self.world = bm_union, loss_sum, loss_parts, world
+        self._bm_in = bm_in  # keep alive
+        self._bm_tab = (ctypes.c_void_p * len(bm_in))(*[t.data_ptr() if hasattr(t, "data_ptr") else int(t) for t in bm_in])
+        self.clear_inputs = clear_inputs
+        self.fmw_off, self.fmv_off = seg_w.offset, seg_v.offset
+        self.N, self.K = cfg.feature_size, cfg.embedding_size
+        self.d0 = (0, seg_w.offset)                          # fm_bias block (padded to the segment alignment)
+        self.d1 = (layout.shadow_range[0], layout.trainable_numel)  # MLP weights, biases, head, BN beta/gamma
+        self.sweep_blocks = sweep_blocks
+
+    def _hyper(self):
+        o = self.o
+        return (c_int(OPT_IDS[o.name]), c_float(o.lr), c_float(o.beta1), c_float(o.beta2), c_float(o.eps),
+                c_float(o.momentum))
+
+    def sweep(self) -> None:
+        _lib.check(_lib.load().dfm_sweep_untouched(
+            _p(self.w), _p(self.s0), _p(self.s1), *self._hyper(), c_float(self.cfg.l2_reg), c_longlong(self.fmw_off),
+            c_longlong(self.fmv_off), c_int(self.N), c_int(self.K), self._bm_tab, c_int(len(self._bm_in)),
+            c_int(1 if self.clear_inputs else 0), _p(self.bm_union), _p(self.step_ptr), _p(self.reg_acc),
+            c_int(self.sweep_blocks), _stream()))
+
+    def tail(self, publish=None, grad_scale: float = 1.0, dense: bool = True, sparse: bool = True,
+             finalize: bool = True) -> None:
+        if publish is None:
+            pub = (None, c_int(0), None, c_int(0))
+        else:
+            src, ring = publish
+            assert src.is_cuda and ring.is_pinned() and ring.dtype == torch.float32 and ring.shape[1] == src.numel()
+            pub = (_p(src), c_int(src.numel()), c_void_p(ring.data_ptr()), c_int(ring.shape[0]))
+        sh = self.L.shadow_range
+        _lib.check(_lib.load().dfm_tail_opt(
+            _p(self.w), _p(self.g), _p(self.s0), _p(self.s1), *self._hyper(), c_float(grad_scale),
+            c_float(self.cfg.l2_reg), c_longlong(self.fmw_off), c_longlong(self.fmv_off), c_int(self.N), c_int(self.K),
+            c_longlong(self.d0[0]), c_longlong(self.d0[1]), c_longlong(self.d1[0]), c_longlong(self.d1[1]),
+            c_longlong(sh[0]), c_longlong(sh[1]), _p(self.shadow), _p(self.bm_union), _p(self.step_ptr), _p(self.reg_acc),
+            _p(self.reg_loss), _p(self.done), _p(self.loss_sum), _p(self.loss_parts), c_int(self.world), pub[0], pub[1],
+            pub[2], pub[3], c_int(1 if dense else 0), c_int(1 if sparse else 0), c_int(1 if finalize else 0), _stream()))

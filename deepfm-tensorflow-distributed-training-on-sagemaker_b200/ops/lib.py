@@ -11,6 +11,8 @@ from typing import Optional
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "_lib", "libdeepfm_b200.so")
+if os.environ.get("DFM_KTRACE") == "1":  # timeline build (python -m deepfm_b200.build --trace; scripts/step_trace.py)
+    LIB_PATH = os.path.join(_HERE, "_lib", "libdeepfm_b200_trace.so")
 _lib: Optional[ctypes.CDLL] = None
 
 
@@ -30,7 +32,7 @@ def load(build_if_missing: bool = True) -> ctypes.CDLL:
         if not build_if_missing:
             raise NativeError("native library not built: run `python -m deepfm_b200.build`")
         from ..build import build_cuda
-        build_cuda()
+        build_cuda(trace=LIB_PATH.endswith("_trace.so"))
     lib = ctypes.CDLL(LIB_PATH)
     lib.dfm_last_error.restype = ctypes.c_char_p
     lib.dfm_gemm_plan_destroy.restype = None

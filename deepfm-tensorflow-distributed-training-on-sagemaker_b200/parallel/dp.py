@@ -239,8 +239,8 @@ class FusedDataParallel(FusedDeepFM):
         if self.rank == src:
             # parameters: one pass of multicast (NVLS) or per-peer P2P stores from inside a kernel (bcast_state)
             lib = _nlib.load()
-            n = (self.P.numel() + 3) // 4 * 4
-            _nlib.check(lib.dfm_bcast_f32(self._tables["P"], c_void_p(self.arena.mc("P")), c_longlong(min(n, self.P.numel() // 4 * 4)),
+            n_p4 = self.P.numel() // 4 * 4  # bcast length: the whole padded buffer (incl. non-trainable BN statistics)
+            _nlib.check(lib.dfm_bcast_f32(self._tables["P"], c_void_p(self.arena.mc("P")), c_longlong(n_p4),
                                           c_int(self.rank), c_int(self.world), c_int(1 if self.use_nvls else 0),
                                           c_void_p(torch.cuda.current_stream().cuda_stream)))
             for r in range(self.world):

@@ -54,11 +54,16 @@ class _Net(nn.Module):
 class ProxyDeepFM:
     def __init__(self, cfg: DeepFMConfig, batch_size: int, optimizer, seed: int, device, world_size: int = 1,
                  rank: int = 0, use_graph: bool = False):
-        """use_graph (or DFM_PROXY_GRAPH=1; `bench.py --impl proxy --proxy_graph`): capture the whole proxy step -
-        forward, backward, NCCL all-reduce, optimizer - in one CUDA graph, the stock PyTorch recipe. That removes the
-        eager launch overhead and is the closer stand-in for a TF-1 graph-mode step. EXPERIMENTAL: written after this
-        round's GPU budget was spent, not yet run on a GPU; the default (eager) proxy is the one every published ratio
-        uses. Adam and SGD only (the optimizers torch can capture)."""
+        """The best stock-PyTorch recipe we know for this model, so the ratio against it is not a launch-overhead ratio:
+
+          * parameters and gradients are views of ONE flat buffer each (the DDP bucket idea): the gradient exchange is a
+            single `dist.all_reduce(flat_grad, AVG)` with no flatten / unflatten copies;
+          * the optimizer is `torch.optim.Adam(fused=True)` over the flat parameter: one multi-tensor kernel;
+          * the whole-table L2 term is added to the flat gradient directly (`g += l2 * w`, one kernel) instead of being
+            differentiated through `pow().sum()`;
+          * `use_graph` (or DFM_PROXY_GRAPH=1; `bench.py --impl proxy --proxy_graph`): forward, backward, NCCL all-reduce
+            and optimizer are captured in ONE CUDA graph (the PyTorch whole-network capture recipe), which is the fair
+            stand-in for a TF-1 graph-mode `session.run(train_op)`. Adam / Momentum / GD (what torch can capture)."""
         import os
         self.cfg, self.B, self.dev = cfg, batch_size, device
         self._use_graph = bool(use_graph or os.environ.get("DFM_PROXY_GRAPH") == "1") and optimizer.name in ("Adam", "GD",
@@ -69,14 +74,33 @@ class ProxyDeepFM:
         self.net = _Net(cfg, init_params(cfg, seed)).to(device)
         name = optimizer.name
         ps = list(self.net.parameters())
+        # ---- one flat parameter buffer + one flat gradient buffer; module parameters / .grad alias slices of them
+        al = lambda n: (n + 63) // 64 * 64
+        total = sum(al(p.numel()) for p in ps)
+        self.flat = torch.zeros(total, device=device)
+        self.flat_grad = torch.zeros(total, device=device)
+        o = 0
+        self._decay = []
+        for p in ps:
+            n = p.numel()
+            self.flat[o:o + n].copy_(p.data.reshape(-1))
+            p.data = self.flat[o:o + n].view_as(p)
+            p.grad = self.flat_grad[o:o + n].view_as(p)
+            if p is self.net.fm_w or p is self.net.fm_v:
+                self._decay.append((o, o + n))
+            o += al(n)
+        self._decay = (min(a for a, _ in self._decay), max(b for _, b in self._decay))
+        self.flat_param = nn.Parameter(self.flat)  # shares storage with every module parameter
+        self.flat_param.grad = self.flat_grad
+        cap = self._use_graph
         if name == "Adam":
-            self.optim = torch.optim.Adam(ps, lr=optimizer.lr, eps=1e-8, capturable=self._use_graph)
+            self.optim = torch.optim.Adam([self.flat_param], lr=optimizer.lr, eps=1e-8, fused=True, capturable=cap)
         elif name == "Adagrad":
-            self.optim = torch.optim.Adagrad(ps, lr=optimizer.lr, initial_accumulator_value=1e-8, eps=0.0)
+            self.optim = torch.optim.Adagrad([self.flat_param], lr=optimizer.lr, initial_accumulator_value=1e-8, eps=0.0)
         elif name == "Momentum":
-            self.optim = torch.optim.SGD(ps, lr=optimizer.lr, momentum=0.95)
+            self.optim = torch.optim.SGD([self.flat_param], lr=optimizer.lr, momentum=0.95)
         else:
-            self.optim = torch.optim.SGD(ps, lr=optimizer.lr)
+            self.optim = torch.optim.SGD([self.flat_param], lr=optimizer.lr)
         self._loss = torch.zeros((), device=device)
         self.kernels_per_step = 0  # library kernels only; none of ours
         self._step = 0
@@ -89,7 +113,7 @@ class ProxyDeepFM:
         self._sids = torch.zeros(self.B, F_, dtype=torch.long, device=self.dev)
         self._svals = torch.zeros(self.B, F_, device=self.dev)
         self._slabels = torch.zeros(self.B, device=self.dev)
-        snap = {k: v.clone() for k, v in self.net.state_dict().items()}
+        snap = self.flat.clone()
         side = torch.cuda.Stream(device=self.dev)
         side.wait_stream(torch.cuda.current_stream(self.dev))
         with torch.cuda.stream(side):
@@ -97,15 +121,14 @@ class ProxyDeepFM:
                 self._eager_step(self._sids, self._svals, self._slabels)
         torch.cuda.current_stream(self.dev).wait_stream(side)
         torch.cuda.synchronize(self.dev)
-        self.net.load_state_dict(snap)
+        self.flat.copy_(snap)
         for st in self.optim.state.values():  # moments back to zero, step counters back to the start
             for k, v in st.items():
                 if torch.is_tensor(v):
                     v.zero_()
-        self.optim.zero_grad(set_to_none=True)
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
-            self._graph_loss = self._eager_step(self._sids, self._svals, self._slabels, zero=False)
+            self._graph_loss = self._eager_step(self._sids, self._svals, self._slabels)
         self._graph = g
 
     def train_step(self, ids, vals, labels, slot_idx: int = 0):
@@ -123,23 +146,21 @@ class ProxyDeepFM:
         self._step += 1
         return loss
 
-    def _eager_step(self, ids, vals, labels, zero: bool = True):
+    def _eager_step(self, ids, vals, labels):
         ids = ids.long()
-        if zero:
-            self.optim.zero_grad(set_to_none=True)
+        self.flat_grad.zero_()  # .grad tensors are views of it: autograd accumulates in place
         y = self.net(ids, vals, True)
         data = F.binary_cross_entropy_with_logits(y, labels.reshape(-1))
-        loss = data + 0.5 * self.cfg.l2_reg * (self.net.fm_w.pow(2).sum() + self.net.fm_v.pow(2).sum())
-        loss.backward()
-        if self.world > 1:  # Horovod-style: average every gradient through one fused buffer
-            grads = [p.grad for p in self.net.parameters()]
-            flat = torch._utils._flatten_dense_tensors(grads)
-            dist.all_reduce(flat)
-            flat.div_(self.world)
-            for g, f in zip(grads, torch._utils._unflatten_dense_tensors(flat, grads)):
-                g.copy_(f)
+        data.backward()
+        a, b = self._decay
+        with torch.no_grad():
+            reg = 0.5 * self.cfg.l2_reg * self.flat[a:b].pow(2).sum()
+            if self.world > 1:  # Horovod-style: average every gradient through one fused buffer (HVD:262)
+                dist.all_reduce(self.flat_grad, op=dist.ReduceOp.AVG)
+            if self.cfg.l2_reg:
+                self.flat_grad[a:b].add_(self.flat[a:b], alpha=self.cfg.l2_reg)
         self.optim.step()
-        self._loss = loss.detach()
+        self._loss = data.detach() + reg
         return self._loss
 
     def last_loss(self):

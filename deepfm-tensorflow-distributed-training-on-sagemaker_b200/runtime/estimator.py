@@ -103,7 +103,11 @@ class Estimator:
         inflight = collections.deque()
         n_local = 0
         limit = agree_min(self.env, steps_hint) if steps_hint is not None else None
-        for batch in input_fn():
+        batches = input_fn()
+        if limit is None and self.env.world_size > 1 and self.strategy != "ps" and self.env.backend != "none":
+            # no step count known up front (pipe mode: a FIFO cannot be counted): agree block by block instead
+            batches = self._agreed_batches(batches)
+        for batch in batches:
             if limit is not None and n_local >= limit:
                 batch.release()
                 break
@@ -142,6 +146,30 @@ class Estimator:
             self.saver.save(tr, self.out)
         print("INFO:deepfm_b200:Loss for final step: %.8g." % self._current_loss(), file=self.out)
         return n_local
+
+    def _agreed_batches(self, batches: Iterable, block: int = 3):
+        """Synchronous strategies on several ranks without a step count known up front (pipe mode, HVD:396-405): the
+        ranks agree every `block` steps on how many of the next `block` full batches ALL of them hold, and stop together
+        at the first short block. A rank whose FIFO holds fewer records can therefore never leave the others waiting in
+        a collective (the Horovod failure described at PDF p22-23)."""
+        it = iter(batches)
+        while True:
+            buf = []
+            while len(buf) < block:
+                b = next(it, None)
+                if b is None:
+                    break
+                if b.rows != self.B:  # drop_remainder: short batches are not steps
+                    b.release()
+                    continue
+                buf.append(b)
+            n = agree_min(self.env, len(buf))
+            for b in buf[n:]:
+                b.release()
+            for b in buf[:n]:
+                yield b
+            if n < block:
+                return
 
     def _current_loss(self) -> float:
         tr = self.trainer

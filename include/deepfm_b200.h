@@ -38,6 +38,9 @@ int dfm_gemm_plan_create(void** plan_out, int mode, const void* A, int lda, cons
                          float mask_scale, int split_k);
 int dfm_gemm_plan_info(void* plan, int* bn, int* grid_x, int* grid_y, int* grid_z);
 int dfm_gemm_plan_set_row_offset(void* plan, int row_offset);
+int dfm_gemm_plan_set_overwrite(void* plan, int on); /* wgrad plans with split_k = 1: out = (plain stores), not += */
+int dfm_gemm_plan_set_colsum(void* plan, float* colsum); /* dgrad plans: colsum[n] += sum_m out[m,n] (bias gradient) */
+int dfm_gemm_plan_set_trace_id(void* plan, int id); /* timeline id (trace build only, see dfm_trace_*) */
 int dfm_gemm_plan_set_out_f32(void* plan, int on); /* forward plans: fp32 output (pre-batch-norm activations) */
 void dfm_gemm_plan_destroy(void* plan);
 int dfm_gemm_run(void* plan, void* stream);
@@ -47,6 +50,11 @@ int dfm_logit_loss(const void* x_bf16, int ldx, int H, const float* w_out, const
                    const float* yfm, const float* labels, int B, float inv_batch, float mask_scale, int train,
                    float* prob, float* logit, float* dy, void* dz_bf16, int lddz, float* loss_sum, float* g_b_out,
                    float* g_fm_bias, void* stream);
+/* Same, plus (train mode, both pointers non-NULL) g_b_top[j] += sum_b dZ[b,j] and g_w_out[j] += sum_b dy[b] x[b,j]. */
+int dfm_logit_loss_cols(const void* x_bf16, int ldx, int H, const float* w_out, const float* b_out, const float* fm_bias,
+                        const float* yfm, const float* labels, int B, float inv_batch, float mask_scale, int train,
+                        float* prob, float* logit, float* dy, void* dz_bf16, int lddz, float* loss_sum, float* g_b_out,
+                        float* g_fm_bias, float* g_b_top, float* g_w_out, void* stream);
 /* out[j] += sum_b a[b,j] * (w ? w[b] : 1): bias gradients (w = NULL) and g_w_out = X_top^T dy (w = dy). */
 int dfm_colsum_bf16(const void* a_bf16, int lda, int B, int H, const float* w, float* out, void* stream);
 
@@ -76,6 +84,28 @@ int dfm_flat_opt_step_pub(float* w, float* g, float* s0, float* s1, long long n,
                           unsigned long long* step_ptr, float* reg_loss, unsigned int* done_counter,
                           const float* pub_src, int pub_n, float* pub_ring, int pub_ring_len, void* stream);
 int dfm_cast_f32_bf16(const float* in, void* out_bf16, long long n, void* stream);
+
+/* ---- split form of the same dense optimizer step (csrc/split_opt.cu) for replicated tables: the whole-table part of the
+ * reference's update (dense ApplyAdam on fm_w / fm_v because of the whole-table L2 term, PS:245-246,269) leaves the
+ * critical path. touched_bitmap marks the rows a batch looks up; sweep_untouched updates every OTHER row (their gradient is
+ * l2*w, nothing from backward is needed) concurrently with forward/backward; tail_opt finishes with the touched rows and the
+ * dense ranges d0/d1 (fm_bias block, MLP block), zeroing the gradients it consumes. Results equal dfm_flat_opt_step.
+ * bm_in: host array of `world` device pointers to per-rank bitmaps of dfm_bitmap_words(N) words (world == 1: the live
+ * bitmap, cleared by the sweep when clear_inputs != 0); bm_union receives their OR. reg_acc: one zero-initialised device
+ * float (sum of w^2 over the decay range; reset by the finalising tail, which writes *reg_loss = 0.5*l2*sum). */
+int dfm_bitmap_words(int N);
+int dfm_touched_bitmap(const int* ids, int B, int F, int N, unsigned int* bitmap, void* stream);
+int dfm_sweep_untouched(float* w, float* s0, float* s1, int opt, float lr, float beta1, float beta2, float eps,
+                        float momentum, float l2, long long fmw_off, long long fmv_off, int N, int K,
+                        const void* const* bm_in, int world, int clear_inputs, unsigned int* bm_union,
+                        unsigned long long* step_ptr, float* reg_acc, int grid_blocks, void* stream);
+int dfm_tail_opt(float* w, float* g, float* s0, float* s1, int opt, float lr, float beta1, float beta2, float eps,
+                 float momentum, float grad_scale, float l2, long long fmw_off, long long fmv_off, int N, int K,
+                 long long d0_begin, long long d0_end, long long d1_begin, long long d1_end, long long shadow_begin,
+                 long long shadow_end, void* shadow_bf16, const unsigned int* bm_union, unsigned long long* step_ptr,
+                 float* reg_acc, float* reg_loss, unsigned int* done_counter, float* loss_sum, const float* loss_parts,
+                 int world, const float* pub_src, int pub_n, float* pub_ring, int pub_ring_len, int do_dense,
+                 int do_sparse, int finalize, void* stream);
 
 /* ---- gradient all-reduce fused with the optimizer step over NVLink peer memory (replaces Horovod's NCCL all-reduce
  * HVD:262 + ApplyAdam PS:269). Pointer tables: host arrays of `world` device pointers into symmetric memory; *_mc are
@@ -142,6 +172,14 @@ int dfm_host_register(void* ptr, unsigned long long bytes, void** dev_ptr); /* p
 /* zero-copy parameter-server pull: out[i,:] = table[ids[i],:], table = device alias of the host store (X3 / row 11) */
 int dfm_ps_gather(const float* table_dev, const long long* ids, int n, int K, float* out, void* stream);
 int dfm_host_unregister(void* ptr);
+
+/* ---- kernel timeline (csrc/common.cuh): %globaltimer stamps per kernel, compiled in only by the trace build
+ * (`python -m deepfm_b200.build --trace` -> libdeepfm_b200_trace.so). out: dfm_trace_words() words, 4 per trace id:
+ * first CTA entered / first CTA past griddepcontrol.wait / last CTA at its end / phase stamp. No reference counterpart. */
+int dfm_trace_enabled(void);
+int dfm_trace_words(void);
+int dfm_trace_reset(void);
+int dfm_trace_read(unsigned long long* out);
 
 /* ---- host-side step driver (csrc/step_driver.cu): one call issues a whole host-fed step - pinned H2D copy into input slot
  * `slot` on copy_stream (after the slot's previous reader), compute_stream waits for it, cudaGraphLaunch of the step's
