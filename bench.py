@@ -47,6 +47,7 @@ def parse_args():
     ap.add_argument("--l2_reg", type=float, default=1e-4)
     ap.add_argument("--proxy_graph", action="store_true",
                     help="--impl proxy only: capture the proxy step in a CUDA graph (see proxy_baseline.py)")
+    ap.add_argument("--no_selfcheck", action="store_true", help="skip the multi-GPU self-check after the timed regions")
     ap.add_argument("--no_baseline", action="store_true",
                     help="skip the in-process baseline arm (graph-captured stock-PyTorch NCCL+cuBLAS proxy) that fills "
                          "vs_baseline for --impl ours --strategy dp")
@@ -259,6 +260,22 @@ def main():
     ms_e2e = f0.elapsed_time(f1)
     clocks = sampler.stop() if rank == 0 else None
 
+    # ---- (3) multi-GPU self-check, outside every timed region: replicas bit-equal across ranks after
+    # all those steps, and the fused exchange kernel == NCCL all_reduce on a copy of the same gradients
+    self_check = None
+    if world > 1 and a.impl == "ours" and a.strategy == "dp" and not a.no_selfcheck:
+        try:
+            from deepfm_b200.parallel.selfcheck import exchange_equals_allreduce, replicas_equal
+            torch.cuda.synchronize()
+            dist.barrier()
+            self_check = {"replicas_bit_equal": replicas_equal(tr.model)}
+            exch = "sparse" if getattr(tr.model, "slots_replicated", False) else "dense"
+            if a.comm != "nccl":
+                self_check["exchange_vs_nccl_allreduce"] = exchange_equals_allreduce(cfg, B, dev, world, rank, comm=a.comm,
+                                                                                     exchange=exch)
+        except Exception as e:
+            self_check = {"error": "%s: %s" % (type(e).__name__, str(e)[:300])}
+
     t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -290,7 +307,7 @@ def main():
                     "api": "deepfm_b200.runtime.trainer.Trainer.train_packed (one pinned H2D copy per batch)"},
             "gpu_launches": launches, "kernels_per_step": tr.kernels_per_step,
             "l2_persist_bytes": int(getattr(getattr(tr, "model", None), "l2_persist_bytes", 0) or 0),
-            "final_loss": final_loss, "e2e_last_loss": losses[-1] if losses else None,
+            "final_loss": final_loss, "e2e_last_loss": losses[-1] if losses else None, "self_check": self_check,
         }
         print(json.dumps(out))
     if hasattr(tr, "close"):

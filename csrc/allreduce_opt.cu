@@ -30,7 +30,7 @@ struct ArOptArgs {
   float* g[kMaxRanks];             // every rank's flat gradient buffer (peer-mapped), index [rank]
   float* p[kMaxRanks];             // every rank's flat parameter buffer
   __nv_bfloat16* sh[kMaxRanks];    // every rank's bf16 shadow buffer
-  uint32_t* flags[kMaxRanks];      // every rank's flag array: [kArMaxBlocks*kMaxRanks] for A, then [kMaxRanks] for B
+  uint32_t* flags[kMaxRanks];      // every rank's flag array: [kMaxRanks] words for barrier A, then [kMaxRanks] for B
   float* reg_parts[kMaxRanks];     // every rank's [kMaxRanks] array of per-rank L2-loss partials
   float* g_mc;                     // multicast mappings (NVLS), may be null
   float* p_mc;
@@ -48,6 +48,15 @@ struct ArOptArgs {
   float* reg_local;                // scratch accumulator (1 float, zero between steps)
   unsigned int* done_counter;      // scratch (1 word, zero between steps)
   unsigned int* seq_ptr;           // barrier sequence number: monotonic, never rewound (unlike the step counter)
+  // optional result publication (all may be null): barrier A deposits *loss_local in loss_parts[rank] of every peer; the
+  // last CTA, after barrier B, writes the GLOBAL log-loss sum and the complete L2 term into scalars_out[0..1] and stores
+  // them into record (step - 1) % pub_ring of a host-mapped ring (as dfm_flat_opt_step_pub does on one GPU)
+  float* loss_parts[kMaxRanks];
+  const float* loss_local;
+  const float* reg_extra;          // optional: an L2 term this rank computed elsewhere (row-sharded tables), added to its part
+  float* scalars_out;
+  float* pub_dst;
+  int pub_ring;
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -80,12 +89,15 @@ __device__ __forceinline__ void multimem_st_bf16x4(__nv_bfloat16* p, uint2 v) {
 // its grid is not limited to what is co-resident (it runs 8 CTAs/SM like the local optimizer).
 __global__ void ar_barrier_kernel(const ArOptArgs a) {
   pdl_launch_dependents();  // let the sweep kernel's CTAs get resident; they block in pdl_wait() until this kernel exits
+  trace_min(TR_BAR_A, 1);
   const uint32_t seq = *a.seq_ptr + 1u;
   if (threadIdx.x < a.world) {
     const int peer = threadIdx.x;
+    if (a.loss_local) a.loss_parts[peer][a.rank] = *a.loss_local;  // ordered before the release below (same thread)
     st_release_sys(a.flags[peer] + a.rank, seq);
     wait_flag_geq(a.flags[a.rank] + peer, seq, peer, 0);
   }
+  trace_max(TR_BAR_A, 2);
 }
 
 template <bool NVLS>
@@ -197,7 +209,7 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
   // ---- last CTA of this rank: publish the L2-loss partial, advance the step, barrier B
   __threadfence();
   if (threadIdx.x < W) {
-    const float part = 0.5f * a.l2 * atomicAdd(a.reg_local, 0.f);
+    const float part = 0.5f * a.l2 * atomicAdd(a.reg_local, 0.f) + (a.reg_extra ? __ldcg(a.reg_extra) : 0.f);
     a.reg_parts[threadIdx.x][a.rank] = part;  // slot [rank] on every peer
   }
   __threadfence_system();
@@ -214,6 +226,24 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
     const uint32_t* bflags_mine = a.flags[a.rank] + kMaxRanks;
     st_release_sys(bflags_peer + a.rank, seq);
     wait_flag_geq(bflags_mine + peer, seq, peer, 1);
+  }
+  trace_end(TR_ALLREDUCE);
+  if (a.scalars_out) {  // every peer's loss sum (barrier A) and L2 partial (before its barrier-B release) are visible now
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float ls = 0.f, rs = 0.f;
+      for (int r = 0; r < W; ++r) {  // fixed order: the same values on every rank
+        ls += __ldcg(a.loss_parts[a.rank] + r);
+        rs += __ldcg(a.reg_parts[a.rank] + r);
+      }
+      a.scalars_out[0] = ls;
+      a.scalars_out[1] = rs;
+      if (a.pub_dst) {
+        float* rec = a.pub_dst + ((t - 1ull) % (unsigned long long)a.pub_ring) * 2ull;
+        rec[0] = ls;
+        rec[1] = rs;
+      }
+    }
   }
 }
 
@@ -268,6 +298,19 @@ int dfm_allreduce_opt_max_blocks(void) { return kArMaxBlocks; }
 
 // Pointer tables are host arrays of `world` device pointers (peer-mapped symmetric memory). mc pointers may be NULL
 // (then the P2P path is used). s0/s1: this rank's slot slices. Ranges in elements, multiples of 4.
+// loss_ptrs (host array of `world` device pointers to 8-float inboxes in symmetric memory), loss_local (this rank's
+// log-loss sum), reg_extra (an L2 term of this rank computed elsewhere, added to its partial), scalars_out (2 floats: global loss sum, L2 term) and pub_ring (pinned HOST ring of pub_ring_len records of 2
+// floats) are optional: all NULL gives the plain step.
+int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* const* sh_ptrs, void* const* flag_ptrs,
+                               void* const* reg_ptrs, void* g_mc, void* p_mc, void* sh_mc, float* s0, float* s1, int rank,
+                               int world, long long slice_begin, long long slice_end, int opt, float lr, float beta1,
+                               float beta2, float eps, float momentum, float grad_scale, long long decay_begin,
+                               long long decay_end, float l2, long long shadow_begin, long long shadow_end,
+                               unsigned long long* step_ptr, float* reg_local, unsigned int* done_counter,
+                               unsigned int* seq_ptr, int use_nvls, int grid_blocks, void* const* loss_ptrs,
+                               const float* loss_local, const float* reg_extra, float* scalars_out, float* pub_ring,
+                               int pub_ring_len, void* stream);
+
 int dfm_allreduce_opt_step(void* const* g_ptrs, void* const* p_ptrs, void* const* sh_ptrs, void* const* flag_ptrs,
                            void* const* reg_ptrs, void* g_mc, void* p_mc, void* sh_mc, float* s0, float* s1, int rank,
                            int world, long long slice_begin, long long slice_end, int opt, float lr, float beta1,
@@ -275,6 +318,25 @@ int dfm_allreduce_opt_step(void* const* g_ptrs, void* const* p_ptrs, void* const
                            long long decay_end, float l2, long long shadow_begin, long long shadow_end,
                            unsigned long long* step_ptr, float* reg_local, unsigned int* done_counter,
                            unsigned int* seq_ptr, int use_nvls, int grid_blocks, void* stream) {
+  return dfm_allreduce_opt_step_pub(g_ptrs, p_ptrs, sh_ptrs, flag_ptrs, reg_ptrs, g_mc, p_mc, sh_mc, s0, s1, rank, world,
+                                    slice_begin, slice_end, opt, lr, beta1, beta2, eps, momentum, grad_scale, decay_begin,
+                                    decay_end, l2, shadow_begin, shadow_end, step_ptr, reg_local, done_counter, seq_ptr,
+                                    use_nvls, grid_blocks, nullptr, nullptr, nullptr, nullptr, nullptr, 0, stream);
+}
+
+int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* const* sh_ptrs, void* const* flag_ptrs,
+                               void* const* reg_ptrs, void* g_mc, void* p_mc, void* sh_mc, float* s0, float* s1, int rank,
+                               int world, long long slice_begin, long long slice_end, int opt, float lr, float beta1,
+                               float beta2, float eps, float momentum, float grad_scale, long long decay_begin,
+                               long long decay_end, float l2, long long shadow_begin, long long shadow_end,
+                               unsigned long long* step_ptr, float* reg_local, unsigned int* done_counter,
+                               unsigned int* seq_ptr, int use_nvls, int grid_blocks, void* const* loss_ptrs,
+                               const float* loss_local, const float* reg_extra, float* scalars_out, float* pub_ring,
+                               int pub_ring_len, void* stream) {
+  DFM_REQUIRE((loss_ptrs == nullptr) == (loss_local == nullptr) && (loss_ptrs != nullptr || scalars_out == nullptr),
+              "allreduce_opt: loss_ptrs, loss_local (and scalars_out) go together");
+  DFM_REQUIRE(pub_ring == nullptr || (scalars_out != nullptr && pub_ring_len >= 1),
+              "allreduce_opt: publication needs scalars_out and a ring length >= 1");
   DFM_REQUIRE(world >= 1 && world <= kMaxRanks, "allreduce_opt: world size %d not in [1,%d]", world, kMaxRanks);
   DFM_REQUIRE(rank >= 0 && rank < world, "allreduce_opt: bad rank");
   DFM_REQUIRE(slice_begin % 4 == 0 && slice_end % 4 == 0 && slice_end >= slice_begin, "allreduce_opt: bad slice");
@@ -287,7 +349,9 @@ int dfm_allreduce_opt_step(void* const* g_ptrs, void* const* p_ptrs, void* const
     a.sh[r] = (__nv_bfloat16*)sh_ptrs[s];
     a.flags[r] = (uint32_t*)flag_ptrs[s];
     a.reg_parts[r] = (float*)reg_ptrs[s];
+    a.loss_parts[r] = loss_ptrs ? (float*)loss_ptrs[s] : nullptr;
   }
+  a.loss_local = loss_local; a.reg_extra = reg_extra; a.scalars_out = scalars_out; a.pub_dst = pub_ring; a.pub_ring = pub_ring_len;
   a.g_mc = (float*)g_mc; a.p_mc = (float*)p_mc; a.sh_mc = (__nv_bfloat16*)sh_mc;
   a.s0 = s0; a.s1 = s1; a.rank = rank; a.world = world;
   a.slice_begin = slice_begin; a.slice_end = slice_end;
@@ -295,11 +359,11 @@ int dfm_allreduce_opt_step(void* const* g_ptrs, void* const* p_ptrs, void* const
   a.grad_scale = grad_scale; a.decay_begin = decay_begin; a.decay_end = decay_end; a.l2 = l2;
   a.shadow_begin = shadow_begin; a.shadow_end = shadow_end;
   a.step_ptr = step_ptr; a.reg_local = reg_local; a.done_counter = done_counter; a.seq_ptr = seq_ptr;
-  // the grid must be IDENTICAL on every rank (barrier A pairs CTA b of rank r with CTA b of every peer)
+  // barrier A is the 1-CTA kernel below (flags[0..7]); barrier B runs in the sweep's last CTA (flags[8..15])
   DFM_REQUIRE(grid_blocks >= 1 && grid_blocks <= kArMaxBlocks, "allreduce_opt: grid_blocks %d not in [1,%d]",
               grid_blocks, kArMaxBlocks);
   const long long blocks = grid_blocks;
-  if (world > 1) {
+  if (world > 1 || loss_local) {  // world 1 with publication: the kernel still deposits the loss sum it later reads back
     ar_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(a);
     DFM_CHECK(cudaGetLastError());
   }

@@ -52,7 +52,7 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
 // [3] free phase stamp (max). Ids: see scripts/step_trace.py. The normal build compiles all of this away.
 enum { TR_EMB_FWD = 0, TR_FWD0 = 1, TR_LOSS = 4, TR_DGRAD0 = 5, TR_WGRAD0 = 8, TR_EMB_BWD = 11, TR_OPT = 12, TR_BITMAP = 13,
        TR_SWEEP = 14, TR_COLSUM = 15, TR_BAR_A = 16, TR_ALLREDUCE = 17, TR_BM_XCHG = 18, TR_AR_DENSE = 20, TR_AR_ROWS = 21,
-       TR_AR_FENCE = 22, TR_OPT_DENSE = 24, TR_OPT_ROWS = 25, TR_OPT_FINAL = 26, TR_MAX = 32 };
+       TR_AR_FENCE = 22, TR_OPT_DENSE = 24, TR_OPT_ROWS = 25, TR_OPT_FINAL = 26, TR_ROWLIST = 19, TR_MAX = 32 };
 #ifdef DFM_KTRACE
 extern __device__ unsigned long long g_dfm_trace[4 * TR_MAX];
 __device__ __forceinline__ void trace_min(int id, int slot) {
@@ -95,6 +95,13 @@ inline void dfm_prefer_max_shared(const void* fn) {
   if (nseen < kCap) seen[nseen++] = fn;
 }
 
+// launch_k attaches the persisting-L2 window (if one is set) to the launch; streaming kernels that touch every byte once
+// (the untouched-row sweep) switch it off for themselves: their lines must not push the step's working set out of L2.
+inline bool& dfm_launch_no_window() {
+  static thread_local bool off = false;
+  return off;
+}
+
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
   cudaLaunchConfig_t cfg = {};
@@ -106,7 +113,8 @@ inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   int na = dfm_pdl_enabled() ? 1 : 0;
-  if (const cudaAccessPolicyWindow* w = dfm_l2_window()) {
+  const cudaAccessPolicyWindow* w = dfm_launch_no_window() ? nullptr : dfm_l2_window();
+  if (w) {
     attr[na].id = cudaLaunchAttributeAccessPolicyWindow;
     attr[na].val.accessPolicyWindow = *w;
     ++na;

@@ -6,8 +6,9 @@
 //
 //   bitmap_exchange   (side stream, right after touched_bitmap)  every rank stores its touched-row bitmap (N/8 bytes) into
 //                     slot [rank] of every peer's inbox with P2P stores (or one multimem.st per word) + flag barrier C.
-//                     sweep_untouched (csrc/split_opt.cu) then ORs the W bitmaps and updates every row NO rank touched,
-//                     locally and identically on every replica (optimizer slots are replicated), off the critical path.
+//                     union_rowlist (csrc/split_opt.cu) then ORs the W bitmaps and lists the touched rows (same list on
+//                     every rank); sweep_untouched updates every row NO rank touched, locally and identically on every
+//                     replica (optimizer slots are replicated), off the critical path.
 //   barrier A         (1-CTA kernel after emb_bwd) also deposits this rank's log-loss sum in every peer (global-mean loss)
 //   sparse_allreduce  in-place all-reduce of [fm_bias block | MLP block | rows in the union bitmap]: item i is reduced by
 //                     exactly one rank — multimem.ld_reduce.add in the switch (NVLS) or peer loads summed in rank order
@@ -36,7 +37,8 @@ struct SaArgs {
   long long fmw_off, fmv_off;
   int N, nwords;
   long long d0_begin, d0_end, d1_begin, d1_end;
-  const uint32_t* bm_union;       // local union bitmap (written by sweep_untouched)
+  const int* rows;                // ascending touched-row ids (union over ranks; identical on every rank)
+  const int* row_count;
   uint32_t* bm_own;               // local live bitmap (bitmap_exchange reads and clears it)
   const float* loss_sum;          // this rank's log-loss sum
   unsigned int* done_counter;
@@ -187,49 +189,50 @@ __global__ void __launch_bounds__(kSaThreads) sparse_allreduce_kernel(const SaAr
   }
 
   trace_max(TR_AR_DENSE, 2);
-  // ---- touched rows: bitmap words dealt round-robin to ranks (touched rows cluster), one warp per word
+  // ---- touched rows: the row list (identical on every rank) split into W equal runs; one thread per (row, 16-byte
+  // chunk), two items in flight per thread
   {
-    constexpr int RPI = 32 / G;
-    const int warps_per_cta = kSaThreads / 32;
-    const int gw = blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
-    for (int k = gw; ; k += gridDim.x * warps_per_cta) {
-      const int wi = k * W + a.rank;
-      if (wi >= a.nwords) break;
-      const int row0 = wi * 32;
-      const int nrows = min(32, a.N - row0);
-      uint32_t u = __ldcg(a.bm_union + wi);
-      if (nrows < 32) u &= (1u << nrows) - 1u;
-      if (u == 0u) continue;
-      if ((u >> lane) & 1u) {  // first-order weight gradient: one scalar per touched row
-        const long long e = a.fmw_off + row0 + lane;
-        if constexpr (NVLS) {
-          sa_mm_st_f1(a.g_mc + e, sa_mm_ld_reduce_f1(a.g_mc + e));
-        } else {
-          float acc = 0.f;
+    const long long count = __ldcg(a.row_count);
+    const long long per = (count + W - 1) / W;
+    const long long lo = (long long)a.rank * per * G, hi = min(count, (long long)(a.rank + 1) * per) * G;
+    const long long stride = (long long)gridDim.x * kSaThreads;
+    auto one = [&](long long it, long long& e4, long long& e1) {
+      const int r = __ldcg(a.rows + it / G);
+      const int c = (int)(it % G);
+      e4 = a.fmv_off + ((long long)r * G + c) * 4;
+      e1 = c == 0 ? a.fmw_off + r : -1;  // the row's first-order gradient rides with chunk 0
+    };
+    auto scalar = [&](long long e) {
+      if constexpr (NVLS) {
+        sa_mm_st_f1(a.g_mc + e, sa_mm_ld_reduce_f1(a.g_mc + e));
+      } else {
+        float acc = 0.f;
 #pragma unroll
-          for (int r = 0; r < kSaMaxRanks; ++r)
-            if (r < W) acc += sa_ld_volatile_f1(a.g[r] + e);
+        for (int r = 0; r < kSaMaxRanks; ++r)
+          if (r < W) acc += sa_ld_volatile_f1(a.g[r] + e);
 #pragma unroll
-          for (int r = 0; r < kSaMaxRanks; ++r)
-            if (r < W) a.g[r][e] = acc;
-        }
+        for (int r = 0; r < kSaMaxRanks; ++r)
+          if (r < W) a.g[r][e] = acc;
       }
-      const int cnt = __popc(u);
-      const int q = lane / G, c = lane % G;
-      for (int k0 = 0; k0 < cnt; k0 += 2 * RPI) {  // two row groups in flight per warp
-        const int ka = k0 + q, kb = k0 + RPI + q;
-        long long ea = -1, eb = -1;
-        if (ka < cnt) ea = a.fmv_off + ((long long)(row0 + __fns(u, 0, ka + 1)) * G + c) * 4;
-        if (kb < cnt) eb = a.fmv_off + ((long long)(row0 + __fns(u, 0, kb + 1)) * G + c) * 4;
-        float4 va, vb;
-        if (ea >= 0) va = reduce4(ea);
-        if (eb >= 0) vb = reduce4(eb);
-        if (ea >= 0) store4(ea, va);
-        if (eb >= 0) store4(eb, vb);
-      }
+    };
+    long long it = lo + (long long)blockIdx.x * kSaThreads + threadIdx.x;
+    for (; it + stride < hi; it += 2 * stride) {
+      long long ea, sa_, eb, sb_;
+      one(it, ea, sa_);
+      one(it + stride, eb, sb_);
+      const float4 va = reduce4(ea), vb = reduce4(eb);
+      store4(ea, va);
+      store4(eb, vb);
+      if (sa_ >= 0) scalar(sa_);
+      if (sb_ >= 0) scalar(sb_);
+    }
+    for (; it < hi; it += stride) {
+      long long ea, sa_;
+      one(it, ea, sa_);
+      store4(ea, reduce4(ea));
+      if (sa_ >= 0) scalar(sa_);
     }
   }
-
   trace_max(TR_AR_ROWS, 2);
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -298,12 +301,12 @@ int dfm_bitmap_exchange(void* const* bm_ptrs, void* bm_mc, void* const* flag_ptr
 }
 
 // Barrier A (deposits *loss_sum into loss_parts[rank] of every peer) + in-place all-reduce of the dense ranges d0 | d1 and
-// of the fm_w / fm_v entries of every row set in bm_union, over the peer-mapped gradient buffers (g_ptrs; g_mc = NVLS
-// multicast mapping or NULL) + barrier B. Every rank must pass the same ranges, N, K and grid_blocks and hold the same
-// bm_union. seq_ab: one zero-initialised device word (advanced by the kernel). done_counter: zeroed scratch word.
+// of the fm_w / fm_v entries of the rows rows[0 .. *row_count) (dfm_union_rowlist), over the peer-mapped gradient buffers
+// (g_ptrs; g_mc = NVLS multicast mapping or NULL) + barrier B. Every rank must pass the same ranges, N, K and hold the same
+// row list. seq_ab: one zero-initialised device word (advanced by the kernel). done_counter: zeroed scratch word.
 int dfm_sparse_allreduce(void* const* g_ptrs, void* g_mc, void* const* flag_ptrs, void* const* loss_ptrs, int rank,
                          int world, long long fmw_off, long long fmv_off, int N, int K, long long d0_begin,
-                         long long d0_end, long long d1_begin, long long d1_end, const unsigned int* bm_union,
+                         long long d0_end, long long d1_begin, long long d1_end, const int* rows, const int* row_count,
                          const float* loss_sum, unsigned int* done_counter, unsigned int* seq_ab, int use_nvls,
                          int grid_blocks, void* stream) {
   DFM_REQUIRE(world >= 1 && world <= kSaMaxRanks && rank >= 0 && rank < world, "sparse_allreduce: bad rank/world");
@@ -315,7 +318,7 @@ int dfm_sparse_allreduce(void* const* g_ptrs, void* g_mc, void* const* flag_ptrs
   fill_ptrs(a, g_ptrs, flag_ptrs, loss_ptrs, nullptr, rank, world);
   a.g_mc = (float*)g_mc; a.fmw_off = fmw_off; a.fmv_off = fmv_off; a.N = N; a.nwords = (N + 31) / 32;
   a.d0_begin = d0_begin; a.d0_end = d0_end; a.d1_begin = d1_begin; a.d1_end = d1_end;
-  a.bm_union = bm_union; a.loss_sum = loss_sum; a.done_counter = done_counter; a.seq_ab = seq_ab;
+  a.rows = rows; a.row_count = row_count; a.loss_sum = loss_sum; a.done_counter = done_counter; a.seq_ab = seq_ab;
   cudaStream_t st = (cudaStream_t)stream;
   DFM_CHECK(launch_k(sa_barrier_a_kernel, dim3(1), dim3(32), 0, st, a));
   switch (K) {

@@ -47,6 +47,8 @@ struct SplitOptArgs {
   int world;
   int clear_inputs;              // sweep: zero bm_in[0] after reading it (single GPU: the input IS the live bitmap)
   uint32_t* bm_union;
+  int* rows;                     // ascending ids of the rows set in bm_union (built by union_rowlist), capacity N
+  int* row_count;                // number of entries in `rows`
   // tail only
   float* loss_sum;               // this rank's log-loss sum (scalars[0]); overwritten with the global sum when world > 1
   const float* loss_parts;       // [world] per-rank sums deposited by the peers (world > 1)
@@ -54,6 +56,7 @@ struct SplitOptArgs {
   float* pub_dst;
   int pub_n, pub_ring;
   int do_dense, do_sparse, finalize;
+  int dense_ctas;                // tail with both parts: CTAs [0, dense_ctas) take the dense ranges, the rest the rows
 };
 
 __device__ __forceinline__ void upd4(const SplitOptArgs& a, float lr_t, float4& w, float4 g, float4& s0, float4& s1,
@@ -102,8 +105,79 @@ __global__ void __launch_bounds__(256) touched_bitmap_kernel(const int* __restri
   }
 }
 
+// ------------------------------------------------------------------------------------------------ union + row list
+// ONE CTA: OR of the per-rank bitmaps -> bm_union, and the ascending list of touched rows (block prefix sum over the word
+// popcounts) -> rows[0 .. *row_count). Deterministic, so every rank derives the same list from the same bitmaps and the
+// exchange can split it by position. Off the critical path (side branch), latency-bound: ~3 us at N = 117581. The list is
+// what lets the tail and the exchange give every touched row its own threads at once; walking the bitmap word by word made
+// a warp chain 2-4 dependent DRAM round trips per word (measured: 14 us for 20 K rows).
+constexpr int kRowlistThreads = 1024;
+__global__ void __launch_bounds__(kRowlistThreads) union_rowlist_kernel(const SplitOptArgs a) {
+  __shared__ int s_warp[kRowlistThreads / 32];
+  pdl_launch_dependents();
+  pdl_wait(TR_ROWLIST);
+  const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+  const int wpt = (a.nwords + kRowlistThreads - 1) / kRowlistThreads;  // consecutive words per thread
+  const int w_begin = t * wpt, w_end = min(a.nwords, w_begin + wpt);
+  int cnt = 0;
+  constexpr int kChunk = 8;  // words whose loads (x world) are in flight together
+  for (int w0 = w_begin; w0 < w_end; w0 += kChunk) {
+    uint32_t u[kChunk];
+#pragma unroll
+    for (int j = 0; j < kChunk; ++j) {
+      u[j] = 0;
+      if (w0 + j < w_end) {
+#pragma unroll
+        for (int r = 0; r < kSplitMaxRanks; ++r)
+          if (r < a.world) u[j] |= __ldcg(a.bm_in[r] + w0 + j);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < kChunk; ++j) {
+      const int wi = w0 + j;
+      if (wi < w_end) {
+        const int nrows = min(32, a.N - wi * 32);
+        if (nrows < 32) u[j] &= (1u << nrows) - 1u;
+        a.bm_union[wi] = u[j];
+        if (a.clear_inputs) const_cast<uint32_t*>(a.bm_in[0])[wi] = 0u;
+        cnt += __popc(u[j]);
+      }
+    }
+  }
+  // exclusive block scan of cnt
+  int incl = cnt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    int v = s_warp[lane];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int x = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += x;
+    }
+    s_warp[lane] = v;  // inclusive over warps
+  }
+  __syncthreads();
+  int pos = incl - cnt + (warp > 0 ? s_warp[warp - 1] : 0);
+  for (int wi = w_begin; wi < w_end; ++wi) {
+    uint32_t u = a.bm_union[wi];
+    while (u) {
+      const int b = __ffs(u) - 1;
+      u &= u - 1;
+      a.rows[pos++] = wi * 32 + b;
+    }
+  }
+  if (t == kRowlistThreads - 1) *a.row_count = pos;
+  trace_end(TR_ROWLIST);
+}
+
 // ------------------------------------------------------------------------------------------------ untouched sweep
-// One warp per bitmap word = 32 consecutive table rows: union of the per-rank words, then the rows whose bit is clear.
+// One warp per word of the union bitmap = 32 consecutive table rows: the rows whose bit is clear.
 template <int G>
 __global__ void __launch_bounds__(kSplitThreads) sweep_untouched_kernel(const SplitOptArgs a) {
   __shared__ float s_lr;
@@ -120,15 +194,7 @@ __global__ void __launch_bounds__(kSplitThreads) sweep_untouched_kernel(const Sp
   const int warps_per_cta = kSplitThreads / 32;
   float reg = 0.f;
   for (int wi = blockIdx.x * warps_per_cta + (threadIdx.x >> 5); wi < a.nwords; wi += gridDim.x * warps_per_cta) {
-    uint32_t u = 0;
-#pragma unroll
-    for (int r = 0; r < kSplitMaxRanks; ++r)
-      if (r < a.world && lane == r) u = __ldcg(a.bm_in[r] + wi);
-    u = __reduce_or_sync(0xffffffffu, u);
-    if (lane == 0) {
-      a.bm_union[wi] = u;
-      if (a.clear_inputs) const_cast<uint32_t*>(a.bm_in[0])[wi] = 0u;
-    }
+    const uint32_t u = __ldcg(a.bm_union + wi);
     const int row0 = wi * 32;
     const int nrows = min(32, a.N - row0);
     // first-order weights: lane j <-> row row0 + j
@@ -159,10 +225,10 @@ __global__ void __launch_bounds__(kSplitThreads) sweep_untouched_kernel(const Sp
         const int r = c / G;
         on[k] = (it0 + k) < G && r < nrows && !((u >> r) & 1u);
         w[k] = s0[k] = s1[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (on[k]) {
-          w[k] = W4[c];
-          if (nslots > 0) s0[k] = S04[c];
-          if (nslots > 1) s1[k] = S14[c];
+        if (on[k]) {  // streaming (evict-first) accesses: every line is touched once per step
+          w[k] = __ldcs(W4 + c);
+          if (nslots > 0) s0[k] = __ldcs(S04 + c);
+          if (nslots > 1) s1[k] = __ldcs(S14 + c);
         }
       }
 #pragma unroll
@@ -170,9 +236,9 @@ __global__ void __launch_bounds__(kSplitThreads) sweep_untouched_kernel(const Sp
         if (on[k]) {
           const int c = (it0 + k) * 32 + lane;
           upd4(a, lr_t, w[k], make_float4(0.f, 0.f, 0.f, 0.f), s0[k], s1[k], decay, reg);
-          W4[c] = w[k];
-          if (nslots > 0) S04[c] = s0[k];
-          if (nslots > 1) S14[c] = s1[k];
+          __stcs(W4 + c, w[k]);
+          if (nslots > 0) __stcs(S04 + c, s0[k]);
+          if (nslots > 1) __stcs(S14 + c, s1[k]);
         }
       }
     }
@@ -199,9 +265,13 @@ __global__ void __launch_bounds__(kSplitThreads) tail_opt_kernel(const SplitOptA
   float reg = 0.f;
   const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
 
-  if (a.do_dense) {
+  // the first `dense_ctas` CTAs sweep the dense ranges, the others take one bitmap word (32 table rows) per warp: the two
+  // parts run side by side (run one after the other in every CTA, the row part — a chain of dependent DRAM round trips per
+  // word — added 13 us behind the dense part's 6)
+  const int dense_ctas = a.do_dense ? (a.do_sparse ? a.dense_ctas : (int)gridDim.x) : 0;
+  if (a.do_dense && (int)blockIdx.x < dense_ctas) {
     const long long n0 = (a.d0_end - a.d0_begin) >> 2, n1 = (a.d1_end - a.d1_begin) >> 2;
-    const long long stride = (long long)gridDim.x * kSplitThreads, n = n0 + n1;
+    const long long stride = (long long)dense_ctas * kSplitThreads, n = n0 + n1;
     auto index_of = [&](long long j) { return j < n0 ? (a.d0_begin >> 2) + j : (a.d1_begin >> 2) + (j - n0); };
     constexpr int UD = 2;  // float4 per thread in flight (x 4 arrays)
     for (long long j0 = (long long)blockIdx.x * kSplitThreads + threadIdx.x; j0 < n; j0 += stride * UD) {
@@ -239,63 +309,44 @@ __global__ void __launch_bounds__(kSplitThreads) tail_opt_kernel(const SplitOptA
     }
   }
 
-  trace_max(TR_OPT_DENSE, 2);
-  if (a.do_sparse) {
-    constexpr int RPI = 32 / G;  // rows per warp iteration (G lanes per row)
-    const int warps_per_cta = kSplitThreads / 32;
-    for (int wi = blockIdx.x * warps_per_cta + (threadIdx.x >> 5); wi < a.nwords; wi += gridDim.x * warps_per_cta) {
-      const int row0 = wi * 32;
-      const int nrows = min(32, a.N - row0);
-      uint32_t u = __ldcg(a.bm_union + wi);
-      if (nrows < 32) u &= (1u << nrows) - 1u;
-      if (u == 0u) continue;  // warp-uniform
-      if ((u >> lane) & 1u) {
-        const long long e = a.fmw_off + row0 + lane;
-        float w = a.w[e], g = a.g[e] * a.grad_scale;
-        float s0 = nslots > 0 ? a.s0[e] : 0.f, s1 = nslots > 1 ? a.s1[e] : 0.f;
-        if (decay) { reg += w * w; g += a.l2 * w; }
-        opt_update(a.h, lr_t, g, w, s0, s1);
-        a.w[e] = w;
-        a.g[e] = 0.f;
-        if (nslots > 0) a.s0[e] = s0;
-        if (nslots > 1) a.s1[e] = s1;
+  if ((int)blockIdx.x < dense_ctas) trace_max(TR_OPT_DENSE, 2);
+  if (a.do_sparse && (int)blockIdx.x >= dense_ctas) {
+    // one thread per (touched row, 16-byte chunk), straight off the row list: every row of the step is in flight at once
+    const long long items = (long long)__ldcg(a.row_count) * G;
+    const long long stride = (long long)((int)gridDim.x - dense_ctas) * kSplitThreads;
+    for (long long it = (long long)((int)blockIdx.x - dense_ctas) * kSplitThreads + threadIdx.x; it < items; it += stride) {
+      const int r = __ldcg(a.rows + it / G);
+      const int c = (int)(it % G);
+      const long long i = (a.fmv_off >> 2) + (long long)r * G + c;
+      float4 w = reinterpret_cast<float4*>(a.w)[i];
+      const float4 g = reinterpret_cast<float4*>(a.g)[i];
+      float4 s0 = nslots > 0 ? reinterpret_cast<float4*>(a.s0)[i] : z4;
+      float4 s1 = nslots > 1 ? reinterpret_cast<float4*>(a.s1)[i] : z4;
+      float w1 = 0.f, g1 = 0.f, s01 = 0.f, s11 = 0.f;
+      const long long e1 = a.fmw_off + r;
+      if (c == 0) {  // the row's first-order weight rides with chunk 0
+        w1 = a.w[e1];
+        g1 = a.g[e1] * a.grad_scale;
+        if (nslots > 0) s01 = a.s0[e1];
+        if (nslots > 1) s11 = a.s1[e1];
       }
-      const int cnt = __popc(u);
-      const int q = lane / G, c = lane % G;
-      // UR row groups in flight per warp: a fully touched word (the hot head of a field's id range) is 32 rows = 32/RPI
-      // groups; one group at a time made its warp the kernel's critical path (one DRAM round trip per group)
-      constexpr int UR = 4;
-      for (int k0 = 0; k0 < cnt; k0 += UR * RPI) {
-        long long idx[UR];
-        float4 w[UR], g[UR], s0[UR], s1[UR];
-#pragma unroll
-        for (int x = 0; x < UR; ++x) {
-          const int k = k0 + x * RPI + q;
-          idx[x] = -1;
-          w[x] = g[x] = s0[x] = s1[x] = z4;
-          if (k < cnt) {
-            idx[x] = (a.fmv_off >> 2) + (long long)(row0 + __fns(u, 0, k + 1)) * G + c;
-            w[x] = reinterpret_cast<float4*>(a.w)[idx[x]];
-            g[x] = reinterpret_cast<float4*>(a.g)[idx[x]];
-            if (nslots > 0) s0[x] = reinterpret_cast<float4*>(a.s0)[idx[x]];
-            if (nslots > 1) s1[x] = reinterpret_cast<float4*>(a.s1)[idx[x]];
-          }
-        }
-#pragma unroll
-        for (int x = 0; x < UR; ++x) {
-          if (idx[x] >= 0) {
-            upd4(a, lr_t, w[x], g[x], s0[x], s1[x], decay, reg);
-            reinterpret_cast<float4*>(a.w)[idx[x]] = w[x];
-            reinterpret_cast<float4*>(a.g)[idx[x]] = z4;
-            if (nslots > 0) reinterpret_cast<float4*>(a.s0)[idx[x]] = s0[x];
-            if (nslots > 1) reinterpret_cast<float4*>(a.s1)[idx[x]] = s1[x];
-          }
-        }
+      upd4(a, lr_t, w, g, s0, s1, decay, reg);
+      reinterpret_cast<float4*>(a.w)[i] = w;
+      reinterpret_cast<float4*>(a.g)[i] = z4;
+      if (nslots > 0) reinterpret_cast<float4*>(a.s0)[i] = s0;
+      if (nslots > 1) reinterpret_cast<float4*>(a.s1)[i] = s1;
+      if (c == 0) {
+        if (decay) { reg += w1 * w1; g1 += a.l2 * w1; }
+        opt_update(a.h, lr_t, g1, w1, s01, s11);
+        a.w[e1] = w1;
+        a.g[e1] = 0.f;
+        if (nslots > 0) a.s0[e1] = s01;
+        if (nslots > 1) a.s1[e1] = s11;
       }
     }
   }
 
-  trace_max(TR_OPT_ROWS, 2);
+  if ((int)blockIdx.x >= dense_ctas) trace_max(TR_OPT_ROWS, 2);
   const float tot = block_sum_to_thread0(reg, s_red);
   if (threadIdx.x == 0) {
     if (tot != 0.f) atomicAdd(a.reg_acc, tot);
@@ -328,7 +379,10 @@ __global__ void __launch_bounds__(kSplitThreads) tail_opt_kernel(const SplitOptA
 template <int G>
 static int launch_sweep(const SplitOptArgs& a, int blocks, cudaStream_t st) {
   dfm_prefer_max_shared(reinterpret_cast<const void*>(sweep_untouched_kernel<G>));
-  DFM_CHECK(launch_k(sweep_untouched_kernel<G>, dim3((unsigned)blocks), dim3(kSplitThreads), 0, st, a));
+  dfm_launch_no_window() = true;
+  const cudaError_t e = launch_k(sweep_untouched_kernel<G>, dim3((unsigned)blocks), dim3(kSplitThreads), 0, st, a);
+  dfm_launch_no_window() = false;
+  DFM_CHECK(e);
   return DFM_OK;
 }
 template <int G>
@@ -381,19 +435,31 @@ static int fill_common(SplitOptArgs& a, float* w, float* g, float* s0, float* s1
   return DFM_OK;
 }
 
-// Sweep of the rows whose bit is clear in the union of `world` bitmaps (bm_in: host array of device pointers, each
-// ceil(N/32) words); writes the union to bm_union; adds sum(w^2) of the swept rows to *reg_acc (when l2 != 0).
+// bm_union = OR of `world` bitmaps (bm_in: host array of device pointers, each ceil(N/32) words; bm_in[0] is zeroed
+// afterwards when clear_inputs != 0), rows[0 .. *row_count) = ascending ids of the rows set in it. One CTA.
+int dfm_union_rowlist(const void* const* bm_in, int world, int clear_inputs, int N, unsigned int* bm_union, int* rows,
+                      int* row_count, void* stream) {
+  DFM_REQUIRE(world >= 1 && world <= kSplitMaxRanks, "union_rowlist: world %d not in [1,%d]", world, kSplitMaxRanks);
+  DFM_REQUIRE(N > 0 && bm_union && rows && row_count, "union_rowlist: empty problem or null pointer");
+  SplitOptArgs a = SplitOptArgs();
+  for (int r = 0; r < kSplitMaxRanks; ++r) a.bm_in[r] = (const uint32_t*)bm_in[r < world ? r : 0];
+  a.world = world; a.clear_inputs = clear_inputs; a.N = N; a.nwords = (N + 31) / 32;
+  a.bm_union = bm_union; a.rows = rows; a.row_count = row_count;
+  dfm_prefer_max_shared(reinterpret_cast<const void*>(union_rowlist_kernel));
+  DFM_CHECK(launch_k(union_rowlist_kernel, dim3(1), dim3(kRowlistThreads), 0, (cudaStream_t)stream, a));
+  return DFM_OK;
+}
+
+// Sweep of the rows whose bit is clear in bm_union; adds sum(w^2) of the swept rows to *reg_acc (when l2 != 0).
 int dfm_sweep_untouched(float* w, float* s0, float* s1, int opt, float lr, float beta1, float beta2, float eps,
                         float momentum, float l2, long long fmw_off, long long fmv_off, int N, int K,
-                        const void* const* bm_in, int world, int clear_inputs, unsigned int* bm_union,
-                        unsigned long long* step_ptr, float* reg_acc, int grid_blocks, void* stream) {
-  DFM_REQUIRE(world >= 1 && world <= kSplitMaxRanks, "sweep_untouched: world %d not in [1,%d]", world, kSplitMaxRanks);
+                        const unsigned int* bm_union, unsigned long long* step_ptr, float* reg_acc, int grid_blocks,
+                        void* stream) {
   SplitOptArgs a;
   int rc = fill_common(a, w, nullptr, s0, s1, opt, lr, beta1, beta2, eps, momentum, 1.f, l2, fmw_off, fmv_off, N, K,
                        step_ptr, reg_acc);
   if (rc) return rc;
-  for (int r = 0; r < kSplitMaxRanks; ++r) a.bm_in[r] = (const uint32_t*)bm_in[r < world ? r : 0];
-  a.world = world; a.clear_inputs = clear_inputs; a.bm_union = bm_union;
+  a.bm_union = const_cast<uint32_t*>(bm_union);
   int blocks = grid_blocks > 0 ? grid_blocks : ceil_div(a.nwords, kSplitThreads / 32);
   if (blocks > 148 * 4) blocks = 148 * 4;
   cudaStream_t st = (cudaStream_t)stream;
@@ -402,14 +468,14 @@ int dfm_sweep_untouched(float* w, float* s0, float* s1, int opt, float lr, float
 #undef CALL
 }
 
-// Tail: dense ranges d0 / d1 (elements, multiples of 4; either may be empty) + the rows set in bm_union; zeroes the
+// Tail: dense ranges d0 / d1 (elements, multiples of 4; either may be empty) + the rows rows[0 .. *row_count); zeroes the
 // gradients it consumes. finalize != 0: the last CTA writes *reg_loss = 0.5 * l2 * *reg_acc (and resets reg_acc), replaces
 // *loss_sum by the sum of loss_parts[0..world) when world > 1, advances *step_ptr and stores pub_n floats from pub_src into
 // record (step - 1) % pub_ring_len of pub_ring (pinned host memory; may be null).
 int dfm_tail_opt(float* w, float* g, float* s0, float* s1, int opt, float lr, float beta1, float beta2, float eps,
                  float momentum, float grad_scale, float l2, long long fmw_off, long long fmv_off, int N, int K,
                  long long d0_begin, long long d0_end, long long d1_begin, long long d1_end, long long shadow_begin,
-                 long long shadow_end, void* shadow, const unsigned int* bm_union, unsigned long long* step_ptr,
+                 long long shadow_end, void* shadow, const int* rows, const int* row_count, unsigned long long* step_ptr,
                  float* reg_acc, float* reg_loss, unsigned int* done_counter, float* loss_sum, const float* loss_parts,
                  int world, const float* pub_src, int pub_n, float* pub_ring, int pub_ring_len, int do_dense,
                  int do_sparse, int finalize, void* stream) {
@@ -424,18 +490,25 @@ int dfm_tail_opt(float* w, float* g, float* s0, float* s1, int opt, float lr, fl
   if (rc) return rc;
   a.d0_begin = d0_begin; a.d0_end = d0_end; a.d1_begin = d1_begin; a.d1_end = d1_end;
   a.shadow_begin = shadow_begin; a.shadow_end = shadow_end; a.shadow = (__nv_bfloat16*)shadow;
-  a.bm_union = const_cast<uint32_t*>(bm_union); a.reg_loss = reg_loss; a.done_counter = done_counter;
+  a.rows = const_cast<int*>(rows); a.row_count = const_cast<int*>(row_count); a.reg_loss = reg_loss;
+  a.done_counter = done_counter;
   a.loss_sum = loss_sum; a.loss_parts = loss_parts; a.world = world;
   a.pub_src = pub_src; a.pub_dst = pub_ring; a.pub_n = pub_n; a.pub_ring = pub_ring_len;
   a.do_dense = do_dense; a.do_sparse = do_sparse; a.finalize = finalize;
-  long long work = 0;
-  if (do_dense) work += ((d0_end - d0_begin) + (d1_end - d1_begin)) / 4;
-  long long blocks = ceil_div_ll(work, kSplitThreads);
-  if (do_sparse) blocks = blocks > ceil_div(a.nwords, kSplitThreads / 32) ? blocks : ceil_div(a.nwords, kSplitThreads / 32);
+  // dense part: 2 CTAs per SM, two float4 x 4 arrays in flight per thread; row part: one warp per bitmap word
+  long long dense_blocks = 0, row_blocks = 0;
+  if (do_dense) {
+    dense_blocks = ceil_div_ll(((d0_end - d0_begin) + (d1_end - d1_begin)) / 4, kSplitThreads * 2);
+    if (dense_blocks > 148 * 2) dense_blocks = 148 * 2;
+    if (dense_blocks < 1) dense_blocks = 1;
+  }
+  if (do_sparse) {  // the row count is only known on the device: enough CTAs for one (row, chunk) item per thread up to
+    row_blocks = ceil_div_ll((long long)N * a.G, kSplitThreads);  // 4 CTAs per SM, grid-stride beyond that
+    if (row_blocks > 148 * 4) row_blocks = 148 * 4;
+  }
+  a.dense_ctas = (int)dense_blocks;
+  long long blocks = dense_blocks + row_blocks;
   if (blocks < 1) blocks = 1;
-  // two CTAs per SM, grid-stride: every CTA ends with same-address atomics (L2 loss sum, completion counter), which
-  // serialise at ~10-20 ns each; with one CTA per 256 float4 (920 CTAs) they were most of the kernel's 17 us
-  if (blocks > 148 * 2) blocks = 148 * 2;
   cudaStream_t st = (cudaStream_t)stream;
 #define CALL(G) launch_tail<G>(a, (int)blocks, st)
   DFM_SPLIT_DISPATCH(K, CALL)

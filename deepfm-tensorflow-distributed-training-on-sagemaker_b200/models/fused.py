@@ -170,11 +170,20 @@ class FusedDeepFM:
     def _slot_numel(self) -> int:
         return self.layout.trainable_numel
 
+    def _wgrad_streams(self, n: int):
+        st = getattr(self, "_wg_streams", None)
+        if st is None or len(st) < n:
+            st = self._wg_streams = [self._side] + [torch.cuda.Stream(device=self.dev) for _ in range(n - 1)]
+        return st[:n]
+
     def _want_split(self) -> bool:
-        """Split dense optimizer (csrc/split_opt.cu): needs the tables in the flat buffer; DFM_SPLIT_OPT=0 keeps the
-        single fused sweep (flat_opt) at the end of the step."""
+        """Split dense optimizer (csrc/split_opt.cu; needs the tables in the flat buffer). Off by default on one GPU
+        (DFM_SPLIT_OPT=1 turns it on): measured on a B200 at batch 1024 the tail (MLP block + 20 K touched rows, random
+        128-byte accesses at ~2 TB/s) is 16-17 us against 20 us for the single streaming sweep, and the concurrent
+        untouched-row sweep slows the latency-bound forward/backward kernels by more than those 3-4 us (94.8 vs 92.0 us per
+        step, profiles/step_timeline.md). It pays where the sweep is the smaller part: parallel/dp_sparse.py."""
         import os
-        return self.layout.include_embeddings and os.environ.get("DFM_SPLIT_OPT", "1") != "0" \
+        return self.layout.include_embeddings and os.environ.get("DFM_SPLIT_OPT", "0") == "1" \
             and type(self)._optimizer_kernels is FusedDeepFM._optimizer_kernels
 
     def _setup_split_optimizer(self) -> None:
@@ -204,8 +213,9 @@ class FusedDeepFM:
         """Side branch of a split-optimizer step (forked at step start, joined before the tail): mark the rows this batch
         looks up, then update every other table row while forward/backward run."""
         K.touched_bitmap(slot["ids"], self.cfg.feature_size, self.bm_own)
+        self.split.union_rowlist()
         self.split.sweep()
-        return 2
+        return 3
 
     def _pre_step(self, side) -> int:
         """Hook at the start of a step (runs inside graph capture); returns #kernels it launched."""
@@ -320,31 +330,40 @@ class FusedDeepFM:
                      None if not self._fold_cols else self._g("mlp%d.bias" % top),
                      None if not self._fold_cols else self._g("deep_out.weight"))
         n += 1
-        side = self._side
+        # Weight gradients: every wgrad_i only needs dz[i] (ready before dgrad_i starts) and nothing needs it before the
+        # optimizer. They are forked late and side by side: wgrad_i of the upper layers waits until dgrad_1 is done, then
+        # all L wgrads run at once on their own branches (28 + 28 + 80 CTAs at 400-400-400: they fit the machine together)
+        # beside dgrad_0 and emb_bwd. Forked as early as possible instead, each shared the SMs, the TMA path and L2 with
+        # the dgrad chain and doubled its kernels' time (scripts/step_trace.py: dgrad 2.9 -> 5.9 us each).
+        sides = self._wgrad_streams(nl)
+        forked = False
         for i in range(top, -1, -1):
             if self.bn:  # dz[i] holds d(BN output); turn it into d(pre-activation) in place (BN + ReLU backward)
                 K.bn_bwd(self.dz[i], self.zbuf[i], self._w("bn_%d.gamma" % i), self.bn_mean[i], self.bn_rstd[i],
                          self._g("bn_%d.gamma" % i), self._g("bn_%d.beta" % i))
                 n += 1
-            # fork: wgrad (+ bias colsum) of layer i only needs dz[i]; the dgrad chain continues on `cur`
-            ev = torch.cuda.Event()
-            ev.record(cur)
-            side.wait_event(ev)
-            with torch.cuda.stream(side):
-                self.wgrad[i].run()
-                n += 1
-                if not self._fold_cols:  # batch-norm path (bn_bwd rewrites dz[i]) / very wide top layer: own pass
-                    K.colsum_bf16(self.dz[i], self._g("mlp%d.bias" % i))
-                    n += 1
-                    if i == top:  # g_w_out = X_top^T dy
-                        K.colsum_bf16(self.acts[top], self._g("deep_out.weight"), self.dy)
+            if i == 0 and not forked:  # dz[0] (and every dz above it) is final here
+                ev = torch.cuda.Event()
+                ev.record(cur)
+                for j in range(top, -1, -1):
+                    sides[j].wait_event(ev)
+                    with torch.cuda.stream(sides[j]):
+                        self.wgrad[j].run()
                         n += 1
+                        if not self._fold_cols:  # batch-norm path / very wide top layer: column sums in their own pass
+                            K.colsum_bf16(self.dz[j], self._g("mlp%d.bias" % j))
+                            n += 1
+                            if j == top:  # g_w_out = X_top^T dy
+                                K.colsum_bf16(self.acts[top], self._g("deep_out.weight"), self.dy)
+                                n += 1
+                forked = True
             self.dgrad[i].run()
             n += 1
         n += self._emb_backward(slot)
-        ev = torch.cuda.Event()
-        ev.record(side)
-        cur.wait_event(ev)  # join
+        for sd in sides:  # join
+            ev = torch.cuda.Event()
+            ev.record(sd)
+            cur.wait_event(ev)
         if split:
             ev2 = torch.cuda.Event()
             ev2.record(self._side2)

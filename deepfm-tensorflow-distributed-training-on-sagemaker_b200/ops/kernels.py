@@ -210,17 +210,24 @@ class SplitOptimizer:
         self.d0 = (0, seg_w.offset)                          # fm_bias block (padded to the segment alignment)
         self.d1 = (layout.shadow_range[0], layout.trainable_numel)  # MLP weights, biases, head, BN beta/gamma
         self.sweep_blocks = sweep_blocks
+        self.rows = torch.zeros(self.N, device=w.device, dtype=torch.int32)       # ascending touched-row ids
+        self.row_count = torch.zeros(1, device=w.device, dtype=torch.int32)
 
     def _hyper(self):
         o = self.o
         return (c_int(OPT_IDS[o.name]), c_float(o.lr), c_float(o.beta1), c_float(o.beta2), c_float(o.eps),
                 c_float(o.momentum))
 
+    def union_rowlist(self) -> None:
+        """One CTA: bm_union = OR of the input bitmaps; rows / row_count = ascending list of the rows set in it."""
+        _lib.check(_lib.load().dfm_union_rowlist(self._bm_tab, c_int(len(self._bm_in)), c_int(1 if self.clear_inputs else 0),
+                                                 c_int(self.N), _p(self.bm_union), _p(self.rows), _p(self.row_count),
+                                                 _stream()))
+
     def sweep(self) -> None:
         _lib.check(_lib.load().dfm_sweep_untouched(
             _p(self.w), _p(self.s0), _p(self.s1), *self._hyper(), c_float(self.cfg.l2_reg), c_longlong(self.fmw_off),
-            c_longlong(self.fmv_off), c_int(self.N), c_int(self.K), self._bm_tab, c_int(len(self._bm_in)),
-            c_int(1 if self.clear_inputs else 0), _p(self.bm_union), _p(self.step_ptr), _p(self.reg_acc),
+            c_longlong(self.fmv_off), c_int(self.N), c_int(self.K), _p(self.bm_union), _p(self.step_ptr), _p(self.reg_acc),
             c_int(self.sweep_blocks), _stream()))
 
     def tail(self, publish=None, grad_scale: float = 1.0, dense: bool = True, sparse: bool = True,
@@ -236,6 +243,7 @@ class SplitOptimizer:
             _p(self.w), _p(self.g), _p(self.s0), _p(self.s1), *self._hyper(), c_float(grad_scale),
             c_float(self.cfg.l2_reg), c_longlong(self.fmw_off), c_longlong(self.fmv_off), c_int(self.N), c_int(self.K),
             c_longlong(self.d0[0]), c_longlong(self.d0[1]), c_longlong(self.d1[0]), c_longlong(self.d1[1]),
-            c_longlong(sh[0]), c_longlong(sh[1]), _p(self.shadow), _p(self.bm_union), _p(self.step_ptr), _p(self.reg_acc),
+            c_longlong(sh[0]), c_longlong(sh[1]), _p(self.shadow), _p(self.rows), _p(self.row_count), _p(self.step_ptr),
+            _p(self.reg_acc),
             _p(self.reg_loss), _p(self.done), _p(self.loss_sum), _p(self.loss_parts), c_int(self.world), pub[0], pub[1],
             pub[2], pub[3], c_int(1 if dense else 0), c_int(1 if sparse else 0), c_int(1 if finalize else 0), _stream()))

@@ -81,7 +81,8 @@ class FusedDataParallel(FusedDeepFM):
         slot_n = n if self._nccl else chunk
         regions = [("P", L.total_numel, torch.float32), ("G", L.total_numel, torch.float32),
                    ("shadow", L.shadow_range[1] - L.shadow_range[0], torch.bfloat16),
-                   ("flags", lib.dfm_allreduce_opt_flag_words(), torch.int32), ("reg_parts", 8, torch.float32)]
+                   ("flags", lib.dfm_allreduce_opt_flag_words(), torch.int32), ("reg_parts", 8, torch.float32),
+                   ("loss_parts", 8, torch.float32)]
         for i in range(nslots):
             regions.append(("S%d" % i, slot_n, torch.float32))
         self.arena = SymmArena(regions, device, self.group)
@@ -90,7 +91,9 @@ class FusedDataParallel(FusedDeepFM):
                          row_offset=rank * batch_size, use_graph=use_graph)
         self.reg_local = torch.zeros(1, device=device, dtype=torch.float32)
         self.seq = torch.zeros(1, device=device, dtype=torch.int32)
-        self._tables = {k: self.arena.ptr_table(k) for k in ("G", "P", "shadow", "flags", "reg_parts")}
+        self._tables = {k: self.arena.ptr_table(k) for k in ("G", "P", "shadow", "flags", "reg_parts", "loss_parts")}
+        # the fused kernel exchanges the per-rank log-loss sums and L2 partials: what it reports is the GLOBAL batch's loss
+        self.loss_is_global = not self._nccl
         # measured on 8xB200: P2P wins at 2 ranks (55 vs 75 us per 18.8 MB step), NVLS multimem from 4 ranks up (71 vs 82 us
         # at 8): in-switch reduction pays once several peers contribute
         use_nvls = (comm == "nvls") or (comm == "auto" and self.arena.mc_ptr != 0 and world_size >= 4)
@@ -154,7 +157,8 @@ class FusedDataParallel(FusedDeepFM):
         decay = L.decay_range if self.cfg.l2_reg > 0 else (0, 0)
         t = self._tables
         st = c_void_p(torch.cuda.current_stream().cuda_stream)
-        _nlib.check(lib.dfm_allreduce_opt_step(
+        ring = getattr(self, "_result_ring", None)
+        _nlib.check(lib.dfm_allreduce_opt_step_pub(
             t["G"], t["P"], t["shadow"], t["flags"], t["reg_parts"], c_void_p(self.arena.mc("G")),
             c_void_p(self.arena.mc("P")), c_void_p(self.arena.mc("shadow")),
             c_void_p(self.S0.data_ptr() if self.S0 is not None else 0),
@@ -163,8 +167,10 @@ class FusedDataParallel(FusedDeepFM):
             c_float(o.beta2), c_float(o.eps), c_float(o.momentum), c_float(1.0), c_longlong(decay[0]),
             c_longlong(decay[1]), c_float(self.cfg.l2_reg), c_longlong(L.shadow_range[0]), c_longlong(L.shadow_range[1]),
             c_void_p(self.step_t.data_ptr()), c_void_p(self.reg_local.data_ptr()), c_void_p(self.done_counter.data_ptr()),
-            c_void_p(self.seq.data_ptr()), c_int(1 if self.use_nvls else 0), c_int(self._grid_blocks), st))
-        return 1
+            c_void_p(self.seq.data_ptr()), c_int(1 if self.use_nvls else 0), c_int(self._grid_blocks), t["loss_parts"],
+            c_void_p(self.loss_sum.data_ptr()), c_void_p(self._reg_extra_ptr()), c_void_p(self.scalars.data_ptr()),
+            c_void_p(ring.data_ptr() if ring is not None else 0), c_int(ring.shape[0] if ring is not None else 0), st))
+        return 2
 
     def _restore(self, snap):
         super()._restore(snap)
@@ -172,14 +178,23 @@ class FusedDataParallel(FusedDeepFM):
         torch.cuda.synchronize()
         dist.barrier(group=self.group)
 
+    def _reg_extra_ptr(self) -> int:
+        """Device address of an L2 term this rank computed outside the flat buffer (row-sharded tables), or 0."""
+        return 0
+
+    def set_result_ring(self, ring) -> bool:
+        """The fused kernel's last CTA stores (global log-loss sum, L2 term) of step t into ring[(t - 1) % len(ring)]."""
+        if self._nccl or self._graphs:
+            return False
+        self._result_ring = ring
+        return ring is not None
+
     def last_loss(self) -> torch.Tensor:
-        if self._nccl:
+        if self._nccl:  # baseline path: a per-rank estimate (this rank's batch scaled to the global one)
             torch.add(self.loss_sum * (self.world / self.global_batch), self.reg_loss, out=self.loss_out)
             return self.loss_out
-        # data loss: each rank holds its local sum -> the global mean needs the other ranks' sums; report the local
-        # estimate scaled to the global batch plus the L2 terms gathered by the kernel (reg_parts from every rank)
-        reg = self.arena.view("reg_parts").sum()
-        torch.add(self.loss_sum * (self.world / self.global_batch), reg, out=self.loss_out)
+        # the kernel left (global log-loss sum, complete L2 term) in scalars: the reference's loss, mean over the GLOBAL batch
+        torch.add(self.loss_sum / self.global_batch, self.reg_loss, out=self.loss_out)
         return self.loss_out
 
     # ---- state: slots are sharded; the chief assembles them through peer-mapped views (no collective needed)

@@ -211,11 +211,10 @@ class ShardedDeepFM(FusedDataParallel):
         self._tsnap = None
         super()._restore(snap)
 
-    def last_loss(self) -> torch.Tensor:
-        reg = self.reg_loss.clone()  # touched-row L2 terms of THIS rank's shard
-        torch.add(self.loss_sum * (self.world / self.global_batch), reg[0] + self.arena.view("reg_parts").sum(),
-                  out=self.loss_out)
-        return self.loss_out
+    def _reg_extra_ptr(self) -> int:
+        # touched-row L2 term of THIS rank's shard (sparse_row_opt adds it to reg_loss before the MLP exchange runs): the
+        # fused kernel adds it to this rank's partial, so the published L2 term covers every shard
+        return self.reg_loss.data_ptr()
 
     # ---- state: the chief assembles full tables through peer-mapped views
     def _gather_table(self, name: str, cols: int) -> torch.Tensor:

@@ -66,9 +66,19 @@ class Trainer:
                                            use_graph=use_graph, params=params, process_group=process_group)
                 self.comm_name = self.model.comm_name
             elif world_size > 1:
-                from ..parallel.dp import FusedDataParallel
-                self.model = FusedDataParallel(cfg, batch_size, self.opt, seed, self.dev, world_size, rank, comm=comm,
-                                               use_graph=use_graph, params=params, process_group=process_group)
+                import os as _os0
+                # default: the dense ZeRO-1 kernel (parallel/dp.py: fused reduce-scatter + sharded optimizer + all-gather);
+                # DFM_DP_EXCHANGE=sparse selects the touched-row exchange + replicated split optimizer
+                # (parallel/dp_sparse.py), which ships fewer bytes but pays random 128-byte row accesses in its tail:
+                # measured slower at this table size (2 GPUs: 141 vs 126 us/step), kept for tables where a batch touches a
+                # small fraction of the rows
+                dense = comm == "nccl" or _os0.environ.get("DFM_DP_EXCHANGE", "dense") != "sparse"
+                if dense:
+                    from ..parallel.dp import FusedDataParallel as _DP
+                else:
+                    from ..parallel.dp_sparse import SparseDataParallel as _DP
+                self.model = _DP(cfg, batch_size, self.opt, seed, self.dev, world_size, rank, comm=comm,
+                                 use_graph=use_graph, params=params, process_group=process_group)
                 self.comm_name = self.model.comm_name
             else:
                 from ..models.fused import FusedDeepFM
@@ -109,9 +119,8 @@ class Trainer:
         # native step driver (csrc/step_driver.cu): one C call per host-fed step once the slot's graph exists
         self._drv = None
         self.native_steps = 0
-        # default: on for single-GPU trainers (validated on a B200 this round); multi-rank trainers keep the Python-issued
-        # sequence unless DFM_NATIVE_STEP=1 asks for it (same code path, not yet re-measured at 2-8 ranks)
-        want = _os.environ.get("DFM_NATIVE_STEP", "1" if world_size == 1 else "0")
+        # default on (DFM_NATIVE_STEP=0 keeps the Python-issued sequence); needs the step captured in a CUDA graph
+        want = _os.environ.get("DFM_NATIVE_STEP", "1")
         if self._cuda and backend == "fused" and want != "0" and getattr(self.model, "use_graph", False):
             import ctypes
             from ..ops import lib as _nlib
@@ -309,8 +318,9 @@ class Trainer:
             torch.cuda.synchronize(self.dev)
             self.check_parse_errors()
             reg_now = None
-            if getattr(self.model, "arena", None) is not None and not getattr(self.model, "_nccl", False):
-                reg_now = float(self.model.arena.view("reg_parts").sum())  # L2 terms, gathered by the fused kernel
+            # the fused engine reports a log-loss SUM: over the global batch where the model exchanges it (the fused dp
+            # kernels), else over this rank's batch (single GPU; the NCCL baseline path: a per-rank estimate)
+            denom = float(self.model.global_batch) if getattr(self.model, "loss_is_global", False) else float(self.B)
             # published results sit at ring[(t - 1) % n] for optimizer step t = step index at issue + 1 + (device step
             # counter - host step count), the last term being the global_step restored from a checkpoint
             shift = (self.model.global_step - self.model.host_step) if (self._publish and self._pending) else 0
@@ -324,7 +334,7 @@ class Trainer:
                     b = reg_now
                 # fused: (local sum of log-loss, L2 term). Under DP the local sum is scaled to the local batch (an
                 # unbiased per-rank estimate of the global mean; the exact mean needs the other ranks' sums)
-                self._host_losses.append(a if mean_flag else a / float(self.B) + b)
+                self._host_losses.append(a if mean_flag else a / denom + b)
             self._pending = []
             self._ring_pos = 0
         if keep:

@@ -90,22 +90,25 @@ int dfm_cast_f32_bf16(const float* in, void* out_bf16, long long n, void* stream
  * critical path. touched_bitmap marks the rows a batch looks up; sweep_untouched updates every OTHER row (their gradient is
  * l2*w, nothing from backward is needed) concurrently with forward/backward; tail_opt finishes with the touched rows and the
  * dense ranges d0/d1 (fm_bias block, MLP block), zeroing the gradients it consumes. Results equal dfm_flat_opt_step.
- * bm_in: host array of `world` device pointers to per-rank bitmaps of dfm_bitmap_words(N) words (world == 1: the live
- * bitmap, cleared by the sweep when clear_inputs != 0); bm_union receives their OR. reg_acc: one zero-initialised device
- * float (sum of w^2 over the decay range; reset by the finalising tail, which writes *reg_loss = 0.5*l2*sum). */
+ * union_rowlist (one CTA) ORs `world` per-rank bitmaps of dfm_bitmap_words(N) words (bm_in: host array of device pointers;
+ * world == 1: the live bitmap, cleared when clear_inputs != 0) into bm_union and lists the set rows in ascending order
+ * (rows: N ints, *row_count entries) for the tail and the exchange. reg_acc: one zero-initialised device float (sum of w^2
+ * over the decay range; reset by the finalising tail, which writes *reg_loss = 0.5*l2*sum). */
 int dfm_bitmap_words(int N);
 int dfm_touched_bitmap(const int* ids, int B, int F, int N, unsigned int* bitmap, void* stream);
+int dfm_union_rowlist(const void* const* bm_in, int world, int clear_inputs, int N, unsigned int* bm_union, int* rows,
+                      int* row_count, void* stream);
 int dfm_sweep_untouched(float* w, float* s0, float* s1, int opt, float lr, float beta1, float beta2, float eps,
                         float momentum, float l2, long long fmw_off, long long fmv_off, int N, int K,
-                        const void* const* bm_in, int world, int clear_inputs, unsigned int* bm_union,
-                        unsigned long long* step_ptr, float* reg_acc, int grid_blocks, void* stream);
+                        const unsigned int* bm_union, unsigned long long* step_ptr, float* reg_acc, int grid_blocks,
+                        void* stream);
 int dfm_tail_opt(float* w, float* g, float* s0, float* s1, int opt, float lr, float beta1, float beta2, float eps,
                  float momentum, float grad_scale, float l2, long long fmw_off, long long fmv_off, int N, int K,
                  long long d0_begin, long long d0_end, long long d1_begin, long long d1_end, long long shadow_begin,
-                 long long shadow_end, void* shadow_bf16, const unsigned int* bm_union, unsigned long long* step_ptr,
-                 float* reg_acc, float* reg_loss, unsigned int* done_counter, float* loss_sum, const float* loss_parts,
-                 int world, const float* pub_src, int pub_n, float* pub_ring, int pub_ring_len, int do_dense,
-                 int do_sparse, int finalize, void* stream);
+                 long long shadow_end, void* shadow_bf16, const int* rows, const int* row_count,
+                 unsigned long long* step_ptr, float* reg_acc, float* reg_loss, unsigned int* done_counter,
+                 float* loss_sum, const float* loss_parts, int world, const float* pub_src, int pub_n, float* pub_ring,
+                 int pub_ring_len, int do_dense, int do_sparse, int finalize, void* stream);
 
 /* ---- gradient all-reduce fused with the optimizer step over NVLink peer memory (replaces Horovod's NCCL all-reduce
  * HVD:262 + ApplyAdam PS:269). Pointer tables: host arrays of `world` device pointers into symmetric memory; *_mc are
@@ -121,6 +124,38 @@ int dfm_allreduce_opt_step(void* const* g_ptrs, void* const* p_ptrs, void* const
                            long long decay_end, float l2, long long shadow_begin, long long shadow_end,
                            unsigned long long* step_ptr, float* reg_local, unsigned int* done_counter,
                            unsigned int* seq_ptr, int use_nvls, int grid_blocks, void* stream);
+
+/* Same step; additionally (loss_ptrs: `world` pointers to 8-float inboxes in symmetric memory) every rank's log-loss sum
+ * is exchanged at barrier A (reg_extra: optional L2 term of this rank from elsewhere, added to its partial) and the last
+ * CTA writes (global loss sum, complete L2 term) to scalars_out[0..1] and into record
+ * (step - 1) % pub_ring_len of pub_ring (page-locked HOST memory, 2 floats per record; NULL = no publication). */
+int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* const* sh_ptrs, void* const* flag_ptrs,
+                               void* const* reg_ptrs, void* g_mc, void* p_mc, void* sh_mc, float* s0, float* s1, int rank,
+                               int world, long long slice_begin, long long slice_end, int opt, float lr, float beta1,
+                               float beta2, float eps, float momentum, float grad_scale, long long decay_begin,
+                               long long decay_end, float l2, long long shadow_begin, long long shadow_end,
+                               unsigned long long* step_ptr, float* reg_local, unsigned int* done_counter,
+                               unsigned int* seq_ptr, int use_nvls, int grid_blocks, void* const* loss_ptrs,
+                               const float* loss_local, const float* reg_extra, float* scalars_out, float* pub_ring,
+                               int pub_ring_len, void* stream);
+
+/* ---- data-parallel exchange for replicated tables that ships only what differs between ranks (csrc/sparse_allreduce.cu;
+ * replaces Horovod's dense NCCL all-reduce, HVD:262). bitmap_exchange: this rank's touched-row bitmap (bm_own, cleared
+ * afterwards) into slot [rank] of every rank's [8][words] inbox + flag barrier; then dfm_union_rowlist / dfm_sweep_untouched
+ * (above). sparse_allreduce: barrier A (deposits *loss_sum in loss_parts[rank] of every peer), in-place all-reduce of the
+ * dense ranges d0 | d1 and of the fm_w / fm_v entries of rows[0 .. *row_count) — each item reduced by one rank
+ * (multimem.ld_reduce, or peer loads in rank order) and stored into every rank's buffer — then barrier B. Pointer tables:
+ * host arrays of `world` device pointers into symmetric memory; *_mc: NVLS multicast mappings or NULL; flags:
+ * dfm_sparse_allreduce_flag_words() zeroed uint32 per rank; seq_*: one zeroed device word each (advanced by the kernels);
+ * done_counter: one zeroed scratch word per entry point. */
+int dfm_sparse_allreduce_flag_words(void);
+int dfm_bitmap_exchange(void* const* bm_ptrs, void* bm_mc, void* const* flag_ptrs, unsigned int* bm_own, int N, int rank,
+                        int world, unsigned int* done_counter, unsigned int* seq_c, int use_nvls, void* stream);
+int dfm_sparse_allreduce(void* const* g_ptrs, void* g_mc, void* const* flag_ptrs, void* const* loss_ptrs, int rank,
+                         int world, long long fmw_off, long long fmv_off, int N, int K, long long d0_begin,
+                         long long d0_end, long long d1_begin, long long d1_end, const int* rows, const int* row_count,
+                         const float* loss_sum, unsigned int* done_counter, unsigned int* seq_ab, int use_nvls,
+                         int grid_blocks, void* stream);
 
 /* ---- state broadcast from one rank into every replica (replaces BroadcastGlobalVariablesHook(0), HVD:372) */
 int dfm_bcast_f32(void* const* ptrs, void* mc, long long n, int rank, int world, int use_nvls, void* stream);

@@ -1,6 +1,19 @@
-"""Multi-GPU check (run under torchrun): FusedDataParallel on W shards of a batch == the oracle on the whole batch,
-for comm in {p2p, nvls (if offered), nccl}; prints device-timed us/step for each."""
-import os, sys, json
+"""Multi-GPU check (run under torchrun): data parallelism on W shards of a batch == the oracle on the whole batch, for
+the sparse touched-row exchange (default) and the dense ZeRO-1 kernel, over p2p / nvls (if offered) / nccl.
+
+Checked per (exchange, comm):
+  1. gradient level: sum over ranks of the per-rank gradients (forward+backward kernels only) == autograd of the
+     bf16-emulating oracle on the concatenated batch, every tensor within 2e-2 of its max (as on one GPU);
+  2. the fused exchange kernel == torch.distributed.all_reduce on a copy of the same gradients (GD, lr = 1, w = 0);
+  3. three optimizer steps == the oracle's: Momentum parameters and slots everywhere within 3e-2; Adam on its SLOTS (m
+     within 8e-2, v within 1.5e-1 of their max, every variable) — Adam's parameter update is g / |g|-like in the first
+     steps, so an element whose gradient flips sign between steps legitimately moves by +-lr; parameters only in bulk;
+  4. replicas (parameters, bf16 shadows, replicated slots) bit-equal across ranks; step counter; logged loss == oracle's
+     global-mean loss (sparse exchange);
+  5. batch_norm + Adam: start/resume broadcast and training run (slot broadcast with BN layouts).
+Prints device-timed us/step for each.
+"""
+import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import torch.distributed as dist
@@ -15,6 +28,8 @@ from deepfm_b200.models import DeepFMConfig, init_params
 from deepfm_b200.models.oracle import oracle_grads
 from deepfm_b200.optim import TF1Optimizer
 from deepfm_b200.parallel.dp import FusedDataParallel
+from deepfm_b200.parallel.dp_sparse import SparseDataParallel
+from deepfm_b200.parallel.selfcheck import exchange_equals_allreduce, replicas_equal
 
 ok = True
 def check(cond, msg):
@@ -27,34 +42,68 @@ def batch(cfg, B, seed):
     g = torch.Generator().manual_seed(seed)
     ids = torch.randint(0, cfg.feature_size, (B, cfg.field_size), generator=g, dtype=torch.int64)
     ids[:, 0] = 3
+    ids[:, 1] = cfg.feature_size - 1
     vals = torch.rand(B, cfg.field_size, generator=g)
     labels = (torch.rand(B, generator=g) < 0.3).float()
     return ids, vals, labels
 
-cfg = DeepFMConfig(field_size=39, feature_size=5000, embedding_size=32, deep_layers=[400, 400, 400],
+cfg = DeepFMConfig(field_size=39, feature_size=5003, embedding_size=32, deep_layers=[400, 400, 400],
                    dropout=[0.5, 0.8, 1.0], l2_reg=1e-4)
-Bl = 256
+Bl = 256 if world > 1 else 512  # global batch >= 512 (the tolerances below are those of the one-GPU oracle tests at 512)
 GB = Bl * world
-modes = ["p2p", "nvls", "nccl"]
-for comm in modes:
-    for opt in (["Momentum", "Adam"] if comm != "nccl" else ["Momentum"]):
-        params = init_params(cfg, seed=3)
+CLS = {"sparse": SparseDataParallel, "dense": FusedDataParallel}
+modes = [("sparse", "p2p"), ("sparse", "nvls"), ("dense", "p2p"), ("dense", "nvls"), ("dense", "nccl")]
+only = os.environ.get("DP_CHECK_ONLY")  # e.g. "sparse" to restrict
+for exch, comm in modes:
+    if only and exch != only:
+        continue
+    tag = "%s/%s" % (exch, comm)
+    # ---- 2. exchange kernel vs NCCL all-reduce
+    if comm != "nccl":
         try:
-            m = FusedDataParallel(cfg, Bl, TF1Optimizer(opt, 1e-2), 77, dev, world, rank, comm=comm, params=params)
+            r = exchange_equals_allreduce(cfg, Bl, dev, world, rank, comm=comm, exchange=exch)
         except RuntimeError as e:
             if rank == 0:
-                print("comm=%s unavailable: %s" % (comm, e), flush=True)
-            break
+                print("%s unavailable: %s" % (tag, e), flush=True)
+            continue
+        check(r["max_rel_err_vs_nccl_allreduce"] < 1e-5, "%s exchange vs all_reduce: %r" % (tag, r))
+        check(r["grads_zeroed"] in (None, True), "%s gradients not zeroed after the tail" % tag)
+        if rank == 0:
+            print("%s exchange==all_reduce: %r" % (tag, r), flush=True)
+    for opt in (["Momentum", "Adam"] if comm != "nccl" else ["Momentum"]):
+        params = init_params(cfg, seed=3)
+        m = CLS[exch](cfg, Bl, TF1Optimizer(opt, 1e-2), 77, dev, world, rank, comm=comm, params=params)
         ref_p = {k: v.clone().to(dev) for k, v in params.items()}
         ref_opt = TF1Optimizer(opt, 1e-2)
         ref_slots = ref_opt.init_slots(ref_p)
+        # ---- 1. gradient level
+        ids, vals, labels = batch(cfg, GB, 0)
+        sl = slice(rank * Bl, (rank + 1) * Bl)
+        g = m.compute_grads(ids[sl].to(dev), vals[sl].to(dev), labels[sl].to(dev))
+        r0 = oracle_grads(ref_p, cfg, ids.to(dev), vals.to(dev), labels.to(dev), True, 77, 0, 0,
+                          compute_dtype=torch.bfloat16)
+        noise_ok = {}
+        for k, ref in r0["grads"].items():
+            tot = g[k].clone()
+            dist.all_reduce(tot)
+            data_ref = ref - (cfg.l2_reg * ref_p[k] if k in ("fm_w", "fm_v") else 0)  # compute_grads: data term only
+            err = float((tot - data_ref).abs().max()) / (float(data_ref.abs().max()) + 1e-12)
+            check(err < 2e-2, "%s %s gradient %s err %.3e" % (tag, opt, k, err))
+            noise_ok[k] = torch.ones_like(ref, dtype=torch.bool)
+        # ---- 3. optimizer steps
+        losses = []
         for step in range(3):
             ids, vals, labels = batch(cfg, GB, step)
-            sl = slice(rank * Bl, (rank + 1) * Bl)
             m.train_step(ids[sl].to(dev), vals[sl].to(dev), labels[sl].to(dev))
+            losses.append(float(m.last_loss()))
             r = oracle_grads(ref_p, cfg, ids.to(dev), vals.to(dev), labels.to(dev), True, 77, step, 0,
                              compute_dtype=torch.bfloat16)
+            for k, gk in r["grads"].items():  # Adam comparison: only elements whose gradient is above the noise floor in
+                noise_ok[k] &= gk.abs() >= 1e-2 * float(gk.abs().max())  # EVERY step (one noisy step moves it by +-lr)
             ref_opt.apply_all(ref_p, r["grads"], ref_slots)
+            if getattr(m, "loss_is_global", False):
+                check(abs(losses[-1] - float(r["loss"])) < 2e-3 * max(1.0, abs(float(r["loss"]))),
+                      "%s %s logged loss %.6f vs oracle global mean %.6f" % (tag, opt, losses[-1], float(r["loss"])))
         torch.cuda.synchronize()
         check(m.global_step == 3, "step counter %d" % m.global_step)
         got = m.named_parameters()
@@ -62,32 +111,36 @@ for comm in modes:
         for k in ref_p:
             a, b = got[k].float(), ref_p[k].float()
             scale = float(b.abs().max()) + 1e-8
-            if opt == "Momentum":
-                err = float((a - b).abs().max()) / scale
-                worst = max(worst, err)
-                check(err < 3e-2, "%s %s %s err %.3e" % (comm, opt, k, err))
-            else:
-                frac = float(((a - b).abs() > 3e-2 * scale).float().mean())
+            d = (a - b).abs()
+            if opt == "Adam":
+                # Adam normalises g: in the first steps the update is ~lr * sign-like, so an element whose gradient changes
+                # sign between steps (or sits in the bf16 noise) legitimately ends up +-lr away. Parameters are therefore
+                # bounded in bulk here; the strict Adam check is on the SLOTS below (m linear, v quadratic in g)
+                frac = float((d > 3e-2 * scale).float().mean())
                 worst = max(worst, frac)
-                check(frac < 0.20, "%s %s %s frac_bad %.3f" % (comm, opt, k, frac))
-        # replicas identical across ranks
-        flat = m.P.clone()
-        ref = flat.clone()
-        dist.broadcast(ref, 0)
-        check(bool(torch.equal(flat, ref)), "%s %s replicas differ across ranks" % (comm, opt))
-        sh = m.shadow.clone(); shr = sh.clone(); dist.broadcast(shr, 0)
-        check(bool(torch.equal(sh, shr)), "%s %s bf16 shadows differ across ranks" % (comm, opt))
-        # chief-side slot assembly round-trips through a state dict
-        if rank == 0:
+                check(frac < 0.05, "%s %s %s frac_bad %.3f" % (tag, opt, k, frac))
+                continue
+            err = float(d.max()) / scale if d.numel() else 0.0
+            worst = max(worst, err)
+            check(err < 3e-2, "%s %s %s err %.3e" % (tag, opt, k, err))
+        # ---- 4. replicas identical across ranks
+        req = replicas_equal(m)
+        check(req["equal"], "%s %s replicas differ: %r" % (tag, opt, req))
+        if rank == 0:  # chief-side state dict (slot assembly for the sharded-slot kernel)
             sd = m.state_dict()
             key = "fm_v/" + ("Momentum" if opt == "Momentum" else "Adam")
             check(key in sd and sd[key].shape == ref_p["fm_v"].shape, "slot %s missing" % key)
-            if opt == "Momentum":
-                e = float((sd[key] - ref_slots["fm_v"][0]).abs().max()) / (float(ref_slots["fm_v"][0].abs().max()) + 1e-8)
-                check(e < 3e-2, "slot mismatch %.3e" % e)
+            sfx = ["Momentum"] if opt == "Momentum" else ["Adam", "Adam_1"]
+            for k in ref_p:  # every optimizer slot of every variable vs the oracle's
+                for si, sf in enumerate(sfx):
+                    refs = ref_slots[k][si].float()
+                    e = float((sd["%s/%s" % (k, sf)].float() - refs).abs().max()) / (float(refs.abs().max()) + 1e-20)
+                    # Adam: weights that moved by +-lr after step 1 change the later gradients themselves (measured 4-5e-2,
+                    # identical for every exchange flavour and for the NCCL path)
+                    tol = 3e-2 if opt == "Momentum" else (8e-2 if si == 0 else 1.5e-1)
+                    check(e < tol, "%s %s slot %s/%s err %.3e" % (tag, opt, k, sf, e))
         # timing
         ids, vals, labels = batch(cfg, GB, 100)
-        sl = slice(rank * Bl, (rank + 1) * Bl)
         m.load_inputs(ids[sl].to(dev), vals[sl].to(dev), labels[sl].to(dev), 0)
         for _ in range(10):
             m.train_step_slot(0)
@@ -100,10 +153,46 @@ for comm in modes:
         us = e0.elapsed_time(e1) * 10.0
         t = torch.tensor([us], device=dev); dist.all_reduce(t, op=dist.ReduceOp.MAX)
         if rank == 0:
-            print("comm=%-5s opt=%-8s world=%d mode=%s worst=%.3e us/step=%.1f loss=%.4f" % (
-                comm, opt, world, m.comm_name, worst, float(t), float(m.last_loss())), flush=True)
+            print("%-12s opt=%-8s world=%d mode=%s worst=%.3e us/step=%.1f loss=%.4f" % (
+                tag, opt, world, m.comm_name, worst, float(t), float(m.last_loss())), flush=True)
         del m
         torch.cuda.synchronize(); dist.barrier()
+
+# ---- 5. batch_norm + Adam: broadcast_state (start/resume path) and a few steps, both exchanges
+bn_cfg = DeepFMConfig(field_size=39, feature_size=3000, embedding_size=32, deep_layers=[128, 64], dropout=[0.8, 1.0],
+                      l2_reg=1e-4, batch_norm=True)
+for exch in ("sparse", "dense"):
+    if only and exch != only:
+        continue
+    params = init_params(bn_cfg, seed=5 + rank)  # ranks start DIFFERENT: the broadcast must make them equal
+    m = CLS[exch](bn_cfg, Bl, TF1Optimizer("Adam", 1e-3), 7, dev, world, rank, comm="auto", params=params)
+    if rank == 0:
+        sd = m.state_dict()
+        sd["global_step"] = torch.tensor([41])
+        for k in sd:
+            if k.endswith("/Adam"):
+                sd[k] = torch.full_like(sd[k], 0.25)
+            if k.endswith("/Adam_1"):
+                sd[k] = torch.full_like(sd[k], 4.0)
+        m.load_state_dict(sd)
+    m.broadcast_state(0)
+    check(m.global_step == 41, "%s bn: step after broadcast %d" % (exch, m.global_step))
+    req = replicas_equal(m)
+    check(req["equal"], "%s bn: replicas differ after broadcast_state: %r" % (exch, req))
+    sdl = m.state_dict()
+    check(abs(float(sdl["fm_v/Adam"].mean()) - 0.25) < 1e-6, "%s bn: slots not broadcast" % exch)
+    for step in range(3):
+        ids, vals, labels = batch(bn_cfg, GB, step)
+        sl = slice(rank * Bl, (rank + 1) * Bl)
+        m.train_step(ids[sl].to(dev), vals[sl].to(dev), labels[sl].to(dev))
+    torch.cuda.synchronize()
+    check(m.global_step == 44, "%s bn: step counter %d" % (exch, m.global_step))
+    lossv = float(m.last_loss())
+    check(lossv == lossv and 0 < lossv < 5, "%s bn: loss %r" % (exch, lossv))
+    if rank == 0:
+        print("batch_norm + Adam over %s: broadcast_state + 3 steps ok, loss %.4f" % (m.comm_name, lossv), flush=True)
+    del m
+    torch.cuda.synchronize(); dist.barrier()
 
 flag = torch.tensor([1 if ok else 0], device=dev); dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 if rank == 0:

@@ -30,6 +30,14 @@ def test_sharded_embeddings_match_oracle():
     assert rc == 0 and "SHARDED_CHECK PASS" in out, out[-3000:]
 
 
+def test_dp_exchange_kernels_single_rank(cuda_lib):
+    """World size 1 runs the SAME exchange kernels (sparse touched-row exchange, dense ZeRO-1 kernel, flag barriers, state
+    broadcast) over self-mapped symmetric memory, so a one-GPU box still checks them against the oracle and NCCL."""
+    rc, out = _torchrun("dp_check.py", 1, 29574)
+    assert rc == 0 and "DP_CHECK PASS" in out, out[-3000:]
+    assert "sparse/p2p exchange==all_reduce" in out and "dense/p2p exchange==all_reduce" in out
+
+
 def test_sharded_single_rank_and_ps_fused_worker(cuda_lib):
     """World size 1 exercises the same kernels (self-mapped symmetric memory) on a single GPU."""
     rc, out = _torchrun("sharded_check.py", 1, 29573)
