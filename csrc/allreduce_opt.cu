@@ -20,6 +20,8 @@
 #include "common.cuh"
 #include "optim_math.cuh"
 
+#include <stdlib.h>
+
 namespace dfm {
 
 constexpr int kMaxRanks = 8;
@@ -57,6 +59,7 @@ struct ArOptArgs {
   float* scalars_out;
   float* pub_dst;
   int pub_ring;
+  int barrier_inside;              // 1: barrier A runs in CTA 0 of the sweep kernel itself (grids of at most one CTA per SM)
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -110,8 +113,30 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
   const uint32_t seq = *a.seq_ptr + 1u;
   if (threadIdx.x == 0) s_lr = opt_step_lr(a.h, t);
 
-  // barrier A ran in the preceding 1-CTA kernel (ar_barrier_kernel): every rank's gradients are complete and visible
+  // barrier A: either the preceding 1-CTA kernel (ar_barrier_kernel), or — small grids — CTA 0 of this kernel while the
+  // other CTAs wait for its local go flag. The separate kernel costs its launch plus ~6 us between its end and this
+  // kernel's first instruction after griddepcontrol.wait (a kernel that wrote peer memory completes only when NVLink has
+  // acknowledged those writes; scripts/step_trace.py at 8 GPUs: barrier end 70.1 us, sweep go 76.4 us).
   pdl_wait(TR_ALLREDUCE);
+  if (a.barrier_inside) {
+    uint32_t* go = a.flags[a.rank] + 2 * kMaxRanks;
+    if (blockIdx.x == 0) {
+      if (threadIdx.x < W) {
+        const int peer = threadIdx.x;
+        if (a.loss_local) a.loss_parts[peer][a.rank] = *a.loss_local;
+        st_release_sys(a.flags[peer] + a.rank, seq);
+        wait_flag_geq(a.flags[a.rank] + peer, seq, peer, 0);
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(go), "r"(seq) : "memory");
+    } else if (threadIdx.x == 0) {
+      uint32_t v;
+      do {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(go) : "memory");
+      } while ((int32_t)(v - seq) < 0);  // CTA 0 needs no other CTA to get here, and it has its own watchdog
+    }
+    trace_max(TR_BAR_A, 2);
+  }
   __syncthreads();
   const float lr_t = s_lr;
   const int nslots = opt_num_slots(a.h.opt);
@@ -293,7 +318,7 @@ int dfm_bcast_f32(void* const* ptrs, void* mc, long long n, int rank, int world,
   return DFM_OK;
 }
 
-int dfm_allreduce_opt_flag_words(void) { return 2 * kMaxRanks; }
+int dfm_allreduce_opt_flag_words(void) { return 2 * kMaxRanks + 1; }  // barrier A, barrier B, local go flag
 int dfm_allreduce_opt_max_blocks(void) { return kArMaxBlocks; }
 
 // Pointer tables are host arrays of `world` device pointers (peer-mapped symmetric memory). mc pointers may be NULL
@@ -363,7 +388,11 @@ int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* c
   DFM_REQUIRE(grid_blocks >= 1 && grid_blocks <= kArMaxBlocks, "allreduce_opt: grid_blocks %d not in [1,%d]",
               grid_blocks, kArMaxBlocks);
   const long long blocks = grid_blocks;
-  if (world > 1 || loss_local) {  // world 1 with publication: the kernel still deposits the loss sum it later reads back
+  // every CTA of a grid of at most one CTA per SM is resident at once, so CTAs spinning on CTA 0's go flag cannot keep it
+  // from being scheduled; larger grids (the P2P flavour at 2 ranks) keep the separate 1-CTA barrier kernel
+  static const bool inside_ok = !(getenv("DFM_AR_BARRIER_KERNEL") && getenv("DFM_AR_BARRIER_KERNEL")[0] == '1');
+  a.barrier_inside = (inside_ok && grid_blocks <= 148) ? 1 : 0;
+  if (!a.barrier_inside && (world > 1 || loss_local)) {  // world 1 with publication: the loss sum is still deposited
     ar_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(a);
     DFM_CHECK(cudaGetLastError());
   }

@@ -30,7 +30,7 @@ constexpr int BK = 64;
 constexpr int kEpiWarps = 8;  // 2 warps per TMEM lane quarter
 constexpr int kGemmThreads = 64 + 32 * kEpiWarps;
 
-enum { EPI_BIAS_ACT = 0, EPI_MASK = 1, EPI_ACCUM_F32 = 2 };
+enum { EPI_BIAS_ACT = 0, EPI_MASK = 1, EPI_ACCUM_F32 = 2, EPI_MASK_BIG = 3 };  // MASK_BIG: same epilogue, whole-SM stage budget
 
 struct GemmParams {
   int M, N, K;
@@ -55,11 +55,12 @@ struct GemmParams {
 // Shared-memory budget per pass (the rest of the step decides it, not the GEMM itself — scripts/step_trace.py):
 //   forward  runs alone on the chain: the whole SM (~200 KB, up to 7 stages). With 20 k-blocks of 26 KB behind a ~1.2 us
 //            TMA round trip, the bytes in flight are the throughput: 4 stages made mlp_fwd0 1.3 us slower than 7.
-//   dgrad    ~124 KB   and   wgrad ~98 KB: one CTA of each fits on an SM TOGETHER. With ~200 KB each (the first version)
+//   dgrad    of the upper layers runs alone too (the wgrads are forked after dgrad_1): whole SM (EPI_MASK_BIG);
+//   dgrad_0  ~124 KB   and   wgrad ~98 KB: one CTA of each fits on an SM TOGETHER. With ~200 KB each (the first version)
 //            the wgrad branch queued for whole SMs behind the dgrad chain, whose programmatic dependent launches keep the
 //            next kernel's CTAs resident while they wait: wgrad2 took 23 us beside the chain, 2.3 us alone.
 template <int EPI>
-struct GemmBudget { static constexpr int BYTES = EPI == 0 ? 200 * 1024 : (EPI == 1 ? 124 * 1024 : 98 * 1024); };
+struct GemmBudget { static constexpr int BYTES = (EPI == 0 || EPI == 3) ? 200 * 1024 : (EPI == 1 ? 124 * 1024 : 98 * 1024); };
 
 template <int BN, int EPI>
 struct GemmCfg {
@@ -217,7 +218,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
           bits[k] = b;
         }
-      } else if constexpr (EPI == EPI_MASK) {
+      } else if constexpr (EPI == EPI_MASK || EPI == EPI_MASK_BIG) {
         fastc[k] = fastc[k] && (p.ldmask % 8 == 0);
         if (fastc[k] && p.mask) {
           const uint4* mp = reinterpret_cast<const uint4*>(p.mask + (size_t)row * p.ldmask + n);
@@ -246,7 +247,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const int n = n0 + c;
       if (n >= p.N) continue;  // warp-uniform
       const bool full16 = (n + 16 <= p.N);
-      if constexpr (EPI == EPI_MASK) {
+      if constexpr (EPI == EPI_MASK || EPI == EPI_MASK_BIG) {
         if (p.colsum) {  // warp-uniform: every lane takes part in the shuffles below, rows past M contribute zeros
           float m[16];
 #pragma unroll
@@ -308,7 +309,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             v[j] = x;
           }
         }
-      } else if constexpr (EPI == EPI_MASK) {
+      } else if constexpr (EPI == EPI_MASK || EPI == EPI_MASK_BIG) {
         if (p.mask) {
           if (fastc[k]) {
 #pragma unroll
@@ -425,6 +426,7 @@ static int make_tmap(CUtensorMap* tm, const void* base, int rows, int cols, int 
 struct GemmPlan {
   CUtensorMap tmA, tmB;
   GemmParams p;
+  int exclusive = 0;  // dgrad: runs with nothing beside it -> whole-SM stage budget
   int mode;  // 0 fwd (KK), 1 dgrad (K,MN), 2 wgrad (MN,MN)
   int bn;
   dim3 grid;
@@ -557,6 +559,14 @@ int dfm_gemm_plan_set_overwrite(void* plan, int on) {
   return DFM_OK;
 }
 
+// dgrad plans: 1 = this GEMM runs with no other GEMM beside it (whole-SM pipeline: all k-blocks of K <= 512 in flight).
+int dfm_gemm_plan_set_exclusive(void* plan, int on) {
+  GemmPlan* pl = reinterpret_cast<GemmPlan*>(plan);
+  DFM_REQUIRE(pl->mode == 1, "exclusive applies to dgrad plans only");
+  pl->exclusive = on ? 1 : 0;
+  return DFM_OK;
+}
+
 // dgrad plans: also accumulate the column sums of the output (= bias gradient of the layer below) into colsum[N] (fp32).
 int dfm_gemm_plan_set_colsum(void* plan, float* colsum) {
   GemmPlan* pl = reinterpret_cast<GemmPlan*>(plan);
@@ -592,6 +602,12 @@ int dfm_gemm_run(void* plan, void* stream_) {
       DFM_GEMM_CASE(96, false, false, EPI_BIAS_ACT)
       DFM_GEMM_CASE(128, false, false, EPI_BIAS_ACT)
       DFM_GEMM_CASE(256, false, false, EPI_BIAS_ACT)
+    }
+  } else if (pl->mode == 1 && pl->exclusive) {
+    switch (pl->bn) {
+      DFM_GEMM_CASE(64, false, true, EPI_MASK_BIG)
+      DFM_GEMM_CASE(128, false, true, EPI_MASK_BIG)
+      DFM_GEMM_CASE(256, false, true, EPI_MASK_BIG)
     }
   } else if (pl->mode == 1) {
     switch (pl->bn) {

@@ -262,6 +262,7 @@ class FusedDeepFM:
             else:
                 self.dgrad.append(K.GemmPlan("dgrad", self.dz[i], Wb, self.dz[i - 1], B, d_in, h,
                                              mask=self.acts[i - 1], mask_scale=1.0 / cfg.dropout[i - 1]))
+                self.dgrad[i].set_exclusive(True)  # the wgrads are forked after dgrad_1: dgrad_i (i >= 1) runs alone
                 if self._fold_cols:  # bias gradient of layer i-1 = column sums of dZ_{i-1}: folded into this epilogue
                     self.dgrad[i].set_colsum(self._g("mlp%d.bias" % (i - 1)))
             x_in = self.acts[i]

@@ -82,6 +82,11 @@ class GemmPlan:
         _lib.check(_lib.load().dfm_gemm_plan_set_overwrite(self._h, c_int(1 if on else 0)))
         return self
 
+    def set_exclusive(self, on: bool = True) -> "GemmPlan":
+        """dgrad plans: no other GEMM runs beside this one, so it may take the whole SM for its TMA stages."""
+        _lib.check(_lib.load().dfm_gemm_plan_set_exclusive(self._h, c_int(1 if on else 0)))
+        return self
+
     def set_colsum(self, out: Optional[torch.Tensor]) -> "GemmPlan":
         """dgrad plans: out[n] += sum_m result[m,n] in the epilogue (the bias gradient of the layer below)."""
         self._keep = self._keep + (out,)

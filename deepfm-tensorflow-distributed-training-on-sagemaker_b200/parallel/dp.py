@@ -170,7 +170,7 @@ class FusedDataParallel(FusedDeepFM):
             c_void_p(self.seq.data_ptr()), c_int(1 if self.use_nvls else 0), c_int(self._grid_blocks), t["loss_parts"],
             c_void_p(self.loss_sum.data_ptr()), c_void_p(self._reg_extra_ptr()), c_void_p(self.scalars.data_ptr()),
             c_void_p(ring.data_ptr() if ring is not None else 0), c_int(ring.shape[0] if ring is not None else 0), st))
-        return 2
+        return 2 if self._grid_blocks > 148 else 1
 
     def _restore(self, snap):
         super()._restore(snap)

@@ -39,6 +39,7 @@ int dfm_gemm_plan_create(void** plan_out, int mode, const void* A, int lda, cons
 int dfm_gemm_plan_info(void* plan, int* bn, int* grid_x, int* grid_y, int* grid_z);
 int dfm_gemm_plan_set_row_offset(void* plan, int row_offset);
 int dfm_gemm_plan_set_overwrite(void* plan, int on); /* wgrad plans with split_k = 1: out = (plain stores), not += */
+int dfm_gemm_plan_set_exclusive(void* plan, int on); /* dgrad plans: no GEMM runs beside it -> whole-SM stage budget */
 int dfm_gemm_plan_set_colsum(void* plan, float* colsum); /* dgrad plans: colsum[n] += sum_m out[m,n] (bias gradient) */
 int dfm_gemm_plan_set_trace_id(void* plan, int id); /* timeline id (trace build only, see dfm_trace_*) */
 int dfm_gemm_plan_set_out_f32(void* plan, int on); /* forward plans: fp32 output (pre-batch-norm activations) */
