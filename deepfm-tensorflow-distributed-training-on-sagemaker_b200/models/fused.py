@@ -489,6 +489,29 @@ class FusedDeepFM:
         return self.prob[:n]
 
     @torch.no_grad()
+    def predict_slot(self, n: int, slot_idx: int = 0) -> torch.Tensor:
+        """Forward pass over the batch already resident in input slot `slot_idx` (rows >= n are padding), replayed from a
+        CUDA graph captured on first use: emb_fm_fwd -> mlp_fwd x L -> logit head, one graph launch per call. The serving
+        path (serving/predictor.py) keeps one engine per batch-size bucket so a 1-row request does not pay for 4096."""
+        g = self.__dict__.get("_pgraphs", {}).get(slot_idx)
+        if g is None:
+            s = self.in_slots[slot_idx]
+            top = self.n_layers - 1
+
+            def fwd():
+                self._forward(s, False)
+                K.logit_loss(self.acts[top], self._w("deep_out.weight"), self._w("deep_out.bias"), self._w("fm_bias"),
+                             self.yfm, None, 1.0, 1.0, False, self.prob, self.logit)
+            fwd()  # warm-up outside capture (module load, function attributes)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                fwd()
+            self.__dict__.setdefault("_pgraphs", {})[slot_idx] = g
+        g.replay()
+        return self.prob[:n]
+
+    @torch.no_grad()
     def eval_step(self, ids, vals, labels, update_auc: bool = True):
         """Forward + loss (+ AUC histogram). Returns (sum of per-example log-loss [1], probs [n])."""
         n = self.load_inputs(ids, vals, labels, 0)

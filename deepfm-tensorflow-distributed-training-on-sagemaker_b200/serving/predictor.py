@@ -24,17 +24,52 @@ from .export import latest_export
 
 
 class Predictor:
-    def __init__(self, cfg: DeepFMConfig, params: Dict[str, torch.Tensor], max_batch: int = 4096, backend: str = "auto"):
+    """`buckets`: batch sizes for which a graph-captured fused forward is kept (one engine each, built on first use). A
+    request of n rows runs on the smallest bucket >= n (chunks of `max_batch` beyond that): inputs go through ONE pinned
+    host buffer and one H2D copy, the forward is one CUDA-graph launch, the probabilities come back with one D2H copy into
+    pinned memory and a single event wait."""
+
+    def __init__(self, cfg: DeepFMConfig, params: Dict[str, torch.Tensor], max_batch: int = 4096, backend: str = "auto",
+                 buckets=(64, 512)):
         self.cfg, self.max_batch = cfg, max_batch
-        use_fused = backend == "fused" or (backend == "auto" and torch.cuda.is_available() and not cfg.batch_norm
-                                           and not cfg.fused_constraints())
+        use_fused = backend == "fused" or (backend == "auto" and torch.cuda.is_available() and not cfg.fused_constraints())
+        self.fused = bool(use_fused)
         if use_fused:
-            from ..models.fused import FusedDeepFM
-            self.model = FusedDeepFM(cfg, max_batch, params=params, use_graph=False, input_slots=1)
-            self.dev = self.model.dev
+            self._params = params
+            self._buckets = sorted({int(b) for b in buckets if 0 < int(b) < max_batch} | {int(max_batch)})
+            self._engines = {}
+            self.dev = torch.device("cuda", torch.cuda.current_device())
+            self.model = self._engine(self._buckets[-1])[0]
         else:
             self.dev = torch.device("cuda" if (torch.cuda.is_available() and backend != "torch-cpu") else "cpu")
             self.model = TorchDeepFM(cfg, max_batch, device=self.dev, params=params)
+
+    def _engine(self, B: int):
+        e = self._engines.get(B)
+        if e is None:
+            from ..models.fused import FusedDeepFM, make_packed_slot
+            from ..optim.tf1 import TF1Optimizer
+            m = FusedDeepFM(self.cfg, B, TF1Optimizer("GD", 0.0), params=self._params, use_graph=False, input_slots=1)
+            host_in = make_packed_slot(B, self.cfg.field_size, "cpu", pin=True)
+            host_out = torch.zeros(B, dtype=torch.float32).pin_memory()
+            e = self._engines[B] = (m, host_in, host_out, torch.cuda.Event())
+        return e
+
+    def _predict_fused(self, ids: torch.Tensor, vals: torch.Tensor) -> torch.Tensor:
+        n = ids.shape[0]
+        B = next(b for b in self._buckets if b >= n)
+        m, hin, hout, ev = self._engine(B)
+        hin["ids"][:n].copy_(ids)  # int64 -> int32 on the way into the pinned slot
+        hin["vals"][:n].copy_(vals)
+        if n < B:  # padding rows: id 0 with value 0
+            hin["ids"][n:].zero_()
+            hin["vals"][n:].zero_()
+        m.load_packed(hin["packed"], 0, non_blocking=True)
+        p = m.predict_slot(n, 0)
+        hout[:n].copy_(p, non_blocking=True)
+        ev.record()
+        ev.synchronize()
+        return hout[:n].clone()
 
     @classmethod
     def load(cls, model_dir: str, max_batch: int = 4096, backend: str = "auto") -> "Predictor":
@@ -52,6 +87,9 @@ class Predictor:
         vals = torch.as_tensor(inputs["feat_vals"], dtype=torch.float32).reshape(-1, self.cfg.field_size)
         out = []
         for s in range(0, ids.shape[0], self.max_batch):
+            if self.fused:
+                out.append(self._predict_fused(ids[s:s + self.max_batch], vals[s:s + self.max_batch]))
+                continue
             p = self.model.predict(ids[s:s + self.max_batch].to(self.dev), vals[s:s + self.max_batch].to(self.dev))
             out.append(p.detach().float().cpu().clone())
         return {"prob": torch.cat(out) if out else torch.zeros(0)}
