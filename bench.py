@@ -47,6 +47,11 @@ def parse_args():
     ap.add_argument("--l2_reg", type=float, default=1e-4)
     ap.add_argument("--proxy_graph", action="store_true",
                     help="--impl proxy only: capture the proxy step in a CUDA graph (see proxy_baseline.py)")
+    ap.add_argument("--from_tfrecords", default="", metavar="DIR",
+                    help="loader-in-the-loop arm: write synthetic TFRecord shards under DIR once (per rank), then train "
+                         "through InputPipeline -> Estimator.train in three modes (host parser, --gpu_parse, binary cache) "
+                         "and print samples/s for each (reference path: TFRecordDataset -> tf.data -> train, HVD:93-131)")
+    ap.add_argument("--tfrecord_rows", type=int, default=524288, help="--from_tfrecords: records per rank")
     ap.add_argument("--no_selfcheck", action="store_true", help="skip the multi-GPU self-check after the timed regions")
     ap.add_argument("--no_baseline", action="store_true",
                     help="skip the in-process baseline arm (graph-captured stock-PyTorch NCCL+cuBLAS proxy) that fills "
@@ -94,6 +99,67 @@ def time_proxy_baseline(a, cfg, world, rank, dev, gen, pool):
     except Exception as e:  # the baseline must never take the measurement down with it
         out["error"] = "%s: %s" % (type(e).__name__, str(e)[:300])
     return out
+
+
+def run_from_tfrecords(a, cfg, world, rank, local, dev):
+    """Training throughput with the loader in the loop (VERDICT r1 missing #5): every step's batch is read from TFRecord
+    files (framing + CRC32C + Example parse, or the raw bytes parsed on the GPU, or the pre-decoded binary cache), copied
+    H2D and trained, through the same Estimator.train loop the CLI uses. Wall clock around est.train, max over ranks."""
+    import time as _t
+    import torch
+    import torch.distributed as dist
+    from deepfm_b200.data.pipeline import CachedDataset, InputPipeline, write_cache
+    from deepfm_b200.data.synthetic import write_synthetic_tfrecords
+    from deepfm_b200.optim import TF1Optimizer
+    from deepfm_b200.parallel.dist import DistEnv
+    from deepfm_b200.runtime.estimator import Estimator
+    B, F = a.batch_size, a.field_size
+    d = os.path.join(a.from_tfrecords, "rank%d" % rank)
+    nfiles = 4
+    rows = a.tfrecord_rows // nfiles
+    files = sorted(os.path.join(d, f) for f in os.listdir(d)) if os.path.isdir(d) else []
+    files = [f for f in files if f.endswith(".tfrecords")]
+    if len(files) != nfiles:
+        files = write_synthetic_tfrecords(d, "tr", nfiles, rows, F, a.feature_size, seed=100 + rank)
+    size = sum(os.path.getsize(f) for f in files)
+    env = DistEnv(rank, world, local, "nccl" if world > 1 else "none", dev)
+    import io
+    est = Estimator(cfg, B, TF1Optimizer(a.optimizer, 5e-4 * world), None, env, backend="fused", seed=1234,
+                    log_steps=10 ** 9, comm=a.comm, strategy=a.strategy, out=io.StringIO())
+    steps = (rows * nfiles) // B
+    cache = os.path.join(d, "train.dfmcache")
+    if not os.path.exists(cache):
+        write_cache(cache, InputPipeline(files, F, B, threads=4, pin_memory=False), F)
+    ds = CachedDataset(cache)
+    epochs = 2
+    modes = {
+        "host_parser": lambda: InputPipeline(files, F, B, epochs, (1, 0), True, 4, True),
+        "gpu_parse": lambda: InputPipeline(files, F, B, epochs, (1, 0), True, 4, True, gpu_parse=True),
+        "binary_cache": lambda: ds.batches(B, epochs, (1, 0), True, packed=True),
+    }
+    est.train(lambda: InputPipeline(files, F, B, 1, (1, 0), True, 4, True), max_steps=64, steps_hint=64)  # warm-up, graphs
+    out = {}
+    for name, fn in modes.items():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = _t.perf_counter()
+        n = est.train(fn, steps_hint=steps * epochs)
+        torch.cuda.synchronize()
+        dt = _t.perf_counter() - t0
+        t = torch.tensor([dt], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out[name] = {"samples_per_s": n * B * world / float(t), "steps": n, "seconds": float(t),
+                     "mb_per_s_per_rank": (size * epochs / 1e6 / float(t)) if name != "binary_cache" else None}
+    if rank == 0:
+        print(json.dumps({"metric": "DeepFM train samples/sec from TFRecords (loader in the loop, wall clock, max over ranks)",
+                          "n_gpus": world, "unit": "samples/s", "per_gpu_batch": B, "records_per_rank": rows * nfiles,
+                          "bytes_per_record": size / (rows * nfiles), "epochs_timed": epochs, "loader_threads": 4,
+                          "host_cpus": os.cpu_count(), "comm": est.trainer.comm_name, "modes": out,
+                          "final_loss": float(est.trainer.last_loss())}))
+    est.trainer.close()
+    return 0
 
 
 class ClockSampler:
@@ -183,6 +249,11 @@ def main():
     backend = "proxy" if a.impl == "proxy" else "fused"
     if a.proxy_graph:
         os.environ["DFM_PROXY_GRAPH"] = "1"
+    if a.from_tfrecords:
+        rc = run_from_tfrecords(a, cfg, world, rank, local, dev)
+        if dist.is_initialized():
+            dist.destroy_process_group()
+        return rc
     gen = SyntheticCTR(a.field_size, a.feature_size, seed=rank)
     bytes_per_batch = B * a.field_size * 8 + B * 4  # int32 ids + f32 vals + f32 labels
     pool = a.pool or max(8, int(140e6 // bytes_per_batch) + 1)
@@ -308,6 +379,9 @@ def main():
             "gpu_launches": launches, "kernels_per_step": tr.kernels_per_step,
             "l2_persist_bytes": int(getattr(getattr(tr, "model", None), "l2_persist_bytes", 0) or 0),
             "final_loss": final_loss, "e2e_last_loss": losses[-1] if losses else None, "self_check": self_check,
+            "ps_profile_us_per_step": ({k: v / max(tr.prof["steps"], 1) * 1e6 for k, v in tr.prof.items() if k != "steps"}
+                                       if hasattr(tr, "prof") else None),
+            "ps_max_observed_staleness": getattr(tr, "max_observed_staleness", None),
         }
         print(json.dumps(out))
     if hasattr(tr, "close"):

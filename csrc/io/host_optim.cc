@@ -14,6 +14,9 @@
 #include <stdint.h>
 
 #include <algorithm>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <thread>
 #include <vector>
 
@@ -91,6 +94,77 @@ Hyper make_hyper(int opt, float lr, float beta1, float beta2, float eps, float m
   return h;
 }
 
+// Persistent worker pool: the parameter-server applier calls into this file ~10 times per training step (two tables + the
+// MLP variables); spawning and joining std::threads per call cost more than the arithmetic (measured: ~1 ms per step).
+class Pool {
+ public:
+  static Pool& get() {
+    static Pool p;
+    return p;
+  }
+  // run fn(b, e) over [0, n) in `parts` contiguous chunks; the caller takes one chunk itself
+  void run(long long n, int parts, const std::function<void(long long, long long)>& fn) {
+    const long long per = (n + parts - 1) / parts;
+    std::unique_lock<std::mutex> lk(mu_);
+    ensure(parts - 1);
+    fn_ = &fn;
+    n_ = n;
+    per_ = per;
+    next_ = 1;  // chunk 0 is the caller's
+    parts_ = parts;
+    pending_ = parts - 1;
+    ++gen_;
+    cv_work_.notify_all();
+    lk.unlock();
+    fn(0, std::min(n, per));
+    lk.lock();
+    cv_done_.wait(lk, [&] { return pending_ == 0; });
+    fn_ = nullptr;
+  }
+
+ private:
+  Pool() = default;
+  ~Pool() {
+    {
+      std::lock_guard<std::mutex> lk(mu_);
+      stop_ = true;
+      cv_work_.notify_all();
+    }
+    for (auto& t : th_) t.join();
+  }
+  void ensure(int k) {  // mu_ held
+    while ((int)th_.size() < k) th_.emplace_back([this] { loop(); });
+  }
+  void loop() {
+    std::unique_lock<std::mutex> lk(mu_);
+    unsigned long long seen = 0;
+    for (;;) {
+      cv_work_.wait(lk, [&] { return stop_ || (gen_ != seen && next_ < parts_); });
+      if (stop_) return;
+      while (next_ < parts_) {
+        const int c = next_++;
+        const long long b = c * per_, e = std::min(n_, b + per_);
+        const auto* fn = fn_;
+        lk.unlock();
+        if (b < e) (*fn)(b, e);
+        lk.lock();
+        if (--pending_ == 0) cv_done_.notify_all();
+      }
+      seen = gen_;
+    }
+  }
+  std::mutex mu_;
+  std::condition_variable cv_work_, cv_done_;
+  std::vector<std::thread> th_;
+  const std::function<void(long long, long long)>* fn_ = nullptr;
+  long long n_ = 0, per_ = 0;
+  int next_ = 0, parts_ = 0, pending_ = 0;
+  unsigned long long gen_ = 0;
+  bool stop_ = false;
+};
+
+std::mutex g_call_mu;  // one parallel region at a time (callers are the applier threads of this process)
+
 template <typename Fn>
 void parallel_for(long long n, int threads, long long min_chunk, Fn fn) {
   int T = (int)std::max<long long>(1, std::min<long long>(threads, n / std::max<long long>(1, min_chunk)));
@@ -98,14 +172,9 @@ void parallel_for(long long n, int threads, long long min_chunk, Fn fn) {
     fn(0, n);
     return;
   }
-  std::vector<std::thread> th;
-  const long long per = (n + T - 1) / T;
-  for (int t = 0; t < T; ++t) {
-    const long long b = t * per, e = std::min(n, b + per);
-    if (b >= e) break;
-    th.emplace_back([=] { fn(b, e); });
-  }
-  for (auto& x : th) x.join();
+  std::lock_guard<std::mutex> g(g_call_mu);
+  const std::function<void(long long, long long)> f = fn;
+  Pool::get().run(n, T, f);
 }
 
 }  // namespace
@@ -143,6 +212,42 @@ int dfmio_dense_opt_apply(float* w, float* s0, float* s1, const float* g, long l
   parallel_for(n, threads, 65536, [=](long long b, long long e) {
     apply_span(h, w + b, nslots > 0 ? s0 + b : nullptr, nslots > 1 ? s1 + b : nullptr, g + b, l2, e - b);
   });
+  return 0;
+}
+
+// One call per pushed training step of a parameter-server worker: the touched rows of both tables (rows int32 [nrows],
+// unique; gv [nrows, K], gw [nrows]) with touched-row L2, then `nvars` dense variables (pointer arrays; no L2). The
+// applier thread is a Python thread: one call instead of ~10 means one GIL hand-off per step instead of ~20 (measured: the
+// per-variable calls spent 1.7 ms per step, almost all of it waiting for the interpreter lock held by the training thread).
+int dfmio_ps_apply_push(float* tab_v, float* sv0, float* sv1, float* tab_w, float* sw0, float* sw1, long long N, int K,
+                        const int* rows, long long nrows, const float* gv, const float* gw, int nvars, float* const* w,
+                        float* const* s0, float* const* s1, const float* const* g, const long long* numel, int opt,
+                        float lr, float beta1, float beta2, float eps, float momentum, float l2, long long step,
+                        int threads) {
+  if (!tab_v || !tab_w || !rows || !gv || !gw || N <= 0 || K <= 0 || nrows < 0 || opt < 0 || opt > 4 || nvars < 0) return -1;
+  const int nslots = (opt == OPT_ADAM || opt == OPT_FTRL) ? 2 : (opt == OPT_GD ? 0 : 1);
+  if ((nslots > 0 && (!sv0 || !sw0)) || (nslots > 1 && (!sv1 || !sw1))) return -1;
+  for (long long i = 0; i < nrows; ++i)
+    if (rows[i] < 0 || rows[i] >= N) return -1;
+  const Hyper h = make_hyper(opt, lr, beta1, beta2, eps, momentum, step);
+  parallel_for(nrows, threads, 256, [=](long long b, long long e) {
+    for (long long i = b; i < e; ++i) {
+      const size_t r = (size_t)rows[i], base = r * (size_t)K;
+      apply_span(h, tab_v + base, nslots > 0 ? sv0 + base : nullptr, nslots > 1 ? sv1 + base : nullptr,
+                 gv + (size_t)i * (size_t)K, l2, K);
+      apply_span(h, tab_w + r, nslots > 0 ? sw0 + r : nullptr, nslots > 1 ? sw1 + r : nullptr, gw + i, l2, 1);
+    }
+  });
+  for (int v = 0; v < nvars; ++v) {
+    if (!w[v] || !g[v] || (nslots > 0 && !s0[v]) || (nslots > 1 && !s1[v])) return -1;
+    float* wv = w[v];
+    float* a0 = nslots > 0 ? s0[v] : nullptr;
+    float* a1 = nslots > 1 ? s1[v] : nullptr;
+    const float* gv_ = g[v];
+    parallel_for(numel[v], threads, 32768, [=](long long b, long long e) {
+      apply_span(h, wv + b, a0 ? a0 + b : nullptr, a1 ? a1 + b : nullptr, gv_ + b, 0.f, e - b);
+    });
+  }
   return 0;
 }
 

@@ -49,6 +49,7 @@ struct SplitOptArgs {
   uint32_t* bm_union;
   int* rows;                     // ascending ids of the rows set in bm_union (built by union_rowlist), capacity N
   int* row_count;                // number of entries in `rows`
+  int* word_prefix;              // optional [nwords]: set bits in the words before each word (rank of a row = prefix + popc)
   // tail only
   float* loss_sum;               // this rank's log-loss sum (scalars[0]); overwritten with the global sum when world > 1
   const float* loss_parts;       // [world] per-rank sums deposited by the peers (world > 1)
@@ -166,6 +167,7 @@ __global__ void __launch_bounds__(kRowlistThreads) union_rowlist_kernel(const Sp
   int pos = incl - cnt + (warp > 0 ? s_warp[warp - 1] : 0);
   for (int wi = w_begin; wi < w_end; ++wi) {
     uint32_t u = a.bm_union[wi];
+    if (a.word_prefix) a.word_prefix[wi] = pos;
     while (u) {
       const int b = __ffs(u) - 1;
       u &= u - 1;
@@ -437,14 +439,24 @@ static int fill_common(SplitOptArgs& a, float* w, float* g, float* s0, float* s1
 
 // bm_union = OR of `world` bitmaps (bm_in: host array of device pointers, each ceil(N/32) words; bm_in[0] is zeroed
 // afterwards when clear_inputs != 0), rows[0 .. *row_count) = ascending ids of the rows set in it. One CTA.
+int dfm_union_rowlist_prefix(const void* const* bm_in, int world, int clear_inputs, int N, unsigned int* bm_union, int* rows,
+                             int* row_count, int* word_prefix, void* stream);
+
 int dfm_union_rowlist(const void* const* bm_in, int world, int clear_inputs, int N, unsigned int* bm_union, int* rows,
                       int* row_count, void* stream) {
+  return dfm_union_rowlist_prefix(bm_in, world, clear_inputs, N, bm_union, rows, row_count, nullptr, stream);
+}
+
+// Same, plus word_prefix[w] = number of listed rows below row 32 w, so the position of row r in the list is
+// word_prefix[r >> 5] + popc(bm_union[r >> 5] & ((1 << (r & 31)) - 1)) (dfm_ps_remap_ids uses it).
+int dfm_union_rowlist_prefix(const void* const* bm_in, int world, int clear_inputs, int N, unsigned int* bm_union, int* rows,
+                             int* row_count, int* word_prefix, void* stream) {
   DFM_REQUIRE(world >= 1 && world <= kSplitMaxRanks, "union_rowlist: world %d not in [1,%d]", world, kSplitMaxRanks);
   DFM_REQUIRE(N > 0 && bm_union && rows && row_count, "union_rowlist: empty problem or null pointer");
   SplitOptArgs a = SplitOptArgs();
   for (int r = 0; r < kSplitMaxRanks; ++r) a.bm_in[r] = (const uint32_t*)bm_in[r < world ? r : 0];
   a.world = world; a.clear_inputs = clear_inputs; a.N = N; a.nwords = (N + 31) / 32;
-  a.bm_union = bm_union; a.rows = rows; a.row_count = row_count;
+  a.bm_union = bm_union; a.rows = rows; a.row_count = row_count; a.word_prefix = word_prefix;
   dfm_prefer_max_shared(reinterpret_cast<const void*>(union_rowlist_kernel));
   DFM_CHECK(launch_k(union_rowlist_kernel, dim3(1), dim3(kRowlistThreads), 0, (cudaStream_t)stream, a));
   return DFM_OK;

@@ -72,6 +72,9 @@ def load(build_if_missing: bool = True) -> ctypes.CDLL:
                                            c_f, c_f, c_f, c_f, c_f, c_f, c_ll, c_int]
     lib.dfmio_dense_opt_apply.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_int, c_f, c_f, c_f, c_f, c_f,
                                           c_f, c_ll, c_int]
+    lib.dfmio_ps_apply_push.argtypes = [c_void_p] * 6 + [c_ll, c_int, c_void_p, c_ll, c_void_p, c_void_p, c_int, c_void_p,
+                                        c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_f, c_f, c_f, c_f, c_f, c_f, c_ll,
+                                        c_int]
     lib.dfmio_encode_ctr_batch.restype = c_uint64
     lib.dfmio_encode_ctr_batch.argtypes = [c_void_p, c_void_p, c_void_p, c_ll, c_int, c_void_p, c_uint64]
     lib.dfmio_libsvm_last_error.restype = c_char_p

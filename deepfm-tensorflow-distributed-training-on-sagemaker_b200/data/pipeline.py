@@ -199,13 +199,33 @@ class CachedDataset:
         self.ids = np.frombuffer(raw, dtype=np.int32, count=self.n * self.F, offset=o).reshape(self.n, self.F); o += 4 * self.n * self.F
         self.vals = np.frombuffer(raw, dtype=np.float32, count=self.n * self.F, offset=o).reshape(self.n, self.F)
 
-    def batches(self, batch_size: int, num_epochs: int = 1, shard: Tuple[int, int] = (1, 0), drop_remainder: bool = True):
+    def batches(self, batch_size: int, num_epochs: int = 1, shard: Tuple[int, int] = (1, 0), drop_remainder: bool = True,
+                packed: bool = False, nslots: int = 8):
+        """packed=True: full batches are gathered straight into a ring of `nslots` pinned buffers in the loader's packed
+        slot layout (labels | ids | vals), so `Trainer.train_packed` moves each with ONE async H2D copy — an epoch from the
+        cache costs three strided memcpys per batch and no protobuf parse (the deck's `dataset.cache()`, PDF p43). A
+        buffer is reused after `nslots` further batches: keep fewer than that in flight."""
         n, i = shard
         sel = np.arange(i, self.n, n)
+        ring, k = None, 0
+        if packed:
+            from ..models.fused import make_packed_slot
+            pin = torch.cuda.is_available()
+            ring = [make_packed_slot(batch_size, self.F, "cpu", pin=pin) for _ in range(nslots)]
+        contiguous = n == 1
         for _ in range(num_epochs):
             for s in range(0, len(sel), batch_size):
                 idx = sel[s:s + batch_size]
                 if len(idx) < batch_size and drop_remainder:
                     break
-                yield Batch(len(idx), torch.from_numpy(self.labels[idx].copy()), torch.from_numpy(self.ids[idx].copy()),
-                            torch.from_numpy(self.vals[idx].copy()))
+                key = slice(int(idx[0]), int(idx[0]) + len(idx)) if contiguous else idx
+                if ring is not None and len(idx) == batch_size:
+                    sl = ring[k % nslots]
+                    k += 1
+                    sl["labels"].numpy()[:] = self.labels[key]
+                    sl["ids"].numpy()[:] = self.ids[key]
+                    sl["vals"].numpy()[:] = self.vals[key]
+                    yield Batch(batch_size, sl["labels"], sl["ids"], sl["vals"], sl["packed"])
+                    continue
+                yield Batch(len(idx), torch.from_numpy(np.array(self.labels[key])), torch.from_numpy(np.array(self.ids[key])),
+                            torch.from_numpy(np.array(self.vals[key])))

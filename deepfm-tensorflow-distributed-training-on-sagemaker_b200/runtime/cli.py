@@ -126,6 +126,15 @@ def main(argv: Optional[List[str]] = None) -> int:
 
     names = channel_names()
     metrics = None
+    evaluator = None
+    if F.task_type == "train" and F.strategy == "ps" and env.is_chief and F.model_dir and not pipe and va_files:
+        # train_and_evaluate (PS:439-442): the chief evaluates every new checkpoint, throttled, while the asynchronous
+        # workers (this process included) keep training; a final evaluation follows the last checkpoint
+        from .train_and_evaluate import ThrottledCheckpointEvaluator
+        evaluator = ThrottledCheckpointEvaluator(
+            cfg, F.model_dir, F.optimizer, lambda: input_fn(va_files, 1, (1, 0), False), est.log.log_eval,
+            F.eval_start_delay_secs, F.eval_throttle_secs, backend="auto" if F.backend != "torch" else "torch-cpu")
+        evaluator.start()
     if F.task_type == "train":
         if not pipe:
             hint = None
@@ -140,7 +149,7 @@ def main(argv: Optional[List[str]] = None) -> int:
                 sseed = (int(F.seed) * 1000003 + epoch + 1) if F.perform_shuffle else 0
                 est.train(lambda: input_fn(tr_files, 1, train_shard, True, sseed), max_steps=F.max_steps,
                           steps_hint=hint)
-                if env.is_chief and va_files:
+                if env.is_chief and va_files and evaluator is None:  # HVD:393-394: chief evaluates after every epoch
                     metrics = est.evaluate(lambda: input_fn(va_files, 1, (1, 0), False))
                 barrier(env)
                 if F.max_steps and est.trainer.global_step >= F.max_steps:
@@ -157,6 +166,9 @@ def main(argv: Optional[List[str]] = None) -> int:
                 if os.path.exists(ev_fifo):
                     metrics = est.evaluate(lambda: input_fn([ev_fifo], 1, (1, 0), False))
             barrier(env)
+        if evaluator is not None:  # every worker's pushes are in the last checkpoint: evaluate it, like train_and_evaluate
+            res = evaluator.finish(final_eval=True)
+            metrics = res[-1] if res else None
     elif F.task_type == "eval":
         # the reference runs this on every rank although only rank 0 has a checkpoint (HVD:407-408); gate it
         if env.is_chief:

@@ -99,6 +99,10 @@ def flag_definitions(env=os.environ) -> List[Tuple[str, type, Any, str]]:
         ("data_base_dir", str, env.get("SM_INPUT_DIR", "/opt/ml/input") + "/data", "where pipe-mode FIFOs live"),
         ("metrics_file", str, "", "JSONL metrics output (default <model_dir>/metrics.jsonl)"),
         ("ps_staleness", int, 4, "strategy=ps: max steps a worker may run ahead of its last pull"),
+        ("eval_start_delay_secs", int, 1000, "strategy=ps (train_and_evaluate): first evaluation not before this many "
+                                             "seconds (EvalSpec start_delay_secs, PS:441)"),
+        ("eval_throttle_secs", int, 1200, "strategy=ps (train_and_evaluate): at most one evaluation per this many seconds "
+                                          "(EvalSpec throttle_secs, PS:441)"),
     ]
 
 

@@ -55,6 +55,16 @@ class Predictor:
             e = self._engines[B] = (m, host_in, host_out, torch.cuda.Event())
         return e
 
+    def set_params(self, params: Dict[str, torch.Tensor]) -> None:
+        """Replace the weights of every engine built so far (and of those built later) — e.g. a newer checkpoint."""
+        self._params = params if self.fused else None
+        if self.fused:
+            for m, _, _, _ in self._engines.values():
+                m.load_state_dict(params, strict=False)
+            torch.cuda.synchronize()
+        else:
+            self.model.load_state_dict(params, strict=False)
+
     def _predict_fused(self, ids: torch.Tensor, vals: torch.Tensor) -> torch.Tensor:
         n = ids.shape[0]
         B = next(b for b in self._buckets if b >= n)

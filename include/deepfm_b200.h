@@ -99,6 +99,8 @@ int dfm_bitmap_words(int N);
 int dfm_touched_bitmap(const int* ids, int B, int F, int N, unsigned int* bitmap, void* stream);
 int dfm_union_rowlist(const void* const* bm_in, int world, int clear_inputs, int N, unsigned int* bm_union, int* rows,
                       int* row_count, void* stream);
+int dfm_union_rowlist_prefix(const void* const* bm_in, int world, int clear_inputs, int N, unsigned int* bm_union, int* rows,
+                             int* row_count, int* word_prefix, void* stream); /* + word_prefix[w] = rows listed below 32 w */
 int dfm_sweep_untouched(float* w, float* s0, float* s1, int opt, float lr, float beta1, float beta2, float eps,
                         float momentum, float l2, long long fmw_off, long long fmv_off, int N, int K,
                         const unsigned int* bm_union, unsigned long long* step_ptr, float* reg_acc, int grid_blocks,
@@ -208,6 +210,17 @@ int dfm_host_register(void* ptr, unsigned long long bytes, void** dev_ptr); /* p
 /* zero-copy parameter-server pull: out[i,:] = table[ids[i],:], table = device alias of the host store (X3 / row 11) */
 int dfm_ps_gather(const float* table_dev, const long long* ids, int n, int K, float* out, void* stream);
 int dfm_host_unregister(void* ptr);
+/* Pipelined parameter-server worker (parallel/ps.py): the batch's unique rows are a device-resident list with a
+ * device-resident count (dfm_touched_bitmap + dfm_union_rowlist_prefix), so nothing waits for a size on the host.
+ * remap_ids: inv[p] = position of ids[p] in the list (out-of-range ids -> oob); pull_list: fm_v rows + fm_w scalars of the
+ * listed rows out of the mapped host store; push_list: the listed gradient rows, the row ids and the count into page-locked
+ * host buffers (device copies zeroed). No reference counterpart beyond the gRPC pulls/pushes of X3. */
+int dfm_ps_remap_ids(const int* ids, long long n, int N, const unsigned int* bm_union, const int* word_prefix, int oob,
+                     int* inv, void* stream);
+int dfm_ps_pull_list(const float* table_v_dev, const float* table_w_dev, const int* rows, const int* count, int max_rows,
+                     int K, float* out_v, float* out_w, void* stream);
+int dfm_ps_push_list(float* g_v, float* g_w, const int* rows, const int* count, int max_rows, int K, float* host_v,
+                     float* host_w, int* host_rows, int* host_count, void* stream);
 
 /* ---- kernel timeline (csrc/common.cuh): %globaltimer stamps per kernel, compiled in only by the trace build
  * (`python -m deepfm_b200.build --trace` -> libdeepfm_b200_trace.so). out: dfm_trace_words() words, 4 per trace id:

@@ -76,6 +76,14 @@ int dfmio_sparse_opt_apply(float* table, float* s0, float* s1, long long N, int 
 int dfmio_dense_opt_apply(float* w, float* s0, float* s1, const float* g, long long n, int opt, float lr, float beta1,
                           float beta2, float eps, float momentum, float l2, long long step, int threads);
 
+/* One pushed step of a parameter-server worker in ONE call: touched rows of fm_v / fm_w (rows int32 [nrows], unique; gv
+ * [nrows, K], gw [nrows]; touched-row L2) followed by nvars dense variables (pointer arrays w / s0 / s1 / g, numel; no L2). */
+int dfmio_ps_apply_push(float* tab_v, float* sv0, float* sv1, float* tab_w, float* sw0, float* sw1, long long N, int K,
+                        const int* rows, long long nrows, const float* gv, const float* gw, int nvars, float* const* w,
+                        float* const* s0, float* const* s1, const float* const* g, const long long* numel, int opt,
+                        float lr, float beta1, float beta2, float eps, float momentum, float l2, long long step,
+                        int threads);
+
 /* ---- TensorFlow tensor bundle (checkpoint V2): <prefix>.index (SSTable) + <prefix>.data-00000-of-00001.
  * dtype is TensorFlow's DataType enum (1 float32, 3 int32, 9 int64); dims holds up to 8 entries. */
 const char* dfmio_bundle_last_error(void);

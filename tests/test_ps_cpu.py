@@ -63,7 +63,8 @@ def test_two_worker_ps_over_gloo(tmp_path):
     write_synthetic_tfrecords(str(d / "val"), "va", 1, 640, F, N, seed=2)
     hp = dict(field_size=F, feature_size=N, embedding_size=8, deep_layers="32,16", dropout="1.0,1.0", batch_size=64,
               learning_rate=0.05, optimizer="Adagrad", backend="torch", task_type="train", num_epochs=3, log_steps=1000,
-              model_dir=str(tmp_path / "ck"), loader_threads=1, ps_staleness=1)
+              model_dir=str(tmp_path / "ck"), loader_threads=1, ps_staleness=1, save_checkpoints_steps=10,
+              eval_start_delay_secs=0, eval_throttle_secs=0)
     env = {"PYTHONPATH": REPO, "CUDA_VISIBLE_DEVICES": "", "MASTER_PORT_HINT": "1"}
     LocalEstimator(hp, {"parameter_server": {"enabled": True, "workers_per_host": 2}}, env=env, cwd=REPO).fit(
         {"training": str(d / "train"), "evaluation": str(d / "val")}, timeout=600)
@@ -73,8 +74,12 @@ def test_two_worker_ps_over_gloo(tmp_path):
     # 2 workers x (1280 rows each per epoch / 64) x 3 epochs = 120 applied pushes (unlocked counter: allow slack)
     assert 60 <= int(ck["global_step"]) <= 120
     m = [json.loads(l) for l in open(tmp_path / "ck" / "metrics.jsonl")]
+    # train_and_evaluate semantics (PS:439-442): the chief evaluated new checkpoints while the workers trained, and the
+    # final checkpoint at the end
     evs = [x for x in m if x.get("eval")]
-    assert len(evs) == 3 and evs[-1]["auc"] > 0.55 and evs[-1]["loss"] < evs[0]["loss"] + 0.02
+    assert len(evs) >= 1 and evs[-1]["auc"] > 0.55 and evs[-1]["global_step"] == int(ck["global_step"])
+    steps = [e["global_step"] for e in evs]
+    assert steps == sorted(steps) and len(set(steps)) == len(steps)  # each checkpoint evaluated once, in order
 
 
 @pytest.mark.parametrize("opt_name", ["Adam", "Adagrad", "Momentum", "ftrl", "GD"])
@@ -117,3 +122,80 @@ def test_native_host_optimizer_matches_tf1_reference_rules(opt_name):
     assert changed == [3, 9]
     with pytest.raises(IOError):
         native.sparse_opt_apply(fm_w, sl1, torch.tensor([N]), torch.tensor([0.5]), opt, 0.0, 1)
+
+
+def test_throttled_checkpoint_evaluator_start_delay_throttle_and_final_eval(tmp_path):
+    """runtime/train_and_evaluate.py: nothing before start_delay, one evaluation per throttle period, every checkpoint at
+    most once, the final checkpoint on finish()."""
+    import time
+    from deepfm_b200.data.synthetic import SyntheticCTR
+    from deepfm_b200.models import DeepFMConfig, init_params
+    from deepfm_b200.optim import TF1Optimizer
+    from deepfm_b200.runtime.train_and_evaluate import ThrottledCheckpointEvaluator, evaluate_checkpoint
+    from deepfm_b200.utils.checkpoint import save_checkpoint
+    cfg = DeepFMConfig(field_size=F, feature_size=N, embedding_size=8, deep_layers=[32, 16], dropout=[1.0, 1.0], l2_reg=1e-5)
+    opt = TF1Optimizer("GD", 0.1)
+    data = SyntheticCTR(F, N, seed=4)
+    held = [data.batch(256, i, ids_dtype=torch.int64) for i in range(3)]
+
+    def ckpt(step, seed):
+        sd = {k: v for k, v in init_params(cfg, seed).items()}
+        sd["global_step"] = torch.tensor([step], dtype=torch.int64)
+        return save_checkpoint(str(tmp_path), sd, opt, 5)
+
+    seen = []
+    ev = ThrottledCheckpointEvaluator(cfg, str(tmp_path), "GD", lambda: iter(held), seen.append, start_delay_secs=0.6,
+                                      throttle_secs=0.5, backend="torch-cpu", poll_secs=0.05)
+    ckpt(10, 1)
+    ev.start()
+    time.sleep(0.3)
+    assert not seen  # start delay
+    time.sleep(0.6)
+    assert [m["global_step"] for m in seen] == [10]
+    ckpt(20, 2)
+    ckpt(30, 3)  # two checkpoints inside one throttle period: only the newest is evaluated when the period ends
+    time.sleep(0.9)
+    assert [m["global_step"] for m in seen] == [10, 30]
+    p40 = ckpt(40, 4)
+    res = ev.finish(final_eval=True)
+    assert [m["global_step"] for m in res][-1] == 40 and len(res) == len(seen) <= 4
+    direct, _ = evaluate_checkpoint(cfg, p40, "GD", iter(held), backend="torch-cpu")
+    assert abs(direct["loss"] - res[-1]["loss"]) < 1e-9 and direct["examples"] == 768 and 0.0 <= direct["auc"] <= 1.0
+
+
+def test_ps_apply_push_single_call_matches_per_variable_calls():
+    """dfmio_ps_apply_push (one native call per pushed step) == the per-variable sparse / dense entry points."""
+    import ctypes
+    from deepfm_b200.data import native
+    from deepfm_b200.optim import OPT_IDS, SLOT_INIT, TF1Optimizer
+    g = torch.Generator().manual_seed(5)
+    Nn, K, n = 300, 8, 57
+    opt = TF1Optimizer("Adam", 1e-2)
+    mk = lambda *s: torch.randn(*s, generator=g)
+    tv, tw = mk(Nn, K), mk(Nn)
+    sv = [torch.full((Nn, K), v) + 0.01 * torch.rand(Nn, K, generator=g) for v in SLOT_INIT["Adam"]]
+    sw = [torch.full((Nn,), v) + 0.01 * torch.rand(Nn, generator=g) for v in SLOT_INIT["Adam"]]
+    dense = [mk(1000), mk(70000)]
+    sd = [[torch.full_like(d, v) for v in SLOT_INIT["Adam"]] for d in dense]
+    rows = torch.randperm(Nn, generator=g)[:n].to(torch.int32)
+    gv, gw = mk(n, K) * 0.1, mk(n) * 0.1
+    gd = [mk(1000) * 0.1, mk(70000) * 0.1]
+    ref = [t.clone() for t in [tv, tw] + sv + sw + dense + sd[0] + sd[1]]
+    rtv, rtw, rsv, rsw, rd, rsd = ref[0], ref[1], ref[2:4], ref[4:6], ref[6:8], [ref[8:10], ref[10:12]]
+    native.sparse_opt_apply(rtv, rsv, rows.long(), gv, opt, 1e-3, 3)
+    native.sparse_opt_apply(rtw, rsw, rows.long(), gw, opt, 1e-3, 3)
+    for d, s, gg in zip(rd, rsd, gd):
+        native.dense_opt_apply(d, s, gg, opt, 0.0, 3)
+    arr = lambda xs: (ctypes.c_void_p * len(xs))(*[x.data_ptr() for x in xs])
+    P = lambda t: ctypes.c_void_p(t.data_ptr())
+    rc = native.load().dfmio_ps_apply_push(P(tv), P(sv[0]), P(sv[1]), P(tw), P(sw[0]), P(sw[1]), Nn, K, P(rows), n, P(gv), P(gw),
+                                           2, arr(dense), arr([s[0] for s in sd]), arr([s[1] for s in sd]), arr(gd),
+                                           (ctypes.c_longlong * 2)(1000, 70000), OPT_IDS["Adam"], opt.lr, opt.beta1, opt.beta2,
+                                           opt.eps, opt.momentum, 1e-3, 3, 3)
+    assert rc == 0
+    for a, b in zip([tv, tw] + sv + sw + dense + sd[0] + sd[1], ref):
+        assert torch.equal(a, b)
+    bad = torch.tensor([Nn], dtype=torch.int32)
+    assert native.load().dfmio_ps_apply_push(P(tv), P(sv[0]), P(sv[1]), P(tw), P(sw[0]), P(sw[1]), Nn, K, P(bad), 1, P(gv), P(gw),
+                                             0, None, None, None, None, None, OPT_IDS["Adam"], opt.lr, opt.beta1, opt.beta2,
+                                             opt.eps, opt.momentum, 0.0, 1, 1) == -1
