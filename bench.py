@@ -347,6 +347,19 @@ def main():
         except Exception as e:
             self_check = {"error": "%s: %s" % (type(e).__name__, str(e)[:300])}
 
+    # ---- (4) row-sharded tables: device time of the fused all-to-all kernels alone (the metric names it)
+    a2a = None
+    if a.strategy == "sharded" and hasattr(tr.model, "time_a2a"):
+        a2a = tr.model.time_a2a(50)
+        ta = torch.tensor([a2a["fwd_us"], a2a["bwd_opt_us"]], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ta, op=dist.ReduceOp.MAX)
+        a2a["fwd_us"], a2a["bwd_opt_us"] = float(ta[0]), float(ta[1])
+        a2a["a2a_us_per_step"] = float(ta[0] + ta[1])
+        # roofline: the slower link direction carries nvlink_bytes/2 per phase at the measured 770 GB/s per direction
+        a2a["nvlink_roofline_us"] = a2a["nvlink_bytes_per_step"] / 770e9 * 1e6
+        a2a["frac_of_nvlink_roofline"] = a2a["nvlink_roofline_us"] / max(a2a["a2a_us_per_step"], 1e-9)
+
     t = torch.tensor([ms, ms_e2e], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -379,6 +392,7 @@ def main():
             "gpu_launches": launches, "kernels_per_step": tr.kernels_per_step,
             "l2_persist_bytes": int(getattr(getattr(tr, "model", None), "l2_persist_bytes", 0) or 0),
             "final_loss": final_loss, "e2e_last_loss": losses[-1] if losses else None, "self_check": self_check,
+            "a2a": a2a, "a2a_us_per_step": a2a["a2a_us_per_step"] if a2a else None,
             "ps_profile_us_per_step": ({k: v / max(tr.prof["steps"], 1) * 1e6 for k, v in tr.prof.items() if k != "steps"}
                                        if hasattr(tr, "prof") else None),
             "ps_max_observed_staleness": getattr(tr, "max_observed_staleness", None),

@@ -280,6 +280,35 @@ __device__ __forceinline__ void wait_flag_geq(const uint32_t* flag, uint32_t seq
   }
 }
 
+// Cross-GPU barrier at the ENTRY of a kernel, whatever its grid: CTA 0 alone exchanges flags with the peers (threads
+// 0..world-1: tell peer p "rank `rank` reached seq", wait until p said the same), then releases a LOCAL go word the other
+// CTAs of this grid wait for. CTA 0 needs no other CTA to make progress, so nothing depends on how many CTAs are resident
+// or on the order in which they are dispatched — a per-CTA flag pairing across ranks (the first version) did.
+// flags[p] = rank p's flag array (peer-mapped); slot = this barrier's first word in it (8 words, one per rank);
+// go = a word of THIS rank's array no peer writes. Sequence numbers only grow.
+__device__ __forceinline__ void grid_entry_barrier(uint32_t* const* flags, size_t slot, uint32_t* go, int rank, int world,
+                                                   uint32_t seq, int what) {
+  if (world <= 1) return;
+  const bool first = blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+  if (first) {
+    if (threadIdx.x < (unsigned)world) {
+      const int peer = threadIdx.x;
+      asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flags[peer] + slot + rank), "r"(seq) : "memory");
+      wait_flag_geq(flags[rank] + slot + peer, seq, peer, what);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(go), "r"(seq) : "memory");
+  } else {
+    if (threadIdx.x == 0) {
+      uint32_t v;
+      do {
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(go) : "memory");
+      } while ((int32_t)(v - seq) < 0);
+    }
+    __syncthreads();
+  }
+}
+
 // ----------------------------------------------------------------------------------- vector memory ops
 __device__ __forceinline__ void red_add_f32x4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)

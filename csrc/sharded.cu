@@ -16,8 +16,9 @@
 //                     L2 mode), zeroing the gradient rows and bitmap words it consumes.
 //
 // Ordering: emb_fm_fwd_a2a begins with a cross-GPU barrier ("every owner finished last step's row updates"),
-// sparse_row_opt begins with one ("every rank finished pushing gradients"). Barriers are per-CTA flag exchanges with
-// release/acquire at system scope on monotonically increasing sequence numbers, as in allreduce_opt.cu.
+// sparse_row_opt begins with one ("every rank finished pushing gradients"). A barrier is ONE flag exchange by CTA 0 with
+// release/acquire at system scope on monotonically increasing sequence numbers (the other CTAs wait for CTA 0's local go
+// word), so no grid size or CTA dispatch order is assumed.
 #include "common.cuh"
 #include "optim_math.cuh"
 
@@ -45,17 +46,11 @@ __device__ __forceinline__ uint32_t sh_ld_acquire_sys(const uint32_t* p) {
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
-// Per-CTA barrier across ranks; every rank must launch the same grid for the kernel that calls it.
+// Barrier across ranks at kernel entry (common.cuh grid_entry_barrier): CTA 0 exchanges the flags of block slot 0 of this
+// phase, the other CTAs wait for the local go word kept in block slot 1 (which no peer ever writes).
 __device__ __forceinline__ void cross_rank_barrier(const ShardPtrs& sp, int phase, uint32_t seq) {
-  if (sp.world > 1) {
-    if (threadIdx.x < sp.world) {
-      const int peer = threadIdx.x;
-      const size_t slot = ((size_t)phase * kShMaxBlocks + blockIdx.x) * kShMaxRanks;
-      sh_st_release_sys(sp.flags[peer] + slot + sp.rank, seq);
-      wait_flag_geq(sp.flags[sp.rank] + slot + peer, seq, peer, 2 + phase);
-    }
-    __syncthreads();
-  }
+  const size_t slot = (size_t)phase * kShMaxBlocks * kShMaxRanks;
+  grid_entry_barrier(sp.flags, slot, sp.flags[sp.rank] + slot + kShMaxRanks, sp.rank, sp.world, seq, 2 + phase);
 }
 __device__ __forceinline__ float4 ld_peer_f4(const float* p) {  // peer data changes every step: never the nc path
   float4 v;

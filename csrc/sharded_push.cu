@@ -42,16 +42,11 @@ struct PushPtrs {
   long long cap;
 };
 
+// Barrier across ranks at kernel entry (common.cuh grid_entry_barrier: CTA 0 exchanges flags, the rest wait for its local
+// go word in block slot 1 of the phase).
 __device__ __forceinline__ void push_barrier(const PushPtrs& pp, int phase, uint32_t seq) {
-  if (pp.world > 1) {
-    if (threadIdx.x < pp.world) {
-      const int peer = threadIdx.x;
-      const size_t slot = ((size_t)phase * kPsMaxBlocks + blockIdx.x) * kPsMaxRanks;
-      asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(pp.flags[peer] + slot + pp.rank), "r"(seq) : "memory");
-      wait_flag_geq(pp.flags[pp.rank] + slot + peer, seq, peer, 10 + phase);
-    }
-    __syncthreads();
-  }
+  const size_t slot = (size_t)phase * kPsMaxBlocks * kPsMaxRanks;
+  grid_entry_barrier(pp.flags, slot, pp.flags[pp.rank] + slot + kPsMaxRanks, pp.rank, pp.world, seq, 10 + phase);
 }
 
 // ------------------------------------------------------------------------------------------------ dispatch

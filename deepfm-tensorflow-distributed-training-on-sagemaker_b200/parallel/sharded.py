@@ -197,6 +197,38 @@ class ShardedDeepFM(FusedDataParallel):
             p(self.step_t), c_int(1), p(self.sh_seq), p(self.sh_done), p(self.reg_loss), c_int(self._opt_blocks), st))
         return 2
 
+    def time_a2a(self, iters: int = 50, slot_idx: int = 0) -> Dict[str, float]:
+        """Device time of the embedding all-to-all kernels alone (BASELINE.json metric: "embedding a2a time/step"): the
+        fused dispatch+gather+combine forward, and the gradient all-to-all + segment-sum + sparse row update backward, each
+        timed with CUDA events over `iters` back-to-back launches on the inputs / upstream gradients of the last step.
+        Collective: every rank must call it. Returns microseconds per launch (this rank; take the max over ranks)."""
+        slot = self.in_slots[slot_idx]
+        out = {}
+        self._train_mode = True
+        try:
+            for name, fn in (("fwd_us", lambda: self._emb_forward(slot)), ("bwd_opt_us", lambda: self._emb_backward(slot))):
+                for _ in range(5):
+                    fn()
+                torch.cuda.synchronize(self.dev)
+                dist.barrier(group=self.group)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(iters):
+                    fn()
+                e1.record()
+                torch.cuda.synchronize(self.dev)
+                out[name] = e0.elapsed_time(e1) * 1e3 / iters
+        finally:
+            self._train_mode = False
+        out["a2a_us_per_step"] = out["fwd_us"] + out["bwd_opt_us"]
+        lookups = self.B * self.cfg.field_size
+        # bytes that must cross NVLink per rank and step: (W-1)/W of the looked-up rows in (forward) and of the gradient rows
+        # out (backward), fp32 rows of K floats + the first-order scalar
+        frac = (self.world - 1) / max(self.world, 1)
+        out["nvlink_bytes_per_step"] = 2 * lookups * (self.cfg.embedding_size + 1) * 4 * frac
+        out["mode"] = "push" if self.push else "pull"
+        return out
+
     def _snapshot(self):
         snap = super()._snapshot()
         self._tsnap = [self.V.clone(), self.Wt.clone()] + [t.clone() for t in self.VS + self.WS]
