@@ -132,6 +132,14 @@ class FusedDeepFM:
         self.auc_thr = torch.from_numpy(thresholds()).to(dev)
         self.auc_hist = torch.zeros(2, NUM_THRESHOLDS + 1, **f32)
 
+        # DFM_DETERMINISTIC=1: embedding gradients by sorted segment-sum (csrc/embed_det.cu) instead of fp32 atomics; with
+        # the store-based wgrads this makes the big gradients bit-reproducible run to run (the bias / head column sums and
+        # the loss scalar still accumulate a few hundred atomics)
+        import os as _os
+        self.det_emb = None
+        if _os.environ.get("DFM_DETERMINISTIC", "0") == "1" and self.layout.include_embeddings \
+                and type(self)._emb_backward is FusedDeepFM._emb_backward and Kd <= 64:
+            self.det_emb = K.DetEmbBwd(B, F_, Kd, cfg.feature_size, dev)
         self._side = torch.cuda.Stream(device=dev)
         self._side2 = torch.cuda.Stream(device=dev)
         self._setup_split_optimizer()
@@ -285,6 +293,9 @@ class FusedDeepFM:
                      self.scalars if zero_scalars else None)
 
     def _emb_backward(self, slot) -> int:
+        if self.det_emb is not None:  # the lookups were sorted on the side branch at step start (_train_kernels)
+            self.det_emb.run(slot["vals"], self._w("fm_v"), self.Ssum, self.dy, self.dx0, self._g("fm_w"), self._g("fm_v"))
+            return 2
         K.emb_bwd(slot["ids"], slot["vals"], self._w("fm_v"), self.Ssum, self.dy, self.dx0, self._g("fm_w"),
                   self._g("fm_v"))
         return 1
@@ -313,6 +324,16 @@ class FusedDeepFM:
         n = 0
         pre = self._pre_step(self._side)
         split = self.split is not None and with_optimizer
+        det_ev = None
+        if self.det_emb is not None:  # fork: sort the lookups by row id (needs only the inputs) while the forward runs
+            ev0 = torch.cuda.Event()
+            ev0.record(cur)
+            self._side2.wait_event(ev0)
+            with torch.cuda.stream(self._side2):
+                self.det_emb.sort(slot["ids"], slot["vals"])
+                n += 4
+                det_ev = torch.cuda.Event()
+                det_ev.record(self._side2)
         if split:  # fork: touched-row bitmap + sweep of the untouched table rows overlap the whole forward/backward
             ev0 = torch.cuda.Event()
             ev0.record(cur)
@@ -360,6 +381,8 @@ class FusedDeepFM:
                 forked = True
             self.dgrad[i].run()
             n += 1
+        if det_ev is not None:
+            cur.wait_event(det_ev)
         n += self._emb_backward(slot)
         for sd in sides:  # join
             ev = torch.cuda.Event()

@@ -46,6 +46,27 @@ def emb_bwd(ids, vals, fm_v, S, dy, dx0, g_w, g_v) -> None:
                                        _p(g_w), _p(g_v), c_int(B), c_int(F), c_int(K), c_int(N), _stream()))
 
 
+class DetEmbBwd:
+    """Deterministic embedding backward (csrc/embed_det.cu): `sort(ids, vals)` on a side stream at step start, `run(...)`
+    in place of emb_bwd. Owns the workspace (sorted keys / indices, cub temporary storage, boundary records)."""
+
+    def __init__(self, B: int, F: int, K: int, N: int, device):
+        lib = _lib.load()
+        lib.dfm_emb_bwd_det_workspace_bytes.restype = c_longlong
+        self.B, self.F, self.K, self.N = B, F, K, N
+        self.nbytes = int(lib.dfm_emb_bwd_det_workspace_bytes(c_int(B), c_int(F), c_int(K)))
+        self.ws = torch.zeros(self.nbytes, dtype=torch.uint8, device=device)
+
+    def sort(self, ids: torch.Tensor, vals: torch.Tensor) -> None:
+        _lib.check(_lib.load().dfm_emb_sort_ids(_p(ids), _p(vals), c_int(self.B), c_int(self.F), c_int(self.K), c_int(self.N),
+                                                _p(self.ws), c_longlong(self.nbytes), _stream()))
+
+    def run(self, vals, fm_v, S, dy, dx0, g_w, g_v) -> None:
+        _lib.check(_lib.load().dfm_emb_bwd_det(_p(vals), _p(fm_v), _p(S), _p(dy), _p(dx0), c_int(dx0.stride(0)), _p(g_w),
+                                               _p(g_v), c_int(self.B), c_int(self.F), c_int(self.K), c_int(self.N),
+                                               _p(self.ws), c_longlong(self.nbytes), _stream()))
+
+
 class GemmPlan:
     """A tcgen05 GEMM bound to fixed buffers (owns the host-side TMA descriptors).
 

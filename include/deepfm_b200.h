@@ -28,6 +28,17 @@ int dfm_emb_fm_fwd(const int* ids, const float* vals, const float* fm_w, const f
 int dfm_emb_bwd(const int* ids, const float* vals, const float* fm_v, const float* S, const float* dy,
                 const void* dx0_bf16, int ldx, float* g_w, float* g_v, int B, int F, int K, int N, void* stream);
 
+/* Deterministic twin of dfm_emb_bwd (csrc/embed_det.cu; TF segment-sums duplicate ids before applying them): sort_ids sorts
+ * the batch's lookups by row id into a caller-owned workspace (needs only ids / vals: side stream, step start), emb_bwd_det
+ * sums every run of equal ids in a fixed order and gives each touched row ONE plain store (no atomics; g_w / g_v are
+ * overwritten, not accumulated). workspace: dfm_emb_bwd_det_workspace_bytes(B, F, K) bytes of device memory. */
+long long dfm_emb_bwd_det_workspace_bytes(int B, int F, int K);
+int dfm_emb_sort_ids(const int* ids, const float* vals, int B, int F, int K, int N, void* workspace,
+                     long long workspace_bytes, void* stream);
+int dfm_emb_bwd_det(const float* vals, const float* fm_v, const float* S, const float* dy, const void* dx0_bf16, int ldx,
+                    float* g_w, float* g_v, int B, int F, int K, int N, void* workspace, long long workspace_bytes,
+                    void* stream);
+
 /* ---- tcgen05 MLP GEMMs (replaces fully_connected fwd/bwd, PS:212-223) ----
  * mode 0 forward: out[M,N] bf16 = dropout(relu(A[M,K] B[N,K]^T + bias));  mode 1 dgrad: out[M,N] bf16 =
  * (A[M,K] B[K,N]) * (mask != 0) * mask_scale;  mode 2 wgrad: out[M,N] f32 += A[K,M]^T B[K,N].

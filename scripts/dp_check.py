@@ -90,6 +90,18 @@ for exch, comm in modes:
             err = float((tot - data_ref).abs().max()) / (float(data_ref.abs().max()) + 1e-12)
             check(err < 2e-2, "%s %s gradient %s err %.3e" % (tag, opt, k, err))
             noise_ok[k] = torch.ones_like(ref, dtype=torch.bool)
+        # ---- 1b. DP-W == DP-1, same kernels: the all-reduced shard gradients vs ONE engine on the concatenated batch
+        # (global-mean loss and dropout keyed by global row make them the same computation up to fp32 summation order)
+        if opt == "Momentum" and comm != "nccl":
+            from deepfm_b200.models.fused import FusedDeepFM
+            one = FusedDeepFM(cfg, GB, TF1Optimizer(opt, 1e-2), 77, dev, params=params, use_graph=False)
+            g1 = one.compute_grads(ids.to(dev), vals.to(dev), labels.to(dev))
+            for k in g1:
+                tot = g[k].clone()
+                dist.all_reduce(tot)
+                err = float((tot - g1[k]).abs().max()) / (float(g1[k].abs().max()) + 1e-12)
+                check(err < 2e-5, "%s DP-%d vs DP-1 gradient %s err %.3e" % (tag, world, k, err))
+            del one
         # ---- 3. optimizer steps
         losses = []
         for step in range(3):

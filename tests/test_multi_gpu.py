@@ -30,6 +30,16 @@ def test_sharded_embeddings_match_oracle():
     assert rc == 0 and "SHARDED_CHECK PASS" in out, out[-3000:]
 
 
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_flag_protocol_stress_skewed_ranks_and_sequence_wrap():
+    """skewed ranks, thousands of steps, sequence numbers wrapping at 2^32 (scripts/flag_stress.py)."""
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29575", os.path.join(REPO, "scripts", "flag_stress.py"),
+                        "--steps", "3000", "--check_every", "1000"], capture_output=True, text=True, timeout=600, cwd=REPO)
+    out = r.stdout + r.stderr
+    assert r.returncode == 0 and "FLAG_STRESS PASS" in out, out[-3000:]
+
+
 def test_dp_exchange_kernels_single_rank(cuda_lib):
     """World size 1 runs the SAME exchange kernels (sparse touched-row exchange, dense ZeRO-1 kernel, flag barriers, state
     broadcast) over self-mapped symmetric memory, so a one-GPU box still checks them against the oracle and NCCL."""
