@@ -48,6 +48,8 @@ struct GemmParams {
   int out_f32;  // EPI_BIAS_ACT only: store fp32 (pre-batch-norm activations must not be rounded to bf16)
   int trace_id; // timeline id (trace build only; -1 = none)
   int overwrite;  // EPI_ACCUM_F32 only: plain stores instead of red.add (needs a single K split)
+  float* bias_out;  // EPI_ACCUM_F32 only: output column N (one past the weight gradient) goes here instead: with a column
+                    // of ones appended to the B operand it is sum_k A[k, m] = the bias gradient, on the tensor core for free
   float* colsum;  // EPI_MASK only: colsum[n] += sum over rows of the (masked, scaled) output = the bias gradient of the
                   // layer that produced the mask (reference: BiasAddGrad); null = off
 };
@@ -245,7 +247,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       float v[16];
       tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c, v);
       const int n = n0 + c;
-      if (n >= p.N) continue;  // warp-uniform
+      int n_lim = p.N;
+      if constexpr (EPI == EPI_ACCUM_F32) n_lim += p.bias_out ? 1 : 0;  // the extra "ones" column
+      if (n >= n_lim) continue;  // warp-uniform
       const bool full16 = (n + 16 <= p.N);
       if constexpr (EPI == EPI_MASK || EPI == EPI_MASK_BIG) {
         if (p.colsum) {  // warp-uniform: every lane takes part in the shuffles below, rows past M contribute zeros
@@ -336,16 +340,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               *reinterpret_cast<float4*>(orow + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
           } else {
 #pragma unroll
-            for (int j = 0; j < 16; ++j)
+            for (int j = 0; j < 16; ++j) {
               if (n + j < p.N) orow[j] = v[j];
+              else if (p.bias_out && n + j == p.N) p.bias_out[row] = v[j];
+            }
           }
         } else if (full16 && (p.ldo % 4 == 0)) {
 #pragma unroll
           for (int j = 0; j < 16; j += 4) red_add_f32x4(orow + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
         } else {
 #pragma unroll
-          for (int j = 0; j < 16; ++j)
+          for (int j = 0; j < 16; ++j) {
             if (n + j < p.N) atomicAdd(orow + j, v[j]);
+            else if (p.bias_out && n + j == p.N) atomicAdd(p.bias_out + row, v[j]);
+          }
         }
       } else if (EPI == EPI_BIAS_ACT && p.out_f32) {
         float* orow = reinterpret_cast<float*>(p.out) + (size_t)row * p.ldo + n;
@@ -474,7 +482,8 @@ extern "C" {
 
 // mode 0: forward   out[M,N] bf16 = act(A[M,K] * B[N,K]^T + bias) with dropout
 // mode 1: dgrad     out[M,N] bf16 = (A[M,K] * B[K,N]) * (mask != 0) * mask_scale
-// mode 2: wgrad     out[M,N] f32 += A[K,M]^T * B[K,N]          (atomic accumulate; split-K)
+// mode 2: wgrad     out[M,N] f32 += A[K,M]^T * B[K,N]          (atomic accumulate; split-K). `bias` non-null in this mode:
+//                   B has a column of ones at index N (ldb > N) and bias[m] receives sum_k A[k,m] (the bias gradient)
 // lda/ldb/ldo/ldmask are leading dimensions in elements; all bf16 leading dims must be multiples of 8.
 int dfm_gemm_plan_create(void** plan_out, int mode, const void* A, int lda, const void* B, int ldb, int M, int N, int K,
                          void* out, int ldo, const float* bias, int relu, float keep_prob, unsigned long long seed,
@@ -497,9 +506,10 @@ int dfm_gemm_plan_create(void** plan_out, int mode, const void* A, int lda, cons
   } else if (mode == 1) {  // A [M,K] K-major, B stored [K,N]
     rc = make_tmap(&pl->tmA, A, M, K, lda, BM);
     if (!rc) rc = make_tmap(&pl->tmB, B, K, N, ldb, BK);
-  } else {  // A stored [K,M], B stored [K,N]
+  } else {  // A stored [K,M], B stored [K,N]; with a bias output, B carries a column of ones at index N (ldb > N)
+    DFM_REQUIRE(bias == nullptr || ldb > N, "wgrad with a bias output needs the ones column: ldb must exceed N");
     rc = make_tmap(&pl->tmA, A, K, M, lda, BK);
-    if (!rc) rc = make_tmap(&pl->tmB, B, K, N, ldb, BK);
+    if (!rc) rc = make_tmap(&pl->tmB, B, K, bias ? N + 1 : N, ldb, BK);
   }
   if (rc) { delete pl; return rc; }
   GemmParams& p = pl->p;
@@ -517,7 +527,8 @@ int dfm_gemm_plan_create(void** plan_out, int mode, const void* A, int lda, cons
   }
   p.k_blocks_per_split = ceil_div(p.num_k_blocks, splits);
   splits = ceil_div(p.num_k_blocks, p.k_blocks_per_split);  // no empty splits
-  p.out = out; p.ldo = ldo; p.bias = bias; p.relu = relu;
+  p.out = out; p.ldo = ldo; p.bias = mode == 2 ? nullptr : bias; p.relu = relu;
+  p.bias_out = mode == 2 ? const_cast<float*>(bias) : nullptr;
   p.drop.enabled = (mode == 0 && keep_prob < 1.0f) ? 1u : 0u;
   p.drop.threshold = keep_prob >= 1.0f ? 0xFFFFFFFFu : (uint32_t)floor((double)keep_prob * 4294967296.0);
   p.drop.scale = keep_prob >= 1.0f ? 1.0f : 1.0f / keep_prob;
@@ -529,7 +540,7 @@ int dfm_gemm_plan_create(void** plan_out, int mode, const void* A, int lda, cons
   p.trace_id = -1;
   p.colsum = nullptr;
   p.overwrite = 0;
-  pl->grid = dim3(m_tiles, ceil_div(N, pl->bn), splits);
+  pl->grid = dim3(m_tiles, ceil_div(N + (p.bias_out ? 1 : 0), pl->bn), splits);
   *plan_out = pl;
   return DFM_OK;
 }

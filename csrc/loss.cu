@@ -31,7 +31,8 @@ logit_loss_kernel(const __nv_bfloat16* __restrict__ x, int ldx, int H, const flo
   // last hidden layer), s_col[1][j] = sum_b dy[b] x[b,j] (gradient of deep_out.weight). One shared-memory atomic per
   // element here replaces two colsum_bf16 launches that re-read dZ and X from global memory.
   extern __shared__ float s_col[];  // [kLossWarps][2][H]: every warp owns a row pair, every lane its columns: no atomics
-  const bool cols = train && g_b_top != nullptr && g_w_out != nullptr;
+  const bool cols = train && g_w_out != nullptr;
+  const bool has_gb = g_b_top != nullptr;  // the bias column sum is optional (the wgrad GEMM can produce it instead)
   if (threadIdx.x < 2) s_scalar[threadIdx.x] = 0.f;
   if (cols)
     for (int j = threadIdx.x; j < 2 * H * kLossWarps; j += kLossThreads) s_col[j] = 0.f;
@@ -105,7 +106,7 @@ logit_loss_kernel(const __nv_bfloat16* __restrict__ x, int ldx, int H, const flo
       float a0 = 0.f, a1 = 0.f;
 #pragma unroll
       for (int w = 0; w < kLossWarps; ++w) { a0 += s_col[(size_t)w * 2 * H + j]; a1 += s_col[(size_t)w * 2 * H + H + j]; }
-      if (a0 != 0.f) atomicAdd(g_b_top + j, a0);
+      if (has_gb && a0 != 0.f) atomicAdd(g_b_top + j, a0);
       if (a1 != 0.f) atomicAdd(g_w_out + j, a1);
     }
   trace_end(TR_LOSS);
@@ -203,11 +204,11 @@ int dfm_logit_loss_cols(const void* x, int ldx, int H, const float* w_out, const
                         float* g_fm_bias, float* g_b_top, float* g_w_out, void* stream) {
   DFM_REQUIRE(B > 0 && H > 0, "logit_loss: empty problem");
   DFM_REQUIRE(ldx % 2 == 0 && (!train || lddz % 2 == 0), "logit_loss: leading dimensions must be even");
-  DFM_REQUIRE((g_b_top == nullptr) == (g_w_out == nullptr), "logit_loss: give both column-sum outputs or neither");
-  DFM_REQUIRE(g_b_top == nullptr || H <= 1024, "logit_loss: column sums need H <= 1024 (shared-memory accumulators)");
+  DFM_REQUIRE(g_b_top == nullptr || g_w_out != nullptr, "logit_loss: g_b_top needs g_w_out as well");
+  DFM_REQUIRE(g_w_out == nullptr || H <= 1024, "logit_loss: column sums need H <= 1024 (shared-memory accumulators)");
   int blocks = ceil_div(B, kLossWarps);
   if (blocks > 148 * 4) blocks = 148 * 4;
-  const size_t smem = (g_b_top && train) ? 2 * (size_t)H * kLossWarps * sizeof(float) : 0;
+  const size_t smem = (g_w_out && train) ? 2 * (size_t)H * kLossWarps * sizeof(float) : 0;
   if (smem > 48 * 1024) {
     static bool big_smem_set = false;
     if (!big_smem_set) {

@@ -115,11 +115,20 @@ class FusedDeepFM:
         # input slots use the native loader's packed slot layout (labels | ids | vals, 256-byte aligned parts) so a
         # whole batch moves host->device with ONE copy
         self.in_slots = [make_packed_slot(B, F_, dev) for _ in range(max(1, input_slots))]
-        self.x0 = torch.zeros(B, F_ * Kd, **bf)
+        # Layer inputs carry a few extra columns (row stride rounded up to 128 bytes), the first of them all ones: the wgrad GEMM dW_i = dZ_i^T [X_i | 1] then yields
+        # the bias gradient (column sums of dZ_i) as one more output column on the tensor core — no colsum kernel, no
+        # atomics, nothing on the critical chain. Kernels see [B, width] views of the padded buffers.
+        def act_buf(width):
+            ld = (width + 1 + 63) // 64 * 64  # rows start on 128-byte lines: every TMA box row is one line, not two halves
+            buf = torch.zeros(B, ld, **bf)
+            buf[:, width] = 1.0
+            return buf, buf[:, :width]
+        self._x0_buf, self.x0 = act_buf(F_ * Kd)
         self.dx0 = torch.zeros(B, F_ * Kd, **bf)
         self.Ssum = torch.zeros(B, Kd, **f32)
         self.yfm = torch.zeros(B, **f32)
-        self.acts = [torch.zeros(B, h, **bf) for h in cfg.deep_layers]
+        self._act_bufs, self.acts = zip(*[act_buf(h) for h in cfg.deep_layers])
+        self.acts = list(self.acts)
         self.dz = [torch.zeros(B, h, **bf) for h in cfg.deep_layers]
         self.bn = bool(cfg.batch_norm)
         if self.bn:  # ReLU outputs (pre-BN) and the saved batch statistics
@@ -243,7 +252,7 @@ class FusedDeepFM:
         cfg, B = self.cfg, self.B
         nl = len(cfg.deep_layers)
         self.fwd_train, self.fwd_eval, self.wgrad, self.dgrad = [], [], [], []
-        # bias / head-weight gradients are column sums of dZ and X: produced inside the kernels that write dZ
+        # bias gradients ride the wgrad GEMMs (ones column), the head-weight gradient X_top^T dy is reduced in logit_loss
         self._fold_cols = (not self.bn) and cfg.deep_layers[-1] <= 1024
         x_in = self.x0
         for i, h in enumerate(cfg.deep_layers):
@@ -260,19 +269,21 @@ class FusedDeepFM:
                                                  row_offset=self.row_offset, step_ptr=self.step_t))
                 self.fwd_eval.append(K.GemmPlan("fwd", x_in, Wb, self.acts[i], B, h, d_in, bias=bias, relu=True))
             import os as _os
+            gb = self._g("mlp%d.bias" % i) if self._fold_cols else None  # bias gradient = the ones column of [X | 1]
             if _os.environ.get("DFM_WGRAD_SPLITK", "0") == "1":  # split-K with red.add (fills the SMs; atomics)
-                self.wgrad.append(K.GemmPlan("wgrad", self.dz[i], x_in, self._g("mlp%d.weight" % i), h, d_in, B))
+                self.wgrad.append(K.GemmPlan("wgrad", self.dz[i], x_in, self._g("mlp%d.weight" % i), h, d_in, B, bias=gb))
             else:  # one K split per tile, plain stores: the weight gradient is written, not accumulated
-                self.wgrad.append(K.GemmPlan("wgrad", self.dz[i], x_in, self._g("mlp%d.weight" % i), h, d_in, B,
+                self.wgrad.append(K.GemmPlan("wgrad", self.dz[i], x_in, self._g("mlp%d.weight" % i), h, d_in, B, bias=gb,
                                              split_k=1).set_overwrite(True))
             if i == 0:
                 self.dgrad.append(K.GemmPlan("dgrad", self.dz[0], Wb, self.dx0, B, d_in, h))
+                import os as _os2
+                if _os2.environ.get("DFM_WGRAD_FORK", "after_dgrad0") != "before_dgrad0":
+                    self.dgrad[0].set_exclusive(True)  # nothing runs beside it: whole-SM pipeline
             else:
                 self.dgrad.append(K.GemmPlan("dgrad", self.dz[i], Wb, self.dz[i - 1], B, d_in, h,
                                              mask=self.acts[i - 1], mask_scale=1.0 / cfg.dropout[i - 1]))
                 self.dgrad[i].set_exclusive(True)  # the wgrads are forked after dgrad_1: dgrad_i (i >= 1) runs alone
-                if self._fold_cols:  # bias gradient of layer i-1 = column sums of dZ_{i-1}: folded into this epilogue
-                    self.dgrad[i].set_colsum(self._g("mlp%d.bias" % (i - 1)))
             x_in = self.acts[i]
             # timeline ids (csrc/common.cuh TR_*): forward 1+i, dgrad 5+i, wgrad 8+i
             if i < 3:
@@ -349,38 +360,46 @@ class FusedDeepFM:
         K.logit_loss(self.acts[top], self._w("deep_out.weight"), self._w("deep_out.bias"), self._w("fm_bias"), self.yfm,
                      slot["labels"], 1.0 / self.global_batch, 1.0 / cfg.dropout[top], True, self.prob, self.logit,
                      self.dy, self.dz[top], self.loss_sum, self._g("deep_out.bias"), self._g("fm_bias"),
-                     None if not self._fold_cols else self._g("mlp%d.bias" % top),
-                     None if not self._fold_cols else self._g("deep_out.weight"))
+                     None, None if not self._fold_cols else self._g("deep_out.weight"))
         n += 1
         # Weight gradients: every wgrad_i only needs dz[i] (ready before dgrad_i starts) and nothing needs it before the
-        # optimizer. They are forked late and side by side: wgrad_i of the upper layers waits until dgrad_1 is done, then
-        # all L wgrads run at once on their own branches (28 + 28 + 80 CTAs at 400-400-400: they fit the machine together)
-        # beside dgrad_0 and emb_bwd. Forked as early as possible instead, each shared the SMs, the TMA path and L2 with
-        # the dgrad chain and doubled its kernels' time (scripts/step_trace.py: dgrad 2.9 -> 5.9 us each).
+        # optimizer. They are forked late and side by side: after the whole dgrad chain, all L wgrads run at once on their
+        # own branches (28 + 28 + 80 CTAs at 400-400-400: they fit the machine together) beside emb_bwd, which is bound by
+        # its atomics and leaves the tensor cores idle. Forked as early as possible instead, each shared the SMs, the TMA
+        # path and L2 with the dgrad chain and doubled its kernels' time (scripts/step_trace.py: dgrad 2.9 -> 5.9 us each;
+        # DFM_WGRAD_FORK=before_dgrad0 starts them one kernel earlier: dgrad_0 3.7 -> 7.1 us).
         sides = self._wgrad_streams(nl)
-        forked = False
+        import os as _os
+        fork_before_dgrad0 = _os.environ.get("DFM_WGRAD_FORK", "after_dgrad0") == "before_dgrad0"
+
+        def fork_wgrads():
+            k = 0
+            ev = torch.cuda.Event()
+            ev.record(cur)
+            for j in range(top, -1, -1):
+                sides[j].wait_event(ev)
+                with torch.cuda.stream(sides[j]):
+                    self.wgrad[j].run()
+                    k += 1
+                    if not self._fold_cols:  # batch-norm path / very wide top layer: column sums in their own pass
+                        K.colsum_bf16(self.dz[j], self._g("mlp%d.bias" % j))
+                        k += 1
+                        if j == top:  # g_w_out = X_top^T dy
+                            K.colsum_bf16(self.acts[top], self._g("deep_out.weight"), self.dy)
+                            k += 1
+            return k
+
         for i in range(top, -1, -1):
             if self.bn:  # dz[i] holds d(BN output); turn it into d(pre-activation) in place (BN + ReLU backward)
                 K.bn_bwd(self.dz[i], self.zbuf[i], self._w("bn_%d.gamma" % i), self.bn_mean[i], self.bn_rstd[i],
                          self._g("bn_%d.gamma" % i), self._g("bn_%d.beta" % i))
                 n += 1
-            if i == 0 and not forked:  # dz[0] (and every dz above it) is final here
-                ev = torch.cuda.Event()
-                ev.record(cur)
-                for j in range(top, -1, -1):
-                    sides[j].wait_event(ev)
-                    with torch.cuda.stream(sides[j]):
-                        self.wgrad[j].run()
-                        n += 1
-                        if not self._fold_cols:  # batch-norm path / very wide top layer: column sums in their own pass
-                            K.colsum_bf16(self.dz[j], self._g("mlp%d.bias" % j))
-                            n += 1
-                            if j == top:  # g_w_out = X_top^T dy
-                                K.colsum_bf16(self.acts[top], self._g("deep_out.weight"), self.dy)
-                                n += 1
-                forked = True
+            if i == 0 and fork_before_dgrad0:  # dz[0] (and every dz above it) is final here
+                n += fork_wgrads()
             self.dgrad[i].run()
             n += 1
+        if not fork_before_dgrad0:
+            n += fork_wgrads()
         if det_ev is not None:
             cur.wait_event(det_ev)
         n += self._emb_backward(slot)
