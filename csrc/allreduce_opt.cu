@@ -59,6 +59,8 @@ struct ArOptArgs {
   float* scalars_out;
   float* pub_dst;
   int pub_ring;
+  long long local_begin, local_end;  // elements whose gradients arrive ALREADY reduced in this rank's own buffer (emb_bwd
+                                     // routed them to their owner): read locally and zeroed here, no NVLink load
   int barrier_inside;              // 1: barrier A runs in CTA 0 of the sweep kernel itself (grids of at most one CTA per SM)
 };
 
@@ -148,6 +150,13 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
   constexpr int U = 2;
   const long long stride = (long long)gridDim.x * kArThreads;
   auto reduce_one = [&](long long i) -> float4 {
+    const long long e0 = i << 2;
+    if (e0 >= a.local_begin && e0 < a.local_end) {  // owner-routed range: the sum is already here
+      float4* lp = reinterpret_cast<float4*>(a.g[a.rank]) + i;
+      const float4 v = *lp;
+      *lp = make_float4(0.f, 0.f, 0.f, 0.f);  // the owner zeroes its own slice (peers add to it again only after barrier B)
+      return v;
+    }
     if constexpr (NVLS) {
       return multimem_ld_reduce_f4(a.g_mc + (i << 2));
     } else {
@@ -324,7 +333,8 @@ int dfm_allreduce_opt_max_blocks(void) { return kArMaxBlocks; }
 // Pointer tables are host arrays of `world` device pointers (peer-mapped symmetric memory). mc pointers may be NULL
 // (then the P2P path is used). s0/s1: this rank's slot slices. Ranges in elements, multiples of 4.
 // loss_ptrs (host array of `world` device pointers to 8-float inboxes in symmetric memory), loss_local (this rank's
-// log-loss sum), reg_extra (an L2 term of this rank computed elsewhere, added to its partial), scalars_out (2 floats: global loss sum, L2 term) and pub_ring (pinned HOST ring of pub_ring_len records of 2
+// log-loss sum), reg_extra (an L2 term of this rank computed elsewhere, added to its partial), [local_begin, local_end)
+// (elements whose gradients dfm_emb_bwd_routed already reduced into their owner's buffer: read locally, then zeroed), scalars_out (2 floats: global loss sum, L2 term) and pub_ring (pinned HOST ring of pub_ring_len records of 2
 // floats) are optional: all NULL gives the plain step.
 int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* const* sh_ptrs, void* const* flag_ptrs,
                                void* const* reg_ptrs, void* g_mc, void* p_mc, void* sh_mc, float* s0, float* s1, int rank,
@@ -334,7 +344,7 @@ int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* c
                                unsigned long long* step_ptr, float* reg_local, unsigned int* done_counter,
                                unsigned int* seq_ptr, int use_nvls, int grid_blocks, void* const* loss_ptrs,
                                const float* loss_local, const float* reg_extra, float* scalars_out, float* pub_ring,
-                               int pub_ring_len, void* stream);
+                               int pub_ring_len, long long local_begin, long long local_end, void* stream);
 
 int dfm_allreduce_opt_step(void* const* g_ptrs, void* const* p_ptrs, void* const* sh_ptrs, void* const* flag_ptrs,
                            void* const* reg_ptrs, void* g_mc, void* p_mc, void* sh_mc, float* s0, float* s1, int rank,
@@ -346,7 +356,7 @@ int dfm_allreduce_opt_step(void* const* g_ptrs, void* const* p_ptrs, void* const
   return dfm_allreduce_opt_step_pub(g_ptrs, p_ptrs, sh_ptrs, flag_ptrs, reg_ptrs, g_mc, p_mc, sh_mc, s0, s1, rank, world,
                                     slice_begin, slice_end, opt, lr, beta1, beta2, eps, momentum, grad_scale, decay_begin,
                                     decay_end, l2, shadow_begin, shadow_end, step_ptr, reg_local, done_counter, seq_ptr,
-                                    use_nvls, grid_blocks, nullptr, nullptr, nullptr, nullptr, nullptr, 0, stream);
+                                    use_nvls, grid_blocks, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0, 0, stream);
 }
 
 int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* const* sh_ptrs, void* const* flag_ptrs,
@@ -357,7 +367,9 @@ int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* c
                                unsigned long long* step_ptr, float* reg_local, unsigned int* done_counter,
                                unsigned int* seq_ptr, int use_nvls, int grid_blocks, void* const* loss_ptrs,
                                const float* loss_local, const float* reg_extra, float* scalars_out, float* pub_ring,
-                               int pub_ring_len, void* stream) {
+                               int pub_ring_len, long long local_begin, long long local_end, void* stream) {
+  DFM_REQUIRE(local_begin % 4 == 0 && local_end % 4 == 0 && local_end >= local_begin,
+              "allreduce_opt: the owner-routed range must be ordered multiples of 4");
   DFM_REQUIRE((loss_ptrs == nullptr) == (loss_local == nullptr) && (loss_ptrs != nullptr || scalars_out == nullptr),
               "allreduce_opt: loss_ptrs, loss_local (and scalars_out) go together");
   DFM_REQUIRE(pub_ring == nullptr || (scalars_out != nullptr && pub_ring_len >= 1),
@@ -376,6 +388,7 @@ int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* c
     a.reg_parts[r] = (float*)reg_ptrs[s];
     a.loss_parts[r] = loss_ptrs ? (float*)loss_ptrs[s] : nullptr;
   }
+  a.local_begin = local_begin; a.local_end = local_end;
   a.loss_local = loss_local; a.reg_extra = reg_extra; a.scalars_out = scalars_out; a.pub_dst = pub_ring; a.pub_ring = pub_ring_len;
   a.g_mc = (float*)g_mc; a.p_mc = (float*)p_mc; a.sh_mc = (__nv_bfloat16*)sh_mc;
   a.s0 = s0; a.s1 = s1; a.rank = rank; a.world = world;

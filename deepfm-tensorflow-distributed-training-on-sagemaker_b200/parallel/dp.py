@@ -92,6 +92,20 @@ class FusedDataParallel(FusedDeepFM):
         self.reg_local = torch.zeros(1, device=device, dtype=torch.float32)
         self.seq = torch.zeros(1, device=device, dtype=torch.int32)
         self._tables = {k: self.arena.ptr_table(k) for k in ("G", "P", "shadow", "flags", "reg_parts", "loss_parts")}
+        # owner routing (csrc/embed.cu EmbRoute): emb_bwd adds every row gradient straight into the buffer of the rank that
+        # reduces it, so the embedding share of the reduce-scatter happens inside emb_bwd and the fused kernel reads it locally
+        import os as _osr
+        self._routed = False
+        self._local_range = (0, 0)
+        # measured (bench.py, batch 1024 per GPU): 2 GPUs 124.5 vs 131.2 us/step with routing, 8 GPUs 155.6 vs 133.3 — 16-byte
+        # remote reductions to seven peers cost more link time than the dense multimem.ld_reduce they replace, so routing
+        # is the default only at 2 ranks (DFM_DP_ROUTED=1 / 0 forces it on / off)
+        want = _osr.environ.get("DFM_DP_ROUTED", "1" if world_size == 2 else "0")
+        if not self._nccl and L.include_embeddings and want != "0":
+            sw, sv = L.segments["fm_w"], L.segments["fm_v"]
+            if sv.offset % cfg.embedding_size == 0 and chunk % cfg.embedding_size == 0:
+                self._routed = True
+                self._local_range = (sw.offset, L.shadow_range[0])  # [fm_w | fm_v] incl. their alignment padding
         # the fused kernel exchanges the per-rank log-loss sums and L2 partials: what it reports is the GLOBAL batch's loss
         self.loss_is_global = not self._nccl
         # measured on 8xB200: P2P wins at 2 ranks (55 vs 75 us per 18.8 MB step), NVLS multimem from 4 ranks up (71 vs 82 us
@@ -139,6 +153,13 @@ class FusedDataParallel(FusedDeepFM):
         ev.record(cur)
         side.wait_event(ev)
         with torch.cuda.stream(side):
+            if self._routed:
+                # the table gradients are zeroed by their OWNER inside the fused kernel (a fast peer may already be adding
+                # next step's rows to them now); only the ranges this rank accumulates locally are cleared here
+                a, b = self._local_range
+                self.G[:a].zero_()
+                self.G[b:].zero_()
+                return 2
             self.G.zero_()
         return 1
 
@@ -169,7 +190,8 @@ class FusedDataParallel(FusedDeepFM):
             c_void_p(self.step_t.data_ptr()), c_void_p(self.reg_local.data_ptr()), c_void_p(self.done_counter.data_ptr()),
             c_void_p(self.seq.data_ptr()), c_int(1 if self.use_nvls else 0), c_int(self._grid_blocks), t["loss_parts"],
             c_void_p(self.loss_sum.data_ptr()), c_void_p(self._reg_extra_ptr()), c_void_p(self.scalars.data_ptr()),
-            c_void_p(ring.data_ptr() if ring is not None else 0), c_int(ring.shape[0] if ring is not None else 0), st))
+            c_void_p(ring.data_ptr() if ring is not None else 0), c_int(ring.shape[0] if ring is not None else 0),
+            c_longlong(self._local_range[0]), c_longlong(self._local_range[1]), st))
         return 2 if self._grid_blocks > 148 else 1
 
     def _restore(self, snap):
@@ -177,6 +199,42 @@ class FusedDataParallel(FusedDeepFM):
         self.reg_local.zero_()
         torch.cuda.synchronize()
         dist.barrier(group=self.group)
+
+    def _emb_backward(self, slot) -> int:
+        if not self._routed:
+            return super()._emb_backward(slot)
+        L, cfg = self.layout, self.cfg
+        _nlib.check(_nlib.load().dfm_emb_bwd_routed(
+            c_void_p(slot["ids"].data_ptr()), c_void_p(slot["vals"].data_ptr()), c_void_p(self._w("fm_v").data_ptr()),
+            c_void_p(self.Ssum.data_ptr()), c_void_p(self.dy.data_ptr()), c_void_p(self.dx0.data_ptr()),
+            c_int(self.dx0.stride(0)), self._tables["G"], c_longlong(L.segments["fm_w"].offset),
+            c_longlong(L.segments["fm_v"].offset), c_longlong(self._chunk), c_int(self.world), c_int(self.B),
+            c_int(cfg.field_size), c_int(cfg.embedding_size), c_int(cfg.feature_size),
+            c_void_p(torch.cuda.current_stream().cuda_stream)))
+        return 1
+
+    def compute_grads(self, ids, vals, labels):
+        """Debug/test path. With owner routing the table gradients of a row live on the rank that owns it (already summed
+        over ranks, nothing elsewhere), so the SUM over ranks of what this returns is still the global gradient; the peers'
+        adds must have landed before the buffer is read."""
+        if not self._routed:
+            return super().compute_grads(ids, vals, labels)
+        from collections import OrderedDict
+        torch.cuda.synchronize(self.dev)
+        dist.barrier(group=self.group)
+        self.G.zero_()
+        torch.cuda.synchronize(self.dev)
+        dist.barrier(group=self.group)
+        self.load_inputs(ids, vals, labels, 0)
+        self._train_kernels(self.in_slots[0], with_optimizer=False)
+        torch.cuda.synchronize(self.dev)
+        dist.barrier(group=self.group)
+        out = OrderedDict((n, self.layout.view(self.G, n).clone()) for n in self.layout.names(trainable_only=True))
+        dist.barrier(group=self.group)
+        self.G.zero_()
+        torch.cuda.synchronize(self.dev)
+        dist.barrier(group=self.group)
+        return out
 
     def _reg_extra_ptr(self) -> int:
         """Device address of an L2 term this rank computed outside the flat buffer (row-sharded tables), or 0."""

@@ -77,13 +77,25 @@ def exchange_equals_allreduce(cfg, batch_size: int, device, world: int, rank: in
             end = seg.offset + seg.numel
             nxt = min([s.offset for s in L.segments.values() if s.offset > seg.offset] + [lt])
             g[end:nxt] = 0
-    m.P.zero_()
-    m.G.zero_()
-    m.G[:lt].copy_(g)
     ref = g.clone()
     torch.cuda.synchronize(device)
     dist.barrier(group=group)
     dist.all_reduce(ref, group=group)
+    m.P.zero_()
+    m.G.zero_()
+    m.G[:lt].copy_(g)
+    if getattr(m, "_routed", False):
+        # owner routing: in a real step emb_bwd has already summed the table gradients into their owner's buffer and left
+        # nothing elsewhere — put the buffer into that state (the routed emb_bwd itself is checked against the oracle by
+        # scripts/dp_check.py); the dense ranges still go through the kernel's own reduction
+        a, b = m._local_range
+        lo, hi = m.slice
+        m.G[a:b].zero_()
+        oa, ob = max(a, lo), min(b, hi)
+        if ob > oa:
+            m.G[oa:ob].copy_(ref[oa:ob])
+    torch.cuda.synchronize(device)
+    dist.barrier(group=group)
     cur = torch.cuda.current_stream()
     if getattr(m, "split", None) is not None:
         m._split_side_kernels(m.in_slots[0])

@@ -39,6 +39,13 @@ int dfm_emb_bwd_det(const float* vals, const float* fm_v, const float* S, const 
                     float* g_w, float* g_v, int B, int F, int K, int N, void* workspace, long long workspace_bytes,
                     void* stream);
 
+/* emb_bwd with owner routing for ZeRO-1 data parallelism: every row gradient is added straight into the flat gradient
+ * buffer of the rank that reduces it (g_ptrs: `world` peer-mapped buffers; element e belongs to rank e / chunk), so the
+ * reduce-scatter of the embedding gradient happens inside this kernel (replaces that share of Horovod's all-reduce, HVD:262). */
+int dfm_emb_bwd_routed(const int* ids, const float* vals, const float* fm_v, const float* S, const float* dy,
+                       const void* dx0_bf16, int ldx, void* const* g_ptrs, long long gw_off, long long gv_off,
+                       long long chunk, int world, int B, int F, int K, int N, void* stream);
+
 /* ---- tcgen05 MLP GEMMs (replaces fully_connected fwd/bwd, PS:212-223) ----
  * mode 0 forward: out[M,N] bf16 = dropout(relu(A[M,K] B[N,K]^T + bias));  mode 1 dgrad: out[M,N] bf16 =
  * (A[M,K] B[K,N]) * (mask != 0) * mask_scale;  mode 2 wgrad: out[M,N] f32 += A[K,M]^T B[K,N].
@@ -141,7 +148,8 @@ int dfm_allreduce_opt_step(void* const* g_ptrs, void* const* p_ptrs, void* const
 
 /* Same step; additionally (loss_ptrs: `world` pointers to 8-float inboxes in symmetric memory) every rank's log-loss sum
  * is exchanged at barrier A (reg_extra: optional L2 term of this rank from elsewhere, added to its partial) and the last
- * CTA writes (global loss sum, complete L2 term) to scalars_out[0..1] and into record
+ * CTA writes (global loss sum, complete L2 term) to scalars_out[0..1]; [local_begin, local_end): elements whose gradients
+ * dfm_emb_bwd_routed already reduced into their owner's buffer (read locally and zeroed, no NVLink load) and into record
  * (step - 1) % pub_ring_len of pub_ring (page-locked HOST memory, 2 floats per record; NULL = no publication). */
 int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* const* sh_ptrs, void* const* flag_ptrs,
                                void* const* reg_ptrs, void* g_mc, void* p_mc, void* sh_mc, float* s0, float* s1, int rank,
@@ -151,7 +159,7 @@ int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* c
                                unsigned long long* step_ptr, float* reg_local, unsigned int* done_counter,
                                unsigned int* seq_ptr, int use_nvls, int grid_blocks, void* const* loss_ptrs,
                                const float* loss_local, const float* reg_extra, float* scalars_out, float* pub_ring,
-                               int pub_ring_len, void* stream);
+                               int pub_ring_len, long long local_begin, long long local_end, void* stream);
 
 /* ---- data-parallel exchange for replicated tables that ships only what differs between ranks (csrc/sparse_allreduce.cu;
  * replaces Horovod's dense NCCL all-reduce, HVD:262). bitmap_exchange: this rank's touched-row bitmap (bm_own, cleared
