@@ -61,6 +61,7 @@ struct ArOptArgs {
   int pub_ring;
   long long local_begin, local_end;  // elements whose gradients arrive ALREADY reduced in this rank's own buffer (emb_bwd
                                      // routed them to their owner): read locally and zeroed here, no NVLink load
+  int finalize;                    // 0: one bucket of several — no step advance, no L2 / loss publication (the last launch does)
   int barrier_inside;              // 1: barrier A runs in CTA 0 of the sweep kernel itself (grids of at most one CTA per SM)
 };
 
@@ -242,7 +243,7 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
 
   // ---- last CTA of this rank: publish the L2-loss partial, advance the step, barrier B
   __threadfence();
-  if (threadIdx.x < W) {
+  if (threadIdx.x < W && a.finalize) {
     const float part = 0.5f * a.l2 * atomicAdd(a.reg_local, 0.f) + (a.reg_extra ? __ldcg(a.reg_extra) : 0.f);
     a.reg_parts[threadIdx.x][a.rank] = part;  // slot [rank] on every peer
   }
@@ -251,7 +252,7 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
   if (threadIdx.x == 0) {
     *a.reg_local = 0.f;
     *a.done_counter = 0u;
-    *a.step_ptr = t;
+    if (a.finalize) *a.step_ptr = t;
     *a.seq_ptr = seq;
   }
   if (threadIdx.x < W) {
@@ -262,7 +263,7 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
     wait_flag_geq(bflags_mine + peer, seq, peer, 1);
   }
   trace_end(TR_ALLREDUCE);
-  if (a.scalars_out) {  // every peer's loss sum (barrier A) and L2 partial (before its barrier-B release) are visible now
+  if (a.scalars_out && a.finalize) {  // every peer's loss sum (barrier A) and L2 partial (before its barrier-B release) are visible now
     __syncthreads();
     if (threadIdx.x == 0) {
       float ls = 0.f, rs = 0.f;
@@ -334,7 +335,8 @@ int dfm_allreduce_opt_max_blocks(void) { return kArMaxBlocks; }
 // (then the P2P path is used). s0/s1: this rank's slot slices. Ranges in elements, multiples of 4.
 // loss_ptrs (host array of `world` device pointers to 8-float inboxes in symmetric memory), loss_local (this rank's
 // log-loss sum), reg_extra (an L2 term of this rank computed elsewhere, added to its partial), [local_begin, local_end)
-// (elements whose gradients dfm_emb_bwd_routed already reduced into their owner's buffer: read locally, then zeroed), scalars_out (2 floats: global loss sum, L2 term) and pub_ring (pinned HOST ring of pub_ring_len records of 2
+// (elements whose gradients dfm_emb_bwd_routed already reduced into their owner's buffer: read locally, then zeroed),
+// finalize (0 = this launch is an early bucket of the step: own flags / seq / scratch, no step advance or publication), scalars_out (2 floats: global loss sum, L2 term) and pub_ring (pinned HOST ring of pub_ring_len records of 2
 // floats) are optional: all NULL gives the plain step.
 int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* const* sh_ptrs, void* const* flag_ptrs,
                                void* const* reg_ptrs, void* g_mc, void* p_mc, void* sh_mc, float* s0, float* s1, int rank,
@@ -344,7 +346,7 @@ int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* c
                                unsigned long long* step_ptr, float* reg_local, unsigned int* done_counter,
                                unsigned int* seq_ptr, int use_nvls, int grid_blocks, void* const* loss_ptrs,
                                const float* loss_local, const float* reg_extra, float* scalars_out, float* pub_ring,
-                               int pub_ring_len, long long local_begin, long long local_end, void* stream);
+                               int pub_ring_len, long long local_begin, long long local_end, int finalize, void* stream);
 
 int dfm_allreduce_opt_step(void* const* g_ptrs, void* const* p_ptrs, void* const* sh_ptrs, void* const* flag_ptrs,
                            void* const* reg_ptrs, void* g_mc, void* p_mc, void* sh_mc, float* s0, float* s1, int rank,
@@ -356,7 +358,7 @@ int dfm_allreduce_opt_step(void* const* g_ptrs, void* const* p_ptrs, void* const
   return dfm_allreduce_opt_step_pub(g_ptrs, p_ptrs, sh_ptrs, flag_ptrs, reg_ptrs, g_mc, p_mc, sh_mc, s0, s1, rank, world,
                                     slice_begin, slice_end, opt, lr, beta1, beta2, eps, momentum, grad_scale, decay_begin,
                                     decay_end, l2, shadow_begin, shadow_end, step_ptr, reg_local, done_counter, seq_ptr,
-                                    use_nvls, grid_blocks, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0, 0, stream);
+                                    use_nvls, grid_blocks, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0, 0, 1, stream);
 }
 
 int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* const* sh_ptrs, void* const* flag_ptrs,
@@ -367,7 +369,7 @@ int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* c
                                unsigned long long* step_ptr, float* reg_local, unsigned int* done_counter,
                                unsigned int* seq_ptr, int use_nvls, int grid_blocks, void* const* loss_ptrs,
                                const float* loss_local, const float* reg_extra, float* scalars_out, float* pub_ring,
-                               int pub_ring_len, long long local_begin, long long local_end, void* stream) {
+                               int pub_ring_len, long long local_begin, long long local_end, int finalize, void* stream) {
   DFM_REQUIRE(local_begin % 4 == 0 && local_end % 4 == 0 && local_end >= local_begin,
               "allreduce_opt: the owner-routed range must be ordered multiples of 4");
   DFM_REQUIRE((loss_ptrs == nullptr) == (loss_local == nullptr) && (loss_ptrs != nullptr || scalars_out == nullptr),
@@ -388,7 +390,7 @@ int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* c
     a.reg_parts[r] = (float*)reg_ptrs[s];
     a.loss_parts[r] = loss_ptrs ? (float*)loss_ptrs[s] : nullptr;
   }
-  a.local_begin = local_begin; a.local_end = local_end;
+  a.local_begin = local_begin; a.local_end = local_end; a.finalize = finalize;
   a.loss_local = loss_local; a.reg_extra = reg_extra; a.scalars_out = scalars_out; a.pub_dst = pub_ring; a.pub_ring = pub_ring_len;
   a.g_mc = (float*)g_mc; a.p_mc = (float*)p_mc; a.sh_mc = (__nv_bfloat16*)sh_mc;
   a.s0 = s0; a.s1 = s1; a.rank = rank; a.world = world;

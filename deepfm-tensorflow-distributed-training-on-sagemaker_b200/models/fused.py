@@ -187,6 +187,13 @@ class FusedDeepFM:
     def _slot_numel(self) -> int:
         return self.layout.trainable_numel
 
+    _wgrad_fork_default = "after_dgrad0"  # where the wgrad branches fork (data-parallel buckets fork one kernel earlier)
+
+    def _post_wgrad_kernels(self, sides) -> int:
+        """Hook: work that only needs the weight gradients (parallel/dp.py launches the MLP bucket of the gradient exchange
+        here, on the wgrad branches). Returns the number of kernels it launched."""
+        return 0
+
     def _wgrad_streams(self, n: int):
         st = getattr(self, "_wg_streams", None)
         if st is None or len(st) < n:
@@ -278,7 +285,7 @@ class FusedDeepFM:
             if i == 0:
                 self.dgrad.append(K.GemmPlan("dgrad", self.dz[0], Wb, self.dx0, B, d_in, h))
                 import os as _os2
-                if _os2.environ.get("DFM_WGRAD_FORK", "after_dgrad0") != "before_dgrad0":
+                if _os2.environ.get("DFM_WGRAD_FORK", self._wgrad_fork_default) != "before_dgrad0":
                     self.dgrad[0].set_exclusive(True)  # nothing runs beside it: whole-SM pipeline
             else:
                 self.dgrad.append(K.GemmPlan("dgrad", self.dz[i], Wb, self.dz[i - 1], B, d_in, h,
@@ -370,7 +377,7 @@ class FusedDeepFM:
         # DFM_WGRAD_FORK=before_dgrad0 starts them one kernel earlier: dgrad_0 3.7 -> 7.1 us).
         sides = self._wgrad_streams(nl)
         import os as _os
-        fork_before_dgrad0 = _os.environ.get("DFM_WGRAD_FORK", "after_dgrad0") == "before_dgrad0"
+        fork_before_dgrad0 = _os.environ.get("DFM_WGRAD_FORK", self._wgrad_fork_default) == "before_dgrad0"
 
         def fork_wgrads():
             k = 0
@@ -396,10 +403,14 @@ class FusedDeepFM:
                 n += 1
             if i == 0 and fork_before_dgrad0:  # dz[0] (and every dz above it) is final here
                 n += fork_wgrads()
+                if with_optimizer:
+                    n += self._post_wgrad_kernels(sides)
             self.dgrad[i].run()
             n += 1
         if not fork_before_dgrad0:
             n += fork_wgrads()
+            if with_optimizer:
+                n += self._post_wgrad_kernels(sides)
         if det_ev is not None:
             cur.wait_event(det_ev)
         n += self._emb_backward(slot)

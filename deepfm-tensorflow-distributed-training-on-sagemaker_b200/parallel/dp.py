@@ -72,17 +72,35 @@ class FusedDataParallel(FusedDeepFM):
         self.comm = comm
         L = self._make_layout(cfg)
         n = L.trainable_numel
-        chunk = ((n + world_size - 1) // world_size + 1023) // 1024 * 1024
-        self.slice = (min(n, rank * chunk), min(n, (rank + 1) * chunk))
-        self._chunk = chunk
         self._nccl = comm == "nccl"
+        # Buckets (SURVEY K12 "launched per bucket so it overlaps backward"; Horovod reduces each gradient as backprop
+        # produces it, HVD:262-263): the flat buffer is exchanged as [fm_bias | fm_w | fm_v] and [MLP block]. Each bucket is
+        # cut into `world` equal slices, so every rank owns one slice of EACH (and the optimizer slots of both). The MLP
+        # bucket is launched on the wgrad branch as soon as the weight gradients exist and runs under emb_bwd; only the
+        # table bucket — which needs emb_bwd — stays on the critical path, and it is 20 % shorter than the whole buffer.
+        import os as _osb
+        split = L.shadow_range[0]
+        # OFF by default (DFM_DP_BUCKETS=1 turns it on): measured at 2 GPUs, batch 1024, it is slower (138 vs 126 us/step). The
+        # weight gradients are complete only ~9 us before emb_bwd ends (scripts/step_trace.py: wgrad_0 ends at 57 us, emb_bwd
+        # at 66 us), the early bucket needs ~20 us (two flag barriers + its sweep), shares NVLink and L2 with emb_bwd while it
+        # runs, and the table bucket cannot be shorter than the link time of its 15 MB — at this step size there is no
+        # backward left to hide a bucket under. Kept for larger batches / deeper MLPs, where the window grows.
+        bucketed = (not self._nccl) and L.include_embeddings and world_size > 1 and _osb.environ.get("DFM_DP_BUCKETS", "0") == "1"
+        rnd = lambda x: ((x + world_size - 1) // world_size + 1023) // 1024 * 1024
+        self._buckets = [(0, split, rnd(split)), (split, n, rnd(n - split))] if bucketed else [(0, n, rnd(n))]
+        self._bucketed = bucketed
+        if bucketed:  # the wgrads must finish early enough for the MLP bucket to run beside emb_bwd
+            self._wgrad_fork_default = "before_dgrad0"
+        chunk = self._buckets[0][2]
+        self._chunk = chunk  # slice length of the FIRST bucket (the one that holds the tables: owner routing uses it)
         lib = _nlib.require_gpu()
         nslots = len(SLOT_INIT[optimizer.name])
-        slot_n = n if self._nccl else chunk
+        slot_n = n if self._nccl else sum(c for _, _, c in self._buckets)
         regions = [("P", L.total_numel, torch.float32), ("G", L.total_numel, torch.float32),
                    ("shadow", L.shadow_range[1] - L.shadow_range[0], torch.bfloat16),
                    ("flags", lib.dfm_allreduce_opt_flag_words(), torch.int32), ("reg_parts", 8, torch.float32),
-                   ("loss_parts", 8, torch.float32)]
+                   ("loss_parts", 8, torch.float32), ("flags2", lib.dfm_allreduce_opt_flag_words(), torch.int32),
+                   ("reg_parts2", 8, torch.float32)]
         for i in range(nslots):
             regions.append(("S%d" % i, slot_n, torch.float32))
         self.arena = SymmArena(regions, device, self.group)
@@ -91,7 +109,12 @@ class FusedDataParallel(FusedDeepFM):
                          row_offset=rank * batch_size, use_graph=use_graph)
         self.reg_local = torch.zeros(1, device=device, dtype=torch.float32)
         self.seq = torch.zeros(1, device=device, dtype=torch.int32)
-        self._tables = {k: self.arena.ptr_table(k) for k in ("G", "P", "shadow", "flags", "reg_parts", "loss_parts")}
+        self._tables = {k: self.arena.ptr_table(k) for k in ("G", "P", "shadow", "flags", "reg_parts", "loss_parts", "flags2",
+                                                             "reg_parts2")}
+        # scratch of the early (MLP) bucket: it runs beside the main chain, so it shares nothing with the final launch
+        self.reg_local2 = torch.zeros(1, device=device, dtype=torch.float32)
+        self.seq2 = torch.zeros(1, device=device, dtype=torch.int32)
+        self.done2 = torch.zeros(1, device=device, dtype=torch.int32)
         # owner routing (csrc/embed.cu EmbRoute): emb_bwd adds every row gradient straight into the buffer of the rank that
         # reduces it, so the embedding share of the reduce-scatter happens inside emb_bwd and the fused kernel reads it locally
         import os as _osr
@@ -116,16 +139,20 @@ class FusedDataParallel(FusedDeepFM):
         self.use_nvls = bool(use_nvls)
         self.comm_name = "nccl-allreduce+flat_opt (baseline)" if self._nccl else \
             ("fused-nvls-multimem" if self.use_nvls else "fused-p2p")
-        blocks = (chunk // 4 + 511) // 512  # two float4 per thread per trip
-        if self.use_nvls:
-            # NVLS: ~4 trips per thread instead of 1. With a single wave every CTA reduces, then every CTA broadcasts, and
-            # the link runs one direction at a time; a few trips per thread let the multimem.st of trip k overlap the
-            # multimem.ld_reduce of trip k+1 (measured at 8 ranks: 287 CTAs 69.7 us, 74 CTAs 58.3 us, 37 CTAs 67.0 us)
-            blocks = max(32, (chunk // 4 + 2047) // 2048)
-        self._grid_blocks = max(1, min(lib.dfm_allreduce_opt_max_blocks(), blocks))
         import os as _os
-        if _os.environ.get("DFM_AR_BLOCKS"):  # tuning knob: must be set identically on every rank
-            self._grid_blocks = max(1, min(lib.dfm_allreduce_opt_max_blocks(), int(_os.environ["DFM_AR_BLOCKS"])))
+
+        def grid_for(ck):
+            blocks = (ck // 4 + 511) // 512  # two float4 per thread per trip
+            if self.use_nvls:
+                # NVLS: ~4 trips per thread instead of 1. With a single wave every CTA reduces, then every CTA broadcasts,
+                # and the link runs one direction at a time; a few trips per thread let the multimem.st of trip k overlap the
+                # multimem.ld_reduce of trip k+1 (measured at 8 ranks: 287 CTAs 69.7 us, 74 CTAs 58.3 us, 37 CTAs 67.0 us)
+                blocks = max(32, (ck // 4 + 2047) // 2048)
+            if _os.environ.get("DFM_AR_BLOCKS"):  # tuning knob: must be set identically on every rank
+                blocks = int(_os.environ["DFM_AR_BLOCKS"])
+            return max(1, min(lib.dfm_allreduce_opt_max_blocks(), blocks))
+        self._grids = [grid_for(c) for _, _, c in self._buckets]
+        self._grid_blocks = self._grids[0]
         import ctypes as _ct, os as _os2
         if _os2.environ.get("DFM_L2_PERSIST", "1") != "0":  # the symmetric arena (P | G | shadow | slot slices) is contiguous
             lib.dfm_set_l2_persist.restype = _ct.c_longlong
@@ -174,29 +201,72 @@ class FusedDataParallel(FusedDeepFM):
                             1.0, decay, self.cfg.l2_reg, L.shadow_range, self.shadow, self.step_t, self.reg_loss,
                             self.done_counter)
             return 1
-        lib = _nlib.load()
+        return self._launch_bucket(len(self._buckets) - 1 if not self._bucketed else 0, final=True)
+
+    def _pieces(self, r: int):
+        """[(global_begin, global_end, offset in rank r's slot storage)] — one slice of every bucket."""
+        out, off = [], 0
+        for (b, e, c) in self._buckets:
+            out.append((min(e, b + r * c), min(e, b + (r + 1) * c), off))
+            off += c
+        return out
+
+    @property
+    def slice(self):  # the first bucket's slice of this rank (kept for callers that predate buckets)
+        p = self._pieces(self.rank)[0]
+        return (p[0], p[1])
+
+    def _launch_bucket(self, bi: int, final: bool) -> int:
+        """The fused reduce-scatter + optimizer + all-gather kernel over this rank's slice of bucket `bi`. final=True: the
+        launch that ends the step (advances the step counter, exchanges the loss / L2 sums, publishes the result)."""
+        o, L, lib = self.opt, self.layout, _nlib.load()
         decay = L.decay_range if self.cfg.l2_reg > 0 else (0, 0)
         t = self._tables
         st = c_void_p(torch.cuda.current_stream().cuda_stream)
-        ring = getattr(self, "_result_ring", None)
+        ring = getattr(self, "_result_ring", None) if final else None
+        gb, ge, off = self._pieces(self.rank)[bi]
+        sp = lambda S: c_void_p(S.data_ptr() + 4 * off if S is not None else 0)
+        fl, rp = (t["flags"], t["reg_parts"]) if final else (t["flags2"], t["reg_parts2"])
+        regl, done, seq = (self.reg_local, self.done_counter, self.seq) if final else (self.reg_local2, self.done2, self.seq2)
         _nlib.check(lib.dfm_allreduce_opt_step_pub(
-            t["G"], t["P"], t["shadow"], t["flags"], t["reg_parts"], c_void_p(self.arena.mc("G")),
-            c_void_p(self.arena.mc("P")), c_void_p(self.arena.mc("shadow")),
-            c_void_p(self.S0.data_ptr() if self.S0 is not None else 0),
-            c_void_p(self.S1.data_ptr() if self.S1 is not None else 0), c_int(self.rank), c_int(self.world),
-            c_longlong(self.slice[0]), c_longlong(self.slice[1]), c_int(OPT_IDS[o.name]), c_float(o.lr), c_float(o.beta1),
+            t["G"], t["P"], t["shadow"], fl, rp, c_void_p(self.arena.mc("G")),
+            c_void_p(self.arena.mc("P")), c_void_p(self.arena.mc("shadow")), sp(self.S0), sp(self.S1), c_int(self.rank),
+            c_int(self.world), c_longlong(gb), c_longlong(ge), c_int(OPT_IDS[o.name]), c_float(o.lr), c_float(o.beta1),
             c_float(o.beta2), c_float(o.eps), c_float(o.momentum), c_float(1.0), c_longlong(decay[0]),
             c_longlong(decay[1]), c_float(self.cfg.l2_reg), c_longlong(L.shadow_range[0]), c_longlong(L.shadow_range[1]),
-            c_void_p(self.step_t.data_ptr()), c_void_p(self.reg_local.data_ptr()), c_void_p(self.done_counter.data_ptr()),
-            c_void_p(self.seq.data_ptr()), c_int(1 if self.use_nvls else 0), c_int(self._grid_blocks), t["loss_parts"],
-            c_void_p(self.loss_sum.data_ptr()), c_void_p(self._reg_extra_ptr()), c_void_p(self.scalars.data_ptr()),
+            c_void_p(self.step_t.data_ptr()), c_void_p(regl.data_ptr()), c_void_p(done.data_ptr()),
+            c_void_p(seq.data_ptr()), c_int(1 if self.use_nvls else 0), c_int(self._grids[bi]),
+            t["loss_parts"] if final else None, c_void_p(self.loss_sum.data_ptr() if final else 0),
+            c_void_p(self._reg_extra_ptr() if final else 0), c_void_p(self.scalars.data_ptr() if final else 0),
             c_void_p(ring.data_ptr() if ring is not None else 0), c_int(ring.shape[0] if ring is not None else 0),
-            c_longlong(self._local_range[0]), c_longlong(self._local_range[1]), st))
-        return 2 if self._grid_blocks > 148 else 1
+            c_longlong(self._local_range[0]), c_longlong(self._local_range[1]), c_int(1 if final else 0), st))
+        return 2 if self._grids[bi] > 148 else 1
+
+    def _post_wgrad_kernels(self, sides) -> int:
+        """Early bucket: once every wgrad branch is done, exchange + update the MLP block on the first of them, beside
+        dgrad_0 / emb_bwd on the main chain (the final join of the step waits for it)."""
+        if not self._bucketed:
+            return 0
+        s0 = sides[0]
+        for sd in sides[1:]:
+            ev = torch.cuda.Event()
+            ev.record(sd)
+            s0.wait_event(ev)
+        with torch.cuda.stream(s0):
+            return self._launch_bucket(1, final=False)
+
+    def _exchange_all(self) -> int:
+        """Every bucket on the current stream (self-checks; a training step launches them on their own branches)."""
+        n = 0
+        if self._bucketed:
+            n += self._launch_bucket(1, final=False)
+        return n + self._optimizer_kernels()
 
     def _restore(self, snap):
         super()._restore(snap)
         self.reg_local.zero_()
+        self.reg_local2.zero_()
+        self.done2.zero_()
         torch.cuda.synchronize()
         dist.barrier(group=self.group)
 
@@ -266,9 +336,10 @@ class FusedDataParallel(FusedDeepFM):
         for i in range(len(SLOT_INIT[self.opt.name])):
             buf = torch.empty(n, device=self.dev, dtype=torch.float32)
             for r in range(self.world):
-                b, e = min(n, r * self._chunk), min(n, (r + 1) * self._chunk)
-                if e > b:
-                    buf[b:e].copy_(self.arena.peer_view("S%d" % i, r)[: e - b])
+                pv = self.arena.peer_view("S%d" % i, r)
+                for b, e, off in self._pieces(r):
+                    if e > b:
+                        buf[b:e].copy_(pv[off:off + e - b])
             full.append(buf)
         out = OrderedDict()
         for name in L.names(trainable_only=True):
@@ -295,8 +366,8 @@ class FusedDataParallel(FusedDeepFM):
             if self._nccl:
                 mine.copy_(full)
             else:
-                b, e = self.slice
-                mine[: e - b].copy_(full[b:e])
+                for b, e, off in self._pieces(self.rank):
+                    mine[off:off + e - b].copy_(full[b:e])
         if "global_step" in sd:
             self.step_t.copy_(sd["global_step"].to(self.dev).reshape(1))
             self.opt.step = int(self.step_t.item())
@@ -337,8 +408,8 @@ class FusedDataParallel(FusedDeepFM):
                     loaded = getattr(self, "_loaded_full", None)
                     full.copy_(loaded[i] if loaded else self._full_slot_for_broadcast(i))
                 dist.broadcast(full, src, group=self.group)
-                b, e = self.slice
-                mine[: e - b].copy_(full[b:e])
+                for b, e, off in self._pieces(self.rank):
+                    mine[off:off + e - b].copy_(full[b:e])
         self._loaded_full = None
         torch.cuda.synchronize(self.dev)
         dist.barrier(group=self.group)
@@ -347,7 +418,8 @@ class FusedDataParallel(FusedDeepFM):
         n = self.layout.trainable_numel
         buf = torch.empty(n, device=self.dev, dtype=torch.float32)
         for r in range(self.world):
-            b, e = min(n, r * self._chunk), min(n, (r + 1) * self._chunk)
-            if e > b:
-                buf[b:e].copy_(self.arena.peer_view("S%d" % i, r)[: e - b])
+            pv = self.arena.peer_view("S%d" % i, r)
+            for b, e, off in self._pieces(r):
+                if e > b:
+                    buf[b:e].copy_(pv[off:off + e - b])
         return buf

@@ -101,7 +101,7 @@ def exchange_equals_allreduce(cfg, batch_size: int, device, world: int, rank: in
         m._split_side_kernels(m.in_slots[0])
     elif hasattr(m, "_pre_step"):
         pass  # dense path: nothing to prepare (gradients are in place)
-    m._optimizer_kernels()
+    getattr(m, "_exchange_all", m._optimizer_kernels)()  # every bucket of the exchange
     cur.synchronize()
     torch.cuda.synchronize(device)
     dist.barrier(group=group)

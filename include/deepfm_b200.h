@@ -149,7 +149,9 @@ int dfm_allreduce_opt_step(void* const* g_ptrs, void* const* p_ptrs, void* const
 /* Same step; additionally (loss_ptrs: `world` pointers to 8-float inboxes in symmetric memory) every rank's log-loss sum
  * is exchanged at barrier A (reg_extra: optional L2 term of this rank from elsewhere, added to its partial) and the last
  * CTA writes (global loss sum, complete L2 term) to scalars_out[0..1]; [local_begin, local_end): elements whose gradients
- * dfm_emb_bwd_routed already reduced into their owner's buffer (read locally and zeroed, no NVLink load) and into record
+ * dfm_emb_bwd_routed already reduced into their owner's buffer (read locally and zeroed, no NVLink load); finalize = 0: an
+ * early bucket of the step (launched per bucket so it overlaps backward) with its own flags / seq / scratch words —
+ * it neither advances the step nor publishes and into record
  * (step - 1) % pub_ring_len of pub_ring (page-locked HOST memory, 2 floats per record; NULL = no publication). */
 int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* const* sh_ptrs, void* const* flag_ptrs,
                                void* const* reg_ptrs, void* g_mc, void* p_mc, void* sh_mc, float* s0, float* s1, int rank,
@@ -159,7 +161,7 @@ int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* c
                                unsigned long long* step_ptr, float* reg_local, unsigned int* done_counter,
                                unsigned int* seq_ptr, int use_nvls, int grid_blocks, void* const* loss_ptrs,
                                const float* loss_local, const float* reg_extra, float* scalars_out, float* pub_ring,
-                               int pub_ring_len, long long local_begin, long long local_end, void* stream);
+                               int pub_ring_len, long long local_begin, long long local_end, int finalize, void* stream);
 
 /* ---- data-parallel exchange for replicated tables that ships only what differs between ranks (csrc/sparse_allreduce.cu;
  * replaces Horovod's dense NCCL all-reduce, HVD:262). bitmap_exchange: this rank's touched-row bitmap (bm_own, cleared
