@@ -68,7 +68,66 @@ struct Entry {
   uint64_t offset = 0, size = 0;
   uint32_t crc = 0;  // masked
   int shard = 0;     // which <prefix>.data-SSSSS-of-NNNNN file holds the bytes
+  // Partitioned variable (tf.fixed_size_partitioner and friends): the full-shape entry carries no bytes, only the list
+  // of slices; each slice's bytes live under their own key (slice_key below). Per dimension (start, length), length -1 =
+  // the whole dimension.
+  std::vector<std::vector<std::pair<int64_t, int64_t>>> slices;
 };
+
+// ---- OrderedCode (the key encoding of slice entries: tensorflow/core/lib/strings/ordered_code.h semantics) -----
+void oc_write_num_increasing(std::string& s, uint64_t v) {
+  uint8_t buf[9];
+  int len = 0;
+  while (v) {
+    buf[8 - len] = (uint8_t)(v & 0xff);
+    v >>= 8;
+    ++len;
+  }
+  buf[8 - len] = (uint8_t)len;
+  s.append((const char*)buf + 8 - len, len + 1);
+}
+void oc_write_string(std::string& s, const std::string& v) {
+  for (unsigned char c : v) {
+    if (c == 0x00) s.append("\x00\xff", 2);
+    else if (c == 0xff) s.append("\xff\x00", 2);
+    else s.push_back((char)c);
+  }
+  s.append("\x00\x01", 2);
+}
+int oc_signed_length(uint64_t x) {  // bytes needed for magnitude x: 7 n - 1 payload bits in n bytes
+  int bits = 0;
+  while (x) {
+    ++bits;
+    x >>= 1;
+  }
+  for (int n = 1; n <= 10; ++n)
+    if (bits <= 7 * n - 1) return n;
+  return 10;
+}
+void oc_write_signed_increasing(std::string& s, int64_t val) {
+  const uint64_t x = val < 0 ? ~(uint64_t)val : (uint64_t)val;
+  const int len = oc_signed_length(x);
+  uint8_t buf[10];
+  const uint8_t sign = val < 0 ? 0xff : 0x00;
+  buf[0] = buf[1] = sign;
+  for (int i = 0; i < 8; ++i) buf[2 + i] = (uint8_t)((uint64_t)val >> (8 * (7 - i)));
+  uint8_t* b = buf + 10 - len;
+  // header: `len` leading one bits (spilling into the second byte for len > 8), xor-ed so negatives sort first
+  for (int i = 0; i < len && i < 16; ++i) b[i / 8] ^= (uint8_t)(0x80 >> (i % 8));
+  s.append((const char*)b, len);
+}
+std::string slice_key(const std::string& name, const std::vector<std::pair<int64_t, int64_t>>& sl) {
+  std::string k;
+  oc_write_num_increasing(k, 0);
+  oc_write_string(k, name);
+  oc_write_num_increasing(k, sl.size());
+  for (auto& d : sl) {
+    oc_write_signed_increasing(k, d.second < 0 ? -1 : d.first);
+    oc_write_signed_increasing(k, d.second < 0 ? -1 : d.second);
+  }
+  return k;
+}
+int dtype_size(int dt) { return dt == 9 || dt == 2 ? 8 : dt == 1 || dt == 3 ? 4 : dt == 14 || dt == 19 ? 2 : dt == 6 || dt == 4 || dt == 10 ? 1 : 0; }
 
 std::string encode_entry(const Entry& e) {
   std::string shape;
@@ -94,10 +153,32 @@ std::string encode_entry(const Entry& e) {
     s.push_back((char)((4 << 3) | 0));
     put_varint(s, e.offset);
   }
-  s.push_back((char)((5 << 3) | 0));
-  put_varint(s, e.size);
-  s.push_back((char)((6 << 3) | 5));
-  put_u32(s, e.crc);
+  if (e.slices.empty()) {
+    s.push_back((char)((5 << 3) | 0));
+    put_varint(s, e.size);
+    s.push_back((char)((6 << 3) | 5));
+    put_u32(s, e.crc);
+  }
+  for (auto& sl : e.slices) {  // slices (7): TensorSliceProto { repeated Extent extent = 1 { start = 1; length = 2 } }
+    std::string tsp;
+    for (auto& d : sl) {
+      std::string ext;
+      if (d.second >= 0) {
+        if (d.first) {
+          ext.push_back((char)((1 << 3) | 0));
+          put_varint(ext, (uint64_t)d.first);
+        }
+        ext.push_back((char)((2 << 3) | 0));
+        put_varint(ext, (uint64_t)d.second);
+      }
+      tsp.push_back((char)((1 << 3) | 2));
+      put_varint(tsp, ext.size());
+      tsp += ext;
+    }
+    s.push_back((char)((7 << 3) | 2));
+    put_varint(s, tsp.size());
+    s += tsp;
+  }
   return s;
 }
 
@@ -167,8 +248,37 @@ bool decode_entry(const uint8_t* p, const uint8_t* e, Entry* out) {
           }
         }
       }
+      if (f == 7) {  // one TensorSliceProto
+        std::vector<std::pair<int64_t, int64_t>> sl;
+        const uint8_t *q = p, *qe = p + n;
+        while (q < qe) {
+          uint64_t t2, m;
+          if (!get_varint(q, qe, &t2)) return false;
+          if ((t2 & 7) == 2) {
+            if (!get_varint(q, qe, &m) || m > (uint64_t)(qe - q)) return false;
+            if ((t2 >> 3) == 1) {  // Extent
+              int64_t start = 0, length = -1;
+              const uint8_t *d = q, *de = q + m;
+              while (d < de) {
+                uint64_t t3, v;
+                if (!get_varint(d, de, &t3) || (t3 & 7) != 0 || !get_varint(d, de, &v)) return false;
+                if ((t3 >> 3) == 1) start = (int64_t)v;
+                else if ((t3 >> 3) == 2) length = (int64_t)v;
+              }
+              sl.emplace_back(start, length);
+            }
+            q += m;
+          } else if ((t2 & 7) == 0) {
+            if (!get_varint(q, qe, &m)) return false;
+          } else {
+            return false;
+          }
+        }
+        out->slices.push_back(std::move(sl));
+      }
       p += n;
     } else if (wt == 1) {
+      if (p + 8 > e) return false;
       p += 8;
     } else {
       return false;
@@ -239,7 +349,8 @@ struct Writer {
 struct Reader {
   std::string prefix;
   int num_shards = 1;
-  std::vector<Entry> entries;
+  std::vector<Entry> entries;                // named tensors (whole or partitioned)
+  std::map<std::string, Entry> slice_data;   // encoded slice key -> where that slice's bytes are
 };
 
 bool read_file(const std::string& path, std::vector<uint8_t>* out) {
@@ -357,6 +468,57 @@ int dfmio_bundle_writer_add(void* wh, const char* name, int dtype, int ndim, con
   return 0;
 }
 
+// Writes `name` as a variable partitioned along axis 0 into `num_parts` near-equal pieces (tf.fixed_size_partitioner):
+// one full-shape index entry listing the slices + one data entry per slice under its encoded slice key. The pieces are
+// spread over the writer's data shards like whole tensors are.
+int dfmio_bundle_writer_add_partitioned(void* wh, const char* name, int dtype, int ndim, const int64_t* dims,
+                                        const void* bytes, uint64_t nbytes, int num_parts) {
+  Writer* w = (Writer*)wh;
+  const size_t esz = (size_t)dtype_size(dtype);
+  if (ndim < 1 || num_parts < 1 || esz == 0 || dims[0] < num_parts) {
+    berr("cannot partition %s into %d parts", name, num_parts);
+    return -1;
+  }
+  uint64_t inner = 1;
+  for (int d = 1; d < ndim; ++d) inner *= (uint64_t)dims[d];
+  if ((uint64_t)dims[0] * inner * esz != nbytes) {
+    berr("size mismatch for %s", name);
+    return -1;
+  }
+  Entry full;
+  full.name = name;
+  full.dtype = dtype;
+  full.dims.assign(dims, dims + ndim);
+  const int64_t base = dims[0] / num_parts, extra = dims[0] % num_parts;
+  int64_t start = 0;
+  for (int p = 0; p < num_parts; ++p) {  // the first `extra` parts get one more row, as TF's partitioner does
+    const int64_t len = base + (p < extra ? 1 : 0);
+    std::vector<std::pair<int64_t, int64_t>> sl;
+    sl.emplace_back(start, len);
+    for (int d = 1; d < ndim; ++d) sl.emplace_back(0, -1);
+    Entry e;
+    e.name = slice_key(name, sl);
+    e.dtype = dtype;
+    e.dims.push_back(len);
+    for (int d = 1; d < ndim; ++d) e.dims.push_back(dims[d]);
+    e.shard = (int)(w->entries.size() % w->data.size());
+    e.offset = w->data_pos[(size_t)e.shard];
+    e.size = (uint64_t)len * inner * esz;
+    const uint8_t* src = (const uint8_t*)bytes + (uint64_t)start * inner * esz;
+    e.crc = mask_crc(dfmio::crc32c(src, e.size));
+    if (e.size && fwrite(src, 1, e.size, w->data[(size_t)e.shard]) != e.size) {
+      berr("write failed for %s", name);
+      return -1;
+    }
+    w->data_pos[(size_t)e.shard] += e.size;
+    w->entries.push_back(std::move(e));
+    full.slices.push_back(std::move(sl));
+    start += len;
+  }
+  w->entries.push_back(std::move(full));
+  return 0;
+}
+
 int dfmio_bundle_writer_finish(void* wh) {
   Writer* w = (Writer*)wh;
   for (FILE* f : w->data) fclose(f);
@@ -449,7 +611,10 @@ void* dfmio_bundle_reader_open(const char* prefix) {
         berr("malformed BundleEntryProto for %s", key.c_str());
         return false;
       }
-      r->entries.push_back(std::move(en));
+      if (key[0] == '\0')  // OrderedCode keys start with the number 0: the bytes of one slice of a partitioned variable
+        r->slice_data[key] = std::move(en);
+      else
+        r->entries.push_back(std::move(en));
       return true;
     });
   });
@@ -474,17 +639,16 @@ int dfmio_bundle_reader_entry(void* rh, int i, char* name, int cap, int* dtype, 
   *ndim = (int)e.dims.size();
   for (size_t k = 0; k < e.dims.size() && k < 8; ++k) dims[k] = e.dims[k];
   *nbytes = e.size;
+  if (!e.slices.empty()) {  // partitioned: the bytes are assembled from the slices on read
+    uint64_t n = (uint64_t)dtype_size(e.dtype);
+    for (int64_t d : e.dims) n *= (uint64_t)(d < 0 ? 0 : d);
+    *nbytes = n;
+  }
   return 0;
 }
 
-int dfmio_bundle_reader_read(void* rh, int i, void* dst, uint64_t cap, int verify_crc) {
-  Reader* r = (Reader*)rh;
-  if (i < 0 || i >= (int)r->entries.size()) return -1;
-  const Entry& e = r->entries[i];
-  if (e.size > cap) {
-    berr("destination too small for %s", e.name.c_str());
-    return -1;
-  }
+namespace {
+int read_span(Reader* r, const Entry& e, void* dst, int verify_crc) {
   if (e.shard < 0 || e.shard >= r->num_shards) {
     berr("%s lives in shard %d of %d", e.name.c_str(), e.shard, r->num_shards);
     return -1;
@@ -504,6 +668,100 @@ int dfmio_bundle_reader_read(void* rh, int i, void* dst, uint64_t cap, int verif
   }
   if (verify_crc && mask_crc(dfmio::crc32c((const uint8_t*)dst, e.size)) != e.crc) {
     berr("tensor CRC mismatch for %s", e.name.c_str());
+    return -1;
+  }
+  return 0;
+}
+
+// Copies one slice (contiguous row-major `src` of extent ext[]) into the full row-major tensor of shape dims[].
+void scatter_slice(uint8_t* dst, const uint8_t* src, const std::vector<int64_t>& dims, const std::vector<int64_t>& start,
+                   const std::vector<int64_t>& ext, size_t esz) {
+  const int nd = (int)dims.size();
+  if (nd == 0) {
+    memcpy(dst, src, esz);
+    return;
+  }
+  std::vector<int64_t> stride(nd, 1);
+  for (int d = nd - 2; d >= 0; --d) stride[d] = stride[d + 1] * dims[d + 1];
+  const int64_t row = ext[nd - 1];
+  int64_t outer = 1;
+  for (int d = 0; d < nd - 1; ++d) outer *= ext[d];
+  std::vector<int64_t> idx(nd, 0);
+  for (int64_t o = 0; o < outer; ++o) {
+    int64_t off = start[nd - 1];
+    for (int d = 0; d < nd - 1; ++d) off += (start[d] + idx[d]) * stride[d];
+    memcpy(dst + (size_t)off * esz, src + (size_t)o * row * esz, (size_t)row * esz);
+    for (int d = nd - 2; d >= 0; --d) {
+      if (++idx[d] < ext[d]) break;
+      idx[d] = 0;
+    }
+  }
+}
+}  // namespace
+
+int dfmio_bundle_reader_read(void* rh, int i, void* dst, uint64_t cap, int verify_crc) {
+  Reader* r = (Reader*)rh;
+  if (i < 0 || i >= (int)r->entries.size()) return -1;
+  const Entry& e = r->entries[i];
+  if (e.slices.empty()) {
+    if (e.size > cap) {
+      berr("destination too small for %s", e.name.c_str());
+      return -1;
+    }
+    return read_span(r, e, dst, verify_crc);
+  }
+  // partitioned variable: every listed slice must be present, inside the full shape, and together cover it exactly once
+  const size_t esz = (size_t)dtype_size(e.dtype);
+  const int nd = (int)e.dims.size();
+  uint64_t total = 1;
+  for (int64_t d : e.dims) {
+    if (d < 0 || (d > 0 && total > (1ull << 40) / (uint64_t)d)) {
+      berr("unreasonable shape for %s", e.name.c_str());
+      return -1;
+    }
+    total *= (uint64_t)d;
+  }
+  if (esz == 0 || total * esz > cap) {
+    berr("destination too small (or unknown dtype) for partitioned %s", e.name.c_str());
+    return -1;
+  }
+  uint64_t covered = 0;
+  std::vector<uint8_t> tmp;
+  for (auto& sl : e.slices) {
+    if ((int)sl.size() != nd) {
+      berr("slice rank mismatch for %s", e.name.c_str());
+      return -1;
+    }
+    std::vector<int64_t> start(nd), ext(nd);
+    uint64_t n = 1;
+    for (int d = 0; d < nd; ++d) {
+      start[d] = sl[d].second < 0 ? 0 : sl[d].first;
+      ext[d] = sl[d].second < 0 ? e.dims[d] : sl[d].second;
+      if (start[d] < 0 || ext[d] < 0 || start[d] > e.dims[d] || ext[d] > e.dims[d] - start[d]) {
+        berr("slice outside the tensor for %s", e.name.c_str());
+        return -1;
+      }
+      n *= (uint64_t)ext[d];
+    }
+    auto it = r->slice_data.find(slice_key(e.name, sl));
+    if (it == r->slice_data.end()) {
+      berr("missing slice data for %s", e.name.c_str());
+      return -1;
+    }
+    if (it->second.size != n * esz) {
+      berr("slice size mismatch for %s", e.name.c_str());
+      return -1;
+    }
+    tmp.resize((size_t)(n * esz));
+    Entry se = it->second;
+    se.name = e.name;
+    if (read_span(r, se, tmp.data(), verify_crc) != 0) return -1;
+    scatter_slice((uint8_t*)dst, tmp.data(), e.dims, start, ext, esz);
+    covered += n;
+  }
+  if (covered != total) {
+    berr("slices of %s cover %llu of %llu elements", e.name.c_str(), (unsigned long long)covered,
+         (unsigned long long)total);
     return -1;
   }
   return 0;

@@ -115,7 +115,7 @@ emb_fm_fwd_a2a_kernel(const ShardPtrs sp, const int* __restrict__ ids, const flo
           pk.x = pack_bf16x2(e.x, e.y);
           pk.y = pack_bf16x2(e.z, e.w);
           *reinterpret_cast<uint2*>(x0 + (size_t)sample * ldx + (size_t)f * K + 4 * g) = pk;
-          *reinterpret_cast<float4*>(e32 + (size_t)sample * ldx + (size_t)f * K + 4 * g) = e;
+          *reinterpret_cast<float4*>(e32 + ((size_t)sample * F + f) * K + 4 * g) = e;  // e32 is dense [B, F*K]
         }
       }
     }
@@ -168,7 +168,7 @@ emb_bwd_a2a_kernel(const ShardPtrs sp, const int* __restrict__ ids, const float*
   const int owner = valid ? id % W : 0;
   const size_t lrow = valid ? (size_t)(id / W) : 0;
   float* gdst = sp.gv[owner] + lrow * K;
-  const float4* ep = reinterpret_cast<const float4*>(e32 + (size_t)b * ldx + (size_t)f * K);
+  const float4* ep = reinterpret_cast<const float4*>(e32 + ((size_t)b * F + f) * K);  // dense [B, F*K]
   const float4* spp = reinterpret_cast<const float4*>(S + (size_t)b * K);
   const uint2* dxp = reinterpret_cast<const uint2*>(dx0 + (size_t)b * ldx + (size_t)f * K);
   // the row's G 16-byte chunks are split over gridDim.y CTAs (shorter serial chain per thread), as in emb_bwd
@@ -390,7 +390,8 @@ extern "C" {
 
 int dfm_sharded_flag_words(void) { return 2 * kShMaxBlocks * kShMaxRanks; }
 
-// grid_blocks must be identical on every rank (<= 1184). x0 bf16 / e32 f32 share ldx.
+// grid_blocks must be identical on every rank (<= 1184). x0 bf16 has row stride ldx (padded activation rows); e32 f32 is
+// dense [B, F*K].
 int dfm_emb_fm_fwd_a2a(void* const* v, void* const* w, void* const* gv, void* const* gw, void* const* bm, void* const* fl,
                        int rank, int world, const int* ids, const float* vals, void* x0, float* e32, int ldx, float* S,
                        float* yfm, int B, int F, int K, long long N, const unsigned int* seq_ptr, int do_barrier,

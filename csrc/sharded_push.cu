@@ -163,7 +163,7 @@ a2a_combine_kernel(const PushPtrs pp, const int* __restrict__ pos_of_pair, const
           pk.x = pack_bf16x2(e.x, e.y);
           pk.y = pack_bf16x2(e.z, e.w);
           *reinterpret_cast<uint2*>(x0 + (size_t)sample * ldx + (size_t)f * K + 4 * g) = pk;
-          if (e32) *reinterpret_cast<float4*>(e32 + (size_t)sample * ldx + (size_t)f * K + 4 * g) = e;
+          if (e32) *reinterpret_cast<float4*>(e32 + ((size_t)sample * F + f) * K + 4 * g) = e;  // dense [B, F*K]
         }
       }
     }

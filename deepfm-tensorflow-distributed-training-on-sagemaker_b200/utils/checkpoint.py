@@ -4,8 +4,10 @@ The reference saves through `tf.estimator.Estimator(model_dir=...)` (PS:435, HVD
 `model.ckpt-<global_step>.{index,data-00000-of-00001}` plus a `checkpoint` text proto naming the latest one,
 keep-5 rotation, restore-latest on start. This module writes/reads exactly that, with the reference's variable
 names (`fm_bias`, `fm_w`, `fm_v`, `Deep-part/mlp{i}/{weights,biases}`, `Deep-part/deep_out/...`,
-optimizer slots `<var>/Adam`, `<var>/Adam_1`, ..., `beta1_power`, `beta2_power`, `global_step`), so a checkpoint
-produced here loads into the reference's `model_fn` and vice versa. MLP weights are stored `[in,out]` as TF does
+optimizer slots `<var>/Adam`, `<var>/Adam_1`, ..., `beta1_power`, `beta2_power`, `global_step`), with the intent that
+a checkpoint produced here loads into the reference's `model_fn` and vice versa. That interchange is UNVERIFIED against
+a TensorFlow-written file (none can be produced offline): the format follows SURVEY Appendix A and round-trips its own
+output, sharded data files and partitioned variables (`slices`) included. MLP weights are stored `[in,out]` as TF does
 and transposed to the native `[out,in]` on load.
 """
 from __future__ import annotations

@@ -3,7 +3,7 @@ from __future__ import annotations
 
 import ctypes
 from ctypes import c_char_p, c_int, c_int64, c_uint64, c_void_p
-from typing import Dict
+from typing import Dict, Optional
 
 import numpy as np
 import torch
@@ -24,6 +24,8 @@ def _lib():
         lib.dfmio_bundle_writer_create_sharded.restype = c_void_p
         lib.dfmio_bundle_writer_create_sharded.argtypes = [c_char_p, c_int]
         lib.dfmio_bundle_writer_add.argtypes = [c_void_p, c_char_p, c_int, c_int, c_void_p, c_void_p, c_uint64]
+        lib.dfmio_bundle_writer_add_partitioned.argtypes = [c_void_p, c_char_p, c_int, c_int, c_void_p, c_void_p, c_uint64,
+                                                            c_int]
         lib.dfmio_bundle_writer_finish.argtypes = [c_void_p]
         lib.dfmio_bundle_reader_open.restype = c_void_p
         lib.dfmio_bundle_reader_open.argtypes = [c_char_p]
@@ -40,10 +42,14 @@ def _err(lib):
     return m.decode() if m else "?"
 
 
-def write_bundle(prefix: str, tensors: Dict[str, torch.Tensor], num_shards: int = 1) -> None:
+def write_bundle(prefix: str, tensors: Dict[str, torch.Tensor], num_shards: int = 1,
+                 partitioned: Optional[Dict[str, int]] = None) -> None:
     """Write `<prefix>.index` + `<prefix>.data-SSSSS-of-NNNNN` holding `tensors` (keys = TF variable names).
     `num_shards` > 1 spreads the variables round-robin over that many data files - the layout the reference's
-    parameter-server jobs leave behind (sharded Saver, one file per PS task); `read_bundle` reads any shard count."""
+    parameter-server jobs leave behind (sharded Saver, one file per PS task); `read_bundle` reads any shard count.
+    `partitioned` = {variable name: number of parts}: those variables are stored the way a TF-1 job with
+    `tf.fixed_size_partitioner(num_shards)` (the deck's advice for big tables, PDF p32) stores them - a full-shape entry
+    listing the slices plus one entry per slice along axis 0; `read_bundle` reassembles them."""
     lib = _lib()
     h = lib.dfmio_bundle_writer_create_sharded(prefix.encode(), int(num_shards))
     if not h:
@@ -53,7 +59,13 @@ def write_bundle(prefix: str, tensors: Dict[str, torch.Tensor], num_shards: int 
         if a.dtype not in _DT:
             a = a.astype(np.float32)
         dims = (c_int64 * max(a.ndim, 1))(*a.shape)
-        if lib.dfmio_bundle_writer_add(h, name.encode(), _DT[a.dtype], a.ndim, dims, a.ctypes.data, a.nbytes) != 0:
+        parts = (partitioned or {}).get(name, 0)
+        if parts > 1:
+            rc = lib.dfmio_bundle_writer_add_partitioned(h, name.encode(), _DT[a.dtype], a.ndim, dims, a.ctypes.data,
+                                                         a.nbytes, int(parts))
+        else:
+            rc = lib.dfmio_bundle_writer_add(h, name.encode(), _DT[a.dtype], a.ndim, dims, a.ctypes.data, a.nbytes)
+        if rc != 0:
             raise IOError(_err(lib))
     if lib.dfmio_bundle_writer_finish(h) != 0:
         raise IOError(_err(lib))

@@ -93,6 +93,11 @@ void* dfmio_bundle_writer_create(const char* prefix);
 void* dfmio_bundle_writer_create_sharded(const char* prefix, int num_shards);
 int dfmio_bundle_writer_add(void* writer, const char* name, int dtype, int ndim, const int64_t* dims, const void* bytes,
                             uint64_t nbytes);
+/* A variable partitioned along axis 0 into num_parts near-equal pieces (tf.fixed_size_partitioner): a full-shape entry
+ * that lists the slices + one data entry per slice under TF's OrderedCode slice key. The reader assembles partitioned
+ * variables (written here or by a TF-1 parameter-server job with a partitioner) back into the full tensor. */
+int dfmio_bundle_writer_add_partitioned(void* writer, const char* name, int dtype, int ndim, const int64_t* dims,
+                                        const void* bytes, uint64_t nbytes, int num_parts);
 int dfmio_bundle_writer_finish(void* writer); /* sorts the keys, writes both files, frees the writer */
 void* dfmio_bundle_reader_open(const char* prefix);
 int dfmio_bundle_reader_count(void* reader);

@@ -58,7 +58,8 @@ for K, opt, mode in [(32, "Adagrad", "pull"), (64, "Adam", "pull"), (32, "GD", "
         scale = float(b.abs().max()) + 1e-8
         if opt == "GD":
             err = float((a - b).abs().max()) / scale; worst = max(worst, err)
-            check(err < 3e-2, "K%d %s %s %s err %.3e" % (K, opt, mode, k, err))
+            check(err < 3e-2, "K%d %s %s %s err %.3e (nan: got %d, oracle %d)" % (
+                K, opt, mode, k, err, int(torch.isnan(a).sum()), int(torch.isnan(b).sum())))
         else:
             frac = float(((a - b).abs() > 3e-2 * scale).float().mean()); worst = max(worst, frac)
             check(frac < 0.20, "K%d %s %s %s frac_bad %.3f" % (K, opt, mode, k, frac))

@@ -201,3 +201,51 @@ def test_uneven_shards_do_not_deadlock_the_job(data, tmp_path):
                    env={"PYTHONPATH": REPO, "CUDA_VISIBLE_DEVICES": ""}, cwd=REPO).fit(
         {"training": str(tmp_path / "train"), "evaluation": str(data / "val")}, timeout=240)
     assert int(read_bundle(latest_checkpoint(str(tmp_path / "ck")))["global_step"]) == 10   # 2 epochs x min(6, 5)
+
+
+def _agree_worker(rank, world, port, counts, q):
+    """One rank of the pipe-mode agreement test: a stream of `counts[rank]` full batches and one short one."""
+    import types
+    import torch.distributed as dist
+    from deepfm_b200.parallel.dist import DistEnv
+    from deepfm_b200.runtime.estimator import Estimator
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+    released = []
+
+    class _Batch:
+        def __init__(self, i, rows):
+            self.i, self.rows = i, rows
+
+        def release(self):
+            released.append(self.i)
+
+    B = 8
+    stream = [_Batch(i, B) for i in range(counts[rank])]
+    stream.insert(min(2, len(stream)), _Batch(-1, B - 3))  # a short batch in the middle is skipped, not a step
+    me = types.SimpleNamespace(B=B, env=DistEnv(rank=rank, world_size=world, backend="gloo"))
+    got = [b.i for b in Estimator._agreed_batches(me, iter(stream), block=3)]
+    q.put((rank, got, sorted(released)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_pipe_mode_ranks_with_uneven_streams_stop_together():
+    """in pipe mode no rank knows its step count up front. Ranks whose FIFOs hold different numbers of
+    records must still run the same number of synchronous steps (a lone extra step would hang in the collective, the
+    Horovod failure of PDF p22-23): `_agreed_batches` agrees block by block over gloo, world size 2."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    counts = [10, 7]
+    port = 29400 + os.getpid() % 500
+    ps = [ctx.Process(target=_agree_worker, args=(r, 2, port, counts, q)) for r in range(2)]
+    for p in ps:
+        p.start()
+    out = sorted(q.get(timeout=120) for _ in ps)
+    for p in ps:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    (_, got0, rel0), (_, got1, rel1) = out
+    # blocks of 3: both have 3, 3, then rank 1 holds only 1 more -> 7 steps on BOTH ranks, and they stop in the same block
+    assert got0 == list(range(7)) and got1 == list(range(7))
+    assert rel0 == [-1, 7, 8] and rel1 == [-1]  # fetched-but-unused batches go back to the loader; nothing leaks

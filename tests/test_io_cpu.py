@@ -361,6 +361,63 @@ def test_sharded_tensor_bundles_like_a_parameter_server_checkpoint(tmp_path):
         read_bundle(prefix)
 
 
+def _ordered_code_slice_key(name: str, extents):
+    """Second derivation of TF's EncodeTensorNameSlice (OrderedCode: tensorflow/core/lib/strings/ordered_code.h): the number
+    0, the escaped name, the rank, then (start, length) per dimension as signed increasing numbers; (-1, -1) = whole axis."""
+    def num_inc(v):
+        b = v.to_bytes((v.bit_length() + 7) // 8, "big") if v else b""
+        return bytes([len(b)]) + b
+
+    def signed_inc(v):
+        x = ~v if v < 0 else v
+        n = 1
+        while x.bit_length() > 7 * n - 1:
+            n += 1
+        raw = bytearray((v & ((1 << 80) - 1)).to_bytes(10, "big")[10 - n:])
+        for i in range(n):  # n leading one bits mark the length; xor keeps negatives below positives
+            raw[i // 8] ^= 0x80 >> (i % 8)
+        return bytes(raw)
+
+    key = num_inc(0) + name.encode().replace(b"\x00", b"\x00\xff").replace(b"\xff", b"\xff\x00") + b"\x00\x01"
+    key += num_inc(len(extents))
+    for start, length in extents:
+        key += signed_inc(start) + signed_inc(length)
+    return key
+
+
+def test_partitioned_variables_like_fixed_size_partitioner(tmp_path):
+    """The deck's advice for big tables on parameter servers is `tf.fixed_size_partitioner` (PDF p32). Such a variable is
+    saved as a full-shape BundleEntryProto that lists `slices` plus one entry per slice under an OrderedCode key; the reader
+    must assemble them into the full tensor, and report missing / inconsistent slices."""
+    from deepfm_b200.utils.tf_bundle import read_bundle, write_bundle
+    assert _ordered_code_slice_key("fm_v", [(0, 58791), (-1, -1)]) == b"\x00fm_v\x00\x01\x01\x02\x80\xe0\xe5\xa7\x7f\x7f"
+    g = torch.Generator().manual_seed(1)
+    tensors = {"fm_w": torch.randn(1001, generator=g), "fm_v": torch.randn(1001, 8, generator=g),
+               "fm_v/Adam": torch.randn(1001, 8, generator=g), "Deep-part/mlp0/weights": torch.randn(32, 16, generator=g),
+               "fm_bias": torch.tensor([0.25]), "global_step": torch.tensor(7)}
+    prefix = str(tmp_path / "model.ckpt-7")
+    write_bundle(prefix, tensors, num_shards=2, partitioned={"fm_v": 3, "fm_w": 2, "fm_v/Adam": 3})
+    raw = open(prefix + ".index", "rb").read()
+    # the first slice of fm_v: rows [0, 334) (1001 = 334 + 334 + 333), every column; stored in full (no shared prefix
+    # with the preceding header key)
+    assert _ordered_code_slice_key("fm_v", [(0, 334), (-1, -1)]) in raw
+    assert _ordered_code_slice_key("fm_v", [(0, 334), (-1, -1)]) == b"\x00fm_v\x00\x01\x01\x02\x80\xc1\x4e\x7f\x7f"
+    back = read_bundle(prefix)
+    assert set(back) == set(tensors)
+    for k, v in tensors.items():
+        assert torch.equal(back[k], v) and back[k].shape == v.shape, k
+    # a checkpoint whose slice data is gone (an index entry without its bytes) is an error, not zeros
+    write_bundle(prefix + "b", {"fm_v": tensors["fm_v"]}, partitioned={"fm_v": 4})
+    idx = bytearray(open(prefix + "b.index", "rb").read())
+    key = _ordered_code_slice_key("fm_v", [(0, 251), (-1, -1)])
+    at = bytes(idx).find(key)
+    assert at > 0
+    idx[at + len(key) - 3] ^= 0x01  # the slice now claims another length: no longer the one the full entry lists
+    open(prefix + "b.index", "wb").write(bytes(idx))
+    with pytest.raises(IOError):
+        read_bundle(prefix + "b")
+
+
 def test_loader_epoch_shuffle_is_a_reproducible_permutation(tmp_path):
     """shuffle_seed != 0: each epoch reads every record of the rank's shard exactly once, in an order that differs from
     the file order, differs between epochs, is identical for the same seed, and respects sharding (parsed and raw mode)."""
