@@ -29,7 +29,10 @@ constexpr int kArThreads = 256;
 constexpr int kArMaxBlocks = 148 * 8;
 
 struct ArOptArgs {
-  float* g[kMaxRanks];             // every rank's flat gradient buffer (peer-mapped), index [rank]
+  // Peer tables are ROTATED by the host wrapper: entry j belongs to rank (rank + j) % world, so entry 0 is this rank and
+  // the kernels index them with compile-time constants only (or pick8): no dynamically indexed parameter array, no stack
+  // frame (see pick8 in common.cuh).
+  float* g[kMaxRanks];             // every rank's flat gradient buffer (peer-mapped)
   float* p[kMaxRanks];             // every rank's flat parameter buffer
   __nv_bfloat16* sh[kMaxRanks];    // every rank's bf16 shadow buffer
   uint32_t* flags[kMaxRanks];      // every rank's flag array: [kMaxRanks] words for barrier A, then [kMaxRanks] for B
@@ -98,10 +101,11 @@ __global__ void ar_barrier_kernel(const ArOptArgs a) {
   trace_min(TR_BAR_A, 1);
   const uint32_t seq = *a.seq_ptr + 1u;
   if (threadIdx.x < a.world) {
-    const int peer = threadIdx.x;
-    if (a.loss_local) a.loss_parts[peer][a.rank] = *a.loss_local;  // ordered before the release below (same thread)
-    st_release_sys(a.flags[peer] + a.rank, seq);
-    wait_flag_geq(a.flags[a.rank] + peer, seq, peer, 0);
+    const int j = threadIdx.x;  // rotated slot; the peer behind it:
+    const int peer = a.rank + j < a.world ? a.rank + j : a.rank + j - a.world;
+    if (a.loss_local) pick8(a.loss_parts, j)[a.rank] = *a.loss_local;  // ordered before the release below (same thread)
+    st_release_sys(pick8(a.flags, j) + a.rank, seq);
+    wait_flag_geq(a.flags[0] + peer, seq, peer, 0);
   }
   trace_max(TR_BAR_A, 2);
 }
@@ -122,13 +126,14 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
   // acknowledged those writes; scripts/step_trace.py at 8 GPUs: barrier end 70.1 us, sweep go 76.4 us).
   pdl_wait(TR_ALLREDUCE);
   if (a.barrier_inside) {
-    uint32_t* go = a.flags[a.rank] + 2 * kMaxRanks;
+    uint32_t* go = a.flags[0] + 2 * kMaxRanks;
     if (blockIdx.x == 0) {
       if (threadIdx.x < W) {
-        const int peer = threadIdx.x;
-        if (a.loss_local) a.loss_parts[peer][a.rank] = *a.loss_local;
-        st_release_sys(a.flags[peer] + a.rank, seq);
-        wait_flag_geq(a.flags[a.rank] + peer, seq, peer, 0);
+        const int j = threadIdx.x;
+        const int peer = a.rank + j < W ? a.rank + j : a.rank + j - W;
+        if (a.loss_local) pick8(a.loss_parts, j)[a.rank] = *a.loss_local;
+        st_release_sys(pick8(a.flags, j) + a.rank, seq);
+        wait_flag_geq(a.flags[0] + peer, seq, peer, 0);
       }
       __syncthreads();
       if (threadIdx.x == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(go), "r"(seq) : "memory");
@@ -144,7 +149,7 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
   const float lr_t = s_lr;
   const int nslots = opt_num_slots(a.h.opt);
   float reg = 0.f;
-  float* wl = a.p[a.rank];
+  float* wl = a.p[0];
   const long long b4 = a.slice_begin >> 2, e4 = a.slice_end >> 2;
   // U float4 per thread per trip: every NVLink load of a trip (U x W peer loads, or U multimem loads) is issued before
   // the first use (branch-free main loop + scalar tail), so a trip costs ~one fabric round trip, not U x W of them.
@@ -153,7 +158,7 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
   auto reduce_one = [&](long long i) -> float4 {
     const long long e0 = i << 2;
     if (e0 >= a.local_begin && e0 < a.local_end) {  // owner-routed range: the sum is already here
-      float4* lp = reinterpret_cast<float4*>(a.g[a.rank]) + i;
+      float4* lp = reinterpret_cast<float4*>(a.g[0]) + i;
       const float4 v = *lp;
       *lp = make_float4(0.f, 0.f, 0.f, 0.f);  // the owner zeroes its own slice (peers add to it again only after barrier B)
       return v;
@@ -165,11 +170,7 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
 #pragma unroll
       for (int r = 0; r < kMaxRanks; ++r) {
         x[r] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (r < W) {
-          int peer = a.rank + r;  // stagger peers across ranks
-          if (peer >= W) peer -= W;
-          x[r] = ld_volatile_f4(a.g[peer] + (i << 2));
-        }
+        if (r < W) x[r] = ld_volatile_f4(a.g[r] + (i << 2));  // rotated table: peers are staggered across ranks
       }
       float4 acc = x[0];
 #pragma unroll
@@ -207,10 +208,8 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
 #pragma unroll
       for (int r = 0; r < kMaxRanks; ++r) {
         if (r < W) {
-          int peer = a.rank + r;
-          if (peer >= W) peer -= W;
-          reinterpret_cast<float4*>(a.p[peer])[i] = w;
-          if (in_shadow) *reinterpret_cast<uint2*>(a.sh[peer] + (e - a.shadow_begin)) = pk;
+          reinterpret_cast<float4*>(a.p[r])[i] = w;
+          if (in_shadow) *reinterpret_cast<uint2*>(a.sh[r] + (e - a.shadow_begin)) = pk;
         }
       }
     }
@@ -245,7 +244,7 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
   __threadfence();
   if (threadIdx.x < W && a.finalize) {
     const float part = 0.5f * a.l2 * atomicAdd(a.reg_local, 0.f) + (a.reg_extra ? __ldcg(a.reg_extra) : 0.f);
-    a.reg_parts[threadIdx.x][a.rank] = part;  // slot [rank] on every peer
+    pick8(a.reg_parts, (int)threadIdx.x)[a.rank] = part;  // slot [rank] on every peer
   }
   __threadfence_system();
   __syncthreads();
@@ -256,9 +255,10 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
     *a.seq_ptr = seq;
   }
   if (threadIdx.x < W) {
-    const int peer = threadIdx.x;
-    uint32_t* bflags_peer = a.flags[peer] + kMaxRanks;
-    const uint32_t* bflags_mine = a.flags[a.rank] + kMaxRanks;
+    const int j = threadIdx.x;
+    const int peer = a.rank + j < W ? a.rank + j : a.rank + j - W;
+    uint32_t* bflags_peer = pick8(a.flags, j) + kMaxRanks;
+    const uint32_t* bflags_mine = a.flags[0] + kMaxRanks;
     st_release_sys(bflags_peer + a.rank, seq);
     wait_flag_geq(bflags_mine + peer, seq, peer, 1);
   }
@@ -268,8 +268,8 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
     if (threadIdx.x == 0) {
       float ls = 0.f, rs = 0.f;
       for (int r = 0; r < W; ++r) {  // fixed order: the same values on every rank
-        ls += __ldcg(a.loss_parts[a.rank] + r);
-        rs += __ldcg(a.reg_parts[a.rank] + r);
+        ls += __ldcg(a.loss_parts[0] + r);
+        rs += __ldcg(a.reg_parts[0] + r);
       }
       a.scalars_out[0] = ls;
       a.scalars_out[1] = rs;
@@ -287,7 +287,7 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
 // multicast stores (NVLS) or per-peer P2P stores. Callers fence with a host barrier before and after (start/resume only).
 template <bool NVLS>
 __global__ void __launch_bounds__(256) bcast_kernel(const ArOptArgs a, long long n4) {
-  const float4* src = reinterpret_cast<const float4*>(a.p[a.rank]);
+  const float4* src = reinterpret_cast<const float4*>(a.p[0]);
   for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n4; i += (long long)gridDim.x * 256) {
     const float4 v = src[i];
     if constexpr (NVLS) {
@@ -295,11 +295,7 @@ __global__ void __launch_bounds__(256) bcast_kernel(const ArOptArgs a, long long
     } else {
 #pragma unroll
       for (int r = 1; r < kMaxRanks; ++r) {
-        if (r < a.world) {
-          int peer = a.rank + r;
-          if (peer >= a.world) peer -= a.world;
-          reinterpret_cast<float4*>(a.p[peer])[i] = v;
-        }
+        if (r < a.world) reinterpret_cast<float4*>(a.p[r])[i] = v;
       }
     }
   }
@@ -318,7 +314,7 @@ int dfm_bcast_f32(void* const* ptrs, void* mc, long long n, int rank, int world,
   DFM_REQUIRE(n > 0 && n % 4 == 0, "bcast: n must be a positive multiple of 4");
   DFM_REQUIRE(!use_nvls || mc, "bcast: NVLS requested without a multicast mapping");
   ArOptArgs a = {};
-  for (int r = 0; r < kMaxRanks; ++r) a.p[r] = (float*)ptrs[r < world ? r : 0];
+  for (int r = 0; r < kMaxRanks; ++r) a.p[r] = (float*)ptrs[r < world ? (rank + r) % world : rank];  // rotated
   a.p_mc = (float*)mc; a.rank = rank; a.world = world;
   long long blocks = ceil_div_ll(n / 4, 256);
   if (blocks > 148 * 8) blocks = 148 * 8;
@@ -370,6 +366,7 @@ int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* c
                                unsigned int* seq_ptr, int use_nvls, int grid_blocks, void* const* loss_ptrs,
                                const float* loss_local, const float* reg_extra, float* scalars_out, float* pub_ring,
                                int pub_ring_len, long long local_begin, long long local_end, int finalize, void* stream) {
+  wd_bind((cudaStream_t)stream);
   DFM_REQUIRE(local_begin % 4 == 0 && local_end % 4 == 0 && local_end >= local_begin,
               "allreduce_opt: the owner-routed range must be ordered multiples of 4");
   DFM_REQUIRE((loss_ptrs == nullptr) == (loss_local == nullptr) && (loss_ptrs != nullptr || scalars_out == nullptr),
@@ -382,7 +379,7 @@ int dfm_allreduce_opt_step_pub(void* const* g_ptrs, void* const* p_ptrs, void* c
   DFM_REQUIRE(!use_nvls || (g_mc && p_mc && sh_mc), "allreduce_opt: NVLS requested without multicast mappings");
   ArOptArgs a;
   for (int r = 0; r < kMaxRanks; ++r) {
-    const int s = r < world ? r : 0;
+    const int s = r < world ? (rank + r) % world : rank;  // rotated: entry 0 = this rank (see ArOptArgs)
     a.g[r] = (float*)g_ptrs[s];
     a.p[r] = (float*)p_ptrs[s];
     a.sh[r] = (__nv_bfloat16*)sh_ptrs[s];

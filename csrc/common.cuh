@@ -261,6 +261,21 @@ __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, int a_mn_ma
 #ifndef DFM_FLAG_TIMEOUT_NS
 #define DFM_FLAG_TIMEOUT_NS 20000000000ull
 #endif
+// What the watchdog saw goes into a record in pinned HOST memory (error.cu: dfm_watchdog_record), not through printf: a
+// device printf gives the kernel a stack frame (its argument buffer), and no kernel of this library has one (see pick8
+// below). The host can still read the record after the trap has killed the context (dfm_watchdog_message; printed by
+// ops/lib.py when a native call or a synchronisation fails). The pointer is a per-translation-unit device variable (the
+// production build has no relocatable device code), bound by wd_bind() from each file's host wrappers.
+static __device__ unsigned int* g_wd_rec = nullptr;
+extern "C" unsigned int* dfm_watchdog_record();
+static inline void wd_bind(cudaStream_t st) {
+  static bool done = false;  // static function: one flag per translation unit, like g_wd_rec
+  if (done) return;
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) return;  // not inside a capture
+  unsigned int* rec = dfm_watchdog_record();
+  if (rec && cudaMemcpyToSymbol(g_wd_rec, &rec, sizeof(rec)) == cudaSuccess) done = true;
+}
 __device__ __forceinline__ void wait_flag_geq(const uint32_t* flag, uint32_t seq, int peer, int what) {
   unsigned long long t0 = 0;
   unsigned int spins = 0;
@@ -272,12 +287,30 @@ __device__ __forceinline__ void wait_flag_geq(const uint32_t* flag, uint32_t seq
       const unsigned long long now = global_timer_ns();
       if (t0 == 0) t0 = now;
       else if (now - t0 > DFM_FLAG_TIMEOUT_NS) {
-        printf("deepfm_b200: timed out waiting for rank %d (barrier %d, seq %u, saw %u)\n", peer, what, seq, v);
+        unsigned int* rec = g_wd_rec;
+        if (rec) {  // [0] valid, [1] missing rank, [2] barrier id, [3] expected sequence number, [4] last value seen
+          rec[1] = (unsigned)peer; rec[2] = (unsigned)what; rec[3] = seq; rec[4] = v;
+          __threadfence_system();
+          rec[0] = 1u;
+          __threadfence_system();
+        }
         __trap();
       }
       __nanosleep(200);
     }
   }
+}
+
+// Element i of an 8-entry table that lives in the KERNEL PARAMETERS, without indexing it dynamically. A dynamic index
+// makes the compiler copy the whole table into a per-thread stack frame (local memory), and a kernel with a stack frame
+// costs far more than its loads: measured on the single-GPU step, 96 bytes of stack in emb_bwd added 8 us per step
+// (cuobjdump -res-usage shows STACK:0 for every kernel of the library; keep it that way).
+template <typename T>
+__device__ __forceinline__ T pick8(T const (&arr)[8], int i) {
+  T v = arr[0];
+#pragma unroll
+  for (int k = 1; k < 8; ++k) v = (i == k) ? arr[k] : v;
+  return v;
 }
 
 // Cross-GPU barrier at the ENTRY of a kernel, whatever its grid: CTA 0 alone exchanges flags with the peers (threads
@@ -286,15 +319,15 @@ __device__ __forceinline__ void wait_flag_geq(const uint32_t* flag, uint32_t seq
 // or on the order in which they are dispatched — a per-CTA flag pairing across ranks (the first version) did.
 // flags[p] = rank p's flag array (peer-mapped); slot = this barrier's first word in it (8 words, one per rank);
 // go = a word of THIS rank's array no peer writes. Sequence numbers only grow.
-__device__ __forceinline__ void grid_entry_barrier(uint32_t* const* flags, size_t slot, uint32_t* go, int rank, int world,
+__device__ __forceinline__ void grid_entry_barrier(uint32_t* const (&flags)[8], size_t slot, uint32_t* go, int rank, int world,
                                                    uint32_t seq, int what) {
   if (world <= 1) return;
   const bool first = blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
   if (first) {
     if (threadIdx.x < (unsigned)world) {
       const int peer = threadIdx.x;
-      asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flags[peer] + slot + rank), "r"(seq) : "memory");
-      wait_flag_geq(flags[rank] + slot + peer, seq, peer, what);
+      asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(pick8(flags, peer) + slot + rank), "r"(seq) : "memory");
+      wait_flag_geq(pick8(flags, rank) + slot + peer, seq, peer, what);
     }
     __syncthreads();
     if (threadIdx.x == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(go), "r"(seq) : "memory");

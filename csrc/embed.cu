@@ -32,10 +32,21 @@ struct EmbRoute {
   long long chunk;       // slice length in elements (a multiple of the row length)
   int world;
 };
-__device__ __forceinline__ float* route_ptr(const EmbRoute& r, float* local, long long off, long long e) {
-  if (r.world <= 0) return local + e;
+// The route type is a template parameter of the kernel: the plain variant (NoRoute) must not carry the pointer table at
+// all (a dynamically indexed kernel-parameter array is copied to a per-thread stack frame: 96 bytes of local memory per
+// thread cost the single-GPU step 8 us), and the routed variant picks the peer pointer with a select chain instead of an
+// indexed load.
+struct NoRoute {
+  static constexpr long long gw_off = 0, gv_off = 0;
+};
+__device__ __forceinline__ float* route_ptr(const NoRoute&, float* local, long long, long long e) { return local + e; }
+__device__ __forceinline__ float* route_ptr(const EmbRoute& r, float*, long long off, long long e) {
   const long long ge = off + e;
-  return r.g[(int)(ge / r.chunk)] + ge;
+  const int owner = (int)(ge / r.chunk);
+  float* base = r.g[0];
+#pragma unroll
+  for (int i = 1; i < 8; ++i) base = owner == i ? r.g[i] : base;
+  return base + ge;
 }
 
 template <int G>
@@ -125,11 +136,11 @@ emb_fm_fwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, c
 //   all 32 lanes equal  -> butterfly reduce, one vector atomic per 16-byte chunk
 //   partial duplicates  -> __match_any_sync groups, the group leader gathers its members with shuffles
 //   unique id           -> direct vector atomic
-template <int G>
+template <int G, typename RouteT>
 __global__ void __launch_bounds__(kEmbThreads)
 emb_bwd_kernel(const int* __restrict__ ids, const float* __restrict__ vals, const float* __restrict__ fm_v,
                const float* __restrict__ S, const float* __restrict__ dy, const __nv_bfloat16* __restrict__ dx0,
-               int ldx, float* __restrict__ g_w, float* __restrict__ g_v, int B, int F, int N, const EmbRoute route) {
+               int ldx, float* __restrict__ g_w, float* __restrict__ g_v, int B, int F, int N, const RouteT route) {
   constexpr int K = 4 * G;
   const int lane = threadIdx.x & 31;
   const long long p = (long long)blockIdx.x * kEmbThreads + threadIdx.x;
@@ -231,8 +242,13 @@ static int launch_bwd(const int* ids, const float* vals, const float* fm_v, cons
   // split the K/4 chunks over up to 4 CTAs in y while the grid stays under ~8 CTAs per SM
   unsigned ysplit = 1;
   while (ysplit < 4 && ysplit * 2 <= (unsigned)G && (unsigned long long)xblocks * ysplit * 2 <= 148ull * 8) ysplit *= 2;
-  DFM_CHECK(launch_k(emb_bwd_kernel<G>, dim3(xblocks, ysplit), dim3(kEmbThreads), 0, st, ids, vals, fm_v, S, dy, dx0, ldx,
-                     g_w, g_v, B, F, N, route));
+  if (route.world > 0) {
+    DFM_CHECK(launch_k(emb_bwd_kernel<G, EmbRoute>, dim3(xblocks, ysplit), dim3(kEmbThreads), 0, st, ids, vals, fm_v, S, dy,
+                       dx0, ldx, g_w, g_v, B, F, N, route));
+  } else {
+    DFM_CHECK(launch_k(emb_bwd_kernel<G, NoRoute>, dim3(xblocks, ysplit), dim3(kEmbThreads), 0, st, ids, vals, fm_v, S, dy,
+                       dx0, ldx, g_w, g_v, B, F, N, NoRoute()));
+  }
   return DFM_OK;
 }
 

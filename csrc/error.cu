@@ -2,6 +2,7 @@
 // and leaves a human-readable message retrievable through dfm_last_error().
 #include <stdarg.h>
 #include <stdio.h>
+#include <string.h>
 #include <cuda_runtime.h>
 
 static thread_local char g_err[1024] = "";
@@ -121,4 +122,28 @@ extern "C" int dfm_trace_read(unsigned long long* out) {
   (void)out;
   return 1;
 #endif
+}
+
+// ---- flag-wait watchdog record (csrc/common.cuh wait_flag_geq): 8 words of pinned, device-mapped host memory. A kernel
+// that gives up waiting for a peer writes (valid, missing rank, barrier id, expected seq, seen value) here and traps; the
+// record survives the dead context because it is host memory.
+static unsigned int* g_wd_host = nullptr;
+extern "C" unsigned int* dfm_watchdog_record() {
+  if (!g_wd_host) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, 8 * sizeof(unsigned int), cudaHostAllocPortable | cudaHostAllocMapped) != cudaSuccess) {
+      cudaGetLastError();
+      return nullptr;
+    }
+    memset(p, 0, 8 * sizeof(unsigned int));
+    g_wd_host = (unsigned int*)p;
+  }
+  return g_wd_host;
+}
+// Writes the watchdog's message into buf and returns 1 if a flag wait has timed out in this process, else returns 0.
+extern "C" int dfm_watchdog_message(char* buf, int cap) {
+  const volatile unsigned int* r = g_wd_host;
+  if (!r || r[0] == 0u || !buf || cap <= 0) return 0;
+  snprintf(buf, (size_t)cap, "deepfm_b200: timed out waiting for rank %u (barrier %u, seq %u, saw %u)", r[1], r[2], r[3], r[4]);
+  return 1;
 }

@@ -50,7 +50,7 @@ __device__ __forceinline__ uint32_t sh_ld_acquire_sys(const uint32_t* p) {
 // phase, the other CTAs wait for the local go word kept in block slot 1 (which no peer ever writes).
 __device__ __forceinline__ void cross_rank_barrier(const ShardPtrs& sp, int phase, uint32_t seq) {
   const size_t slot = (size_t)phase * kShMaxBlocks * kShMaxRanks;
-  grid_entry_barrier(sp.flags, slot, sp.flags[sp.rank] + slot + kShMaxRanks, sp.rank, sp.world, seq, 2 + phase);
+  grid_entry_barrier(sp.flags, slot, pick8(sp.flags, sp.rank) + slot + kShMaxRanks, sp.rank, sp.world, seq, 2 + phase);
 }
 __device__ __forceinline__ float4 ld_peer_f4(const float* p) {  // peer data changes every step: never the nc path
   float4 v;
@@ -102,7 +102,7 @@ emb_fm_fwd_a2a_kernel(const ShardPtrs sp, const int* __restrict__ ids, const flo
       for (int u = 0; u < kShUnroll; ++u) {
         const int owner = id[u] % W;
         const size_t lrow = (size_t)(id[u] / W);
-        row[u] = ld_peer_f4(sp.v[owner] + lrow * K + 4 * g);
+        row[u] = ld_peer_f4(pick8(sp.v, owner) + lrow * K + 4 * g);
       }
 #pragma unroll
       for (int u = 0; u < kShUnroll; ++u) {
@@ -133,7 +133,7 @@ emb_fm_fwd_a2a_kernel(const ShardPtrs sp, const int* __restrict__ ids, const flo
     }
     for (int f = lane; f < F; f += 32) {
       const int id = __ldg(sid + f);
-      if ((unsigned)id < (unsigned long long)N) acc += ld_peer_f1(sp.w[id % W] + (size_t)(id / W)) * __ldg(sval + f);
+      if ((unsigned)id < (unsigned long long)N) acc += ld_peer_f1(pick8(sp.w, id % W) + (size_t)(id / W)) * __ldg(sval + f);
     }
     acc = warp_sum(acc);
     if (lane == 0) yfm[sample] = acc;
@@ -167,7 +167,7 @@ emb_bwd_a2a_kernel(const ShardPtrs sp, const int* __restrict__ ids, const float*
   const float d = valid ? __ldg(dy + b) : 0.f;
   const int owner = valid ? id % W : 0;
   const size_t lrow = valid ? (size_t)(id / W) : 0;
-  float* gdst = sp.gv[owner] + lrow * K;
+  float* gdst = pick8(sp.gv, owner) + lrow * K;
   const float4* ep = reinterpret_cast<const float4*>(e32 + ((size_t)b * F + f) * K);  // dense [B, F*K]
   const float4* spp = reinterpret_cast<const float4*>(S + (size_t)b * K);
   const uint2* dxp = reinterpret_cast<const uint2*>(dx0 + (size_t)b * ldx + (size_t)f * K);
@@ -220,8 +220,8 @@ emb_bwd_a2a_kernel(const ShardPtrs sp, const int* __restrict__ ids, const float*
     gw = acc;
   }
   if (is_leader) {
-    atomicAdd(sp.gw[owner] + lrow, gw);
-    atomicOr(sp.bitmap[owner] + (lrow >> 5), 1u << (lrow & 31));  // mark the row touched on its owner
+    atomicAdd(pick8(sp.gw, owner) + lrow, gw);
+    atomicOr(pick8(sp.bitmap, owner) + (lrow >> 5), 1u << (lrow & 31));  // mark the row touched on its owner
   }
 }
 
@@ -396,6 +396,7 @@ int dfm_emb_fm_fwd_a2a(void* const* v, void* const* w, void* const* gv, void* co
                        int rank, int world, const int* ids, const float* vals, void* x0, float* e32, int ldx, float* S,
                        float* yfm, int B, int F, int K, long long N, const unsigned int* seq_ptr, int do_barrier,
                        int grid_blocks, void* stream) {
+  wd_bind((cudaStream_t)stream);
   ShardPtrs sp;
   int rc = fill_ptrs(sp, v, w, gv, gw, bm, fl, rank, world);
   if (rc) return rc;
@@ -411,6 +412,7 @@ int dfm_emb_fm_fwd_a2a(void* const* v, void* const* w, void* const* gv, void* co
 int dfm_emb_bwd_a2a(void* const* v, void* const* w, void* const* gv, void* const* gw, void* const* bm, void* const* fl,
                     int rank, int world, const int* ids, const float* vals, const float* e32, const float* S,
                     const float* dy, const void* dx0, int ldx, int B, int F, int K, long long N, void* stream) {
+  wd_bind((cudaStream_t)stream);
   ShardPtrs sp;
   int rc = fill_ptrs(sp, v, w, gv, gw, bm, fl, rank, world);
   if (rc) return rc;
@@ -432,6 +434,7 @@ int dfm_sparse_row_opt(void* const* v, void* const* w, void* const* gv, void* co
                        int K, int opt, float lr, float beta1, float beta2, float eps, float momentum, float l2,
                        const unsigned long long* step_ptr, int step_offset, unsigned int* seq_ptr,
                        unsigned int* done_counter, float* reg_loss, int grid_blocks, void* stream) {
+  wd_bind((cudaStream_t)stream);
   ShardPtrs sp;
   int rc = fill_ptrs(sp, v, w, gv, gw, bm, fl, rank, world);
   if (rc) return rc;

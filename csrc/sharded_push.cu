@@ -46,7 +46,7 @@ struct PushPtrs {
 // go word in block slot 1 of the phase).
 __device__ __forceinline__ void push_barrier(const PushPtrs& pp, int phase, uint32_t seq) {
   const size_t slot = (size_t)phase * kPsMaxBlocks * kPsMaxRanks;
-  grid_entry_barrier(pp.flags, slot, pp.flags[pp.rank] + slot + kPsMaxRanks, pp.rank, pp.world, seq, 10 + phase);
+  grid_entry_barrier(pp.flags, slot, pick8(pp.flags, pp.rank) + slot + kPsMaxRanks, pp.rank, pp.world, seq, 10 + phase);
 }
 
 // ------------------------------------------------------------------------------------------------ dispatch
@@ -77,7 +77,7 @@ a2a_dispatch_kernel(const PushPtrs pp, const int* __restrict__ ids, const float*
   if (valid) {
     Req r;
     r.lrow = id / W; r.dest = (int)p; r.val = v; r.pad = 0;
-    *reinterpret_cast<int4*>(pp.req[owner] + (size_t)pp.rank * pp.cap + pos) = *reinterpret_cast<const int4*>(&r);
+    *reinterpret_cast<int4*>(pick8(pp.req, owner) + (size_t)pp.rank * pp.cap + pos) = *reinterpret_cast<const int4*>(&r);
   }
   // last CTA publishes the per-owner request counts into the owners' inboxes
   __shared__ bool s_last;
@@ -91,7 +91,7 @@ a2a_dispatch_kernel(const PushPtrs pp, const int* __restrict__ ids, const float*
     __threadfence();
     if (threadIdx.x < W) {
       const int n = atomicAdd(cnt_local + threadIdx.x, 0);
-      pp.req_cnt[threadIdx.x][pp.rank] = n;
+      pick8(pp.req_cnt, (int)threadIdx.x)[pp.rank] = n;
     }
     if (threadIdx.x == 0) *done_counter = 0u;
   }
@@ -108,10 +108,10 @@ a2a_serve_kernel(const PushPtrs pp, const float* __restrict__ V, const float* __
   const long long group = ((long long)blockIdx.x * kPsThreads + threadIdx.x) / G;
   const long long ngroups = (long long)gridDim.x * kPsThreads / G;
   for (int src = 0; src < pp.world; ++src) {
-    const int n = pp.req_cnt[pp.rank][src];
-    const Req* inbox = pp.req[pp.rank] + (size_t)src * pp.cap;
-    float* rows_dst = pp.rows_in[src];
-    float* wv_dst = pp.wv_in[src];
+    const int n = pick8(pp.req_cnt, pp.rank)[src];
+    const Req* inbox = pick8(pp.req, pp.rank) + (size_t)src * pp.cap;
+    float* rows_dst = pick8(pp.rows_in, src);
+    float* wv_dst = pick8(pp.wv_in, src);
     for (long long e = group; e < n; e += ngroups) {
       const int4 raw = *reinterpret_cast<const int4*>(inbox + e);
       const int lrow = raw.x, dest = raw.y;
@@ -211,8 +211,8 @@ a2a_grad_push_kernel(const PushPtrs pp, const int* __restrict__ ids, const float
   const float4 gr = make_float4(v * (bf16_lo(dx.x) + d * (s.x - e.x)), v * (bf16_hi(dx.x) + d * (s.y - e.y)),
                                 v * (bf16_lo(dx.y) + d * (s.z - e.z)), v * (bf16_hi(dx.y) + d * (s.w - e.w)));
   const size_t slot = (size_t)pp.rank * pp.cap + pos;
-  *reinterpret_cast<float4*>(pp.grad_in[owner] + slot * K + 4 * g) = gr;  // P2P store into the owner's inbox
-  if (g == 0) pp.gw_in[owner][slot] = d * v;
+  *reinterpret_cast<float4*>(pick8(pp.grad_in, owner) + slot * K + 4 * g) = gr;  // P2P store into the owner's inbox
+  if (g == 0) pick8(pp.gw_in, owner)[slot] = d * v;
 }
 
 // ------------------------------------------------------------------------------------------------ gradient apply
@@ -233,10 +233,10 @@ a2a_grad_apply_kernel(const PushPtrs pp, float* __restrict__ GV, float* __restri
   const long long warp_global = (long long)blockIdx.x * (kPsThreads / 32) + (threadIdx.x >> 5);
   const long long nwarps = (long long)gridDim.x * (kPsThreads / 32);
   for (int src = 0; src < pp.world; ++src) {
-    const int n = pp.req_cnt[pp.rank][src];
-    const Req* inbox = pp.req[pp.rank] + (size_t)src * pp.cap;
-    const float* gin = pp.grad_in[pp.rank] + (size_t)src * pp.cap * K;
-    const float* gwin = pp.gw_in[pp.rank] + (size_t)src * pp.cap;
+    const int n = pick8(pp.req_cnt, pp.rank)[src];
+    const Req* inbox = pick8(pp.req, pp.rank) + (size_t)src * pp.cap;
+    const float* gin = pick8(pp.grad_in, pp.rank) + (size_t)src * pp.cap * K;
+    const float* gwin = pick8(pp.gw_in, pp.rank) + (size_t)src * pp.cap;
     for (long long e0 = warp_global * 32; e0 < n; e0 += nwarps * 32) {
       const bool has = e0 + lane < n;
       const int my_row = has ? inbox[e0 + lane].lrow : -1;
@@ -322,6 +322,7 @@ int dfm_a2a_push_forward(void* const* req, void* const* cnt, void* const* rows, 
                          const float* vals, const float* V, const float* Wt, int* cnt_local, int* pos_of_pair,
                          unsigned int* done_counter, void* x0, float* e32, int ldx, float* S, float* yfm, int B, int F,
                          int K, long long N, const unsigned int* seq_ptr, int grid_blocks, void* stream) {
+  wd_bind((cudaStream_t)stream);
   PushPtrs pp;
   int rc = fill_push(pp, req, cnt, rows, wv, gin, gwin, fl, rank, world, cap);
   if (rc) return rc;
@@ -347,6 +348,7 @@ int dfm_a2a_push_backward(void* const* req, void* const* cnt, void* const* rows,
                           const float* vals, const int* pos_of_pair, const float* /*unused*/ e32, const float* S, const float* dy,
                           const void* dx0, int ldx, float* GV, float* GW, void* bitmap, int B, int F, int K,
                           const unsigned int* seq_ptr, int grid_blocks, void* stream) {
+  wd_bind((cudaStream_t)stream);
   PushPtrs pp;
   int rc = fill_push(pp, req, cnt, rows, wv, gin, gwin, fl, rank, world, cap);
   if (rc) return rc;

@@ -84,8 +84,8 @@ __device__ __forceinline__ void sa_mm_st_u32(uint32_t* p, uint32_t v) {
 __device__ __forceinline__ void sa_flag_barrier(const SaArgs& a, int base, uint32_t seq, int what) {
   if (threadIdx.x < a.world) {
     const int peer = threadIdx.x;
-    sa_st_release_sys(a.flags[peer] + base + a.rank, seq);
-    wait_flag_geq(a.flags[a.rank] + base + peer, seq, peer, what);
+    sa_st_release_sys(pick8(a.flags, peer) + base + a.rank, seq);  // pick8: no dynamically indexed parameter table
+    wait_flag_geq(pick8(a.flags, a.rank) + base + peer, seq, peer, what);
   }
 }
 
@@ -130,7 +130,7 @@ __global__ void sa_barrier_a_kernel(const SaArgs a) {
   pdl_launch_dependents();
   pdl_wait(TR_BAR_A);
   const uint32_t seq = *a.seq_ab + 1u;
-  if (threadIdx.x < a.world) a.loss_parts[threadIdx.x][a.rank] = *a.loss_sum;  // ordered before the release below
+  if (threadIdx.x < a.world) pick8(a.loss_parts, (int)threadIdx.x)[a.rank] = *a.loss_sum;  // ordered before the release below
   sa_flag_barrier(a, kSaFlagA, seq, 0);
   trace_end(TR_BAR_A);
 }
@@ -285,6 +285,7 @@ int dfm_sparse_allreduce_flag_words(void) { return 3 * kSaMaxRanks; }
 // mapping of the inbox or NULL), then flag barrier C. seq_c: one zero-initialised device word (advanced by the kernel).
 int dfm_bitmap_exchange(void* const* bm_ptrs, void* bm_mc, void* const* flag_ptrs, unsigned int* bm_own, int N, int rank,
                         int world, unsigned int* done_counter, unsigned int* seq_c, int use_nvls, void* stream) {
+  wd_bind((cudaStream_t)stream);
   DFM_REQUIRE(world >= 1 && world <= kSaMaxRanks && rank >= 0 && rank < world, "bitmap_exchange: bad rank/world");
   DFM_REQUIRE(!use_nvls || bm_mc, "bitmap_exchange: NVLS requested without a multicast mapping");
   SaArgs a = {};
@@ -309,6 +310,7 @@ int dfm_sparse_allreduce(void* const* g_ptrs, void* g_mc, void* const* flag_ptrs
                          long long d0_end, long long d1_begin, long long d1_end, const int* rows, const int* row_count,
                          const float* loss_sum, unsigned int* done_counter, unsigned int* seq_ab, int use_nvls,
                          int grid_blocks, void* stream) {
+  wd_bind((cudaStream_t)stream);
   DFM_REQUIRE(world >= 1 && world <= kSaMaxRanks && rank >= 0 && rank < world, "sparse_allreduce: bad rank/world");
   DFM_REQUIRE(!use_nvls || g_mc, "sparse_allreduce: NVLS requested without a multicast mapping");
   DFM_REQUIRE(fmw_off % 4 == 0 && fmv_off % 4 == 0 && d0_begin % 4 == 0 && d0_end % 4 == 0 && d1_begin % 4 == 0 &&

@@ -40,10 +40,21 @@ def load(build_if_missing: bool = True) -> ctypes.CDLL:
     return lib
 
 
+def watchdog_message() -> Optional[str]:
+    """The device-side flag-wait watchdog's report ("timed out waiting for rank r ..."), if one fired in this process. The
+    record lives in pinned host memory, so this works after the trap has killed the CUDA context."""
+    if _lib is None:
+        return None
+    buf = ctypes.create_string_buffer(256)
+    return buf.value.decode() if _lib.dfm_watchdog_message(buf, 256) == 1 else None
+
+
 def check(rc: int) -> None:
     if rc != 0:
         msg = load().dfm_last_error()
-        raise NativeError("deepfm_b200 native call failed (%d): %s" % (rc, msg.decode() if msg else "?"))
+        wd = watchdog_message()
+        raise NativeError("deepfm_b200 native call failed (%d): %s%s" % (rc, msg.decode() if msg else "?",
+                                                                         "; " + wd if wd else ""))
 
 
 def require_gpu() -> ctypes.CDLL:

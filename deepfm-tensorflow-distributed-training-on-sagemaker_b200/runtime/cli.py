@@ -59,6 +59,22 @@ def configure_host_threads(F, env) -> None:
 
 
 def main(argv: Optional[List[str]] = None) -> int:
+    try:
+        return _main(argv)
+    except BaseException:
+        # a device-side flag wait that timed out has trapped the kernel: say WHICH rank went missing before the CUDA
+        # error ("unspecified launch failure") propagates (the analogue of Horovod's stall report, PDF p21)
+        try:
+            from ..ops import lib as _nlib
+            wd = _nlib.watchdog_message()
+            if wd:
+                print("ERROR:" + wd, file=sys.stderr, flush=True)
+        except Exception:
+            pass
+        raise
+
+
+def _main(argv: Optional[List[str]] = None) -> int:
     argv = list(sys.argv[1:] if argv is None else argv)
     if "--help" in argv or "-h" in argv:
         print(__doc__)

@@ -102,6 +102,12 @@ int dfm_flat_opt_step_pub(float* w, float* g, float* s0, float* s1, long long n,
                           long long decay_end, float l2, long long shadow_begin, long long shadow_end, void* shadow,
                           unsigned long long* step_ptr, float* reg_loss, unsigned int* done_counter,
                           const float* pub_src, int pub_n, float* pub_ring, int pub_ring_len, void* stream);
+/* Flag-wait watchdog: a kernel that waits longer than DFM_FLAG_TIMEOUT_NS (20 s) for a peer's flag records (missing rank,
+ * barrier id, expected sequence number, value seen) in 8 words of pinned host memory and traps. dfm_watchdog_record returns
+ * that record (allocated on first use, NULL on failure); dfm_watchdog_message formats it into buf and returns 1 if a wait
+ * has timed out in this process, else 0 — it works after the trap, when the CUDA context is already dead. */
+unsigned int* dfm_watchdog_record(void);
+int dfm_watchdog_message(char* buf, int cap);
 int dfm_cast_f32_bf16(const float* in, void* out_bf16, long long n, void* stream);
 
 /* ---- split form of the same dense optimizer step (csrc/split_opt.cu) for replicated tables: the whole-table part of the
