@@ -124,6 +124,10 @@ inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_
   return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
 }
 
+// Tensor map of a bf16 row-major matrix [rows, cols] with leading dimension ld (elements), 128B swizzle, box = {64 inner,
+// box_rows}, out-of-bounds elements read as zero (csrc/gemm_tcgen05.cu).
+int make_tmap(CUtensorMap* tm, const void* base, int rows, int cols, int ld, int box_rows);
+
 __host__ __device__ constexpr int ceil_div(int a, int b) { return (a + b - 1) / b; }
 __host__ __device__ constexpr long long ceil_div_ll(long long a, long long b) { return (a + b - 1) / b; }
 

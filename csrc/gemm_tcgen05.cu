@@ -410,7 +410,7 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // bf16 row-major matrix [rows, cols] with leading dimension ld (elements); box = {64 inner, box_rows}.
-static int make_tmap(CUtensorMap* tm, const void* base, int rows, int cols, int ld, int box_rows) {
+int make_tmap(CUtensorMap* tm, const void* base, int rows, int cols, int ld, int box_rows) {  // declared in common.cuh
   EncodeTiledFn enc = get_encode_fn();
   if (!enc) {
     dfm_set_error("cuTensorMapEncodeTiled is unavailable (no CUDA driver?)");

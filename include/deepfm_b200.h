@@ -102,6 +102,20 @@ int dfm_flat_opt_step_pub(float* w, float* g, float* s0, float* s1, long long n,
                           long long decay_end, float l2, long long shadow_begin, long long shadow_end, void* shadow,
                           unsigned long long* step_ptr, float* reg_loss, unsigned int* done_counter,
                           const float* pub_src, int pub_n, float* pub_ring, int pub_ring_len, void* stream);
+/* Fused MLP forward (csrc/mlp_fused.cu): all L <= 4 layers X_{l+1} = dropout(relu(X_l W_l^T + b_l)) in one kernel; a
+ * thread-block cluster per 128 batch rows keeps the activations in distributed shared memory between layers. W[l] bf16
+ * [H_l, K_l] (ldw[l]), out[l] bf16 [M, H_l] (ldo[l]), keep[l] dropout keep probabilities, layer_ids[l] the Philox stream
+ * ids the per-layer GEMM plans would use (identical masks). Widths must be multiples of 16 and <= 448, leading dimensions
+ * multiples of 8; otherwise DFM_ERR_ARG and the caller keeps the per-layer plans. Reference: PS:212-226 / HVD:204-218. */
+int dfm_mlp_fwd_plan_create(void** plan_out, const void* X, int ldx, int M, int K0, int L, const void* const* W,
+                            const int* ldw, const int* H, void* const* out, const int* ldo, const float* const* bias,
+                            int relu, const float* keep, unsigned long long seed, const int* layer_ids, int row_offset,
+                            const unsigned long long* step_ptr);
+int dfm_mlp_fwd_plan_info(void* plan, int* bn, int* cluster, int* m_tiles);
+int dfm_mlp_fwd_plan_set_trace_id(void* plan, int id);
+int dfm_mlp_fwd_run(void* plan, void* stream);
+void dfm_mlp_fwd_plan_destroy(void* plan);
+
 /* Flag-wait watchdog: a kernel that waits longer than DFM_FLAG_TIMEOUT_NS (20 s) for a peer's flag records (missing rank,
  * barrier id, expected sequence number, value seen) in 8 words of pinned host memory and traps. dfm_watchdog_record returns
  * that record (allocated on first use, NULL on failure); dfm_watchdog_message formats it into buf and returns 1 if a wait
