@@ -10,9 +10,15 @@
 // barrier each CTA holds the full [128, H_l] activation block as the resident A operand of layer l+1 and only has to
 // fetch its slice of W_{l+1} (prefetched by TMA while the epilogue of layer l runs).
 //
-// What it replaces: L kernels of csrc/gemm_tcgen05.cu (mode 0), i.e. per layer boundary a grid-completion flush, the
+// What it would replace: L kernels of csrc/gemm_tcgen05.cu (mode 0), i.e. per layer boundary a grid-completion flush, the
 // next kernel's griddepcontrol.wait, a first TMA round trip for A and the pipeline fill (~3 us each at B = 1024,
 // scripts/step_trace.py). Layer 0 (K = F*K, streamed from global memory through a 7-stage TMA ring) is unchanged.
+//
+// STATUS: correct (bit-identical to the per-layer chain, tests/test_kernels_gpu.py) and NOT used by the model. Measured on
+// a B200 at the headline shape (scripts/fused_mlp_bench.py, in-kernel stamps): the DSMEM broadcast of one 128 x 400 bf16
+// block to 5 CTAs takes 4-7 us per layer — distributed shared memory moves ~17-21 B/cycle/SM — against the ~3 us of the
+// kernel boundary it removes: 32 us fused vs 16 us for the three per-layer kernels. Kept as the measured experiment behind
+// that statement, and as the starting point if a later part has a faster SM-to-SM path.
 //
 //   warp 0      TMA producer (layer 0: A and B tiles through the stage ring; layers >= 1: the whole W_l slice at once)
 //   warp 1      MMA issuer (one elected thread, tcgen05.mma.cta_group::1.kind::f16, UMMA 128 x BN x 16)
@@ -45,6 +51,7 @@ struct MlpFwdParams {
   int relu;
   const unsigned long long* step_ptr;
   int trace_id;
+  unsigned long long* dbg;  // optional: [cta][32] globaltimer stamps (development aid; null in production)
 };
 
 template <int BN>
@@ -139,6 +146,8 @@ mlp_fwd_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
   // a CTA whose slice lies beyond a layer's width idles through that layer (it still takes part in the barriers)
   auto active = [&](int l) -> bool { return n0 < p.H[l]; };
   auto nkb_of = [&](int l) -> int { return ((l == 0 ? p.K0 : p.H[l - 1]) + FBK - 1) / FBK; };
+  const int cta_lin = blockIdx.y * gridDim.x + blockIdx.x;
+  auto stamp = [&](int slot) { if (p.dbg) p.dbg[cta_lin * 32 + slot] = global_timer_ns(); };
   auto tmw = [&](int l) -> const CUtensorMap* { return l == 0 ? &tmW0 : l == 1 ? &tmW1 : l == 2 ? &tmW2 : &tmW3; };
 
   if (warp == 0) {
@@ -288,9 +297,11 @@ mlp_fwd_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
               bits[k] = b;
             }
           }
+          if (threadIdx.x == 64 && l == 0) stamp(0);
           mbar_wait(tmem_full_bar, full_phase);
           full_phase ^= 1;
           tc_fence_after();
+          if (threadIdx.x == 64) stamp(1 + l * 6);
           if (last) pdl_launch_dependents();  // late, as in the single-layer GEMM: the accumulator of the last layer is done
           const float scale = drop.enabled ? drop.scale : 1.f;
           __nv_bfloat16* orow = p.out[l] + (size_t)row * p.ldo[l];
@@ -321,8 +332,10 @@ mlp_fwd_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
           }
         }
         if (!last) {
+          if (threadIdx.x == 64) stamp(2 + l * 6);
           tc_fence_before();   // the accumulator has been read: the next layer's MMAs may overwrite it after B2
           cluster_sync_all();  // B1: nobody's tensor core reads the old activation block / ring any more
+          if (threadIdx.x == 64) stamp(3 + l * 6);
           if (act) {
             const int Hl = p.H[l];
             const uint32_t a_local = smem_u32(a_res);
@@ -354,8 +367,11 @@ mlp_fwd_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_const
               *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
             }
           }
+          if (threadIdx.x == 64) stamp(4 + l * 6);
           fence_proxy_async();  // generic-proxy stores -> visible to the async proxy (tcgen05.mma operand reads)
+          if (threadIdx.x == 64) stamp(5 + l * 6);
           cluster_sync_all();   // B2
+          if (threadIdx.x == 64) stamp(6 + l * 6);
         }
       }
     }
@@ -485,6 +501,12 @@ int dfm_mlp_fwd_plan_info(void* plan, int* bn, int* cluster, int* m_tiles) {
 int dfm_mlp_fwd_plan_set_trace_id(void* plan, int id) {
   DFM_REQUIRE(plan, "null plan");
   ((MlpFwdPlan*)plan)->p.trace_id = id;
+  return DFM_OK;
+}
+
+int dfm_mlp_fwd_plan_set_debug(void* plan, unsigned long long* dbg) {
+  DFM_REQUIRE(plan, "null plan");
+  ((MlpFwdPlan*)plan)->p.dbg = dbg;
   return DFM_OK;
 }
 

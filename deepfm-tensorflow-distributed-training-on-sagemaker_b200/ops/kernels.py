@@ -158,6 +158,58 @@ def auc_hist(prob: torch.Tensor, labels: torch.Tensor, thr: torch.Tensor, hist: 
                                         _p(hist), _stream()))
 
 
+class MlpFwdPlan:
+    """The whole MLP forward in one kernel (csrc/mlp_fused.cu): X_{l+1} = dropout(relu(X_l W_l^T + b_l)) for all layers, a
+    thread-block cluster per 128 rows keeping the activations in distributed shared memory between layers. Same Philox
+    streams as the per-layer `GemmPlan("fwd", ...)` chain, so both produce identical activations and masks.
+
+    x: bf16 [M, K0] (view, stride = its padded buffer); weights[l]: bf16 [H_l, K_l]; outs[l]: bf16 [M, H_l] views."""
+
+    def __init__(self, x: torch.Tensor, weights, outs, biases, M: int, relu: bool = True, keep_probs=None, seed: int = 0,
+                 layer_ids=None, row_offset: int = 0, step_ptr: Optional[torch.Tensor] = None):
+        L = len(weights)
+        _chk_dev(x, step_ptr, *weights, *outs, *[b for b in biases if b is not None])
+        self._keep = (x, tuple(weights), tuple(outs), tuple(biases), step_ptr)
+        VP, IP, FP = c_void_p * L, c_int * L, c_float * L
+        W = VP(*[w.data_ptr() for w in weights])
+        O = VP(*[o.data_ptr() for o in outs])
+        Bp = VP(*[(b.data_ptr() if b is not None else None) for b in biases])
+        ldw = IP(*[w.stride(0) for w in weights])
+        H = IP(*[w.shape[0] for w in weights])
+        ldo = IP(*[o.stride(0) for o in outs])
+        keep = FP(*[float(k) for k in (keep_probs or [1.0] * L)])
+        ids = IP(*[int(i) for i in (layer_ids or range(L))])
+        h = c_void_p()
+        _lib.check(_lib.load().dfm_mlp_fwd_plan_create(
+            ctypes.byref(h), _p(x), c_int(x.stride(0)), c_int(M), c_int(x.shape[1]), c_int(L), W, ldw, H, O, ldo, Bp,
+            c_int(1 if relu else 0), keep, c_uint64(seed), ids, c_int(row_offset), _p(step_ptr)))
+        self._h = h
+        self.L = L
+
+    @staticmethod
+    def supported(widths, lds) -> bool:
+        return 1 <= len(widths) <= 4 and all(h % 16 == 0 and 0 < h <= 448 for h in widths) and all(d % 8 == 0 for d in lds)
+
+    def info(self):
+        bn, cl, mt = c_int(), c_int(), c_int()
+        _lib.load().dfm_mlp_fwd_plan_info(self._h, ctypes.byref(bn), ctypes.byref(cl), ctypes.byref(mt))
+        return {"bn": bn.value, "cluster": cl.value, "m_tiles": mt.value}
+
+    def set_trace_id(self, tid: int) -> "MlpFwdPlan":
+        _lib.check(_lib.load().dfm_mlp_fwd_plan_set_trace_id(self._h, c_int(tid)))
+        return self
+
+    def run(self) -> None:
+        _lib.check(_lib.load().dfm_mlp_fwd_run(self._h, _stream()))
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                _lib.load().dfm_mlp_fwd_plan_destroy(self._h)
+        except Exception:
+            pass
+
+
 def flat_opt_step(w, g, s0, s1, opt_name: str, lr: float, beta1: float, beta2: float, eps: float, momentum: float,
                   grad_scale: float, decay_range, l2: float, shadow_range, shadow, step_ptr, reg_loss,
                   done_counter, publish=None) -> None:

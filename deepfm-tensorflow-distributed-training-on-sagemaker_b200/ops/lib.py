@@ -36,6 +36,8 @@ def load(build_if_missing: bool = True) -> ctypes.CDLL:
     lib = ctypes.CDLL(LIB_PATH)
     lib.dfm_last_error.restype = ctypes.c_char_p
     lib.dfm_gemm_plan_destroy.restype = None
+    if hasattr(lib, "dfm_mlp_fwd_plan_destroy"):
+        lib.dfm_mlp_fwd_plan_destroy.restype = None
     _lib = lib
     return lib
 

@@ -113,6 +113,7 @@ int dfm_mlp_fwd_plan_create(void** plan_out, const void* X, int ldx, int M, int 
                             const unsigned long long* step_ptr);
 int dfm_mlp_fwd_plan_info(void* plan, int* bn, int* cluster, int* m_tiles);
 int dfm_mlp_fwd_plan_set_trace_id(void* plan, int id);
+int dfm_mlp_fwd_plan_set_debug(void* plan, unsigned long long* dbg); /* development aid: [cta][32] globaltimer stamps */
 int dfm_mlp_fwd_run(void* plan, void* stream);
 void dfm_mlp_fwd_plan_destroy(void* plan);
 

@@ -58,6 +58,57 @@ def test_gemm_fwd_dropout_matches_philox(cuda_lib):
     assert 0.45 < keep.float().mean().item() < 0.55
 
 
+@pytest.mark.parametrize("M,K0,widths,keeps", [
+    (1024, 1248, [400, 400, 400], [0.5, 0.8, 1.0]),   # the headline shape: cluster of 5 x BN 80
+    (300, 1248, [400, 400, 400], [0.5, 0.5, 0.5]),    # partial last row block
+    (256, 312, [128, 64, 32], [0.9, 0.9, 0.9]),       # the reference's default widths: cluster of 2 x BN 64, idle CTAs
+    (200, 72, [256], [1.0]),                          # one layer, K0 not a multiple of 64
+    (130, 640, [448, 16, 400, 80], [0.7, 1.0, 0.6, 1.0]),  # four layers, widest allowed, narrowest allowed
+])
+def test_fused_mlp_forward_equals_the_per_layer_gemm_chain(cuda_lib, M, K0, widths, keeps):
+    """csrc/mlp_fused.cu (one cluster kernel for all layers) against the chain of per-layer tcgen05 GEMM plans it replaces:
+    same bf16 roundings at the same places and the same Philox streams, so every activation must be IDENTICAL; and both
+    against the fp32 reference with the host-side Philox mask."""
+    from deepfm_b200.ops.kernels import GemmPlan, MlpFwdPlan
+    from deepfm_b200.utils.philox import dropout_keep_mask
+    g = torch.Generator(device="cuda").manual_seed(M + K0 + len(widths))
+    def buf(rows, width):  # padded rows with a ones column, like models/fused.py act_buf
+        ld = (width + 1 + 63) // 64 * 64
+        b = torch.full((rows, ld), 7.0, device="cuda", dtype=torch.bfloat16)
+        return b, b[:, :width]
+    xb, x = buf(M, K0)
+    x.copy_((torch.randn(M, K0, device="cuda", generator=g) * 0.5).bfloat16())
+    Ws, bs, d_in = [], [], K0
+    for h in widths:
+        Ws.append((torch.randn(h, d_in, device="cuda", generator=g) * (1.0 / d_in ** 0.5)).bfloat16())
+        bs.append(torch.randn(h, device="cuda", generator=g) * 0.1)
+        d_in = h
+    step = torch.tensor([11], device="cuda", dtype=torch.int64)
+    seed, row_offset = 4321, 5
+    outs_a = [buf(M, h) for h in widths]
+    outs_b = [buf(M, h) for h in widths]
+    cur = x
+    for l, h in enumerate(widths):
+        GemmPlan("fwd", cur, Ws[l], outs_a[l][1], M, h, cur.shape[1], bias=bs[l], relu=True, keep_prob=keeps[l], seed=seed,
+                 layer=l, row_offset=row_offset, step_ptr=step).run()
+        cur = outs_a[l][1]
+    plan = MlpFwdPlan(x, Ws, [o[1] for o in outs_b], bs, M, relu=True, keep_probs=keeps, seed=seed, row_offset=row_offset,
+                      step_ptr=step)
+    plan.run()
+    torch.cuda.synchronize()
+    ref = x.float()
+    for l, h in enumerate(widths):
+        ref = torch.relu(ref @ Ws[l].float().t() + bs[l])
+        if keeps[l] < 1.0:
+            keep = torch.from_numpy(dropout_keep_mask(M, h, keeps[l], seed, 11, l, row_offset=row_offset)).cuda()
+            ref = torch.where(keep, ref / keeps[l], torch.zeros((), device="cuda"))
+        got = outs_b[l][1].float()
+        assert torch.equal(outs_b[l][0], outs_a[l][0]), (l, plan.info(), float((got - outs_a[l][1].float()).abs().max()))
+        assert _rel_err(got, ref) < 2e-2, (l, _rel_err(got, ref), plan.info())
+        assert bool((outs_b[l][0][:, h:] == 7.0).all())  # padding / ones column untouched
+        ref = got  # next layer's reference starts from the rounded activations, as the kernels do
+
+
 @pytest.mark.parametrize("M,N,K", GEMM_SHAPES)
 def test_gemm_dgrad(cuda_lib, M, N, K):
     """out[M,N] = (dZ[M,K] @ W[K,N]) * (mask != 0) * scale — B operand is N-major (no transpose materialised)."""
