@@ -15,6 +15,8 @@
 // Lanes own 4 consecutive embedding columns each (K = 4*G, G | 32).
 #include "common.cuh"
 
+#include <stdlib.h>
+
 namespace dfm {
 
 constexpr int kEmbThreads = 256;
@@ -242,6 +244,14 @@ static int launch_bwd(const int* ids, const float* vals, const float* fm_v, cons
   // split the K/4 chunks over up to 4 CTAs in y while the grid stays under ~8 CTAs per SM
   unsigned ysplit = 1;
   while (ysplit < 4 && ysplit * 2 <= (unsigned)G && (unsigned long long)xblocks * ysplit * 2 <= 148ull * 8) ysplit *= 2;
+  // emb_bwd runs BESIDE the weight-gradient GEMMs (98 KB of shared memory per CTA). With the default carve-out its CTAs put
+  // every SM they reach first into a small-shared-memory configuration, and a GEMM CTA cannot be placed there until the SM
+  // has drained (scripts/step_trace.py: wgrad_0 entered 10 us late). DFM_EMB_BWD_CARVEOUT=0 restores the default.
+  static const bool big_carveout = !(getenv("DFM_EMB_BWD_CARVEOUT") && getenv("DFM_EMB_BWD_CARVEOUT")[0] == '0');
+  if (big_carveout) {
+    dfm_prefer_max_shared(reinterpret_cast<const void*>(emb_bwd_kernel<G, EmbRoute>));
+    dfm_prefer_max_shared(reinterpret_cast<const void*>(emb_bwd_kernel<G, NoRoute>));
+  }
   if (route.world > 0) {
     DFM_CHECK(launch_k(emb_bwd_kernel<G, EmbRoute>, dim3(xblocks, ysplit), dim3(kEmbThreads), 0, st, ids, vals, fm_v, S, dy,
                        dx0, ldx, g_w, g_v, B, F, N, route));
