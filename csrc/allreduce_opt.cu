@@ -223,6 +223,7 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
     for (int u = 0; u < U; ++u) update_one(i0 + u * stride, g[u]);
   }
   for (; i0 < e4; i0 += stride) update_one(i0, reduce_one(i0));
+  trace_max(TR_AR_DENSE, 2);  // last CTA done with its reduce + update + broadcast trips (stores still in flight)
   reg = warp_sum(reg);
   if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = reg;
   __syncthreads();
@@ -247,6 +248,7 @@ __global__ void __launch_bounds__(kArThreads, 3) allreduce_opt_kernel(const ArOp
     pick8(a.reg_parts, (int)threadIdx.x)[a.rank] = part;  // slot [rank] on every peer
   }
   __threadfence_system();
+  trace_max(TR_AR_FENCE, 2);  // NVLink has acknowledged every peer store of this rank
   __syncthreads();
   if (threadIdx.x == 0) {
     *a.reg_local = 0.f;

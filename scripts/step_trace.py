@@ -22,7 +22,7 @@ NAMES = {0: "emb_fm_fwd", 1: "mlp_fwd0", 2: "mlp_fwd1", 3: "mlp_fwd2", 4: "logit
          7: "dgrad2", 8: "wgrad0", 9: "wgrad1", 10: "wgrad2", 11: "emb_bwd", 12: "tail_opt/flat_opt", 13: "touched_bitmap",
          14: "sweep_untouched", 15: "colsum (all)", 16: "barrier_A", 17: "allreduce", 18: "bitmap_exchange", 19: "union_rowlist",
          24: "  tail_opt: dense part done", 25: "  tail_opt: rows done", 26: "  tail_opt: finalised",
-         20: "  allreduce: dense part done", 21: "  allreduce: rows done", 22: "  allreduce: fence.sys done"}
+         20: "  allreduce: sweep done (last CTA)", 21: "  allreduce: rows done", 22: "  allreduce: fence.sys done"}
 
 
 def main():
