@@ -3,7 +3,9 @@
 // Replaces, in one kernel per step per rank (SURVEY K12 + X1; reference: Horovod's NCCL ring all-reduce of the
 // 16-19 MB fusion buffer HVD:262 followed by 11 ApplyAdam launches PS:269):
 //
-//   1. cross-GPU barrier A   (its own 1-CTA kernel) every rank's backward has finished writing its gradient buffer
+//   1. cross-GPU barrier A   every rank's backward has finished writing its gradient buffer (and deposited its log-loss
+//                            sum with every peer). Grids of at most one CTA per SM: CTA 0 of the sweep kernel runs it and
+//                            releases the other CTAs through a local go word; larger grids: its own 1-CTA kernel
 //   2. reduce-scatter        rank r sums ITS 1/W slice of the gradients across all W ranks
 //                              P2P  : ld.volatile.global.v4.f32 from each peer's mapped buffer
 //                              NVLS : multimem.ld_reduce.add.v4.f32 on the multicast address (reduced in the switch)
@@ -11,12 +13,15 @@
 //                            slots are sharded W ways (the HBM sweep shrinks W-fold compared with a replicated step)
 //   4. all-gather            updated fp32 weights and bf16 GEMM shadows stored straight into EVERY rank's replica
 //                              P2P  : st.global.v4 to each peer pointer       NVLS : multimem.st
-//   5. cross-GPU barrier B   by the last CTA to finish: all replicas are complete when any rank's kernel exits
+//   5. cross-GPU barrier B   by the last CTA to finish: all replicas are complete when any rank's kernel exits; it then
+//                            publishes the GLOBAL loss sum and L2 term (scalars_out, pinned host ring)
 //
-// Gradients are NOT zeroed here: peers may still be reading them; the step graph zeroes them with a memset node
-// that overlaps the next forward pass. Barriers use monotonically increasing sequence numbers (the step counter),
-// release/acquire at system scope, one flag per peer for A and one per peer for B. Only single CTAs ever spin (the
-// barrier kernel, and the last CTA of the sweep), so no co-residency assumption is needed.
+// Gradients are NOT zeroed here (except an owner-routed range, which only its owner reads): peers may still be reading
+// them; the step graph zeroes them on a forked branch that overlaps the next forward pass. Barriers use their own
+// monotonically increasing sequence number (seq_ptr; never rewound, unlike the step counter), release/acquire at system
+// scope, one flag per peer for A and one per peer for B. Only single CTAs ever spin on a peer's flag (the barrier kernel or
+// CTA 0, and the last CTA of the sweep); CTAs waiting for CTA 0's local go word are all co-resident by construction.
+// Peer-pointer tables arrive rotated by rank (entry 0 = this rank), so no kernel indexes a parameter array dynamically.
 #include "common.cuh"
 #include "optim_math.cuh"
 
