@@ -386,3 +386,24 @@ def test_deterministic_mode_training_step_matches_default(cuda_lib, monkeypatch)
     for k in grads[0]:
         if k.endswith("weight") and k.startswith("mlp"):
             assert torch.equal(grads[1][k], grads[2][k]), k  # store-based wgrads are deterministic too
+
+
+def test_watchdog_record_is_readable_from_the_host(cuda_lib):
+    """The flag-wait watchdog reports through 8 words of pinned host memory (csrc/error.cu) instead of a device printf:
+    the record must exist, read as "nothing happened", and turn into the message once a kernel has filled it in (here the
+    test plays the kernel and writes the words the way wait_flag_geq does)."""
+    import ctypes
+    from deepfm_b200.ops import lib as nlib
+    lib = nlib.load()
+    lib.dfm_watchdog_record.restype = ctypes.POINTER(ctypes.c_uint)
+    rec = lib.dfm_watchdog_record()
+    assert bool(rec)
+    assert nlib.watchdog_message() is None
+    rec[1], rec[2], rec[3], rec[4] = 5, 1, 4242, 4241
+    rec[0] = 1
+    try:
+        msg = nlib.watchdog_message()
+        assert msg is not None and "rank 5" in msg and "barrier 1" in msg and "4242" in msg and "4241" in msg
+    finally:
+        rec[0] = 0
+    assert nlib.watchdog_message() is None
