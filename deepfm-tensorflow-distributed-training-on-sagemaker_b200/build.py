@@ -29,7 +29,7 @@ OBJ_DIR = os.path.join(REPO, "build", "obj")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "-I", INC, "-I", CSRC]
-CXX_FLAGS = ["-O3", "-std=c++17", "-fPIC", "-msse4.2", "-pthread", "-I", INC, "-I", CSRC, "-Wall"]
+CXX_FLAGS = ["-O3", "-fno-math-errno", "-std=c++17", "-fPIC", "-msse4.2", "-pthread", "-I", INC, "-I", CSRC, "-Wall"]
 
 
 def _nvcc() -> str:
