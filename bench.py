@@ -132,9 +132,11 @@ def run_from_tfrecords(a, cfg, world, rank, local, dev):
         write_cache(cache, InputPipeline(files, F, B, threads=4, pin_memory=False), F)
     ds = CachedDataset(cache)
     epochs = 2
+    # parser threads per rank: what the host has per rank, between 4 and 8 (one 16-CPU box per GPU: 8; 32 CPUs for 8 ranks: 4)
+    nthr = min(8, max(4, (os.cpu_count() or 4) // max(world, 1)))
     modes = {
-        "host_parser": lambda: InputPipeline(files, F, B, epochs, (1, 0), True, 4, True),
-        "gpu_parse": lambda: InputPipeline(files, F, B, epochs, (1, 0), True, 4, True, gpu_parse=True),
+        "host_parser": lambda: InputPipeline(files, F, B, epochs, (1, 0), True, nthr, True),
+        "gpu_parse": lambda: InputPipeline(files, F, B, epochs, (1, 0), True, nthr, True, gpu_parse=True),
         "binary_cache": lambda: ds.batches(B, epochs, (1, 0), True, packed=True),
     }
     est.train(lambda: InputPipeline(files, F, B, 1, (1, 0), True, 4, True), max_steps=64, steps_hint=64)  # warm-up, graphs
@@ -155,7 +157,7 @@ def run_from_tfrecords(a, cfg, world, rank, local, dev):
     if rank == 0:
         print(json.dumps({"metric": "DeepFM train samples/sec from TFRecords (loader in the loop, wall clock, max over ranks)",
                           "n_gpus": world, "unit": "samples/s", "per_gpu_batch": B, "records_per_rank": rows * nfiles,
-                          "bytes_per_record": size / (rows * nfiles), "epochs_timed": epochs, "loader_threads": 4,
+                          "bytes_per_record": size / (rows * nfiles), "epochs_timed": epochs, "loader_threads": nthr,
                           "host_cpus": os.cpu_count(), "comm": est.trainer.comm_name, "modes": out,
                           "final_loss": float(est.trainer.last_loss())}))
     est.trainer.close()
