@@ -137,7 +137,11 @@ def _main(argv: Optional[List[str]] = None) -> int:
     def input_fn(files, num_epochs=1, shard=(1, 0), drop_remainder=True, shuffle_seed=0):
         gpu_parse = bool(F.gpu_parse) and drop_remainder and env.device is not None and F.strategy != "ps" \
             and F.backend != "torch"
-        return InputPipeline(files, F.field_size, F.batch_size, num_epochs, shard, drop_remainder, F.loader_threads, pin,
+        nthr = F.loader_threads
+        if nthr <= 0:  # auto: the CPUs this rank can count on, between 2 and 8 (the deck's num_parallel_calls advice, PDF p13)
+            local_world = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", F.worker_per_host or 1)))
+            nthr = min(8, max(2, (os.cpu_count() or 4) // local_world))
+        return InputPipeline(files, F.field_size, F.batch_size, num_epochs, shard, drop_remainder, nthr, pin,
                              gpu_parse=gpu_parse, shuffle_seed=shuffle_seed)
 
     names = channel_names()

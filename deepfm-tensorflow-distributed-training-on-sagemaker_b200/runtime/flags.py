@@ -93,7 +93,7 @@ def flag_definitions(env=os.environ) -> List[Tuple[str, type, Any, str]]:
         ("save_checkpoints_secs", int, 600, "checkpoint period in seconds (Estimator default)"),
         ("save_checkpoints_steps", int, 0, "checkpoint period in steps (overrides secs when > 0)"),
         ("keep_checkpoint_max", int, 5, "checkpoints to keep"),
-        ("loader_threads", int, 4, "parser threads of the native loader"),
+        ("loader_threads", int, 4, "parser threads of the native loader (0 = as many as this rank has CPUs, 2..8)"),
         ("gpu_parse", bool, False, "decode the Example protos on the GPU (host only walks/CRC-checks/copies records)"),
         ("scale_lr_by_world", bool, True, "multiply learning_rate by the number of workers (HVD:149)"),
         ("data_base_dir", str, env.get("SM_INPUT_DIR", "/opt/ml/input") + "/data", "where pipe-mode FIFOs live"),
