@@ -81,6 +81,27 @@ for K, opt, mode in [(32, "Adagrad", "pull"), (64, "Adam", "pull"), (32, "GD", "
         print("sharded K=%d opt=%-7s a2a=%s world=%d worst=%.3e us/step=%.1f loss=%.4f (%s)" % (K, opt, mode, world, worst, float(tt), float(m.last_loss()), m.comm_name), flush=True)
     del m
     torch.cuda.synchronize(); dist.barrier()
+# ---- batch_norm + Adam: the start / resume broadcast (BN layouts have non-trainable statistics behind the trainable block;
+# the slot broadcast used the padded length) and a few steps
+bn_cfg = DeepFMConfig(field_size=39, feature_size=5003, embedding_size=32, deep_layers=[128, 64], dropout=[0.8, 1.0],
+                      l2_reg=1e-4, l2_mode="touched", batch_norm=True)
+for mode in ("pull", "push"):
+    m = ShardedDeepFM(bn_cfg, 256, TF1Optimizer("Adam", 1e-3), 77, dev, world, rank, params=init_params(bn_cfg, seed=3),
+                      a2a_mode=mode)
+    m.broadcast_state(0)
+    for step in range(3):
+        ids, vals, labels = batch(bn_cfg, 256 * world, step)
+        sl = slice(rank * 256, (rank + 1) * 256)
+        m.train_step(ids[sl].to(dev), vals[sl].to(dev), labels[sl].to(dev))
+    torch.cuda.synchronize()
+    lossv = float(m.last_loss())
+    check(lossv == lossv and 0 < lossv < 5, "bn %s: loss %r" % (mode, lossv))
+    check(int(m.global_step) == 3, "bn %s: step counter %r" % (mode, m.global_step))
+    if rank == 0:
+        print("sharded batch_norm + Adam a2a=%s world=%d: broadcast_state + 3 steps ok, loss %.4f" % (mode, world, lossv), flush=True)
+    del m
+    torch.cuda.synchronize(); dist.barrier()
+
 flag = torch.tensor([1 if ok else 0], device=dev); dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 if rank == 0: print("SHARDED_CHECK", "PASS" if int(flag) == 1 else "FAIL", flush=True)
 dist.destroy_process_group()
