@@ -100,6 +100,8 @@ int main(int argc, char** argv) {
     dfmio_bundle_writer_add(w, "fm_w", 1, 1, d1, a, 28);
     dfmio_bundle_writer_add(w, "Deep-part/mlp0/weights", 1, 2, d2, a, 48);
     dfmio_bundle_writer_add(w, "global_step", 9, 0, d1, &step, 8);
+    // a partitioned variable (full-shape entry + slices under OrderedCode keys): its decoder sees the mutated index too
+    dfmio_bundle_writer_add_partitioned(w, "fm_v", 1, 2, d2, a, 48, 2);
     dfmio_bundle_writer_finish(w);
   }
   const std::vector<uint8_t> index_ok = read_file(bprefix + ".index");
@@ -167,6 +169,7 @@ int main(int argc, char** argv) {
     // (3) checkpoint index with corruptions
     {
       write_file(bprefix + ".index", it % 4 == 0 ? index_ok : mutate(index_ok));
+      dfmio_bundle_check_block_crc(it % 2);  // every other round without the block checksum: the decoders see the damage
       if (void* r = dfmio_bundle_reader_open(bprefix.c_str())) {
         const int cnt = dfmio_bundle_reader_count(r);
         for (int i = 0; i < cnt; ++i) {
@@ -181,8 +184,10 @@ int main(int argc, char** argv) {
           }
         }
         dfmio_bundle_reader_close(r);
+        dfmio_bundle_check_block_crc(1);
         bundle_ok++;
       } else {
+        dfmio_bundle_check_block_crc(1);
         bundle_err++;
       }
     }

@@ -372,6 +372,8 @@ bool read_file(const std::string& path, std::vector<uint8_t>* out) {
   return true;
 }
 
+bool g_check_block_crc = true;  // dfmio_bundle_check_block_crc(0): the fuzzer reaches the decoders behind the CRC
+
 bool check_block(const std::vector<uint8_t>& file, Handle h, const uint8_t** b, const uint8_t** e) {
   if (h.off + h.size + 5 > file.size()) {
     berr("block handle out of range");
@@ -384,7 +386,7 @@ bool check_block(const std::vector<uint8_t>& file, Handle h, const uint8_t** b, 
   }
   uint32_t c;
   memcpy(&c, p + h.size + 1, 4);
-  if (mask_crc(dfmio::crc32c(p, h.size + 1)) != c) {
+  if (g_check_block_crc && mask_crc(dfmio::crc32c(p, h.size + 1)) != c) {
     berr("table block CRC mismatch");
     return false;
   }
@@ -420,6 +422,10 @@ bool iterate_block(const uint8_t* b, const uint8_t* e, Fn fn) {
 extern "C" {
 
 const char* dfmio_bundle_last_error() { return g_berr; }
+
+// Table-block CRC verification of the index reader, on by default. Switching it off is for fuzzing only: a mutated index
+// then gets past the checksum and exercises the key / BundleEntryProto / slice decoders (csrc/io/fuzz_main.cc).
+void dfmio_bundle_check_block_crc(int on) { g_check_block_crc = on != 0; }
 
 // num_shards data files (an Estimator's Saver is sharded: one file per parameter-server task in the reference's PS mode,
 // one file otherwise); variable k goes to shard k % num_shards.
