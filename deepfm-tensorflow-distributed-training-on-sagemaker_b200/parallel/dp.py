@@ -393,23 +393,35 @@ class FusedDataParallel(FusedDeepFM):
                 if self.P.numel() % 4:
                     self.arena.peer_view("P", r)[-(self.P.numel() % 4):].copy_(self.P[-(self.P.numel() % 4):])
                 self.arena.peer_view("shadow", r).copy_(self.shadow)
-        step = self.step_t.clone()
-        dist.broadcast(step, src, group=self.group)
-        self.step_t.copy_(step)
-        self.opt.step = int(step.item())
-        # slot slices: every rank re-derives ITS slice from src's full vector (only src loaded the checkpoint)
-        for i in range(len(SLOT_INIT[self.opt.name])):
-            mine = self.S0 if i == 0 else self.S1
-            if self._nccl:
-                dist.broadcast(mine, src, group=self.group)
-            else:
-                full = torch.empty(n, device=self.dev, dtype=torch.float32)
-                if self.rank == src:
+        nslots = len(SLOT_INIT[self.opt.name])
+        if self._nccl:  # the NCCL baseline arm keeps replicated slots and NCCL broadcasts
+            step = self.step_t.clone()
+            dist.broadcast(step, src, group=self.group)
+            self.step_t.copy_(step)
+            for i in range(nslots):
+                dist.broadcast(self.S0 if i == 0 else self.S1, src, group=self.group)
+        else:
+            # slot slices and the step counter: src stores every rank's pieces straight into that rank's arena through the
+            # peer mappings (only src loaded the checkpoint) - no NCCL on the start / resume path. The 8-byte step travels
+            # in the first words of the "reg_parts2" scratch region (rewritten by the kernels before they read it).
+            if self.rank == src:
+                for i in range(nslots):
+                    full = torch.empty(n, device=self.dev, dtype=torch.float32)
                     loaded = getattr(self, "_loaded_full", None)
                     full.copy_(loaded[i] if loaded else self._full_slot_for_broadcast(i))
-                dist.broadcast(full, src, group=self.group)
-                for b, e, off in self._pieces(self.rank):
-                    mine[off:off + e - b].copy_(full[b:e])
+                    for r in range(self.world):
+                        pv = self.arena.peer_view("S%d" % i, r)
+                        for b, e, off in self._pieces(r):
+                            if e > b:
+                                pv[off:off + e - b].copy_(full[b:e])
+                for r in range(self.world):
+                    self.arena.peer_view("reg_parts2", r).view(torch.int64)[0:1].copy_(self.step_t.view(torch.int64))
+            torch.cuda.synchronize(self.dev)
+            dist.barrier(group=self.group)
+            box = self.arena.view("reg_parts2").view(torch.int64)
+            self.step_t.copy_(box[0:1].view(self.step_t.dtype))
+            box.zero_()
+        self.opt.step = int(self.step_t.item())
         self._loaded_full = None
         torch.cuda.synchronize(self.dev)
         dist.barrier(group=self.group)
