@@ -423,6 +423,19 @@ extern "C" {
 
 const char* dfmio_bundle_last_error() { return g_berr; }
 
+// The index key under which one slice of a partitioned variable is stored (TF: checkpoint::EncodeTensorNameSlice, OrderedCode).
+// starts[d] / lens[d] per dimension, lens[d] < 0 = the whole dimension. Writes the key bytes into out (cap bytes) and returns
+// its length, or -1 if it does not fit. Exposed so the encoding can be tested against an independent derivation.
+int dfmio_bundle_slice_key(const char* name, int ndim, const int64_t* starts, const int64_t* lens, uint8_t* out, int cap) {
+  if (!name || ndim < 0 || (ndim > 0 && (!starts || !lens)) || !out) return -1;
+  std::vector<std::pair<int64_t, int64_t>> sl;
+  for (int d = 0; d < ndim; ++d) sl.emplace_back(starts[d], lens[d]);
+  const std::string k = slice_key(name, sl);
+  if ((int)k.size() > cap) return -1;
+  memcpy(out, k.data(), k.size());
+  return (int)k.size();
+}
+
 // Table-block CRC verification of the index reader, on by default. Switching it off is for fuzzing only: a mutated index
 // then gets past the checksum and exercises the key / BundleEntryProto / slice decoders (csrc/io/fuzz_main.cc).
 void dfmio_bundle_check_block_crc(int on) { g_check_block_crc = on != 0; }

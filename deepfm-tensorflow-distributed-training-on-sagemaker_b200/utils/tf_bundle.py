@@ -96,3 +96,31 @@ def read_bundle(prefix: str, verify_crc: bool = True) -> Dict[str, torch.Tensor]
     finally:
         lib.dfmio_bundle_reader_close(h)
     return out
+
+
+def ordered_code_slice_key(name, extents) -> bytes:
+    """Pure-Python derivation of TF's EncodeTensorNameSlice (OrderedCode, tensorflow/core/lib/strings/ordered_code.h): the
+    number 0, the escaped name, the rank, then (start, length) per dimension as signed increasing numbers; (-1, -1) = the
+    whole axis. The C++ codec has its own encoder (csrc/io/tensor_bundle.cc slice_key); the tests hold the two against
+    each other, and `inspect_checkpoint` can use this one to explain the keys of a partitioned variable."""
+    raw = name if isinstance(name, (bytes, bytearray)) else name.encode()
+
+    def num_inc(v):
+        b = v.to_bytes((v.bit_length() + 7) // 8, "big") if v else b""
+        return bytes([len(b)]) + b
+
+    def signed_inc(v):
+        x = ~v if v < 0 else v
+        n = 1
+        while x.bit_length() > 7 * n - 1:
+            n += 1
+        out = bytearray((v & ((1 << 80) - 1)).to_bytes(10, "big")[10 - n:])
+        for i in range(n):  # n leading one bits mark the length; xor keeps negatives below positives
+            out[i // 8] ^= 0x80 >> (i % 8)
+        return bytes(out)
+
+    key = num_inc(0) + bytes(raw).replace(b"\x00", b"\x00\xff").replace(b"\xff", b"\xff\x00") + b"\x00\x01"
+    key += num_inc(len(extents))
+    for start, length in extents:
+        key += signed_inc(start) + signed_inc(length)
+    return key

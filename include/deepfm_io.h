@@ -87,6 +87,9 @@ int dfmio_ps_apply_push(float* tab_v, float* sv0, float* sv1, float* tab_w, floa
 /* ---- TensorFlow tensor bundle (checkpoint V2): <prefix>.index (SSTable) + <prefix>.data-00000-of-00001.
  * dtype is TensorFlow's DataType enum (1 float32, 3 int32, 9 int64); dims holds up to 8 entries. */
 const char* dfmio_bundle_last_error(void);
+/* Index key of one slice of a partitioned variable (TF's OrderedCode encoding of name + per-dimension (start, length);
+ * length < 0 = whole dimension); returns the key length or -1. */
+int dfmio_bundle_slice_key(const char* name, int ndim, const int64_t* starts, const int64_t* lens, uint8_t* out, int cap);
 void dfmio_bundle_check_block_crc(int on); /* 1 (default) = verify the index's table-block CRCs; 0 = fuzzing only */
 void* dfmio_bundle_writer_create(const char* prefix);
 /* num_shards data files (<prefix>.data-SSSSS-of-NNNNN), variable k in shard k % num_shards: the layout a sharded TF Saver

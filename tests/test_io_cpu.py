@@ -361,28 +361,9 @@ def test_sharded_tensor_bundles_like_a_parameter_server_checkpoint(tmp_path):
         read_bundle(prefix)
 
 
-def _ordered_code_slice_key(name: str, extents):
-    """Second derivation of TF's EncodeTensorNameSlice (OrderedCode: tensorflow/core/lib/strings/ordered_code.h): the number
-    0, the escaped name, the rank, then (start, length) per dimension as signed increasing numbers; (-1, -1) = whole axis."""
-    def num_inc(v):
-        b = v.to_bytes((v.bit_length() + 7) // 8, "big") if v else b""
-        return bytes([len(b)]) + b
-
-    def signed_inc(v):
-        x = ~v if v < 0 else v
-        n = 1
-        while x.bit_length() > 7 * n - 1:
-            n += 1
-        raw = bytearray((v & ((1 << 80) - 1)).to_bytes(10, "big")[10 - n:])
-        for i in range(n):  # n leading one bits mark the length; xor keeps negatives below positives
-            raw[i // 8] ^= 0x80 >> (i % 8)
-        return bytes(raw)
-
-    key = num_inc(0) + name.encode().replace(b"\x00", b"\x00\xff").replace(b"\xff", b"\xff\x00") + b"\x00\x01"
-    key += num_inc(len(extents))
-    for start, length in extents:
-        key += signed_inc(start) + signed_inc(length)
-    return key
+def _ordered_code_slice_key(name, extents):
+    from deepfm_b200.utils.tf_bundle import ordered_code_slice_key
+    return ordered_code_slice_key(name, extents)
 
 
 def test_partitioned_variables_like_fixed_size_partitioner(tmp_path):

@@ -67,3 +67,30 @@ def test_bucketed_auc_tracks_exact_auc(seed, n):
     a = StreamingAUC()
     a.update(y, p)
     assert abs(a.result() - exact_auc(y.numpy(), p.numpy())) < 1e-2
+
+
+@settings(max_examples=300, deadline=None)
+@given(name=st.binary(min_size=1, max_size=24).filter(lambda b: True),
+       extents=st.lists(st.one_of(st.just((-1, -1)),
+                                  st.tuples(st.integers(0, 2 ** 40), st.integers(0, 2 ** 40))), min_size=0, max_size=4))
+def test_slice_key_encoding_matches_an_independent_ordered_code_derivation(name, extents):
+    """Partitioned variables are found in a TF checkpoint index under OrderedCode keys (name, rank, (start, length) per
+    dimension). The C++ encoder (csrc/io/tensor_bundle.cc) against the Python derivation of the same rules in
+    P/utils/tf_bundle.py: every magnitude class of the signed varint (1..6 bytes), the (-1, -1) "whole axis" marker and
+    names with 0x00 / 0xff bytes (escaped)."""
+    import ctypes
+    from deepfm_b200.data import native
+    from deepfm_b200.utils.tf_bundle import ordered_code_slice_key
+    lib = native.load()
+    n = len(extents)
+    starts = (ctypes.c_int64 * max(n, 1))(*[e[0] for e in extents])
+    lens = (ctypes.c_int64 * max(n, 1))(*[e[1] for e in extents])
+    out = (ctypes.c_uint8 * 512)()
+    # names reach C as NUL-terminated strings: a name with an embedded 0 byte cannot be passed, 0xff can
+    cname = name.replace(b"\x00", b"\x01")
+    lib.dfmio_bundle_slice_key.argtypes = [ctypes.c_char_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                           ctypes.c_int]
+    k = lib.dfmio_bundle_slice_key(cname, n, starts, lens, out, 512)
+    assert k > 0
+    expect = ordered_code_slice_key(cname, extents)
+    assert bytes(out[:k]) == expect
